@@ -1,0 +1,172 @@
+/*
+ * l2hmc_b200.h -- C ABI of the B200-native L2HMC / HMC leapfrog path for the 2D U(1)
+ * lattice gauge model.
+ *
+ * The reference (saforem2/l2hmc) is pure Python on TensorFlow 1.x and has no FFI; the path
+ * sits behind the Python classes GaugeLattice / GaugeDynamics / GenericNet / ConvNet3D.
+ * The host-side mirror of those classes lives in l2hmc_b200/*.py and binds the entry
+ * points below with ctypes (see INTEGRATION.md for the stub a maintainer would add to the
+ * reference).  Each entry point names the reference code it replaces (file:line under
+ * l2hmc/ in the reference tree).
+ *
+ * Conventions (all entry points):
+ *   - every pointer is caller-owned DEVICE memory (fp32 unless stated), row-major;
+ *     a chain is D = 2*T*X contiguous floats laid out [t][x][mu]
+ *     (mu = 0 is the link along t, mu = 1 along x) == lattice.samples (N,T,X,2) flattened
+ *     (lattice/lattice.py:121-129, 351-352);
+ *   - nothing is allocated, nothing is synchronised: work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *   - return value 0 = enqueued, non-zero = L2HMC_ERR_*; l2hmc_last_error() gives the text;
+ *   - `nonfinite_flag` (nullable, device int32) is OR-ed with 1 when an exp() produced a
+ *     non-finite value -- the device-side mirror of tf.check_numerics
+ *     (dynamics/gauge_dynamics.py:26-28); the host wrapper raises on it;
+ *   - re-entrant, no global state apart from the thread-local error string.
+ */
+#ifndef L2HMC_B200_H_
+#define L2HMC_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define L2HMC_OK 0
+#define L2HMC_ERR_INVALID 1     /* bad argument (null pointer, size, alignment) */
+#define L2HMC_ERR_UNSUPPORTED 2 /* shape has no kernel instantiation */
+#define L2HMC_ERR_CUDA 3        /* launch failed; see l2hmc_last_error() */
+
+#define L2HMC_ABI_VERSION 1
+
+int l2hmc_abi_version(void);
+const char* l2hmc_last_error(void);
+
+/* Device limits the host side sizes its launches with. */
+int l2hmc_device_info(int* sm_count, int* max_smem_per_block);
+
+/* ------------------------------------------------------------------ K1: plaquette stencil
+ * Wilson action S(x) = sum_{t,x} (1 - cos P) and/or force g = d(beta*S)/dx.
+ *   P(t,x) = U0(t,x) - U1(t,x) - U0(t,x+1) + U1(t+1,x)   (periodic, left-associated)
+ * replaces GaugeLattice.total_action (lattice/lattice.py:337-362) and
+ * GaugeDynamics.grad_potential (dynamics/gauge_dynamics.py:698-709, tf.gradients of the above).
+ * `action` and `force` are each nullable; any T, X >= 1. */
+int l2hmc_u1_action_force(const float* x, float beta, int N, int T, int X,
+                          float* action /*[N]*/, float* force /*[N,2TX]*/, void* stream);
+
+/* ------------------------------------------------------------------ K4: observables
+ * action, avg plaquette = sum cos P / (T*X), real-valued charge sum(proj P)/2pi, and the
+ * integer charge floor(0.1 + sum(proj P)/2pi), proj(P) = P - 2pi floor((P+pi)/2pi).
+ * replaces GaugeLattice.calc_plaq_observables (lattice/lattice.py:285-313) and
+ * GaugeModel._calc_total_actions/_calc_avg_plaqs/_calc_top_charges (gauge_model.py:683-716).
+ * All outputs nullable. */
+int l2hmc_u1_observables(const float* x, int N, int T, int X, float* action, float* avg_plaq,
+                         float* q_float, int32_t* q_int, void* stream);
+
+/* 0.5 * sum_d v^2 per chain.  GaugeDynamics.kinetic_energy (dynamics/gauge_dynamics.py:683-689). */
+int l2hmc_kinetic_energy(const float* v, int N, int D, float* ke, void* stream);
+
+/* ------------------------------------------------------------------ K2: augmented leapfrog updates
+ * dir = +1: GaugeDynamics._update_momentum_forward (dynamics/gauge_dynamics.py:486-508)
+ *     v' = v*exp(eps/2*S) - eps/2*(exp(eps*Q)*g - T),      logdet += sum_d  eps/2*S
+ * dir = -1: _update_momentum_backward (:537-561)
+ *     v' = exp(-eps/2*S)*(v + eps/2*(exp(eps*Q)*g - T)),   logdet += sum_d -eps/2*S
+ * S,T,Q nullable together (plain HMC, :102-108).  `logdet` [N] is ACCUMULATED into
+ * (nullable).  v_out may alias v. */
+int l2hmc_update_momentum(const float* v, const float* g, const float* S, const float* Tr,
+                          const float* Q, float eps, int dir, int N, int D, float* v_out,
+                          float* logdet, int32_t* nonfinite_flag, void* stream);
+
+/* dir = +1: _update_position_forward (dynamics/gauge_dynamics.py:511-534)
+ *     x' = m*x + mbar*(x*exp(eps*S) + eps*(exp(eps*Q)*v + T)),  logdet += sum_d mbar*eps*S
+ * dir = -1: _update_position_backward (:565-590)
+ *     x' = m*x + mbar*exp(-eps*S)*(x - eps*(exp(eps*Q)*v + T)), logdet += sum_d mbar*(-eps*S)
+ * `mask` is one row [D] of GaugeDynamics.mask (:651-661); invert_mask != 0 swaps (m, mbar),
+ * the second half-update of each LF step (:434-437).  No mod-2pi here (as in the reference). */
+int l2hmc_update_position(const float* x, const float* v, const float* S, const float* Tr,
+                          const float* Q, const float* mask, int invert_mask, float eps, int dir,
+                          int N, int D, float* x_out, float* logdet, int32_t* nonfinite_flag,
+                          void* stream);
+
+/* out = mask_row (*) x  (or (1-mask_row) (*) x): the `mask * position` network input
+ * (dynamics/gauge_dynamics.py:515-517). */
+int l2hmc_mask_mul(const float* x, const float* mask, int invert_mask, int N, int D, float* out,
+                   void* stream);
+
+/* ------------------------------------------------------------------ accept / reject
+ * GaugeDynamics._compute_accept_prob (dynamics/gauge_dynamics.py:592-609):
+ *     p = exp(min(h_old - h_new + sumlogdet, 0)), non-finite -> 0. */
+int l2hmc_accept_prob(const float* h_old, const float* h_new, const float* sumlogdet /*nullable*/,
+                      int N, float* p, int32_t* nonfinite_flag, void* stream);
+
+/* GaugeDynamics.apply_transition's blends (dynamics/gauge_dynamics.py:220-257):
+ *   fm = [u_dir > 0.5]; x_post = fm*x_f + (1-fm)*x_b (same for v, p);
+ *   am = [p > u_acc] (strict); x_out = am*x_post + (1-am)*x.
+ * wrap_2pi != 0 additionally applies the host-side np.mod(x_out, 2pi) of
+ * gauge_model.py:1180,1388 to x_out.  x_b/v_b/p_b nullable (single direction computed).
+ * accepted [N] uint8 nullable. */
+int l2hmc_mh_select(const float* x, const float* x_f, const float* x_b, const float* v_f,
+                    const float* v_b, const float* p_f, const float* p_b, const float* u_dir,
+                    const float* u_acc, int N, int D, int wrap_2pi, float* x_post, float* v_post,
+                    float* p, float* x_out, uint8_t* accepted, void* stream);
+
+/* ------------------------------------------------------------------ fused plain-HMC path (S=T=Q=0)
+ * One leapfrog step per launch for all chains, x and v streamed once (16 B / link-update):
+ *     v -= s*eps/2*g(x);  x += s*eps*v;  v -= s*eps/2*g(x)       s = dir[n] in {+1,-1}
+ * == _forward_lf / _backward_lf with the hmc stubs (dynamics/gauge_dynamics.py:102-108,412-483).
+ * `dir` [N] int8 nullable (NULL = all +1).  x_out/v_out may alias x/v.
+ * Shapes: (T,X) in {4x4, 8x8, 16x16, 32x32, 8x16, 16x32}; others -> L2HMC_ERR_UNSUPPORTED
+ * (the host falls back to K1 + K2). */
+int l2hmc_u1_hmc_step(const float* x, const float* v, float beta, float eps, const int8_t* dir,
+                      int N, int T, int X, float* x_out, float* v_out, void* stream);
+
+/* Whole Monte-Carlo step in one launch: momentum (injected or Philox), M leapfrog steps with
+ * links and momenta resident on-chip, both Hamiltonians, accept probability, direction and
+ * accept/reject select == GaugeDynamics.apply_transition with hmc=True
+ * (dynamics/gauge_dynamics.py:195-313), computing only the direction each chain selects.
+ *
+ *   momentum: v_f / v_b [N,D] are the draws of the forward / backward transition_kernel
+ *             (:269); chain n uses v_f if it goes forward else v_b.  v_b NULL -> v_f for all.
+ *             v_f NULL -> drawn in-kernel: Philox4x32-10 keyed (seed), counter
+ *             (chain0 + n, link, mc_step) -- independent of sharding.
+ *   direction: u_dir [N] nullable; NULL -> in-kernel uniform if v_f is NULL, else
+ *             `default_dir` (+1/-1) for all chains (== transition_kernel(forward=...)).
+ *   accept:   u_acc [N] nullable; NULL -> in-kernel uniform if v_f is NULL, else no select.
+ *   outputs (each nullable): x_post, v_post [N,D], accept_prob [N], x_out [N,D],
+ *             accepted [N] uint8, h_old / h_new [N].
+ */
+typedef struct {
+  const float* x;
+  const float* v_f;
+  const float* v_b;
+  const float* u_dir;
+  const float* u_acc;
+  float beta;
+  float eps;
+  int num_steps;
+  int default_dir;
+  int wrap_2pi;
+  uint64_t seed;
+  uint64_t mc_step;
+  uint64_t chain0;
+  int N, T, X;
+  float* x_post;
+  float* v_post;
+  float* accept_prob;
+  float* x_out;
+  uint8_t* accepted;
+  float* h_old;
+  float* h_new;
+  int32_t* nonfinite_flag;
+} l2hmc_hmc_mc_args;
+
+int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* args, void* stream);
+
+/* The momenta / uniforms the in-kernel generator would use, written out (tests, and the
+ * generic path's free-running mode).  normals [N,D], u_dir/u_acc [N], each nullable. */
+int l2hmc_philox_draws(uint64_t seed, uint64_t mc_step, uint64_t chain0, int N, int D,
+                       float* normals, float* u_dir, float* u_acc, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* L2HMC_B200_H_ */

@@ -1,0 +1,114 @@
+"""ctypes binding of the C-ABI CUDA library (include/l2hmc_b200.h).
+
+There is deliberately NO fallback: if libl2hmc_b200.so cannot be loaded, or no CUDA device is
+present, every compute entry point raises.  PyTorch is used only for device memory, streams and
+torch.distributed.
+"""
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_uint64, c_void_p
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libl2hmc_b200.so")
+
+_lib = None
+
+
+class HmcMcArgs(Structure):
+    """l2hmc_hmc_mc_args (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("x", c_void_p), ("v_f", c_void_p), ("v_b", c_void_p), ("u_dir", c_void_p), ("u_acc", c_void_p),
+        ("beta", c_float), ("eps", c_float), ("num_steps", c_int), ("default_dir", c_int), ("wrap_2pi", c_int),
+        ("seed", c_uint64), ("mc_step", c_uint64), ("chain0", c_uint64),
+        ("N", c_int), ("T", c_int), ("X", c_int),
+        ("x_post", c_void_p), ("v_post", c_void_p), ("accept_prob", c_void_p), ("x_out", c_void_p),
+        ("accepted", c_void_p), ("h_old", c_void_p), ("h_new", c_void_p), ("nonfinite_flag", c_void_p),
+    ]
+
+
+# name -> argtypes; every function returns int status except the two noted below.
+SIGNATURES = {
+    "l2hmc_abi_version": [],
+    "l2hmc_last_error": [],
+    "l2hmc_device_info": [POINTER(c_int), POINTER(c_int)],
+    "l2hmc_u1_action_force": [c_void_p, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_u1_observables": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_kinetic_energy": [c_void_p, c_int, c_int, c_void_p, c_void_p],
+    "l2hmc_update_momentum": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int, c_int,
+                              c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_update_position": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_int,
+                              c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_mask_mul": [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p],
+    "l2hmc_accept_prob": [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_mh_select": [c_void_p] * 9 + [c_int, c_int, c_int] + [c_void_p] * 5 + [c_void_p],
+    "l2hmc_u1_hmc_step": [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                          c_void_p],
+    "l2hmc_u1_hmc_mc_step": [POINTER(HmcMcArgs), c_void_p],
+    "l2hmc_philox_draws": [c_uint64, c_uint64, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+}
+
+L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
+
+
+class L2hmcError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"l2hmc_b200 error {code}: {text}")
+        self.code = code
+
+
+def load_library(path=LIB_PATH):
+    """dlopen the library and bind every declared symbol (no device needed)."""
+    if not os.path.exists(path):
+        raise ImportError(
+            f"{path} is missing: build it with `python -m l2hmc_b200.build` (nvcc, sm_100a). "
+            "l2hmc_b200 has no CPU or eager fallback.")
+    lib = ctypes.CDLL(path)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = c_char_p if name == "l2hmc_last_error" else c_int
+    return lib
+
+
+def get_lib():
+    global _lib
+    if _lib is None:
+        _lib = load_library()
+        if _lib.l2hmc_abi_version() != 1:
+            raise ImportError("libl2hmc_b200.so ABI version mismatch; rebuild")
+    return _lib
+
+
+def require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("l2hmc_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+
+
+def check(rc):
+    if rc != 0:
+        raise L2hmcError(rc, get_lib().l2hmc_last_error().decode())
+
+
+def stream_ptr():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def dptr(t, dtype=torch.float32):
+    """Device pointer of a contiguous CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.is_contiguous() and t.dtype == dtype):
+        raise TypeError(f"expected a contiguous CUDA {dtype} tensor, got "
+                        f"{type(t).__name__} {getattr(t, 'dtype', None)} {getattr(t, 'device', None)}")
+    return c_void_p(t.data_ptr())
+
+
+def device_info():
+    sms, smem = c_int(0), c_int(0)
+    check(get_lib().l2hmc_device_info(ctypes.byref(sms), ctypes.byref(smem)))
+    return sms.value, smem.value
+
+
+FUSED_HMC_SHAPES = {(4, 4), (8, 8), (16, 16), (32, 32), (8, 16), (16, 32)}

@@ -1,0 +1,42 @@
+// C-ABI glue shared by all entry points: error text, version, device limits.
+#include <stdarg.h>
+
+#include "common.cuh"
+
+namespace l2hmc {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof(g_error), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return L2HMC_ERR_CUDA;
+  }
+  return L2HMC_OK;
+}
+
+}  // namespace l2hmc
+
+extern "C" int l2hmc_abi_version(void) { return L2HMC_ABI_VERSION; }
+
+extern "C" const char* l2hmc_last_error(void) { return l2hmc::g_error; }
+
+extern "C" int l2hmc_device_info(int* sm_count, int* max_smem_per_block) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    l2hmc::set_error("cudaGetDevice: %s", cudaGetErrorString(e));
+    return L2HMC_ERR_CUDA;
+  }
+  if (sm_count) cudaDeviceGetAttribute(sm_count, cudaDevAttrMultiProcessorCount, dev);
+  if (max_smem_per_block) cudaDeviceGetAttribute(max_smem_per_block, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return L2HMC_OK;
+}

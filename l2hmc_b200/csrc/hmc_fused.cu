@@ -1,0 +1,432 @@
+// Fused plain-HMC kernels for the 2D U(1) gauge model (S = T = Q = 0 path of L2HMC).
+//
+//   hmc_kernel<T, X, /*MC=*/false>  one leapfrog step per launch: x, v streamed once
+//                                   (16 B / link-update) -- the HBM-roofline kernel.
+//   hmc_kernel<T, X, /*MC=*/true>   a whole Monte-Carlo step per launch: momenta (injected or
+//                                   Philox), M leapfrog steps with x, v resident on-chip, both
+//                                   Hamiltonians, accept probability, direction + accept select.
+//
+// Replaces GaugeDynamics.apply_transition / transition_kernel / _forward_lf / _backward_lf with
+// the hmc stubs (reference l2hmc/dynamics/gauge_dynamics.py:102-108, 195-313, 412-483) and the
+// force tf.gradients(beta * total_action) (:698-709, lattice/lattice.py:337-362).
+//
+// Structure (B200): persistent CTAs, 8 compute warps + 1 copy warp.  A tile is 2048 links =
+// 8 KB of x (+ 8 KB of v) = 256/TPC whole chains; the copy warp moves tiles HBM <-> shared
+// memory with 1-D bulk async copies (TMA engine, mbarrier completion) through a 2-stage ring,
+// so compute warps never wait on global memory.  Each compute thread owns a strip of four
+// sites of one chain (8 links, contiguous) in registers; the plaquette needs the next row and
+// the next column (shared memory / one shuffle), the force needs beta*sin P of the previous
+// row and column (shared memory / one shuffle): two named barriers per force evaluation.
+//
+// Arithmetic keeps the reference's fp32 op order (every product and sum rounded separately, no
+// FMA contraction: this file is compiled with -fmad=false):
+//   P  = ((U0 - U1) - U0[x+1]) + U1[t+1]            lattice.py:354-357
+//   b  = beta * sin P;  g0 = b - b[x-1];  g1 = -b + b[t-1]   (adjoint of the roll graph)
+//   v' = v - (eps/2) * g;   x' = x + eps * v'        gauge_dynamics.py:486-534 with S=T=Q=0
+// and the backward step is the same with eps -> -eps (bit-identical to :537-590).
+#include "common.cuh"
+
+namespace l2hmc {
+
+namespace {
+
+constexpr int kComputeThreads = 256;
+constexpr int kThreads = kComputeThreads + 32;
+constexpr int kStages = 2;
+constexpr int kTileFloats = 2048;  // links per tile (8 KB)
+
+struct HmcParams {
+  const float* x;
+  const float* v_f;
+  const float* v_b;
+  const float* u_dir;
+  const float* u_acc;
+  const int8_t* dir;
+  float beta, eps;
+  int num_steps, default_dir, wrap, N, num_tiles;
+  unsigned long long seed, mc_step, chain0;
+  float* x_post;
+  float* v_post;
+  float* accept_prob;
+  float* x_out;
+  uint8_t* accepted;
+  float* h_old;
+  float* h_new;
+  int32_t* flag;
+};
+
+template <int T, int X>
+struct Geo {
+  static constexpr int SITES = T * X;
+  static constexpr int D = 2 * SITES;
+  static constexpr int TPC = SITES / 4;              // threads per chain
+  static constexpr int CPB = kComputeThreads / TPC;  // chains per tile
+  static constexpr int XG = X / 4;                   // threads per lattice row
+  static_assert(X % 4 == 0, "strip of four sites per thread");
+  static_assert(TPC >= 1 && TPC <= kComputeThreads && kComputeThreads % TPC == 0, "chain must fit one CTA");
+  static_assert(XG >= 1 && XG <= 32 && (XG & (XG - 1)) == 0, "row neighbours by warp shuffle");
+  static_assert(CPB * D == kTileFloats, "tile is always 8 KB");
+};
+
+template <bool MC>
+struct Smem {
+  static constexpr int kBufsPerStage = MC ? 3 : 2;  // x, v, (x_out)
+  static constexpr int kStageFloats = kBufsPerStage * kTileFloats;
+  static constexpr int kBFloats = 2 * (kTileFloats / 2);  // beta*sin P, double-buffered
+  static constexpr int kRedFloats = 8 * 4;
+  static constexpr size_t bytes = sizeof(float) * (kStages * kStageFloats + kBFloats + kRedFloats) +
+                                  sizeof(uint64_t) * 2 * kStages;
+};
+
+template <int T, int X, bool MC>
+__global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcParams p) {
+  using G = Geo<T, X>;
+  constexpr int D = G::D, TPC = G::TPC, CPB = G::CPB, XG = G::XG;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  float* s_stage = reinterpret_cast<float*>(smem_raw);
+  float* s_b = s_stage + kStages * Smem<MC>::kStageFloats;
+  float* s_red = s_b + Smem<MC>::kBFloats;
+  uint64_t* full = reinterpret_cast<uint64_t*>(s_red + Smem<MC>::kRedFloats);
+  uint64_t* done = full + kStages;
+
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&done[s], kComputeThreads);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const bool rng = MC && (p.v_f == nullptr);
+
+  if (warp == kComputeThreads / 32) {
+    // ------------------------------------------------------------------ copy warp
+    auto store_tile = [&](int tile, int s) {
+      const int chain_base = tile * CPB;
+      const int nvalid = min(CPB, p.N - chain_base);
+      const uint32_t bytes = static_cast<uint32_t>(nvalid) * D * 4u;
+      float* sx = s_stage + s * Smem<MC>::kStageFloats;
+      const size_t goff = static_cast<size_t>(chain_base) * D;
+      if (p.x_post) bulk_s2g(p.x_post + goff, sx, bytes);
+      if (p.v_post) bulk_s2g(p.v_post + goff, sx + kTileFloats, bytes);
+      if (MC && p.x_out) bulk_s2g(p.x_out + goff, sx + 2 * kTileFloats, bytes);
+      bulk_commit();
+    };
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int s = it % kStages;
+      if (it >= kStages) {  // the stage's previous tile: wait for the compute warps, write it back
+        if (lane == 0) {
+          mbar_wait(&done[s], ((it / kStages) - 1) & 1);
+          store_tile(tile - kStages * static_cast<int>(gridDim.x), s);
+          bulk_wait_read_all();
+        }
+        __syncwarp();
+      }
+      const int chain_base = tile * CPB;
+      const int nvalid = min(CPB, p.N - chain_base);
+      const uint32_t bytes = static_cast<uint32_t>(nvalid) * D * 4u;
+      float* sx = s_stage + s * Smem<MC>::kStageFloats;
+      const size_t goff = static_cast<size_t>(chain_base) * D;
+      const bool per_chain_v = MC && !rng && p.v_b != nullptr;
+      if (lane == 0) mbar_arrive_expect_tx(&full[s], rng ? bytes : 2u * bytes);
+      __syncwarp();
+      if (lane == 0) {
+        bulk_g2s(sx, p.x + goff, bytes, &full[s]);
+        if (!rng && !per_chain_v) bulk_g2s(sx + kTileFloats, p.v_f + goff, bytes, &full[s]);
+      }
+      if (per_chain_v) {
+        for (int c = lane; c < nvalid; c += 32) {
+          const bool fwd = p.u_dir ? (p.u_dir[chain_base + c] > 0.5f) : (p.default_dir >= 0);
+          const float* src = (fwd ? p.v_f : p.v_b) + goff + static_cast<size_t>(c) * D;
+          bulk_g2s(sx + kTileFloats + c * D, src, D * 4u, &full[s]);
+        }
+      }
+      __syncwarp();
+    }
+    if (lane == 0) {
+      for (int j = max(0, it - kStages); j < it; ++j) {
+        const int s = j % kStages;
+        mbar_wait(&done[s], (j / kStages) & 1);
+        store_tile(static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x), s);
+      }
+      bulk_wait_all();
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- compute warps
+  const int k = tid % TPC, c = tid / TPC;
+  const int t = k / XG, cg = k % XG;
+  const int x0 = 4 * cg;
+  const int lane_right = (lane & ~(XG - 1)) | ((lane + 1) & (XG - 1));
+  const int lane_left = (lane & ~(XG - 1)) | ((lane + XG - 1) & (XG - 1));
+  const int off_own = c * D + 8 * k;
+  const int off_dn = c * D + (((t + 1) % T) * X + x0) * 2;
+  const int boff_own = c * G::SITES + t * X + x0;
+  const int boff_up = c * G::SITES + ((t + T - 1) % T) * X + x0;
+  const float beta = p.beta;
+  const float half_eps = __fmul_rn(0.5f, p.eps);
+
+  float xs[8], vs[8], g[8];
+  unsigned eval_parity = 0;
+
+  // One force evaluation; x of every chain of the tile must be visible in `sx`.
+  auto force = [&](const float* sx, bool want_cos, float& act_part) {
+    const float4 d0 = *reinterpret_cast<const float4*>(sx + off_dn);
+    const float4 d1 = *reinterpret_cast<const float4*>(sx + off_dn + 4);
+    const float u0r = __shfl_sync(0xffffffffu, xs[0], lane_right);
+    float P[4];
+    P[0] = __fadd_rn(__fsub_rn(__fsub_rn(xs[0], xs[1]), xs[2]), d0.y);
+    P[1] = __fadd_rn(__fsub_rn(__fsub_rn(xs[2], xs[3]), xs[4]), d0.w);
+    P[2] = __fadd_rn(__fsub_rn(__fsub_rn(xs[4], xs[5]), xs[6]), d1.y);
+    P[3] = __fadd_rn(__fsub_rn(__fsub_rn(xs[6], xs[7]), u0r), d1.w);
+    float b[4];
+    if (want_cos) {
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float sn, cs;
+        sincosf(P[j], &sn, &cs);
+        b[j] = __fmul_rn(beta, sn);
+        acc = __fadd_rn(acc, __fsub_rn(1.f, cs));
+      }
+      act_part = acc;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = __fmul_rn(beta, sinf(P[j]));
+    }
+    float* sb = s_b + (eval_parity & 1u) * (kTileFloats / 2);
+    eval_parity ^= 1u;
+    *reinterpret_cast<float4*>(sb + boff_own) = make_float4(b[0], b[1], b[2], b[3]);
+    named_bar_sync(1, kComputeThreads);
+    const float4 bu = *reinterpret_cast<const float4*>(sb + boff_up);
+    const float bl = __shfl_sync(0xffffffffu, b[3], lane_left);
+    g[0] = __fsub_rn(b[0], bl);
+    g[1] = __fsub_rn(bu.x, b[0]);
+    g[2] = __fsub_rn(b[1], b[0]);
+    g[3] = __fsub_rn(bu.y, b[1]);
+    g[4] = __fsub_rn(b[2], b[1]);
+    g[5] = __fsub_rn(bu.z, b[2]);
+    g[6] = __fsub_rn(b[3], b[2]);
+    g[7] = __fsub_rn(bu.w, b[3]);
+  };
+
+  int it = 0;
+  for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    const int s = it % kStages;
+    float* sx = s_stage + s * Smem<MC>::kStageFloats;
+    float* sv = sx + kTileFloats;
+    const int chain = tile * CPB + c;
+    const bool valid = chain < p.N;
+
+    // per-chain direction (global reads issued before the smem wait)
+    float sgn = 1.f, u_acc = 2.f;
+    bool have_acc = false;
+    if (MC) {
+      if (rng) {
+        float ud, ua;
+        philox_uniform2(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, ud, ua);
+        sgn = (p.u_dir ? (valid ? p.u_dir[chain] : 1.f) : ud) > 0.5f ? 1.f : -1.f;
+        u_acc = p.u_acc ? (valid ? p.u_acc[chain] : 0.f) : ua;
+        have_acc = true;
+      } else {
+        if (p.u_dir) sgn = (valid ? p.u_dir[chain] : 1.f) > 0.5f ? 1.f : -1.f;
+        else sgn = p.default_dir >= 0 ? 1.f : -1.f;
+        if (p.u_acc) {
+          u_acc = valid ? p.u_acc[chain] : 0.f;
+          have_acc = true;
+        }
+      }
+    } else if (p.dir) {
+      sgn = (valid ? p.dir[chain] : 1) >= 0 ? 1.f : -1.f;
+    }
+    const float eps_d = __fmul_rn(sgn, p.eps);
+    const float heps_d = __fmul_rn(sgn, half_eps);
+
+    mbar_wait(&full[s], (it / kStages) & 1);
+
+    if (valid) {
+      const float4 a0 = *reinterpret_cast<const float4*>(sx + off_own);
+      const float4 a1 = *reinterpret_cast<const float4*>(sx + off_own + 4);
+      xs[0] = a0.x, xs[1] = a0.y, xs[2] = a0.z, xs[3] = a0.w;
+      xs[4] = a1.x, xs[5] = a1.y, xs[6] = a1.z, xs[7] = a1.w;
+      if (rng) {
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k, vs);
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k + 1u, vs + 4);
+      } else {
+        const float4 w0 = *reinterpret_cast<const float4*>(sv + off_own);
+        const float4 w1 = *reinterpret_cast<const float4*>(sv + off_own + 4);
+        vs[0] = w0.x, vs[1] = w0.y, vs[2] = w0.z, vs[3] = w0.w;
+        vs[4] = w1.x, vs[5] = w1.y, vs[6] = w1.z, vs[7] = w1.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) xs[j] = 0.f, vs[j] = 0.f;
+      *reinterpret_cast<float4*>(sx + off_own) = make_float4(0.f, 0.f, 0.f, 0.f);
+      *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+
+    float xs0[8];
+    float act0 = 0.f, act1 = 0.f, ke0 = 0.f, ke1 = 0.f;
+    if (MC) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        xs0[j] = xs[j];
+        ke0 = __fadd_rn(ke0, __fmul_rn(vs[j], vs[j]));
+      }
+    }
+    // tail tiles zero-fill invalid chains in smem; make that visible before neighbours read
+    if (tile * CPB + CPB > p.N) named_bar_sync(1, kComputeThreads);
+
+    force(sx, MC, act0);
+    const int nsteps = MC ? p.num_steps : 1;
+    for (int step = 0; step < nsteps; ++step) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
+        xs[j] = __fadd_rn(xs[j], __fmul_rn(eps_d, vs[j]));
+      }
+      *reinterpret_cast<float4*>(sx + off_own) = make_float4(xs[0], xs[1], xs[2], xs[3]);
+      *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(xs[4], xs[5], xs[6], xs[7]);
+      named_bar_sync(1, kComputeThreads);
+      force(sx, MC && step == nsteps - 1, act1);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
+    }
+    *reinterpret_cast<float4*>(sv + off_own) = make_float4(vs[0], vs[1], vs[2], vs[3]);
+    *reinterpret_cast<float4*>(sv + off_own + 4) = make_float4(vs[4], vs[5], vs[6], vs[7]);
+
+    if (MC) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) ke1 = __fadd_rn(ke1, __fmul_rn(vs[j], vs[j]));
+      // per-chain sums of (action0, kinetic0, action1, kinetic1)
+      float r0, r1, r2, r3;
+      if (TPC <= 32) {
+        r0 = group_sum<(TPC < 32 ? TPC : 32)>(act0);
+        r1 = group_sum<(TPC < 32 ? TPC : 32)>(ke0);
+        r2 = group_sum<(TPC < 32 ? TPC : 32)>(act1);
+        r3 = group_sum<(TPC < 32 ? TPC : 32)>(ke1);
+      } else {
+        r0 = warp_sum(act0), r1 = warp_sum(ke0), r2 = warp_sum(act1), r3 = warp_sum(ke1);
+        if (lane == 0) *reinterpret_cast<float4*>(s_red + 4 * warp) = make_float4(r0, r1, r2, r3);
+        named_bar_sync(1, kComputeThreads);
+        constexpr int WPC = TPC > 32 ? TPC / 32 : 1;
+        r0 = r1 = r2 = r3 = 0.f;
+#pragma unroll
+        for (int w = 0; w < WPC; ++w) {
+          const float4 q = *reinterpret_cast<const float4*>(s_red + 4 * (c * WPC + w));
+          r0 += q.x, r1 += q.y, r2 += q.z, r3 += q.w;
+        }
+      }
+      const float h0 = __fadd_rn(__fmul_rn(beta, r0), __fmul_rn(0.5f, r1));
+      const float h1 = __fadd_rn(__fmul_rn(beta, r2), __fmul_rn(0.5f, r3));
+      const float dh = __fsub_rn(h0, h1);
+      float prob = expf(fminf(dh, 0.f));
+      if (isnan(dh)) prob = 0.f;  // tf.minimum propagates NaN; is_finite -> 0 (gauge_dynamics.py:604-609)
+      const bool acc = have_acc ? (prob > u_acc) : true;
+      if (valid && k == 0) {
+        if (p.accept_prob) p.accept_prob[chain] = prob;
+        if (p.accepted) p.accepted[chain] = acc ? 1 : 0;
+        if (p.h_old) p.h_old[chain] = h0;
+        if (p.h_new) p.h_new[chain] = h1;
+        if (isnan(dh) && p.flag) atomicOr(p.flag, 1);
+      }
+      if (p.x_out) {
+        float* so = sx + 2 * kTileFloats;
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          o[j] = acc ? xs[j] : xs0[j];
+          if (p.wrap) o[j] = wrap_2pi(o[j]);
+        }
+        *reinterpret_cast<float4*>(so + off_own) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(so + off_own + 4) = make_float4(o[4], o[5], o[6], o[7]);
+      }
+    }
+    fence_proxy_async_smem();
+    mbar_arrive(&done[s]);
+  }
+}
+
+template <int T, int X, bool MC>
+int launch(const HmcParams& p_in, cudaStream_t stream) {
+  HmcParams p = p_in;
+  using G = Geo<T, X>;
+  static int blocks_per_sm = 0, sm_count = 0;
+  auto kern = hmc_kernel<T, X, MC>;
+  if (blocks_per_sm == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(Smem<MC>::bytes));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(hmc_kernel): %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+    int dev = 0, bps = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kThreads, Smem<MC>::bytes);
+    if (e != cudaSuccess || bps < 1) {
+      set_error("hmc_kernel does not fit an SM: %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+    blocks_per_sm = bps;
+  }
+  p.num_tiles = (p.N + G::CPB - 1) / G::CPB;
+  if (p.num_tiles == 0) return L2HMC_OK;
+  const int grid = min(p.num_tiles, blocks_per_sm * sm_count);
+  kern<<<grid, kThreads, Smem<MC>::bytes, stream>>>(p);
+  return check_launch("hmc_kernel");
+}
+
+template <bool MC>
+int dispatch(const HmcParams& p, int T, int X, cudaStream_t stream) {
+#define L2HMC_SHAPE(TT, XX) \
+  if (T == TT && X == XX) return launch<TT, XX, MC>(p, stream);
+  L2HMC_SHAPE(4, 4)
+  L2HMC_SHAPE(8, 8)
+  L2HMC_SHAPE(16, 16)
+  L2HMC_SHAPE(32, 32)
+  L2HMC_SHAPE(8, 16)
+  L2HMC_SHAPE(16, 32)
+#undef L2HMC_SHAPE
+  set_error("no fused HMC kernel for a %dx%d lattice", T, X);
+  return L2HMC_ERR_UNSUPPORTED;
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+extern "C" int l2hmc_u1_hmc_step(const float* x, const float* v, float beta, float eps, const int8_t* dir, int N,
+                                 int T, int X, float* x_out, float* v_out, void* stream) {
+  L2HMC_REQUIRE(x && v && x_out && v_out, "l2hmc_u1_hmc_step: null pointer");
+  L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_hmc_step: bad sizes N=%d T=%d X=%d", N, T, X);
+  L2HMC_REQUIRE(aligned16(x) && aligned16(v) && aligned16(x_out) && aligned16(v_out),
+                "l2hmc_u1_hmc_step: pointers must be 16-byte aligned");
+  HmcParams p{};
+  p.x = x, p.v_f = v, p.dir = dir, p.beta = beta, p.eps = eps, p.num_steps = 1, p.N = N;
+  p.x_post = x_out, p.v_post = v_out;
+  return dispatch<false>(p, T, X, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* a, void* stream) {
+  L2HMC_REQUIRE(a && a->x, "l2hmc_u1_hmc_mc_step: null x");
+  L2HMC_REQUIRE(a->N >= 0 && a->T > 0 && a->X > 0 && a->num_steps >= 1, "l2hmc_u1_hmc_mc_step: bad sizes");
+  L2HMC_REQUIRE(a->v_f || !a->v_b, "l2hmc_u1_hmc_mc_step: v_b given without v_f");
+  L2HMC_REQUIRE(aligned16(a->x) && aligned16(a->v_f) && aligned16(a->v_b) && aligned16(a->x_post) &&
+                    aligned16(a->v_post) && aligned16(a->x_out),
+                "l2hmc_u1_hmc_mc_step: pointers must be 16-byte aligned");
+  HmcParams p{};
+  p.x = a->x, p.v_f = a->v_f, p.v_b = a->v_b, p.u_dir = a->u_dir, p.u_acc = a->u_acc;
+  p.beta = a->beta, p.eps = a->eps, p.num_steps = a->num_steps, p.default_dir = a->default_dir;
+  p.wrap = a->wrap_2pi, p.N = a->N, p.seed = a->seed, p.mc_step = a->mc_step, p.chain0 = a->chain0;
+  p.x_post = a->x_post, p.v_post = a->v_post, p.accept_prob = a->accept_prob, p.x_out = a->x_out;
+  p.accepted = a->accepted, p.h_old = a->h_old, p.h_new = a->h_new, p.flag = a->nonfinite_flag;
+  return dispatch<true>(p, a->T, a->X, static_cast<cudaStream_t>(stream));
+}

@@ -1,0 +1,143 @@
+// K1 / K4: plaquette stencil for any T x X lattice -- Wilson action, force, plaquette and
+// topological-charge observables in one pass over the links.
+//
+// Replaces (reference l2hmc/...):
+//   lattice/lattice.py:337-362      GaugeLattice.total_action
+//   lattice/lattice.py:285-313      GaugeLattice.calc_plaq_observables
+//   dynamics/gauge_dynamics.py:698-709  GaugeDynamics.grad_potential (tf.gradients of beta*S)
+//   gauge_model.py:659-716          _calc_plaq_sums/_calc_total_actions/_calc_avg_plaqs/_calc_top_charges
+//
+// One warp owns one chain at a time: the chain's D links are staged once through shared
+// memory (coalesced float2 loads; each link is used by three plaquettes), beta*sin P goes to a
+// second per-warp buffer for the force's backward differences, and the per-chain sums are
+// lane-strided partials closed by a shuffle tree (deterministic).  Only __syncwarp is needed.
+// HBM traffic: 4 B/link read (+ 4 B/link written when the force is requested).
+#include "common.cuh"
+
+namespace l2hmc {
+namespace {
+
+struct StencilParams {
+  const float* x;
+  float beta;
+  int N, T, X;
+  float* action;
+  float* force;
+  float* avg_plaq;
+  float* q_float;
+  int32_t* q_int;
+};
+
+__global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int warps_per_block) {
+  extern __shared__ __align__(16) float s_all[];
+  const int T = p.T, X = p.X, SITES = T * X, D = 2 * SITES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* sx = s_all + static_cast<size_t>(warp) * ((D + SITES + 1) & ~1);  // keep float2 alignment
+  float* sb = sx + D;
+  const bool want_force = p.force != nullptr;
+  const bool want_cos = p.action != nullptr || p.avg_plaq != nullptr;
+  const bool want_q = p.q_float != nullptr || p.q_int != nullptr;
+
+  for (int n = blockIdx.x * warps_per_block + warp; n < p.N; n += gridDim.x * warps_per_block) {
+    const float2* gx = reinterpret_cast<const float2*>(p.x + static_cast<size_t>(n) * D);
+    for (int s = lane; s < SITES; s += 32) reinterpret_cast<float2*>(sx)[s] = gx[s];
+    __syncwarp();
+    float act = 0.f, csum = 0.f, qsum = 0.f;
+    for (int s = lane; s < SITES; s += 32) {
+      const int t = s / X, xx = s - t * X;
+      const int sr = t * X + (xx + 1 == X ? 0 : xx + 1);   // (t, x+1)
+      const int sd = (t + 1 == T ? 0 : t + 1) * X + xx;    // (t+1, x)
+      const float P =
+          __fadd_rn(__fsub_rn(__fsub_rn(sx[2 * s], sx[2 * s + 1]), sx[2 * sr]), sx[2 * sd + 1]);
+      if (want_force && want_cos) {
+        float sn, cs;
+        sincosf(P, &sn, &cs);
+        sb[s] = __fmul_rn(p.beta, sn);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+      } else if (want_force) {
+        sb[s] = __fmul_rn(p.beta, sinf(P));
+      } else if (want_cos) {
+        const float cs = cosf(P);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+      }
+      if (want_q) qsum = __fadd_rn(qsum, project_angle(P));
+    }
+    if (want_force) {
+      __syncwarp();
+      float2* gf = reinterpret_cast<float2*>(p.force + static_cast<size_t>(n) * D);
+      for (int s = lane; s < SITES; s += 32) {
+        const int t = s / X, xx = s - t * X;
+        const int sl = t * X + (xx == 0 ? X - 1 : xx - 1);  // (t, x-1)
+        const int su = (t == 0 ? T - 1 : t - 1) * X + xx;   // (t-1, x)
+        const float b = sb[s];
+        gf[s] = make_float2(__fsub_rn(b, sb[sl]), __fsub_rn(sb[su], b));
+      }
+    }
+    if (want_cos) {
+      act = warp_sum(act);
+      csum = warp_sum(csum);
+    }
+    if (want_q) qsum = warp_sum(qsum);
+    if (lane == 0) {
+      if (p.action) p.action[n] = act;
+      if (p.avg_plaq) p.avg_plaq[n] = __fdiv_rn(csum, static_cast<float>(SITES));
+      const float qf = __fdiv_rn(qsum, kTwoPi);
+      if (p.q_float) p.q_float[n] = qf;
+      if (p.q_int) p.q_int[n] = static_cast<int32_t>(floorf(__fadd_rn(0.1f, qf)));
+    }
+    __syncwarp();
+  }
+}
+
+int launch_stencil(const StencilParams& p, cudaStream_t stream) {
+  if (p.N == 0) return L2HMC_OK;
+  const size_t per_warp = sizeof(float) * ((3u * p.T * p.X + 1u) & ~1u);
+  int dev = 0, max_smem = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int warps = 8;
+  while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
+  const size_t smem = per_warp * warps;
+  if (smem > static_cast<size_t>(max_smem)) {
+    set_error("stencil: a %dx%d chain (%zu B) does not fit shared memory (%d B)", p.T, p.X, smem, max_smem);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(stencil_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(stencil_kernel): %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+  }
+  const int blocks_needed = (p.N + warps - 1) / warps;
+  const int grid = min(blocks_needed, sms * 16);
+  stencil_kernel<<<grid, warps * 32, smem, stream>>>(p, warps);
+  return check_launch("stencil_kernel");
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+extern "C" int l2hmc_u1_action_force(const float* x, float beta, int N, int T, int X, float* action, float* force,
+                                     void* stream) {
+  L2HMC_REQUIRE(x, "l2hmc_u1_action_force: null x");
+  L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_action_force: bad sizes N=%d T=%d X=%d", N, T, X);
+  L2HMC_REQUIRE(action || force, "l2hmc_u1_action_force: nothing requested");
+  StencilParams p{x, beta, N, T, X, action, force, nullptr, nullptr, nullptr};
+  return launch_stencil(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int l2hmc_u1_observables(const float* x, int N, int T, int X, float* action, float* avg_plaq,
+                                    float* q_float, int32_t* q_int, void* stream) {
+  L2HMC_REQUIRE(x, "l2hmc_u1_observables: null x");
+  L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_observables: bad sizes N=%d T=%d X=%d", N, T, X);
+  L2HMC_REQUIRE(action || avg_plaq || q_float || q_int, "l2hmc_u1_observables: nothing requested");
+  StencilParams p{x, 0.f, N, T, X, action, nullptr, avg_plaq, q_float, q_int};
+  return launch_stencil(p, static_cast<cudaStream_t>(stream));
+}
