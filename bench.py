@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- link-updates/s of the U(1) leapfrog path on N B200s.
+
+Workload (BASELINE.json metric / config 4): 32x32 lattice, 65 536 chains PER GPU (weak
+scaling; the 1 GB of links+momenta per GPU is ~8x the 126 MB L2), plain HMC, M = 10 leapfrog
+steps, eps = 0.1, beta = 4, hot start, free-running Philox momenta.  A "step" is one MC step
+(GaugeDynamics.apply_transition + observables) = N*D*M link-updates.
+
+  value      device-resident throughput of the product path (one-launch MC step)
+  e2e        same through GaugeSampler.step with pinned HOST buffers (H2D + D2H inside)
+  roofline   the fused leapfrog-STEP kernel (x,v streamed once per LF step, 16 B/link-update),
+             the kernel the north-star's >= 70 % HBM target names, timed live in its own loop
+  roofline_mc  the one-launch MC-step kernel against its own algorithmic HBM bytes
+  cpu_baseline the oracle restatement of the reference's TF graph on the host cores
+
+`--impl reference` times that CPU restatement alone (TensorFlow 1.x cannot be installed here,
+DESIGN.md section 7), rank 0 only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+T = X = 32
+D = 2 * T * X
+M = 10
+EPS = 0.1
+BETA = 4.0
+METRIC = "link-updates/s"
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm, reasons, mx = [], set(), None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for nm, val in zip(names, r[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            except (ValueError, IndexError):
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_run(steps, warmup, chains):
+    """The oracle restatement of the reference's TF graph (apply_transition: BOTH directions
+    integrated, one discarded, exactly as gauge_dynamics.py:211-241) on the host cores.
+    Returns (link-updates/s, s/step, threads).  Only this function touches oracle/."""
+    import numpy as np
+    import torch
+    from oracle import u1_oracle as orc
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    rng = np.random.default_rng(0)
+    dyn = orc.OracleDynamics(T, X, M, EPS, hmc=True, mask=np.zeros((M, D), np.float32))
+    x = rng.uniform(0, 2 * np.pi, (chains, D)).astype(np.float32)
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            vf = rng.standard_normal((chains, D)).astype(np.float32)
+            vb = rng.standard_normal((chains, D)).astype(np.float32)
+            ud, ua = rng.uniform(size=chains).astype(np.float32), rng.uniform(size=chains).astype(np.float32)
+            t0 = time.perf_counter()
+            _, _, _, xo = dyn.apply_transition(x, BETA, vf, vb, ud, ua)
+            orc.plaq_observables(xo, T, X)
+            x = orc.wrap_2pi(xo.numpy())
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    per_step = sum(times) / len(times)
+    return chains * D * M / per_step, per_step, threads
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    chains = args.cpu_chains
+    value, per_step, threads = cpu_reference_run(args.steps, args.warmup, chains)
+    sample = (f"{chains} chains of the 32x32 workload per step (the GPU arm runs {args.chains_per_gpu} per GPU); "
+              f"torch-CPU fp32 restatement of the TF graph, both directions integrated like the reference")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "link-updates/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, args.chains_per_gpu),
+        "cpu_baseline": {"value": value, "unit": "link-updates/s", "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "link-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "TensorFlow 1.x is not installable in this image: the reference arm is the oracle port",
+    }))
+
+
+def workload_config(args, chains_per_gpu):
+    return {"workload": "U(1) 32x32 plain-HMC MC step (BASELINE config 4), hot start",
+            "lattice": "32x32", "chains_per_gpu": chains_per_gpu, "total_chains": chains_per_gpu * args.gpus,
+            "lf_steps": M, "eps": EPS, "beta": BETA, "momenta": "Philox4x32-10 in-kernel",
+            "observables": "action, plaquette, integer charge every step",
+            "cache": "inputs larger than L2 (x and v are 512 MiB each per GPU vs 126 MB L2)",
+            "parallelism": f"chains sharded over {args.gpus} GPU(s), no data-path collective"}
+
+
+def run_gpu(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from l2hmc_b200 import GaugeDynamics, GaugeLattice, _lib
+    from l2hmc_b200.sampler import GaugeSampler
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.get_lib()                                   # fail loudly if the CUDA library is missing
+    N = args.chains_per_gpu
+    K, W = args.steps, max(args.warmup, 3)
+    lat = GaugeLattice(T, X, 2, "U1", num_samples=1)
+    dyn = GaugeDynamics(lat, hmc=True, num_steps=M, eps=EPS, seed=2024, chain_offset=rank * N, device=dev)
+    gen = torch.Generator(device=dev).manual_seed(1000 + rank)
+    x = torch.rand(N, D, device=dev, generator=gen) * (2 * np.pi)      # synthetic hot start
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    # ------------------------------------------------ device-resident MC steps (the headline `value`)
+    xa, xb = x.clone(), torch.empty_like(x)
+    p = torch.empty(N, device=dev)
+    act, plaq = torch.empty(N, device=dev), torch.empty(N, device=dev)
+    q = torch.empty(N, dtype=torch.int32, device=dev)
+    sums = torch.zeros(4, dtype=torch.float64, device=dev)
+    lib = _lib.get_lib()
+
+    def mc_step(src, dst):
+        a = _lib.HmcMcArgs()
+        a.x, a.x_out, a.accept_prob = _lib.dptr(src), _lib.dptr(dst), _lib.dptr(p)
+        a.beta, a.eps, a.num_steps, a.default_dir, a.wrap_2pi = BETA, EPS, M, 1, 1
+        a.seed, a.mc_step, a.chain0 = dyn.seed, dyn._mc_step, dyn.chain_offset
+        a.N, a.T, a.X = N, T, X
+        a.nonfinite_flag = _lib.dptr(dyn._flag, torch.int32)
+        _lib.check(lib.l2hmc_u1_hmc_mc_step(a, _lib.stream_ptr()))
+        _lib.check(lib.l2hmc_u1_observables(_lib.dptr(dst), N, T, X, _lib.dptr(act), _lib.dptr(plaq), None,
+                                            _lib.dptr(q, torch.int32), _lib.stream_ptr()))
+        dyn._mc_step += 1
+
+    for _ in range(W):
+        mc_step(xa, xb)
+        xa, xb = xb, xa
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    time.sleep(0.3)
+    barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev_mc = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    ev[0].record()
+    for i in range(K):
+        ev_mc[i][0].record()
+        mc_step(xa, xb)
+        ev_mc[i][1].record()
+        xa, xb = xb, xa
+    sums += torch.stack([plaq.sum(dtype=torch.float64), act.sum(dtype=torch.float64), p.sum(dtype=torch.float64),
+                         torch.tensor(float(N), dtype=torch.float64, device=dev)])
+    if world > 1:
+        dist.all_reduce(sums)                      # the only collective: O(1) observable accumulators
+    ev[1].record()
+    barrier()
+    ms_total = max_over_ranks(ev[0].elapsed_time(ev[1]))
+    step_ms = ms_total / K
+    value = world * N * D * M / (step_ms * 1e-3)
+    dyn.raise_if_nonfinite()
+    obs = {"avg_plaq": float(sums[0] / sums[3]), "accept_prob": float(sums[2] / sums[3])}
+
+    # ------------------------------------------------ the fused LF-step kernel, its own timed loop
+    v = torch.randn(N, D, device=dev, generator=gen)
+    x1, v1 = torch.empty_like(x), torch.empty_like(v)
+    bufs = [(xa, v), (x1, v1)]
+
+    def lf_launch(i):
+        (sx, sv), (dx, dv) = bufs[i % 2], bufs[(i + 1) % 2]
+        _lib.check(lib.l2hmc_u1_hmc_step(_lib.dptr(sx), _lib.dptr(sv), BETA, EPS, None, N, T, X, _lib.dptr(dx),
+                                         _lib.dptr(dv), _lib.stream_ptr()))
+    for i in range(4):
+        lf_launch(i)
+    barrier()
+    nl = K * M
+    ev[0].record()
+    for i in range(nl):
+        lf_launch(i)
+    ev[1].record()
+    barrier()
+    lf_ms = max_over_ranks(ev[0].elapsed_time(ev[1])) / nl
+    clk = clocks.stop()
+
+    peak, peak_kind = measured_peaks()
+    lf_bytes = 16.0 * N * D                           # read x, v; write x, v
+    lf_gbs = lf_bytes / (lf_ms * 1e-3) / 1e9
+    mc_kernel_ms = sum(a.elapsed_time(b) for a, b in ev_mc) / K
+    mc_bytes = 8.0 * N * D + 4.0 * N * D              # MC kernel: read x, write x_out; observables: read x_out
+    mc_gbs = mc_bytes / (mc_kernel_ms * 1e-3) / 1e9
+    return dict(value=value, step_ms=step_ms, clk=clk, obs=obs, peak=peak, peak_kind=peak_kind,
+                lf=dict(ms=lf_ms, gbs=lf_gbs, bytes=lf_bytes), mc=dict(ms=mc_kernel_ms, gbs=mc_gbs, bytes=mc_bytes),
+                ctx=dict(dyn=dyn, dev=dev, N=N, K=K, W=W, barrier=barrier, max_over_ranks=max_over_ranks, x=xa,
+                         GaugeSampler=GaugeSampler, torch=torch, world=world))
+
+
+def run_e2e(r):
+    """Same MC step through GaugeSampler.step: pinned host links in, host results out, every step."""
+    c = r["ctx"]
+    torch, N, K = c["torch"], c["N"], c["K"]
+    sampler = c["GaugeSampler"](c["dyn"], N, chunk_chains=8192)
+    host = torch.empty(N, D, dtype=torch.float32).pin_memory()
+    host.copy_(c["x"])
+    for _ in range(2):
+        res = sampler.step(host, BETA)
+        host.copy_(res.samples)
+    c["barrier"]()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record()
+    for _ in range(K):
+        res = sampler.step(host, BETA)          # H2D of the links, MC step, observables, D2H of everything
+        host, sampler.h_out = res.samples, host  # next step feeds what this one returned (no host copy)
+    ev[1].record()
+    c["barrier"]()
+    ms = c["max_over_ranks"](ev[0].elapsed_time(ev[1]))   # step() ends with a host sync: covers copies + kernels
+    step_ms = ms / K
+    return {"value": c["world"] * N * D * M / (step_ms * 1e-3), "unit": "link-updates/s",
+            "h2d_bytes_per_step": sampler.h2d_bytes, "d2h_bytes_per_step": sampler.d2h_bytes,
+            "ms_per_step": step_ms, "launches_per_step": sampler.launches_per_step,
+            "plaq": float(res.plaqs.mean()), "charge_diff": res.charge_diff}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--chains-per-gpu", type=int, default=65536)
+    ap.add_argument("--cpu-chains", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    r = run_gpu(args, rank, local_rank, world)
+    e2e = None if args.no_e2e else run_e2e(r)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, per_step, threads = cpu_reference_run(steps=5, warmup=1, chains=args.cpu_chains)
+        cpu = {"value": v, "unit": "link-updates/s", "cores": threads, "kind": "port",
+               "sample": f"{args.cpu_chains} chains of the same 32x32 M=10 workload, 5 MC steps after 1 warm-up, "
+                         f"{per_step:.3f} s/step; oracle restatement of the TF graph (TF 1.x not installable)"}
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    K = r["ctx"]["K"]
+    launches = K * 2 + K * M + 4 + (0 if e2e is None else (K + 2) * e2e["launches_per_step"])
+    line = {
+        "metric": METRIC, "value": r["value"], "unit": "link-updates/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": r["ctx"]["W"], "ms_per_step": r["step_ms"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, args.chains_per_gpu),
+        "clocks": r["clk"], "gpu_launches": launches, "e2e": e2e,
+        "roofline": {"bound": "hbm", "kernel": "hmc_kernel<32,32,false> (fused leapfrog step, one launch per LF step)",
+                     "achieved": r["lf"]["gbs"], "peak": r["peak"], "peak_kind": r["peak_kind"], "unit": "GB/s",
+                     "frac": r["lf"]["gbs"] / r["peak"], "traffic": None, "algorithmic_bytes": r["lf"]["bytes"],
+                     "ms_per_launch": r["lf"]["ms"],
+                     "link_updates_per_s": args.chains_per_gpu * D / (r["lf"]["ms"] * 1e-3)},
+        "roofline_mc": {"bound": "hbm", "kernel": "hmc_kernel<32,32,true> + stencil_kernel (one MC step, M LF steps "
+                        "on-chip: issue-bound, not HBM-bound)",
+                        "achieved": r["mc"]["gbs"], "peak": r["peak"], "unit": "GB/s",
+                        "frac": r["mc"]["gbs"] / r["peak"], "algorithmic_bytes": r["mc"]["bytes"],
+                        "ms_per_step": r["mc"]["ms"]},
+        "cpu_baseline": cpu, "observables": r["obs"],
+    }
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -62,6 +62,11 @@ int l2hmc_u1_action_force(const float* x, float beta, int N, int T, int X,
 int l2hmc_u1_observables(const float* x, int N, int T, int X, float* action, float* avg_plaq,
                          float* q_float, int32_t* q_int, void* stream);
 
+/* H = beta*S(x) + 0.5*sum_d v^2 per chain in one pass over x and v.
+ * GaugeDynamics.hamiltonian (dynamics/gauge_dynamics.py:691-696). */
+int l2hmc_u1_hamiltonian(const float* x, const float* v, float beta, int N, int T, int X,
+                         float* h /*[N]*/, void* stream);
+
 /* 0.5 * sum_d v^2 per chain.  GaugeDynamics.kinetic_energy (dynamics/gauge_dynamics.py:683-689). */
 int l2hmc_kinetic_energy(const float* v, int N, int D, float* ke, void* stream);
 

@@ -35,6 +35,7 @@ SIGNATURES = {
     "l2hmc_device_info": [POINTER(c_int), POINTER(c_int)],
     "l2hmc_u1_action_force": [c_void_p, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_u1_observables": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_u1_hamiltonian": [c_void_p, c_void_p, c_float, c_int, c_int, c_int, c_void_p, c_void_p],
     "l2hmc_kinetic_energy": [c_void_p, c_int, c_int, c_void_p, c_void_p],
     "l2hmc_update_momentum": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int, c_int,
                               c_void_p, c_void_p, c_void_p, c_void_p],

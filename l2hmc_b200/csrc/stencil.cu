@@ -26,6 +26,8 @@ struct StencilParams {
   float* avg_plaq;
   float* q_float;
   int32_t* q_int;
+  const float* v;   // with `hamil`: kinetic term
+  float* hamil;     // beta*S + 0.5*sum v^2
 };
 
 __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int warps_per_block) {
@@ -35,7 +37,7 @@ __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int
   float* sx = s_all + static_cast<size_t>(warp) * ((D + SITES + 1) & ~1);  // keep float2 alignment
   float* sb = sx + D;
   const bool want_force = p.force != nullptr;
-  const bool want_cos = p.action != nullptr || p.avg_plaq != nullptr;
+  const bool want_cos = p.action != nullptr || p.avg_plaq != nullptr || p.hamil != nullptr;
   const bool want_q = p.q_float != nullptr || p.q_int != nullptr;
 
   for (int n = blockIdx.x * warps_per_block + warp; n < p.N; n += gridDim.x * warps_per_block) {
@@ -80,6 +82,16 @@ __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int
       csum = warp_sum(csum);
     }
     if (want_q) qsum = warp_sum(qsum);
+    if (p.hamil) {
+      const float2* gv = reinterpret_cast<const float2*>(p.v + static_cast<size_t>(n) * D);
+      float ke = 0.f;
+      for (int s = lane; s < SITES; s += 32) {
+        const float2 a = gv[s];
+        ke = __fadd_rn(ke, __fadd_rn(__fmul_rn(a.x, a.x), __fmul_rn(a.y, a.y)));
+      }
+      ke = warp_sum(ke);
+      if (lane == 0) p.hamil[n] = __fadd_rn(__fmul_rn(p.beta, act), __fmul_rn(0.5f, ke));
+    }
     if (lane == 0) {
       if (p.action) p.action[n] = act;
       if (p.avg_plaq) p.avg_plaq[n] = __fdiv_rn(csum, static_cast<float>(SITES));
@@ -129,7 +141,7 @@ extern "C" int l2hmc_u1_action_force(const float* x, float beta, int N, int T, i
   L2HMC_REQUIRE(x, "l2hmc_u1_action_force: null x");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_action_force: bad sizes N=%d T=%d X=%d", N, T, X);
   L2HMC_REQUIRE(action || force, "l2hmc_u1_action_force: nothing requested");
-  StencilParams p{x, beta, N, T, X, action, force, nullptr, nullptr, nullptr};
+  StencilParams p{x, beta, N, T, X, action, force, nullptr, nullptr, nullptr, nullptr, nullptr};
   return launch_stencil(p, static_cast<cudaStream_t>(stream));
 }
 
@@ -138,6 +150,14 @@ extern "C" int l2hmc_u1_observables(const float* x, int N, int T, int X, float* 
   L2HMC_REQUIRE(x, "l2hmc_u1_observables: null x");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_observables: bad sizes N=%d T=%d X=%d", N, T, X);
   L2HMC_REQUIRE(action || avg_plaq || q_float || q_int, "l2hmc_u1_observables: nothing requested");
-  StencilParams p{x, 0.f, N, T, X, action, nullptr, avg_plaq, q_float, q_int};
+  StencilParams p{x, 0.f, N, T, X, action, nullptr, avg_plaq, q_float, q_int, nullptr, nullptr};
+  return launch_stencil(p, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int l2hmc_u1_hamiltonian(const float* x, const float* v, float beta, int N, int T, int X, float* h,
+                                    void* stream) {
+  L2HMC_REQUIRE(x && v && h, "l2hmc_u1_hamiltonian: null pointer");
+  L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_hamiltonian: bad sizes N=%d T=%d X=%d", N, T, X);
+  StencilParams p{x, beta, N, T, X, nullptr, nullptr, nullptr, nullptr, nullptr, v, h};
   return launch_stencil(p, static_cast<cudaStream_t>(stream));
 }
