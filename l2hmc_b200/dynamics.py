@@ -160,7 +160,7 @@ class GaugeDynamics(object):
 
     def _x(self, a):
         t = to_device(a, self.device)
-        return t.reshape(t.shape[0], -1) if t.dim() > 2 else t
+        return t.reshape(t.shape[0], self.x_dim) if t.dim() != 2 else t
 
     def _beta(self, beta):
         return _f32(beta.item() if isinstance(beta, torch.Tensor) else beta)

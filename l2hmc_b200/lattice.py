@@ -109,10 +109,10 @@ class GaugeLattice(object):
         D = self.num_links
         if x.dim() == 1:
             x = x.reshape(1, -1)
-        x = x.reshape(x.shape[0], -1)
-        if x.shape[1] != D:
-            raise ValueError(f"samples have {x.shape[1]} links per chain, lattice has {D}")
-        return x
+        per_chain = int(np.prod(x.shape[1:]))
+        if per_chain != D:
+            raise ValueError(f"samples have {per_chain} links per chain, lattice has {D}")
+        return x.reshape(x.shape[0], D)
 
     def get_energy_function(self, samples=None):
         """fn(samples) -> total action per chain (lattice.py:274-283)."""
