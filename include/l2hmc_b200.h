@@ -137,7 +137,10 @@ int l2hmc_u1_hmc_step(const float* x, const float* v, float beta, float eps, con
  *             `default_dir` (+1/-1) for all chains (== transition_kernel(forward=...)).
  *   accept:   u_acc [N] nullable; NULL -> in-kernel uniform if v_f is NULL, else no select.
  *   outputs (each nullable): x_post, v_post [N,D], accept_prob [N], x_out [N,D],
- *             accepted [N] uint8, h_old / h_new [N].
+ *             accepted [N] uint8, h_old / h_new [N]; obs_action / obs_plaq [N] and
+ *             obs_charge [N] int32: the observables of l2hmc_u1_observables for the state
+ *             each chain ends the step in (x_post if accepted, else x), evaluated on the
+ *             un-wrapped links at no extra HBM traffic.
  */
 typedef struct {
   const float* x;
@@ -162,6 +165,9 @@ typedef struct {
   float* h_old;
   float* h_new;
   int32_t* nonfinite_flag;
+  float* obs_action;
+  float* obs_plaq;
+  int32_t* obs_charge;
 } l2hmc_hmc_mc_args;
 
 int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* args, void* stream);

@@ -25,6 +25,7 @@ class HmcMcArgs(Structure):
         ("N", c_int), ("T", c_int), ("X", c_int),
         ("x_post", c_void_p), ("v_post", c_void_p), ("accept_prob", c_void_p), ("x_out", c_void_p),
         ("accepted", c_void_p), ("h_old", c_void_p), ("h_new", c_void_p), ("nonfinite_flag", c_void_p),
+        ("obs_action", c_void_p), ("obs_plaq", c_void_p), ("obs_charge", c_void_p),
     ]
 
 

@@ -15,8 +15,12 @@
 // memory with 1-D bulk async copies (TMA engine, mbarrier completion) through a 2-stage ring,
 // so compute warps never wait on global memory.  Each compute thread owns a strip of four
 // sites of one chain (8 links, contiguous) in registers; the plaquette needs the next row and
-// the next column (shared memory / one shuffle), the force needs beta*sin P of the previous
-// row and column (shared memory / one shuffle): two named barriers per force evaluation.
+// the next column (a shared-memory plane of the mu=1 links / one shuffle), the force needs
+// beta*sin P of the previous row and column (a second plane / one shuffle): per force evaluation
+// two conflict-free float4 stores, two float4 loads, two shuffles and two named barriers.
+// sin/cos are the branch-free fast_sin.cuh versions (abs. error 1.6e-7).  The MC-step kernel also
+// emits the observables (action, plaquette, integer charge) of the state each chain ends in:
+// P is already in registers at both ends of the trajectory, so they cost no HBM traffic.
 //
 // Arithmetic keeps the reference's fp32 op order (every product and sum rounded separately, no
 // FMA contraction: this file is compiled with -fmad=false):
@@ -25,6 +29,7 @@
 //   v' = v - (eps/2) * g;   x' = x + eps * v'        gauge_dynamics.py:486-534 with S=T=Q=0
 // and the backward step is the same with eps -> -eps (bit-identical to :537-590).
 #include "common.cuh"
+#include "fast_sin.cuh"
 
 namespace l2hmc {
 
@@ -52,6 +57,9 @@ struct HmcParams {
   uint8_t* accepted;
   float* h_old;
   float* h_new;
+  float* obs_action;
+  float* obs_plaq;
+  int32_t* obs_charge;
   int32_t* flag;
 };
 
@@ -72,8 +80,8 @@ template <bool MC>
 struct Smem {
   static constexpr int kBufsPerStage = MC ? 3 : 2;  // x, v, (x_out)
   static constexpr int kStageFloats = kBufsPerStage * kTileFloats;
-  static constexpr int kBFloats = 2 * (kTileFloats / 2);  // beta*sin P, double-buffered
-  static constexpr int kRedFloats = 8 * 4;
+  static constexpr int kBFloats = 2 * (kTileFloats / 2);  // two site planes: mu=1 links, beta*sin P
+  static constexpr int kRedFloats = 8 * 8;
   static constexpr size_t bytes = sizeof(float) * (kStages * kStageFloats + kBFloats + kRedFloats) +
                                   sizeof(uint64_t) * 2 * kStages;
 };
@@ -165,46 +173,50 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
   const int x0 = 4 * cg;
   const int lane_right = (lane & ~(XG - 1)) | ((lane + 1) & (XG - 1));
   const int lane_left = (lane & ~(XG - 1)) | ((lane + XG - 1) & (XG - 1));
-  const int off_own = c * D + 8 * k;
-  const int off_dn = c * D + (((t + 1) % T) * X + x0) * 2;
-  const int boff_own = c * G::SITES + t * X + x0;
-  const int boff_up = c * G::SITES + ((t + T - 1) % T) * X + x0;
+  const int off_own = c * D + 8 * k;                                   // own strip in a stage buffer
+  const int boff_own = c * G::SITES + t * X + x0;                      // own 4 sites in a site plane
+  const int boff_dn = c * G::SITES + ((t + 1) % T) * X + x0;           // row t+1
+  const int boff_up = c * G::SITES + ((t + T - 1) % T) * X + x0;       // row t-1
+  float* s_u1 = s_b;                        // plane of the mu=1 links (what row t-1 needs from row t)
+  float* s_bs = s_b + kTileFloats / 2;      // plane of beta*sin P
   const float beta = p.beta;
   const float half_eps = __fmul_rn(0.5f, p.eps);
 
   float xs[8], vs[8], g[8];
-  unsigned eval_parity = 0;
 
-  // One force evaluation; x of every chain of the tile must be visible in `sx`.
-  auto force = [&](const float* sx, bool want_cos, float& act_part) {
-    const float4 d0 = *reinterpret_cast<const float4*>(sx + off_dn);
-    const float4 d1 = *reinterpret_cast<const float4*>(sx + off_dn + 4);
+  // One force evaluation from the links in registers.  Exchanges through two site planes in
+  // shared memory (one float4 store + one float4 load each, conflict-free) and two shuffles.
+  // obs != nullptr additionally accumulates {sum(1-cos P), sum cos P, sum proj(P)}.
+  auto force = [&](float* obs) {
+    *reinterpret_cast<float4*>(s_u1 + boff_own) = make_float4(xs[1], xs[3], xs[5], xs[7]);
+    named_bar_sync(1, kComputeThreads);
+    const float4 dn = *reinterpret_cast<const float4*>(s_u1 + boff_dn);
     const float u0r = __shfl_sync(0xffffffffu, xs[0], lane_right);
     float P[4];
-    P[0] = __fadd_rn(__fsub_rn(__fsub_rn(xs[0], xs[1]), xs[2]), d0.y);
-    P[1] = __fadd_rn(__fsub_rn(__fsub_rn(xs[2], xs[3]), xs[4]), d0.w);
-    P[2] = __fadd_rn(__fsub_rn(__fsub_rn(xs[4], xs[5]), xs[6]), d1.y);
-    P[3] = __fadd_rn(__fsub_rn(__fsub_rn(xs[6], xs[7]), u0r), d1.w);
+    P[0] = __fadd_rn(__fsub_rn(__fsub_rn(xs[0], xs[1]), xs[2]), dn.x);
+    P[1] = __fadd_rn(__fsub_rn(__fsub_rn(xs[2], xs[3]), xs[4]), dn.y);
+    P[2] = __fadd_rn(__fsub_rn(__fsub_rn(xs[4], xs[5]), xs[6]), dn.z);
+    P[3] = __fadd_rn(__fsub_rn(__fsub_rn(xs[6], xs[7]), u0r), dn.w);
     float b[4];
-    if (want_cos) {
-      float acc = 0.f;
+    if (obs != nullptr) {
+      float act = 0.f, csum = 0.f, qsum = 0.f;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float sn, cs;
-        sincosf(P[j], &sn, &cs);
+        fast_sincos(P[j], &sn, &cs);
         b[j] = __fmul_rn(beta, sn);
-        acc = __fadd_rn(acc, __fsub_rn(1.f, cs));
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+        qsum = __fadd_rn(qsum, project_angle(P[j]));
       }
-      act_part = acc;
+      obs[0] = act, obs[1] = csum, obs[2] = qsum;
     } else {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = __fmul_rn(beta, sinf(P[j]));
+      for (int j = 0; j < 4; ++j) b[j] = __fmul_rn(beta, fast_sin(P[j]));
     }
-    float* sb = s_b + (eval_parity & 1u) * (kTileFloats / 2);
-    eval_parity ^= 1u;
-    *reinterpret_cast<float4*>(sb + boff_own) = make_float4(b[0], b[1], b[2], b[3]);
+    *reinterpret_cast<float4*>(s_bs + boff_own) = make_float4(b[0], b[1], b[2], b[3]);
     named_bar_sync(1, kComputeThreads);
-    const float4 bu = *reinterpret_cast<const float4*>(sb + boff_up);
+    const float4 bu = *reinterpret_cast<const float4*>(s_bs + boff_up);
     const float bl = __shfl_sync(0xffffffffu, b[3], lane_left);
     g[0] = __fsub_rn(b[0], bl);
     g[1] = __fsub_rn(bu.x, b[0]);
@@ -224,7 +236,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
     const int chain = tile * CPB + c;
     const bool valid = chain < p.N;
 
-    // per-chain direction (global reads issued before the smem wait)
+    // per-chain direction / accept draw (global reads issued before the smem wait)
     float sgn = 1.f, u_acc = 2.f;
     bool have_acc = false;
     if (MC) {
@@ -264,15 +276,14 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         vs[0] = w0.x, vs[1] = w0.y, vs[2] = w0.z, vs[3] = w0.w;
         vs[4] = w1.x, vs[5] = w1.y, vs[6] = w1.z, vs[7] = w1.w;
       }
-    } else {
+    } else {  // tail tile: chains past N integrate zeros and are never stored
 #pragma unroll
       for (int j = 0; j < 8; ++j) xs[j] = 0.f, vs[j] = 0.f;
-      *reinterpret_cast<float4*>(sx + off_own) = make_float4(0.f, 0.f, 0.f, 0.f);
-      *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
 
     float xs0[8];
-    float act0 = 0.f, act1 = 0.f, ke0 = 0.f, ke1 = 0.f;
+    float obs0[3] = {0.f, 0.f, 0.f}, obs1[3] = {0.f, 0.f, 0.f};
+    float ke0 = 0.f, ke1 = 0.f;
     if (MC) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -280,10 +291,8 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         ke0 = __fadd_rn(ke0, __fmul_rn(vs[j], vs[j]));
       }
     }
-    // tail tiles zero-fill invalid chains in smem; make that visible before neighbours read
-    if (tile * CPB + CPB > p.N) named_bar_sync(1, kComputeThreads);
 
-    force(sx, MC, act0);
+    force(MC ? obs0 : nullptr);
     const int nsteps = MC ? p.num_steps : 1;
     for (int step = 0; step < nsteps; ++step) {
 #pragma unroll
@@ -291,40 +300,44 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
         xs[j] = __fadd_rn(xs[j], __fmul_rn(eps_d, vs[j]));
       }
-      *reinterpret_cast<float4*>(sx + off_own) = make_float4(xs[0], xs[1], xs[2], xs[3]);
-      *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(xs[4], xs[5], xs[6], xs[7]);
-      named_bar_sync(1, kComputeThreads);
-      force(sx, MC && step == nsteps - 1, act1);
+      force((MC && step == nsteps - 1) ? obs1 : nullptr);
 #pragma unroll
       for (int j = 0; j < 8; ++j) vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
     }
+    *reinterpret_cast<float4*>(sx + off_own) = make_float4(xs[0], xs[1], xs[2], xs[3]);
+    *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(xs[4], xs[5], xs[6], xs[7]);
     *reinterpret_cast<float4*>(sv + off_own) = make_float4(vs[0], vs[1], vs[2], vs[3]);
     *reinterpret_cast<float4*>(sv + off_own + 4) = make_float4(vs[4], vs[5], vs[6], vs[7]);
 
     if (MC) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) ke1 = __fadd_rn(ke1, __fmul_rn(vs[j], vs[j]));
-      // per-chain sums of (action0, kinetic0, action1, kinetic1)
-      float r0, r1, r2, r3;
+      // per-chain sums of {action, kinetic, sum cos, sum proj} at both ends of the trajectory
+      float r[8] = {obs0[0], ke0, obs0[1], obs0[2], obs1[0], ke1, obs1[1], obs1[2]};
       if (TPC <= 32) {
-        r0 = group_sum<(TPC < 32 ? TPC : 32)>(act0);
-        r1 = group_sum<(TPC < 32 ? TPC : 32)>(ke0);
-        r2 = group_sum<(TPC < 32 ? TPC : 32)>(act1);
-        r3 = group_sum<(TPC < 32 ? TPC : 32)>(ke1);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = group_sum<(TPC < 32 ? TPC : 32)>(r[j]);
       } else {
-        r0 = warp_sum(act0), r1 = warp_sum(ke0), r2 = warp_sum(act1), r3 = warp_sum(ke1);
-        if (lane == 0) *reinterpret_cast<float4*>(s_red + 4 * warp) = make_float4(r0, r1, r2, r3);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = warp_sum(r[j]);
+        if (lane == 0) {
+          *reinterpret_cast<float4*>(s_red + 8 * warp) = make_float4(r[0], r[1], r[2], r[3]);
+          *reinterpret_cast<float4*>(s_red + 8 * warp + 4) = make_float4(r[4], r[5], r[6], r[7]);
+        }
         named_bar_sync(1, kComputeThreads);
         constexpr int WPC = TPC > 32 ? TPC / 32 : 1;
-        r0 = r1 = r2 = r3 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[j] = 0.f;
 #pragma unroll
         for (int w = 0; w < WPC; ++w) {
-          const float4 q = *reinterpret_cast<const float4*>(s_red + 4 * (c * WPC + w));
-          r0 += q.x, r1 += q.y, r2 += q.z, r3 += q.w;
+          const float4 q0 = *reinterpret_cast<const float4*>(s_red + 8 * (c * WPC + w));
+          const float4 q1 = *reinterpret_cast<const float4*>(s_red + 8 * (c * WPC + w) + 4);
+          r[0] += q0.x, r[1] += q0.y, r[2] += q0.z, r[3] += q0.w;
+          r[4] += q1.x, r[5] += q1.y, r[6] += q1.z, r[7] += q1.w;
         }
       }
-      const float h0 = __fadd_rn(__fmul_rn(beta, r0), __fmul_rn(0.5f, r1));
-      const float h1 = __fadd_rn(__fmul_rn(beta, r2), __fmul_rn(0.5f, r3));
+      const float h0 = __fadd_rn(__fmul_rn(beta, r[0]), __fmul_rn(0.5f, r[1]));
+      const float h1 = __fadd_rn(__fmul_rn(beta, r[4]), __fmul_rn(0.5f, r[5]));
       const float dh = __fsub_rn(h0, h1);
       float prob = expf(fminf(dh, 0.f));
       if (isnan(dh)) prob = 0.f;  // tf.minimum propagates NaN; is_finite -> 0 (gauge_dynamics.py:604-609)
@@ -335,6 +348,11 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         if (p.h_old) p.h_old[chain] = h0;
         if (p.h_new) p.h_new[chain] = h1;
         if (isnan(dh) && p.flag) atomicOr(p.flag, 1);
+        // observables of the state the chain ends the MC step in (lattice.py:300-311)
+        const float act = acc ? r[4] : r[0], csum = acc ? r[6] : r[2], qsum = acc ? r[7] : r[3];
+        if (p.obs_action) p.obs_action[chain] = act;
+        if (p.obs_plaq) p.obs_plaq[chain] = __fdiv_rn(csum, static_cast<float>(G::SITES));
+        if (p.obs_charge) p.obs_charge[chain] = static_cast<int32_t>(floorf(__fadd_rn(0.1f, __fdiv_rn(qsum, kTwoPi))));
       }
       if (p.x_out) {
         float* so = sx + 2 * kTileFloats;
@@ -405,6 +423,7 @@ using namespace l2hmc;
 
 extern "C" int l2hmc_u1_hmc_step(const float* x, const float* v, float beta, float eps, const int8_t* dir, int N,
                                  int T, int X, float* x_out, float* v_out, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x && v && x_out && v_out, "l2hmc_u1_hmc_step: null pointer");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_hmc_step: bad sizes N=%d T=%d X=%d", N, T, X);
   L2HMC_REQUIRE(aligned16(x) && aligned16(v) && aligned16(x_out) && aligned16(v_out),
@@ -416,7 +435,9 @@ extern "C" int l2hmc_u1_hmc_step(const float* x, const float* v, float beta, flo
 }
 
 extern "C" int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* a, void* stream) {
-  L2HMC_REQUIRE(a && a->x, "l2hmc_u1_hmc_mc_step: null x");
+  L2HMC_REQUIRE(a, "l2hmc_u1_hmc_mc_step: null args");
+  if (a->N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(a->x, "l2hmc_u1_hmc_mc_step: null x");
   L2HMC_REQUIRE(a->N >= 0 && a->T > 0 && a->X > 0 && a->num_steps >= 1, "l2hmc_u1_hmc_mc_step: bad sizes");
   L2HMC_REQUIRE(a->v_f || !a->v_b, "l2hmc_u1_hmc_mc_step: v_b given without v_f");
   L2HMC_REQUIRE(aligned16(a->x) && aligned16(a->v_f) && aligned16(a->v_b) && aligned16(a->x_post) &&
@@ -428,5 +449,6 @@ extern "C" int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* a, void* stream) {
   p.wrap = a->wrap_2pi, p.N = a->N, p.seed = a->seed, p.mc_step = a->mc_step, p.chain0 = a->chain0;
   p.x_post = a->x_post, p.v_post = a->v_post, p.accept_prob = a->accept_prob, p.x_out = a->x_out;
   p.accepted = a->accepted, p.h_old = a->h_old, p.h_new = a->h_new, p.flag = a->nonfinite_flag;
+  p.obs_action = a->obs_action, p.obs_plaq = a->obs_plaq, p.obs_charge = a->obs_charge;
   return dispatch<true>(p, a->T, a->X, static_cast<cudaStream_t>(stream));
 }

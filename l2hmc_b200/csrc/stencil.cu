@@ -138,6 +138,7 @@ using namespace l2hmc;
 
 extern "C" int l2hmc_u1_action_force(const float* x, float beta, int N, int T, int X, float* action, float* force,
                                      void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x, "l2hmc_u1_action_force: null x");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_action_force: bad sizes N=%d T=%d X=%d", N, T, X);
   L2HMC_REQUIRE(action || force, "l2hmc_u1_action_force: nothing requested");
@@ -147,6 +148,7 @@ extern "C" int l2hmc_u1_action_force(const float* x, float beta, int N, int T, i
 
 extern "C" int l2hmc_u1_observables(const float* x, int N, int T, int X, float* action, float* avg_plaq,
                                     float* q_float, int32_t* q_int, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x, "l2hmc_u1_observables: null x");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_observables: bad sizes N=%d T=%d X=%d", N, T, X);
   L2HMC_REQUIRE(action || avg_plaq || q_float || q_int, "l2hmc_u1_observables: nothing requested");
@@ -156,6 +158,7 @@ extern "C" int l2hmc_u1_observables(const float* x, int N, int T, int X, float* 
 
 extern "C" int l2hmc_u1_hamiltonian(const float* x, const float* v, float beta, int N, int T, int X, float* h,
                                     void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x && v && h, "l2hmc_u1_hamiltonian: null pointer");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0, "l2hmc_u1_hamiltonian: bad sizes N=%d T=%d X=%d", N, T, X);
   StencilParams p{x, beta, N, T, X, nullptr, nullptr, nullptr, nullptr, nullptr, v, h};

@@ -253,6 +253,7 @@ using namespace l2hmc;
 extern "C" int l2hmc_update_momentum(const float* v, const float* g, const float* S, const float* Tr, const float* Q,
                                      float eps, int dir, int N, int D, float* v_out, float* logdet,
                                      int32_t* nonfinite_flag, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(v && g && v_out, "l2hmc_update_momentum: null pointer");
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_update_momentum: bad sizes N=%d D=%d", N, D);
   L2HMC_REQUIRE(dir == 1 || dir == -1, "l2hmc_update_momentum: dir must be +1 or -1");
@@ -275,6 +276,7 @@ extern "C" int l2hmc_update_momentum(const float* v, const float* g, const float
 extern "C" int l2hmc_update_position(const float* x, const float* v, const float* S, const float* Tr, const float* Q,
                                      const float* mask, int invert_mask, float eps, int dir, int N, int D,
                                      float* x_out, float* logdet, int32_t* nonfinite_flag, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x && v && mask && x_out, "l2hmc_update_position: null pointer");
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_update_position: bad sizes N=%d D=%d", N, D);
   L2HMC_REQUIRE(dir == 1 || dir == -1, "l2hmc_update_position: dir must be +1 or -1");
@@ -298,6 +300,7 @@ extern "C" int l2hmc_update_position(const float* x, const float* v, const float
 
 extern "C" int l2hmc_mask_mul(const float* x, const float* mask, int invert_mask, int N, int D, float* out,
                               void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x && mask && out, "l2hmc_mask_mul: null pointer");
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_mask_mul: bad sizes");
   if (N == 0) return L2HMC_OK;
@@ -308,6 +311,7 @@ extern "C" int l2hmc_mask_mul(const float* x, const float* mask, int invert_mask
 }
 
 extern "C" int l2hmc_kinetic_energy(const float* v, int N, int D, float* ke, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(v && ke, "l2hmc_kinetic_energy: null pointer");
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_kinetic_energy: bad sizes");
   if (N == 0) return L2HMC_OK;
@@ -317,6 +321,7 @@ extern "C" int l2hmc_kinetic_energy(const float* v, int N, int D, float* ke, voi
 
 extern "C" int l2hmc_accept_prob(const float* h_old, const float* h_new, const float* sumlogdet, int N, float* p,
                                  int32_t* nonfinite_flag, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(h_old && h_new && p, "l2hmc_accept_prob: null pointer");
   L2HMC_REQUIRE(N >= 0, "l2hmc_accept_prob: bad N");
   if (N == 0) return L2HMC_OK;
@@ -329,6 +334,7 @@ extern "C" int l2hmc_mh_select(const float* x, const float* x_f, const float* x_
                                const float* p_f, const float* p_b, const float* u_dir, const float* u_acc, int N,
                                int D, int wrap_2pi, float* x_post, float* v_post, float* p, float* x_out,
                                uint8_t* accepted, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(x && x_f && p_f, "l2hmc_mh_select: null pointer");
   L2HMC_REQUIRE(!v_post || v_f, "l2hmc_mh_select: v_post requested without v_f");
   L2HMC_REQUIRE(!x_b || (p_b && (!v_post || v_b)), "l2hmc_mh_select: backward arrays must be given together");
@@ -341,6 +347,7 @@ extern "C" int l2hmc_mh_select(const float* x, const float* x_f, const float* x_
 
 extern "C" int l2hmc_philox_draws(uint64_t seed, uint64_t mc_step, uint64_t chain0, int N, int D, float* normals,
                                   float* u_dir, float* u_acc, void* stream) {
+  if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_philox_draws: bad sizes");
   L2HMC_REQUIRE(normals || u_dir || u_acc, "l2hmc_philox_draws: nothing requested");
   if (N == 0) return L2HMC_OK;

@@ -334,7 +334,7 @@ class GaugeDynamics(object):
         return self.hmc and self.use_fused and (self.T, self.X) in _lib.FUSED_HMC_SHAPES
 
     def _fused_mc(self, x, beta, v_f, v_b, u_dir, u_acc, default_dir, want_post=True, want_out=True,
-                  wrap=False, want_h=False):
+                  wrap=False, want_h=False, want_obs=False):
         N, D = x.shape
         dev = x.device
         new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
@@ -355,6 +355,10 @@ class GaugeDynamics(object):
         a.x_post, a.v_post, a.accept_prob, a.x_out = _lib.dptr(x_post), _lib.dptr(v_post), _lib.dptr(p), _lib.dptr(x_out)
         a.accepted, a.h_old, a.h_new = _lib.dptr(acc, torch.uint8), _lib.dptr(h0), _lib.dptr(h1)
         a.nonfinite_flag = _lib.dptr(self._flag, torch.int32)
+        if want_obs:   # observables of the state each chain ends in, fused into the same launch
+            self.last_observables = (new(N), new(N), torch.empty(N, dtype=torch.int32, device=dev))
+            a.obs_action, a.obs_plaq = _lib.dptr(self.last_observables[0]), _lib.dptr(self.last_observables[1])
+            a.obs_charge = _lib.dptr(self.last_observables[2], torch.int32)
         with torch.cuda.device(dev):
             self._lib_call(_lib.get_lib().l2hmc_u1_hmc_mc_step, ctypes.byref(a))
         return x_post, v_post, p, x_out, acc, h0, h1
@@ -382,13 +386,14 @@ class GaugeDynamics(object):
 
     # ------------------------------------------------------------------ MC step
     def apply_transition(self, position, beta, momentum_f=None, momentum_b=None, direction_uniform=None,
-                         accept_uniform=None, wrap=False):
+                         accept_uniform=None, wrap=False, observables=False):
         """Propose and accept/reject (gauge_dynamics.py:195-259).
 
         Returns (position_post, momentum_post, accept_prob, position_out).  The four keyword
         arguments inject the reference's in-graph draws (:269 twice, :223, :246); all-None runs the
         free-running Philox stream.  wrap=True also applies the host loop's np.mod(x_out, 2 pi)
-        (gauge_model.py:1180,1388) to position_out.
+        (gauge_model.py:1180,1388) to position_out.  observables=True leaves (action, avg_plaq,
+        integer charge) of position_out in self.last_observables (lattice.py:285-313).
         """
         x = self._x(position)
         N, D = x.shape
@@ -405,7 +410,8 @@ class GaugeDynamics(object):
 
         if self._fused_ok():
             x_post, v_post, p, x_out, self.last_accepted, _, _ = self._fused_mc(
-                x, beta, v_f, v_b if inject and momentum_b is not None else None, u_dir, u_acc, +1, wrap=wrap)
+                x, beta, v_f, v_b if inject and momentum_b is not None else None, u_dir, u_acc, +1, wrap=wrap,
+                want_obs=observables)
             if not inject:
                 self._mc_step += 1
             return x_post, v_post, p, x_out
@@ -434,6 +440,9 @@ class GaugeDynamics(object):
                        _lib.dptr(p_post), None, None, _lib.dptr(u_acc), N, D, int(bool(wrap)), None, None, None,
                        _lib.dptr(x_out), _lib.dptr(acc, torch.uint8))
         self.last_accepted = acc
+        if observables:
+            a_, p_, _, q_ = self.lattice.observables(x_out)
+            self.last_observables = (a_, p_, q_)
         return x_post, v_post, p_post, x_out
 
     def call(self, position, beta, **inject):

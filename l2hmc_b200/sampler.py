@@ -3,7 +3,7 @@
 Mirrors what one iteration of GaugeModel.run does around the dynamics call
 (reference l2hmc/gauge_model.py:1379-1388): feed `samples` from the host, fetch
 [x_out, px, actions, plaqs, charges, charge_diff], then `samples = np.mod(x_out, 2 pi)`.
-Here the mod is fused into the MC-step kernel, the observables are one pass over x_out, and
+Here the mod and the observables are fused into the one-launch MC-step kernel, and
 the host<->device copies are pipelined against compute in chain chunks over three CUDA
 streams (chains are independent, so chunking changes nothing numerically: the Philox stream
 is keyed by the global chain index).
@@ -46,7 +46,7 @@ class GaugeSampler(object):
         self.streams = [torch.cuda.Stream(device=self.dev) for _ in range(self.nbuf)]
         self.h2d_bytes = self.N * self.D * 4
         self.d2h_bytes = self.N * self.D * 4 + 3 * self.N * 4 + 2 * self.N * 4
-        self.launches_per_step = 2 * nchunks
+        self.launches_per_step = nchunks
 
     def pinned_like(self, samples):
         """A pinned host copy of `samples` (N, D) to feed step()."""
@@ -77,10 +77,9 @@ class GaugeSampler(object):
                 a.N, a.T, a.X = n, dyn.T, dyn.X
                 a.accept_prob = _lib.dptr(self.d_px[lo:hi])
                 a.nonfinite_flag = _lib.dptr(dyn._flag, torch.int32)
+                a.obs_action, a.obs_plaq = _lib.dptr(self.d_act[lo:hi]), _lib.dptr(self.d_plaq[lo:hi])
+                a.obs_charge = _lib.dptr(self.d_q[lo:hi], torch.int32)
                 _lib.check(lib.l2hmc_u1_hmc_mc_step(a, _lib.stream_ptr()))
-                _lib.check(lib.l2hmc_u1_observables(
-                    _lib.dptr(xout), n, dyn.T, dyn.X, _lib.dptr(self.d_act[lo:hi]), _lib.dptr(self.d_plaq[lo:hi]),
-                    None, _lib.dptr(self.d_q[lo:hi], torch.int32), _lib.stream_ptr()))
                 self.h_out[lo:hi].copy_(xout, non_blocking=True)
         for st in self.streams:
             main.wait_stream(st)

@@ -69,7 +69,12 @@ def test_fused_equals_generic_and_oracle(pkg, T, X, N):
     for fused in (True, False):
         dyn = pkg.GaugeDynamics(lat, hmc=True, num_steps=M, eps=eps, use_fused=fused)
         outs.append(dyn.apply_transition(x, beta, momentum_f=vf, momentum_b=vb, direction_uniform=ud,
-                                         accept_uniform=ua, wrap=True) + (dyn.last_accepted,))
+                                         accept_uniform=ua, wrap=True, observables=True) + (dyn.last_accepted,))
+        # observables of x_out (fused into the MC-step launch on the fused path) vs the stencil kernel
+        a_, p_, _, q_ = lat.observables(outs[-1][3])
+        close(dyn.last_observables[0], a_, rtol=1e-5, atol=1e-4)
+        close(dyn.last_observables[1], p_, rtol=1e-5, atol=1e-6)
+        assert torch.equal(dyn.last_observables[2], q_)
     for a, b in zip(outs[0][:2], outs[1][:2]):
         close(a, b, rtol=0, atol=2e-6)                 # same op order; sinf vs sincosf may differ by an ulp
     close(outs[0][2], outs[1][2], rtol=1e-4, atol=1e-6)
