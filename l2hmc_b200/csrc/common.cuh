@@ -73,6 +73,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (++spins > (1u << 24)) __trap();
   }
 }
+// Same, for a warp that has nothing else to do (the copy warp): sleep between polls so the
+// spin does not take issue slots from the compute warps of the SM.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(256);
+    if (++spins > (1u << 22)) __trap();
+  }
+}
 // 1-D bulk async copy global -> shared (TMA engine, no tensor map); completes on `bar`.
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
   asm volatile(
@@ -100,6 +109,44 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// ------------------------------------------------------------------ packed fp32x2 (Blackwell FFMA2/FADD2/FMUL2)
+// Two IEEE fp32 lanes per instruction, each rounded exactly like the scalar op: the issue-bound
+// fused kernels do their element-wise math on pairs.  NOTE ptxas contracts mul.rn.f32x2 followed
+// by add.rn.f32x2 into one FFMA2 (even with explicit .rn); where the reference's separately
+// rounded `a + b*c` is wanted, use madd2_unfused(), whose add is an FFMA2 by a RUNTIME 1.0.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float lo2(f32x2 v) { return __uint_as_float(static_cast<unsigned>(v)); }
+__device__ __forceinline__ float hi2(f32x2 v) { return __uint_as_float(static_cast<unsigned>(v >> 32)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// a + b*c with the product and the sum rounded separately (`one` must be a runtime (1,1)).
+__device__ __forceinline__ f32x2 madd2_unfused(f32x2 a, f32x2 b, f32x2 c, f32x2 one) {
+  return fma2(a, one, mul2(b, c));
+}
+
 // ------------------------------------------------------------------ reference fp32 idioms
 // p - 2pi*floor((p + pi)/2pi) with every op rounded separately (lattice/lattice.py:47-49).
 __device__ __forceinline__ float project_angle(float p) {
@@ -108,8 +155,19 @@ __device__ __forceinline__ float project_angle(float p) {
 }
 // numpy's float32 np.mod(x, 2pi): fmod, then shift negatives up by the divisor.
 __device__ __forceinline__ float wrap_2pi(float x) {
-  float r = fmodf(x, kTwoPi);
-  if (r != 0.f && r < 0.f) r = __fadd_rn(r, kTwoPi);
+  const float ax = fabsf(x);
+  float r;
+  if (__builtin_expect(ax < 65536.f, 1)) {
+    // exact fmod(|x|, c): for q = floor(|x|/c) the value |x| - q*c is a multiple of 2^-21 below 8,
+    // hence representable, and one FMA delivers it exactly; q from the reciprocal can be off by one.
+    float q = floorf(__fmul_rn(ax, 0.15915494309189535f));
+    r = fmaf(-q, kTwoPi, ax);
+    if (r < 0.f) r = fmaf(-(q - 1.f), kTwoPi, ax);
+    else if (r >= kTwoPi) r = fmaf(-(q + 1.f), kTwoPi, ax);
+  } else {
+    r = fmodf(ax, kTwoPi);
+  }
+  if (x < 0.f && r != 0.f) r = __fadd_rn(-r, kTwoPi);   // numpy: negative remainder + divisor
   return r;
 }
 
@@ -146,9 +204,9 @@ __device__ __forceinline__ float u01(uint32_t r) { return static_cast<float>(r >
 __device__ __forceinline__ void box_muller(uint32_t r0, uint32_t r1, float& z0, float& z1) {
   float u1 = static_cast<float>((r0 >> 8) + 1u) * 5.9604644775390625e-08f;  // (0,1]
   float u2 = u01(r1);
-  float rad = sqrtf(-2.f * logf(u1));
+  float rad = sqrtf(-2.f * __logf(u1));        // MUFU.LG2 / MUFU.SIN / MUFU.COS: plenty for a generator
   float s, c;
-  sincosf(kTwoPi * u2, &s, &c);
+  __sincosf(kTwoPi * u2 - kPi, &s, &c);        // argument in [-pi, pi): the intrinsics' accurate range
   z0 = rad * c;
   z1 = rad * s;
 }

@@ -72,4 +72,26 @@ __device__ __forceinline__ void fast_sincos(float x, float* sn, float* cs) {
   *cs = q.fold ? -c : c;
 }
 
+// Two sines per instruction stream (FFMA2/FADD2/FMUL2): the same reduction, fold and polynomial
+// as fast_sin on each lane.  The caller guarantees |x| <= 4e4 on both lanes.
+__device__ __forceinline__ f32x2 fast_sin2(f32x2 x) {
+  const f32x2 magic = pack2(12582912.0f, 12582912.0f);
+  const f32x2 j = sub2(fma2(x, pack2(0.15915494309189535f, 0.15915494309189535f), magic), magic);
+  f32x2 r = fma2(j, pack2(-6.28125f, -6.28125f), x);
+  r = fma2(j, pack2(-0.0019350051879882812f, -0.0019350051879882812f), r);
+  r = fma2(j, pack2(-3.019916050561733e-07f, -3.019916050561733e-07f), r);
+  const f32x2 a = r & 0x7fffffff7fffffffULL;
+  const f32x2 folded = add2(sub2(pack2(3.14159274101257324f, 3.14159274101257324f), a),
+                            pack2(-8.742277657347586e-08f, -8.742277657347586e-08f));
+  // |r| <= pi (+ rounding): min(|r|, pi - |r|) takes the fold exactly when |r| > pi/2
+  const f32x2 m = pack2(fminf(lo2(a), lo2(folded)), fminf(hi2(a), hi2(folded)));
+  const f32x2 rr = m ^ (r & 0x8000000080000000ULL);
+  const f32x2 s = mul2(rr, rr);
+  f32x2 p = fma2(pack2(2.599861772978329e-06f, 2.599861772978329e-06f), s,
+                 pack2(-0.0001980652887141332f, -0.0001980652887141332f));
+  p = fma2(p, s, pack2(0.008333016186952591f, 0.008333016186952591f));
+  p = fma2(p, s, pack2(-0.16666656732559204f, -0.16666656732559204f));
+  return fma2(mul2(rr, s), p, rr);
+}
+
 }  // namespace l2hmc

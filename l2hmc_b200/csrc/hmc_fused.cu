@@ -28,6 +28,8 @@
 //   b  = beta * sin P;  g0 = b - b[x-1];  g1 = -b + b[t-1]   (adjoint of the roll graph)
 //   v' = v - (eps/2) * g;   x' = x + eps * v'        gauge_dynamics.py:486-534 with S=T=Q=0
 // and the backward step is the same with eps -> -eps (bit-identical to :537-590).
+// The element-wise math runs on packed fp32x2 pairs (FFMA2 / FADD2 / FMUL2: two IEEE lanes per
+// issue slot -- the kernels are issue-bound, not HBM-bound, once the trajectory is on-chip).
 #include "common.cuh"
 #include "fast_sin.cuh"
 
@@ -47,7 +49,7 @@ struct HmcParams {
   const float* u_dir;
   const float* u_acc;
   const int8_t* dir;
-  float beta, eps;
+  float beta, eps, one;
   int num_steps, default_dir, wrap, N, num_tiles;
   unsigned long long seed, mc_step, chain0;
   float* x_post;
@@ -129,7 +131,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       const int s = it % kStages;
       if (it >= kStages) {  // the stage's previous tile: wait for the compute warps, write it back
         if (lane == 0) {
-          mbar_wait(&done[s], ((it / kStages) - 1) & 1);
+          mbar_wait_sleep(&done[s], ((it / kStages) - 1) & 1);
           store_tile(tile - kStages * static_cast<int>(gridDim.x), s);
           bulk_wait_read_all();
         }
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
     if (lane == 0) {
       for (int j = max(0, it - kStages); j < it; ++j) {
         const int s = j % kStages;
-        mbar_wait(&done[s], (j / kStages) & 1);
+        mbar_wait_sleep(&done[s], (j / kStages) & 1);
         store_tile(static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x), s);
       }
       bulk_wait_all();
@@ -182,23 +184,27 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
   const float beta = p.beta;
   const float half_eps = __fmul_rn(0.5f, p.eps);
 
-  float xs[8], vs[8], g[8];
+  // Thread state, packed fp32x2 in SoA order: X0a = (U0(s0), U0(s1)), X0b = (U0(s2), U0(s3)),
+  // X1a/X1b the mu=1 links, same for momenta V* and force G* (s0..s3 = the thread's four sites).
+  f32x2 X0a, X0b, X1a, X1b, V0a, V0b, V1a, V1b, G0a, G0b, G1a, G1b;
+  const f32x2 one = pack2(p.one, p.one);   // runtime 1.0: keeps ptxas from contracting mul+add
+  const f32x2 beta2 = pack2(beta, beta);
 
   // One force evaluation from the links in registers.  Exchanges through two site planes in
   // shared memory (one float4 store + one float4 load each, conflict-free) and two shuffles.
   // obs != nullptr additionally accumulates {sum(1-cos P), sum cos P, sum proj(P)}.
   auto force = [&](float* obs) {
-    *reinterpret_cast<float4*>(s_u1 + boff_own) = make_float4(xs[1], xs[3], xs[5], xs[7]);
+    *reinterpret_cast<float4*>(s_u1 + boff_own) = make_float4(lo2(X1a), hi2(X1a), lo2(X1b), hi2(X1b));
     named_bar_sync(1, kComputeThreads);
     const float4 dn = *reinterpret_cast<const float4*>(s_u1 + boff_dn);
-    const float u0r = __shfl_sync(0xffffffffu, xs[0], lane_right);
-    float P[4];
-    P[0] = __fadd_rn(__fsub_rn(__fsub_rn(xs[0], xs[1]), xs[2]), dn.x);
-    P[1] = __fadd_rn(__fsub_rn(__fsub_rn(xs[2], xs[3]), xs[4]), dn.y);
-    P[2] = __fadd_rn(__fsub_rn(__fsub_rn(xs[4], xs[5]), xs[6]), dn.z);
-    P[3] = __fadd_rn(__fsub_rn(__fsub_rn(xs[6], xs[7]), u0r), dn.w);
-    float b[4];
-    if (obs != nullptr) {
+    const float u0r = __shfl_sync(0xffffffffu, lo2(X0a), lane_right);
+    // P = ((U0 - U1) - U0[x+1]) + U1[t+1]   (lattice.py:354-357), two plaquettes per instruction
+    f32x2 Pa = add2(sub2(sub2(X0a, X1a), pack2(hi2(X0a), lo2(X0b))), pack2(dn.x, dn.y));
+    f32x2 Pb = add2(sub2(sub2(X0b, X1b), pack2(hi2(X0b), u0r)), pack2(dn.z, dn.w));
+    const float pmax = fmaxf(fmaxf(fabsf(lo2(Pa)), fabsf(hi2(Pa))), fmaxf(fabsf(lo2(Pb)), fabsf(hi2(Pb))));
+    f32x2 Ba, Bb;
+    if (obs != nullptr || !(pmax <= 40000.f)) {   // trajectory ends (need cos) or out-of-range angles
+      float P[4] = {lo2(Pa), hi2(Pa), lo2(Pb), hi2(Pb)}, b[4];
       float act = 0.f, csum = 0.f, qsum = 0.f;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -209,23 +215,20 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         csum = __fadd_rn(csum, cs);
         qsum = __fadd_rn(qsum, project_angle(P[j]));
       }
-      obs[0] = act, obs[1] = csum, obs[2] = qsum;
+      if (obs != nullptr) obs[0] = act, obs[1] = csum, obs[2] = qsum;
+      Ba = pack2(b[0], b[1]), Bb = pack2(b[2], b[3]);
     } else {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) b[j] = __fmul_rn(beta, fast_sin(P[j]));
+      Ba = mul2(beta2, fast_sin2(Pa));
+      Bb = mul2(beta2, fast_sin2(Pb));
     }
-    *reinterpret_cast<float4*>(s_bs + boff_own) = make_float4(b[0], b[1], b[2], b[3]);
+    *reinterpret_cast<float4*>(s_bs + boff_own) = make_float4(lo2(Ba), hi2(Ba), lo2(Bb), hi2(Bb));
     named_bar_sync(1, kComputeThreads);
     const float4 bu = *reinterpret_cast<const float4*>(s_bs + boff_up);
-    const float bl = __shfl_sync(0xffffffffu, b[3], lane_left);
-    g[0] = __fsub_rn(b[0], bl);
-    g[1] = __fsub_rn(bu.x, b[0]);
-    g[2] = __fsub_rn(b[1], b[0]);
-    g[3] = __fsub_rn(bu.y, b[1]);
-    g[4] = __fsub_rn(b[2], b[1]);
-    g[5] = __fsub_rn(bu.z, b[2]);
-    g[6] = __fsub_rn(b[3], b[2]);
-    g[7] = __fsub_rn(bu.w, b[3]);
+    const float bl = __shfl_sync(0xffffffffu, hi2(Bb), lane_left);
+    G0a = sub2(Ba, pack2(bl, lo2(Ba)));              // g0 = b - b[x-1]
+    G0b = sub2(Bb, pack2(hi2(Ba), lo2(Bb)));
+    G1a = sub2(pack2(bu.x, bu.y), Ba);               // g1 = -b + b[t-1]
+    G1b = sub2(pack2(bu.z, bu.w), Bb);
   };
 
   int it = 0;
@@ -257,61 +260,65 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
     } else if (p.dir) {
       sgn = (valid ? p.dir[chain] : 1) >= 0 ? 1.f : -1.f;
     }
-    const float eps_d = __fmul_rn(sgn, p.eps);
-    const float heps_d = __fmul_rn(sgn, half_eps);
+    // v' = v + (-s*eps/2)*g and x' = x + (s*eps)*v': the negated factor gives bit-identical results
+    // to the reference's v - (eps/2)*g (and to its backward step for s = -1)
+    const float eps_s = __fmul_rn(sgn, p.eps);
+    const float nheps_s = -__fmul_rn(sgn, half_eps);
+    const f32x2 eps2 = pack2(eps_s, eps_s), nheps2 = pack2(nheps_s, nheps_s);
 
     mbar_wait(&full[s], (it / kStages) & 1);
 
     if (valid) {
       const float4 a0 = *reinterpret_cast<const float4*>(sx + off_own);
       const float4 a1 = *reinterpret_cast<const float4*>(sx + off_own + 4);
-      xs[0] = a0.x, xs[1] = a0.y, xs[2] = a0.z, xs[3] = a0.w;
-      xs[4] = a1.x, xs[5] = a1.y, xs[6] = a1.z, xs[7] = a1.w;
+      X0a = pack2(a0.x, a0.z), X1a = pack2(a0.y, a0.w);
+      X0b = pack2(a1.x, a1.z), X1b = pack2(a1.y, a1.w);
       if (rng) {
-        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k, vs);
-        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k + 1u, vs + 4);
+        float z[8];
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k, z);
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k + 1u, z + 4);
+        V0a = pack2(z[0], z[2]), V1a = pack2(z[1], z[3]);
+        V0b = pack2(z[4], z[6]), V1b = pack2(z[5], z[7]);
       } else {
         const float4 w0 = *reinterpret_cast<const float4*>(sv + off_own);
         const float4 w1 = *reinterpret_cast<const float4*>(sv + off_own + 4);
-        vs[0] = w0.x, vs[1] = w0.y, vs[2] = w0.z, vs[3] = w0.w;
-        vs[4] = w1.x, vs[5] = w1.y, vs[6] = w1.z, vs[7] = w1.w;
+        V0a = pack2(w0.x, w0.z), V1a = pack2(w0.y, w0.w);
+        V0b = pack2(w1.x, w1.z), V1b = pack2(w1.y, w1.w);
       }
     } else {  // tail tile: chains past N integrate zeros and are never stored
-#pragma unroll
-      for (int j = 0; j < 8; ++j) xs[j] = 0.f, vs[j] = 0.f;
+      X0a = X0b = X1a = X1b = V0a = V0b = V1a = V1b = 0ULL;
     }
 
-    float xs0[8];
+    f32x2 S0a = X0a, S0b = X0b, S1a = X1a, S1b = X1b;   // x at the start of the trajectory (reject)
     float obs0[3] = {0.f, 0.f, 0.f}, obs1[3] = {0.f, 0.f, 0.f};
     float ke0 = 0.f, ke1 = 0.f;
-    if (MC) {
+    auto kinetic = [&]() {   // sum v^2 in link order, every term and sum rounded separately
+      const float v[8] = {lo2(V0a), lo2(V1a), hi2(V0a), hi2(V1a), lo2(V0b), lo2(V1b), hi2(V0b), hi2(V1b)};
+      float acc = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        xs0[j] = xs[j];
-        ke0 = __fadd_rn(ke0, __fmul_rn(vs[j], vs[j]));
-      }
-    }
+      for (int j = 0; j < 8; ++j) acc = __fadd_rn(acc, __fmul_rn(v[j], v[j]));
+      return acc;
+    };
+    if (MC) ke0 = kinetic();
 
     force(MC ? obs0 : nullptr);
     const int nsteps = MC ? p.num_steps : 1;
     for (int step = 0; step < nsteps; ++step) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
-        xs[j] = __fadd_rn(xs[j], __fmul_rn(eps_d, vs[j]));
-      }
+      V0a = madd2_unfused(V0a, nheps2, G0a, one), V0b = madd2_unfused(V0b, nheps2, G0b, one);
+      V1a = madd2_unfused(V1a, nheps2, G1a, one), V1b = madd2_unfused(V1b, nheps2, G1b, one);
+      X0a = madd2_unfused(X0a, eps2, V0a, one), X0b = madd2_unfused(X0b, eps2, V0b, one);
+      X1a = madd2_unfused(X1a, eps2, V1a, one), X1b = madd2_unfused(X1b, eps2, V1b, one);
       force((MC && step == nsteps - 1) ? obs1 : nullptr);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) vs[j] = __fsub_rn(vs[j], __fmul_rn(heps_d, g[j]));
+      V0a = madd2_unfused(V0a, nheps2, G0a, one), V0b = madd2_unfused(V0b, nheps2, G0b, one);
+      V1a = madd2_unfused(V1a, nheps2, G1a, one), V1b = madd2_unfused(V1b, nheps2, G1b, one);
     }
-    *reinterpret_cast<float4*>(sx + off_own) = make_float4(xs[0], xs[1], xs[2], xs[3]);
-    *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(xs[4], xs[5], xs[6], xs[7]);
-    *reinterpret_cast<float4*>(sv + off_own) = make_float4(vs[0], vs[1], vs[2], vs[3]);
-    *reinterpret_cast<float4*>(sv + off_own + 4) = make_float4(vs[4], vs[5], vs[6], vs[7]);
+    *reinterpret_cast<float4*>(sx + off_own) = make_float4(lo2(X0a), lo2(X1a), hi2(X0a), hi2(X1a));
+    *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(lo2(X0b), lo2(X1b), hi2(X0b), hi2(X1b));
+    *reinterpret_cast<float4*>(sv + off_own) = make_float4(lo2(V0a), lo2(V1a), hi2(V0a), hi2(V1a));
+    *reinterpret_cast<float4*>(sv + off_own + 4) = make_float4(lo2(V0b), lo2(V1b), hi2(V0b), hi2(V1b));
 
     if (MC) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) ke1 = __fadd_rn(ke1, __fmul_rn(vs[j], vs[j]));
+      ke1 = kinetic();
       // per-chain sums of {action, kinetic, sum cos, sum proj} at both ends of the trajectory
       float r[8] = {obs0[0], ke0, obs0[1], obs0[2], obs1[0], ke1, obs1[1], obs1[2]};
       if (TPC <= 32) {
@@ -356,11 +363,11 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       }
       if (p.x_out) {
         float* so = sx + 2 * kTileFloats;
-        float o[8];
+        const f32x2 O0a = acc ? X0a : S0a, O0b = acc ? X0b : S0b, O1a = acc ? X1a : S1a, O1b = acc ? X1b : S1b;
+        float o[8] = {lo2(O0a), lo2(O1a), hi2(O0a), hi2(O1a), lo2(O0b), lo2(O1b), hi2(O0b), hi2(O1b)};
+        if (p.wrap) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          o[j] = acc ? xs[j] : xs0[j];
-          if (p.wrap) o[j] = wrap_2pi(o[j]);
+          for (int j = 0; j < 8; ++j) o[j] = wrap_2pi(o[j]);
         }
         *reinterpret_cast<float4*>(so + off_own) = make_float4(o[0], o[1], o[2], o[3]);
         *reinterpret_cast<float4*>(so + off_own + 4) = make_float4(o[4], o[5], o[6], o[7]);
@@ -395,6 +402,7 @@ int launch(const HmcParams& p_in, cudaStream_t stream) {
     blocks_per_sm = bps;
   }
   p.num_tiles = (p.N + G::CPB - 1) / G::CPB;
+  p.one = 1.0f;
   if (p.num_tiles == 0) return L2HMC_OK;
   const int grid = min(p.num_tiles, blocks_per_sm * sm_count);
   kern<<<grid, kThreads, Smem<MC>::bytes, stream>>>(p);

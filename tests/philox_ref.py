@@ -51,8 +51,8 @@ def philox_normals(seed, mc_step, chain0, N, D):
         u2 = (r[:, j + 1] >> np.uint64(8)).astype(np.float64) * 2.0 ** -24
         u1 = u1.astype(np.float32).astype(np.float64)
         rad = np.sqrt(-2.0 * np.log(u1))
-        ang = np.float64(np.float32(2 * np.pi)) * u2
-        ang = ang.astype(np.float32).astype(np.float64)
+        ang = (np.float64(np.float32(2 * np.pi)) * u2).astype(np.float32)       # fp32 product,
+        ang = (ang - np.float32(np.pi)).astype(np.float32).astype(np.float64)    # then fp32 shift to [-pi, pi)
         out[:, j] = rad * np.cos(ang)
         out[:, j + 1] = rad * np.sin(ang)
     return out.reshape(N, quads * 4)[:, :D].astype(np.float32)
