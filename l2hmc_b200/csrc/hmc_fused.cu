@@ -4,32 +4,32 @@
 //                                   (16 B / link-update) -- the HBM-roofline kernel.
 //   hmc_kernel<T, X, /*MC=*/true>   a whole Monte-Carlo step per launch: momenta (injected or
 //                                   Philox), M leapfrog steps with x, v resident on-chip, both
-//                                   Hamiltonians, accept probability, direction + accept select.
+//                                   Hamiltonians, accept probability, direction + accept select,
+//                                   mod-2pi wrap and the observables of the resulting state.
 //
 // Replaces GaugeDynamics.apply_transition / transition_kernel / _forward_lf / _backward_lf with
-// the hmc stubs (reference l2hmc/dynamics/gauge_dynamics.py:102-108, 195-313, 412-483) and the
-// force tf.gradients(beta * total_action) (:698-709, lattice/lattice.py:337-362).
+// the hmc stubs (reference l2hmc/dynamics/gauge_dynamics.py:102-108, 195-313, 412-483), the
+// force tf.gradients(beta * total_action) (:698-709, lattice/lattice.py:337-362) and the
+// observables of lattice/lattice.py:285-313.
 //
-// Structure (B200): persistent CTAs, 8 compute warps + 1 copy warp.  A tile is 2048 links =
-// 8 KB of x (+ 8 KB of v) = 256/TPC whole chains; the copy warp moves tiles HBM <-> shared
-// memory with 1-D bulk async copies (TMA engine, mbarrier completion) through a 2-stage ring,
-// so compute warps never wait on global memory.  Each compute thread owns a strip of four
-// sites of one chain (8 links, contiguous) in registers; the plaquette needs the next row and
-// the next column (a shared-memory plane of the mu=1 links / one shuffle), the force needs
-// beta*sin P of the previous row and column (a second plane / one shuffle): per force evaluation
-// two conflict-free float4 stores, two float4 loads, two shuffles and two named barriers.
-// sin/cos are the branch-free fast_sin.cuh versions (abs. error 1.6e-7).  The MC-step kernel also
-// emits the observables (action, plaquette, integer charge) of the state each chain ends in:
-// P is already in registers at both ends of the trajectory, so they cost no HBM traffic.
+// Structure (B200): persistent CTAs of 8 warps.  A tile is 2048 links = 8 KB of x (+ 8 KB of v)
+// = 256/TPC whole chains.  Tiles move HBM <-> shared memory with 1-D bulk async copies (TMA
+// engine): loads land in a 2-deep ring and complete on an mbarrier, issued TWO tiles ahead as
+// soon as the ring slot has been read into registers; results are staged in shared memory and
+// leave as bulk stores.  No thread ever waits on a global load, and no warp polls.
+// Each thread owns a strip of four sites of one chain (8 links, contiguous) in registers as
+// packed fp32x2 pairs; the plaquette needs the next row and column (a shared-memory plane of the
+// mu=1 links / one shuffle), the force needs beta*sin P of the previous row and column (a second
+// plane / one shuffle): per force evaluation two conflict-free float4 stores, two float4 loads,
+// two shuffles and two named barriers.
 //
-// Arithmetic keeps the reference's fp32 op order (every product and sum rounded separately, no
-// FMA contraction: this file is compiled with -fmad=false):
+// Arithmetic keeps the reference's fp32 op order (every product and sum rounded separately):
 //   P  = ((U0 - U1) - U0[x+1]) + U1[t+1]            lattice.py:354-357
 //   b  = beta * sin P;  g0 = b - b[x-1];  g1 = -b + b[t-1]   (adjoint of the roll graph)
 //   v' = v - (eps/2) * g;   x' = x + eps * v'        gauge_dynamics.py:486-534 with S=T=Q=0
-// and the backward step is the same with eps -> -eps (bit-identical to :537-590).
-// The element-wise math runs on packed fp32x2 pairs (FFMA2 / FADD2 / FMUL2: two IEEE lanes per
-// issue slot -- the kernels are issue-bound, not HBM-bound, once the trajectory is on-chip).
+// and the backward step is the same with eps -> -eps (bit-identical to :537-590).  The math
+// runs on FFMA2 / FADD2 / FMUL2 (two IEEE lanes per issue slot: with the trajectory on-chip the
+// kernels are issue-bound, not HBM-bound); sin/cos are the branch-free fast_sin.cuh versions.
 #include "common.cuh"
 #include "fast_sin.cuh"
 
@@ -37,9 +37,7 @@ namespace l2hmc {
 
 namespace {
 
-constexpr int kComputeThreads = 256;
-constexpr int kThreads = kComputeThreads + 32;
-constexpr int kStages = 2;
+constexpr int kThreads = 256;
 constexpr int kTileFloats = 2048;  // links per tile (8 KB)
 
 struct HmcParams {
@@ -63,149 +61,123 @@ struct HmcParams {
   float* obs_plaq;
   int32_t* obs_charge;
   int32_t* flag;
+  // shared-memory layout, in floats (filled by launch())
+  int in_floats;   // one load-ring slot: x (+ v when momenta are injected)
+  int off_out;     // start of the output staging area
+  int off_xpost, off_vpost, off_xout;   // offsets inside the staging area, -1 = not requested
+  int off_planes;  // two site planes (mu=1 links, beta*sin P)
+  int off_red;     // per-warp partial sums
+  int off_bar;     // two mbarriers
 };
 
 template <int T, int X>
 struct Geo {
   static constexpr int SITES = T * X;
   static constexpr int D = 2 * SITES;
-  static constexpr int TPC = SITES / 4;              // threads per chain
-  static constexpr int CPB = kComputeThreads / TPC;  // chains per tile
-  static constexpr int XG = X / 4;                   // threads per lattice row
+  static constexpr int TPC = SITES / 4;       // threads per chain
+  static constexpr int CPB = kThreads / TPC;  // chains per tile
+  static constexpr int XG = X / 4;            // threads per lattice row
   static_assert(X % 4 == 0, "strip of four sites per thread");
-  static_assert(TPC >= 1 && TPC <= kComputeThreads && kComputeThreads % TPC == 0, "chain must fit one CTA");
+  static_assert(TPC >= 1 && TPC <= kThreads && kThreads % TPC == 0, "chain must fit one CTA");
   static_assert(XG >= 1 && XG <= 32 && (XG & (XG - 1)) == 0, "row neighbours by warp shuffle");
   static_assert(CPB * D == kTileFloats, "tile is always 8 KB");
 };
 
-template <bool MC>
-struct Smem {
-  static constexpr int kBufsPerStage = MC ? 3 : 2;  // x, v, (x_out)
-  static constexpr int kStageFloats = kBufsPerStage * kTileFloats;
-  static constexpr int kBFloats = 2 * (kTileFloats / 2);  // two site planes: mu=1 links, beta*sin P
-  static constexpr int kRedFloats = 8 * 8;
-  static constexpr size_t bytes = sizeof(float) * (kStages * kStageFloats + kBFloats + kRedFloats) +
-                                  sizeof(uint64_t) * 2 * kStages;
-};
+// 128-bit shared-memory accesses by 32-bit shared address (no generic-pointer arithmetic in the loop)
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 template <int T, int X, bool MC>
 __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcParams p) {
   using G = Geo<T, X>;
   constexpr int D = G::D, TPC = G::TPC, CPB = G::CPB, XG = G::XG;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  float* s_stage = reinterpret_cast<float*>(smem_raw);
-  float* s_b = s_stage + kStages * Smem<MC>::kStageFloats;
-  float* s_red = s_b + Smem<MC>::kBFloats;
-  uint64_t* full = reinterpret_cast<uint64_t*>(s_red + Smem<MC>::kRedFloats);
-  uint64_t* done = full + kStages;
+  extern __shared__ __align__(128) float smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + p.off_bar);
+  float* s_red = smem + p.off_red;
 
   const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31;
+  const bool rng = MC && (p.v_f == nullptr);
+  const bool per_chain_v = MC && !rng && p.v_b != nullptr;
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full[s], 1);
-      mbar_init(&done[s], kComputeThreads);
-    }
+    mbar_init(&full[0], 1);
+    mbar_init(&full[1], 1);
     mbar_fence_init();
   }
   __syncthreads();
 
-  const bool rng = MC && (p.v_f == nullptr);
-
-  if (warp == kComputeThreads / 32) {
-    // ------------------------------------------------------------------ copy warp
-    auto store_tile = [&](int tile, int s) {
-      const int chain_base = tile * CPB;
-      const int nvalid = min(CPB, p.N - chain_base);
-      const uint32_t bytes = static_cast<uint32_t>(nvalid) * D * 4u;
-      float* sx = s_stage + s * Smem<MC>::kStageFloats;
-      const size_t goff = static_cast<size_t>(chain_base) * D;
-      if (p.x_post) bulk_s2g(p.x_post + goff, sx, bytes);
-      if (p.v_post) bulk_s2g(p.v_post + goff, sx + kTileFloats, bytes);
-      if (MC && p.x_out) bulk_s2g(p.x_out + goff, sx + 2 * kTileFloats, bytes);
-      bulk_commit();
-    };
-    int it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-      const int s = it % kStages;
-      if (it >= kStages) {  // the stage's previous tile: wait for the compute warps, write it back
-        if (lane == 0) {
-          mbar_wait_sleep(&done[s], ((it / kStages) - 1) & 1);
-          store_tile(tile - kStages * static_cast<int>(gridDim.x), s);
-          bulk_wait_read_all();
-        }
-        __syncwarp();
-      }
-      const int chain_base = tile * CPB;
-      const int nvalid = min(CPB, p.N - chain_base);
-      const uint32_t bytes = static_cast<uint32_t>(nvalid) * D * 4u;
-      float* sx = s_stage + s * Smem<MC>::kStageFloats;
-      const size_t goff = static_cast<size_t>(chain_base) * D;
-      const bool per_chain_v = MC && !rng && p.v_b != nullptr;
-      if (lane == 0) mbar_arrive_expect_tx(&full[s], rng ? bytes : 2u * bytes);
-      __syncwarp();
-      if (lane == 0) {
-        bulk_g2s(sx, p.x + goff, bytes, &full[s]);
-        if (!rng && !per_chain_v) bulk_g2s(sx + kTileFloats, p.v_f + goff, bytes, &full[s]);
-      }
-      if (per_chain_v) {
-        for (int c = lane; c < nvalid; c += 32) {
-          const bool fwd = p.u_dir ? (p.u_dir[chain_base + c] > 0.5f) : (p.default_dir >= 0);
-          const float* src = (fwd ? p.v_f : p.v_b) + goff + static_cast<size_t>(c) * D;
-          bulk_g2s(sx + kTileFloats + c * D, src, D * 4u, &full[s]);
-        }
-      }
-      __syncwarp();
-    }
+  // Warp 0 issues the bulk load of `tile` into ring slot `slot` (lane 0: links; momenta: one
+  // copy, or one per chain from v_f / v_b according to the chain's direction).
+  auto issue_load = [&](int tile, int slot) {
+    const int chain_base = tile * CPB;
+    const int nvalid = min(CPB, p.N - chain_base);
+    const uint32_t bytes = static_cast<uint32_t>(nvalid) * D * 4u;
+    float* sx = smem + slot * p.in_floats;
+    const size_t goff = static_cast<size_t>(chain_base) * D;
     if (lane == 0) {
-      for (int j = max(0, it - kStages); j < it; ++j) {
-        const int s = j % kStages;
-        mbar_wait_sleep(&done[s], (j / kStages) & 1);
-        store_tile(static_cast<int>(blockIdx.x) + j * static_cast<int>(gridDim.x), s);
-      }
-      bulk_wait_all();
+      mbar_arrive_expect_tx(&full[slot], rng ? bytes : 2u * bytes);
+      bulk_g2s(sx, p.x + goff, bytes, &full[slot]);
+      if (!rng && !per_chain_v) bulk_g2s(sx + kTileFloats, p.v_f + goff, bytes, &full[slot]);
     }
-    return;
+    __syncwarp();
+    if (per_chain_v) {
+      for (int cc = lane; cc < nvalid; cc += 32) {
+        const bool fwd = p.u_dir ? (p.u_dir[chain_base + cc] > 0.5f) : (p.default_dir >= 0);
+        const float* src = (fwd ? p.v_f : p.v_b) + goff + static_cast<size_t>(cc) * D;
+        bulk_g2s(sx + kTileFloats + cc * D, src, D * 4u, &full[slot]);
+      }
+      __syncwarp();
+    }
+  };
+  if (warp == 0) {
+    issue_load(blockIdx.x, 0);
+    if (blockIdx.x + gridDim.x < p.num_tiles) issue_load(blockIdx.x + gridDim.x, 1);
   }
 
-  // -------------------------------------------------------------------- compute warps
   const int k = tid % TPC, c = tid / TPC;
   const int t = k / XG, cg = k % XG;
   const int x0 = 4 * cg;
   const int lane_right = (lane & ~(XG - 1)) | ((lane + 1) & (XG - 1));
   const int lane_left = (lane & ~(XG - 1)) | ((lane + XG - 1) & (XG - 1));
-  const int off_own = c * D + 8 * k;                                   // own strip in a stage buffer
-  const int boff_own = c * G::SITES + t * X + x0;                      // own 4 sites in a site plane
-  const int boff_dn = c * G::SITES + ((t + 1) % T) * X + x0;           // row t+1
-  const int boff_up = c * G::SITES + ((t + T - 1) % T) * X + x0;       // row t-1
-  float* s_u1 = s_b;                        // plane of the mu=1 links (what row t-1 needs from row t)
-  float* s_bs = s_b + kTileFloats / 2;      // plane of beta*sin P
+  const int off_own = c * D + 8 * k;  // own strip inside a tile buffer (floats)
+  const uint32_t planes = smem_u32(smem + p.off_planes);
+  const uint32_t a_u1_own = planes + 4u * (c * G::SITES + t * X + x0);               // mu=1 links, own sites
+  const uint32_t a_u1_dn = planes + 4u * (c * G::SITES + ((t + 1) % T) * X + x0);    // ... of row t+1
+  const uint32_t a_b_own = a_u1_own + 4u * (kTileFloats / 2);                        // beta*sin P, own sites
+  const uint32_t a_b_up = planes + 4u * (kTileFloats / 2 + c * G::SITES + ((t + T - 1) % T) * X + x0);
   const float beta = p.beta;
   const float half_eps = __fmul_rn(0.5f, p.eps);
+  const f32x2 one = pack2(p.one, p.one);  // runtime 1.0: keeps ptxas from contracting mul+add
+  const f32x2 beta2 = pack2(beta, beta);
 
   // Thread state, packed fp32x2 in SoA order: X0a = (U0(s0), U0(s1)), X0b = (U0(s2), U0(s3)),
   // X1a/X1b the mu=1 links, same for momenta V* and force G* (s0..s3 = the thread's four sites).
   f32x2 X0a, X0b, X1a, X1b, V0a, V0b, V1a, V1b, G0a, G0b, G1a, G1b;
-  const f32x2 one = pack2(p.one, p.one);   // runtime 1.0: keeps ptxas from contracting mul+add
-  const f32x2 beta2 = pack2(beta, beta);
 
-  // One force evaluation from the links in registers.  Exchanges through two site planes in
-  // shared memory (one float4 store + one float4 load each, conflict-free) and two shuffles.
-  // obs != nullptr additionally accumulates {sum(1-cos P), sum cos P, sum proj(P)}.
+  auto publish_u1 = [&]() {
+    sts128(a_u1_own, lo2(X1a), hi2(X1a), lo2(X1b), hi2(X1b));
+    named_bar_sync(1, kThreads);
+  };
+  // Force from the links in registers, after publish_u1().  obs != nullptr additionally
+  // accumulates {sum(1-cos P), sum cos P, sum proj(P)} (the trajectory's two ends).
   auto force = [&](float* obs) {
-    *reinterpret_cast<float4*>(s_u1 + boff_own) = make_float4(lo2(X1a), hi2(X1a), lo2(X1b), hi2(X1b));
-    named_bar_sync(1, kComputeThreads);
-    const float4 dn = *reinterpret_cast<const float4*>(s_u1 + boff_dn);
+    const float4 dn = lds128(a_u1_dn);
     const float u0r = __shfl_sync(0xffffffffu, lo2(X0a), lane_right);
     // P = ((U0 - U1) - U0[x+1]) + U1[t+1]   (lattice.py:354-357), two plaquettes per instruction
-    f32x2 Pa = add2(sub2(sub2(X0a, X1a), pack2(hi2(X0a), lo2(X0b))), pack2(dn.x, dn.y));
-    f32x2 Pb = add2(sub2(sub2(X0b, X1b), pack2(hi2(X0b), u0r)), pack2(dn.z, dn.w));
+    const f32x2 Pa = add2(sub2(sub2(X0a, X1a), pack2(hi2(X0a), lo2(X0b))), pack2(dn.x, dn.y));
+    const f32x2 Pb = add2(sub2(sub2(X0b, X1b), pack2(hi2(X0b), u0r)), pack2(dn.z, dn.w));
     const float pmax = fmaxf(fmaxf(fabsf(lo2(Pa)), fabsf(hi2(Pa))), fmaxf(fabsf(lo2(Pb)), fabsf(hi2(Pb))));
     f32x2 Ba, Bb;
-    if (obs != nullptr || !(pmax <= 40000.f)) {   // trajectory ends (need cos) or out-of-range angles
-      float P[4] = {lo2(Pa), hi2(Pa), lo2(Pb), hi2(Pb)}, b[4];
-      float act = 0.f, csum = 0.f, qsum = 0.f;
+    if (obs != nullptr || !(pmax <= 40000.f)) {  // trajectory ends (need cos) or out-of-range angles
+      const float P[4] = {lo2(Pa), hi2(Pa), lo2(Pb), hi2(Pb)};
+      float b[4], act = 0.f, csum = 0.f, qsum = 0.f;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float sn, cs;
@@ -221,31 +193,38 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       Ba = mul2(beta2, fast_sin2(Pa));
       Bb = mul2(beta2, fast_sin2(Pb));
     }
-    *reinterpret_cast<float4*>(s_bs + boff_own) = make_float4(lo2(Ba), hi2(Ba), lo2(Bb), hi2(Bb));
-    named_bar_sync(1, kComputeThreads);
-    const float4 bu = *reinterpret_cast<const float4*>(s_bs + boff_up);
+    sts128(a_b_own, lo2(Ba), hi2(Ba), lo2(Bb), hi2(Bb));
+    named_bar_sync(1, kThreads);
+    const float4 bu = lds128(a_b_up);
     const float bl = __shfl_sync(0xffffffffu, hi2(Bb), lane_left);
-    G0a = sub2(Ba, pack2(bl, lo2(Ba)));              // g0 = b - b[x-1]
+    G0a = sub2(Ba, pack2(bl, lo2(Ba)));  // g0 = b - b[x-1]
     G0b = sub2(Bb, pack2(hi2(Ba), lo2(Bb)));
-    G1a = sub2(pack2(bu.x, bu.y), Ba);               // g1 = -b + b[t-1]
+    G1a = sub2(pack2(bu.x, bu.y), Ba);   // g1 = -b + b[t-1]
     G1b = sub2(pack2(bu.z, bu.w), Bb);
   };
 
+  constexpr int GW = TPC < 32 ? TPC : 32;  // lanes of a warp that belong to the same chain
   int it = 0;
   for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-    const int s = it % kStages;
-    float* sx = s_stage + s * Smem<MC>::kStageFloats;
-    float* sv = sx + kTileFloats;
+    const int slot = it & 1;
+    const float* sx = smem + slot * p.in_floats;
     const int chain = tile * CPB + c;
     const bool valid = chain < p.N;
 
-    // per-chain direction / accept draw (global reads issued before the smem wait)
+    // the previous tile's bulk store must have drained the staging area before it is rewritten
+    // (it is rewritten only after the many barriers below, which thread 0 reaches after this wait)
+    if (tid == 0 && it > 0) bulk_wait_read_all();
+
+    // per-chain direction / accept draw (global reads issued before the shared-memory wait)
     float sgn = 1.f, u_acc = 2.f;
     bool have_acc = false;
     if (MC) {
       if (rng) {
-        float ud, ua;
-        philox_uniform2(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, ud, ua);
+        float ud = 0.f, ua = 0.f;
+        if ((lane & (GW - 1)) == 0)   // one Philox call per chain and warp, then broadcast
+          philox_uniform2(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, ud, ua);
+        ud = __shfl_sync(0xffffffffu, ud, lane & ~(GW - 1));
+        ua = __shfl_sync(0xffffffffu, ua, lane & ~(GW - 1));
         sgn = (p.u_dir ? (valid ? p.u_dir[chain] : 1.f) : ud) > 0.5f ? 1.f : -1.f;
         u_acc = p.u_acc ? (valid ? p.u_acc[chain] : 0.f) : ua;
         have_acc = true;
@@ -266,7 +245,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
     const float nheps_s = -__fmul_rn(sgn, half_eps);
     const f32x2 eps2 = pack2(eps_s, eps_s), nheps2 = pack2(nheps_s, nheps_s);
 
-    mbar_wait(&full[s], (it / kStages) & 1);
+    mbar_wait(&full[slot], (it >> 1) & 1);
 
     if (valid) {
       const float4 a0 = *reinterpret_cast<const float4*>(sx + off_own);
@@ -280,8 +259,8 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         V0a = pack2(z[0], z[2]), V1a = pack2(z[1], z[3]);
         V0b = pack2(z[4], z[6]), V1b = pack2(z[5], z[7]);
       } else {
-        const float4 w0 = *reinterpret_cast<const float4*>(sv + off_own);
-        const float4 w1 = *reinterpret_cast<const float4*>(sv + off_own + 4);
+        const float4 w0 = *reinterpret_cast<const float4*>(sx + kTileFloats + off_own);
+        const float4 w1 = *reinterpret_cast<const float4*>(sx + kTileFloats + off_own + 4);
         V0a = pack2(w0.x, w0.z), V1a = pack2(w0.y, w0.w);
         V0b = pack2(w1.x, w1.z), V1b = pack2(w1.y, w1.w);
       }
@@ -289,10 +268,10 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       X0a = X0b = X1a = X1b = V0a = V0b = V1a = V1b = 0ULL;
     }
 
-    f32x2 S0a = X0a, S0b = X0b, S1a = X1a, S1b = X1b;   // x at the start of the trajectory (reject)
+    const f32x2 S0a = X0a, S0b = X0b, S1a = X1a, S1b = X1b;  // x at the start of the trajectory (reject)
     float obs0[3] = {0.f, 0.f, 0.f}, obs1[3] = {0.f, 0.f, 0.f};
     float ke0 = 0.f, ke1 = 0.f;
-    auto kinetic = [&]() {   // sum v^2 in link order, every term and sum rounded separately
+    auto kinetic = [&]() {  // sum v^2 in link order, every term and sum rounded separately
       const float v[8] = {lo2(V0a), lo2(V1a), hi2(V0a), hi2(V1a), lo2(V0b), lo2(V1b), hi2(V0b), hi2(V1b)};
       float acc = 0.f;
 #pragma unroll
@@ -301,6 +280,10 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
     };
     if (MC) ke0 = kinetic();
 
+    publish_u1();
+    // every thread has now copied its strip out of the ring slot: refill it two tiles ahead
+    if (warp == 0 && tile + 2 * static_cast<int>(gridDim.x) < p.num_tiles)
+      issue_load(tile + 2 * static_cast<int>(gridDim.x), slot);
     force(MC ? obs0 : nullptr);
     const int nsteps = MC ? p.num_steps : 1;
     for (int step = 0; step < nsteps; ++step) {
@@ -308,14 +291,23 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       V1a = madd2_unfused(V1a, nheps2, G1a, one), V1b = madd2_unfused(V1b, nheps2, G1b, one);
       X0a = madd2_unfused(X0a, eps2, V0a, one), X0b = madd2_unfused(X0b, eps2, V0b, one);
       X1a = madd2_unfused(X1a, eps2, V1a, one), X1b = madd2_unfused(X1b, eps2, V1b, one);
+      publish_u1();
       force((MC && step == nsteps - 1) ? obs1 : nullptr);
       V0a = madd2_unfused(V0a, nheps2, G0a, one), V0b = madd2_unfused(V0b, nheps2, G0b, one);
       V1a = madd2_unfused(V1a, nheps2, G1a, one), V1b = madd2_unfused(V1b, nheps2, G1b, one);
     }
-    *reinterpret_cast<float4*>(sx + off_own) = make_float4(lo2(X0a), lo2(X1a), hi2(X0a), hi2(X1a));
-    *reinterpret_cast<float4*>(sx + off_own + 4) = make_float4(lo2(X0b), lo2(X1b), hi2(X0b), hi2(X1b));
-    *reinterpret_cast<float4*>(sv + off_own) = make_float4(lo2(V0a), lo2(V1a), hi2(V0a), hi2(V1a));
-    *reinterpret_cast<float4*>(sv + off_own + 4) = make_float4(lo2(V0b), lo2(V1b), hi2(V0b), hi2(V1b));
+
+    float* so = smem + p.off_out;
+    if (p.off_xpost >= 0) {
+      float* q = so + p.off_xpost + off_own;
+      *reinterpret_cast<float4*>(q) = make_float4(lo2(X0a), lo2(X1a), hi2(X0a), hi2(X1a));
+      *reinterpret_cast<float4*>(q + 4) = make_float4(lo2(X0b), lo2(X1b), hi2(X0b), hi2(X1b));
+    }
+    if (p.off_vpost >= 0) {
+      float* q = so + p.off_vpost + off_own;
+      *reinterpret_cast<float4*>(q) = make_float4(lo2(V0a), lo2(V1a), hi2(V0a), hi2(V1a));
+      *reinterpret_cast<float4*>(q + 4) = make_float4(lo2(V0b), lo2(V1b), hi2(V0b), hi2(V1b));
+    }
 
     if (MC) {
       ke1 = kinetic();
@@ -323,7 +315,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       float r[8] = {obs0[0], ke0, obs0[1], obs0[2], obs1[0], ke1, obs1[1], obs1[2]};
       if (TPC <= 32) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) r[j] = group_sum<(TPC < 32 ? TPC : 32)>(r[j]);
+        for (int j = 0; j < 8; ++j) r[j] = group_sum<GW>(r[j]);
       } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j) r[j] = warp_sum(r[j]);
@@ -331,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
           *reinterpret_cast<float4*>(s_red + 8 * warp) = make_float4(r[0], r[1], r[2], r[3]);
           *reinterpret_cast<float4*>(s_red + 8 * warp + 4) = make_float4(r[4], r[5], r[6], r[7]);
         }
-        named_bar_sync(1, kComputeThreads);
+        named_bar_sync(1, kThreads);
         constexpr int WPC = TPC > 32 ? TPC / 32 : 1;
 #pragma unroll
         for (int j = 0; j < 8; ++j) r[j] = 0.f;
@@ -361,51 +353,79 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
         if (p.obs_plaq) p.obs_plaq[chain] = __fdiv_rn(csum, static_cast<float>(G::SITES));
         if (p.obs_charge) p.obs_charge[chain] = static_cast<int32_t>(floorf(__fadd_rn(0.1f, __fdiv_rn(qsum, kTwoPi))));
       }
-      if (p.x_out) {
-        float* so = sx + 2 * kTileFloats;
+      if (p.off_xout >= 0) {
         const f32x2 O0a = acc ? X0a : S0a, O0b = acc ? X0b : S0b, O1a = acc ? X1a : S1a, O1b = acc ? X1b : S1b;
         float o[8] = {lo2(O0a), lo2(O1a), hi2(O0a), hi2(O1a), lo2(O0b), lo2(O1b), hi2(O0b), hi2(O1b)};
         if (p.wrap) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) o[j] = wrap_2pi(o[j]);
         }
-        *reinterpret_cast<float4*>(so + off_own) = make_float4(o[0], o[1], o[2], o[3]);
-        *reinterpret_cast<float4*>(so + off_own + 4) = make_float4(o[4], o[5], o[6], o[7]);
+        float* q = so + p.off_xout + off_own;
+        *reinterpret_cast<float4*>(q) = make_float4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<float4*>(q + 4) = make_float4(o[4], o[5], o[6], o[7]);
       }
     }
+    // staged results -> HBM: one bulk store per requested output, issued by thread 0
     fence_proxy_async_smem();
-    mbar_arrive(&done[s]);
+    named_bar_sync(1, kThreads);
+    if (tid == 0) {
+      const int chain_base = tile * CPB;
+      const uint32_t bytes = static_cast<uint32_t>(min(CPB, p.N - chain_base)) * D * 4u;
+      const size_t goff = static_cast<size_t>(chain_base) * D;
+      if (p.off_xpost >= 0) bulk_s2g(p.x_post + goff, so + p.off_xpost, bytes);
+      if (p.off_vpost >= 0) bulk_s2g(p.v_post + goff, so + p.off_vpost, bytes);
+      if (p.off_xout >= 0) bulk_s2g(p.x_out + goff, so + p.off_xout, bytes);
+      bulk_commit();
+    }
   }
+  if (tid == 0) bulk_wait_read_all();  // shared memory must outlive the last store's reads
 }
 
 template <int T, int X, bool MC>
 int launch(const HmcParams& p_in, cudaStream_t stream) {
   HmcParams p = p_in;
   using G = Geo<T, X>;
-  static int blocks_per_sm = 0, sm_count = 0;
   auto kern = hmc_kernel<T, X, MC>;
-  if (blocks_per_sm == 0) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(Smem<MC>::bytes));
-    if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(hmc_kernel): %s", cudaGetErrorString(e));
-      return L2HMC_ERR_CUDA;
-    }
-    int dev = 0, bps = 0;
+  // shared-memory layout (floats): [ring slot 0][ring slot 1][staging][planes][partials][mbarriers]
+  const bool rng = MC && p.v_f == nullptr;
+  p.in_floats = rng ? kTileFloats : 2 * kTileFloats;
+  int nout = 0;
+  p.off_xpost = p.x_post ? (nout++) * kTileFloats : -1;
+  p.off_vpost = p.v_post ? (nout++) * kTileFloats : -1;
+  p.off_xout = (MC && p.x_out) ? (nout++) * kTileFloats : -1;
+  p.off_out = 2 * p.in_floats;
+  p.off_planes = p.off_out + nout * kTileFloats;
+  p.off_red = p.off_planes + kTileFloats;
+  p.off_bar = p.off_red + 64;
+  const size_t smem_bytes = sizeof(float) * static_cast<size_t>(p.off_bar) + 2 * sizeof(uint64_t);
+
+  static int sm_count = 0;
+  static size_t smem_opted = 0;
+  if (sm_count == 0) {
+    int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kThreads, Smem<MC>::bytes);
-    if (e != cudaSuccess || bps < 1) {
-      set_error("hmc_kernel does not fit an SM: %s", cudaGetErrorString(e));
+  }
+  if (smem_bytes > smem_opted) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem_bytes));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(hmc_kernel, %zu B): %s", smem_bytes, cudaGetErrorString(e));
       return L2HMC_ERR_CUDA;
     }
-    blocks_per_sm = bps;
+    smem_opted = smem_bytes;
+  }
+  int bps = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, kThreads, smem_bytes);
+  if (e != cudaSuccess || bps < 1) {
+    set_error("hmc_kernel does not fit an SM (%zu B shared): %s", smem_bytes, cudaGetErrorString(e));
+    return L2HMC_ERR_CUDA;
   }
   p.num_tiles = (p.N + G::CPB - 1) / G::CPB;
   p.one = 1.0f;
   if (p.num_tiles == 0) return L2HMC_OK;
-  const int grid = min(p.num_tiles, blocks_per_sm * sm_count);
-  kern<<<grid, kThreads, Smem<MC>::bytes, stream>>>(p);
+  const int grid = min(p.num_tiles, bps * sm_count);
+  kern<<<grid, kThreads, smem_bytes, stream>>>(p);
   return check_launch("hmc_kernel");
 }
 
