@@ -25,6 +25,7 @@
 #ifndef L2HMC_B200_H_
 #define L2HMC_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -176,6 +177,80 @@ int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* args, void* stream);
  * generic path's free-running mode).  normals [N,D], u_dir/u_acc [N], each nullable. */
 int l2hmc_philox_draws(uint64_t seed, uint64_t mc_step, uint64_t chain0, int N, int D,
                        float* normals, float* u_dir, float* u_acc, void* stream);
+
+/* ------------------------------------------------------------------ K3: S/T/Q networks
+ * Dense trunk + heads of GenericNet.call (network/generic_net.py:129-146) and of ConvNet3D.call
+ * after its conv front-end (network/conv_net.py:262-280):
+ *     h1 = relu(in0.Wv + bv + in1.Wx + bx + tau.Wt + bt)     (the FIRST input goes through v_layer)
+ *     h2 = relu(h1.Wh + bh)
+ *     S  = tanh(h2.Ws + bs) * exp(coeff_s);  T = h2.Wt' + bt';  Q = (h2.Wq + bq) * exp(coeff_q)
+ * Weights are device fp32 in Keras (in, out) layout, caller-owned.  `packed` (nullable) is the
+ * buffer filled by l2hmc_net_pack(): weights pre-tiled and TF32-split for the tcgen05 path, used
+ * when the shapes qualify (rows >= 128, K, H, D multiples of the tile sizes). */
+typedef struct {
+  int K;                          /* features of each of the two inputs */
+  int H;                          /* hidden width */
+  int D;                          /* outputs per head (= x_dim) */
+  const float *w_in0, *b_in0;     /* v_layer: kernel [K,H], bias [H] (first input) */
+  const float *w_in1, *b_in1;     /* x_layer: kernel [K,H], bias [H] (second input) */
+  const float *w_t, *b_t;         /* t_layer: kernel [2,H], bias [H] */
+  const float *w_h, *b_h;         /* h_layer: kernel [H,H], bias [H] */
+  const float *w_s, *b_s;         /* scale_layer: kernel [H,D], bias [D] */
+  const float *w_tr, *b_tr;       /* translation_layer */
+  const float *w_q, *b_q;         /* transformation_layer */
+  const float *coeff_s, *coeff_q; /* [D] */
+  int tanh_on_q;                  /* 0 for the gauge nets; 1 = MoG net (utils/network.py:108-111) */
+  const void* packed;             /* from l2hmc_net_pack(), nullable */
+} l2hmc_net_weights;
+
+#define L2HMC_NET_STQ 0      /* write S, T, Q */
+#define L2HMC_NET_MOMENTUM 1 /* heads feed _update_momentum_{forward,backward} in the GEMM epilogue */
+#define L2HMC_NET_POSITION 2 /* heads feed _update_position_{forward,backward} in the GEMM epilogue */
+
+typedef struct {
+  const float* in0;      /* [N,K] first trunk input */
+  const float* in1;      /* [N,K] second trunk input */
+  const float* in1_mask; /* nullable [K] 0/1 row multiplied into in1 on load (the `mask * position`
+                            input of position_fn, dynamics/gauge_dynamics.py:515-517) */
+  int in1_mask_invert;   /* use 1 - mask */
+  float tau_cos, tau_sin;/* the time embedding row (dynamics/gauge_dynamics.py:625-633) */
+  int N;
+  int mode;              /* L2HMC_NET_* */
+  /* L2HMC_NET_STQ: outputs [N,D] */
+  float *S, *T, *Q;
+  /* update modes (formulas of l2hmc_update_momentum / l2hmc_update_position) */
+  float eps;
+  int dir;               /* +1 / -1 */
+  const float* x;        /* POSITION: links to update [N,D] */
+  const float* v;        /* MOMENTUM: momenta to update; POSITION: momenta [N,D] */
+  const float* g;        /* MOMENTUM: force [N,D] */
+  const float* mask;     /* POSITION: mask row [D] */
+  int mask_invert;       /* POSITION: swap (m, mbar) */
+  float* out;            /* updated v (MOMENTUM) or x (POSITION), [N,D]; may alias the input */
+  float* logdet;         /* [N], accumulated into; nullable */
+  int32_t* nonfinite_flag;
+  void* workspace;       /* >= l2hmc_net_workspace_bytes(...) bytes of device memory */
+  size_t workspace_bytes;
+} l2hmc_net_call;
+
+size_t l2hmc_net_workspace_bytes(int K, int H, int D, int N);
+int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* call, void* stream);
+
+/* Conv front-end of ConvNet3D for one input stream (network/conv_net.py:247-260, reshape_5D
+ * :283-311; channels_last): (N,T,X,2,1) -> Conv3D(F,(3,3,2),same,relu) -> MaxPool3D(2,2,same)
+ * -> Conv3D(2F,(2,2,2),same,relu) -> MaxPool3D(2,2,same) -> flatten, written as
+ * feat [N, l2hmc_conv3d_num_features(T,X,F)] (the trunk's in0 / in1).  Kernels in Keras layout
+ * (kd,kh,kw,cin,cout).  `mask` (nullable [2TX]) multiplies the input on load (position_fn's
+ * `mask * x`). */
+typedef struct {
+  const float *w1, *b1; /* conv_{x,v}1: kernel [3,3,2,1,F], bias [F] */
+  const float *w2, *b2; /* conv_{x,v}2: kernel [2,2,2,F,2F], bias [2F] */
+  int F;
+} l2hmc_conv3d_weights;
+
+int l2hmc_conv3d_num_features(int T, int X, int F);
+int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float* in, const float* mask, int mask_invert,
+                          int N, int T, int X, float* feat, void* stream);
 
 #ifdef __cplusplus
 }

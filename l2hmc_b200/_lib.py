@@ -6,7 +6,7 @@ torch.distributed.
 """
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_uint64, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_size_t, c_uint64, c_void_p
 
 import torch
 
@@ -29,6 +29,38 @@ class HmcMcArgs(Structure):
     ]
 
 
+class NetWeights(Structure):
+    """l2hmc_net_weights (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("K", c_int), ("H", c_int), ("D", c_int),
+        ("w_in0", c_void_p), ("b_in0", c_void_p), ("w_in1", c_void_p), ("b_in1", c_void_p),
+        ("w_t", c_void_p), ("b_t", c_void_p), ("w_h", c_void_p), ("b_h", c_void_p),
+        ("w_s", c_void_p), ("b_s", c_void_p), ("w_tr", c_void_p), ("b_tr", c_void_p),
+        ("w_q", c_void_p), ("b_q", c_void_p), ("coeff_s", c_void_p), ("coeff_q", c_void_p),
+        ("tanh_on_q", c_int), ("packed", c_void_p),
+    ]
+
+
+class NetCall(Structure):
+    """l2hmc_net_call (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("in0", c_void_p), ("in1", c_void_p), ("in1_mask", c_void_p), ("in1_mask_invert", c_int),
+        ("tau_cos", c_float), ("tau_sin", c_float), ("N", c_int), ("mode", c_int),
+        ("S", c_void_p), ("T", c_void_p), ("Q", c_void_p),
+        ("eps", c_float), ("dir", c_int),
+        ("x", c_void_p), ("v", c_void_p), ("g", c_void_p), ("mask", c_void_p), ("mask_invert", c_int),
+        ("out", c_void_p), ("logdet", c_void_p), ("nonfinite_flag", c_void_p),
+        ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+    ]
+
+
+class Conv3dWeights(Structure):
+    """l2hmc_conv3d_weights (include/l2hmc_b200.h)."""
+    _fields_ = [("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p), ("F", c_int)]
+
+
+NET_STQ, NET_MOMENTUM, NET_POSITION = 0, 1, 2
+
 # name -> argtypes; every function returns int status except the two noted below.
 SIGNATURES = {
     "l2hmc_abi_version": [],
@@ -49,7 +81,14 @@ SIGNATURES = {
                           c_void_p],
     "l2hmc_u1_hmc_mc_step": [POINTER(HmcMcArgs), c_void_p],
     "l2hmc_philox_draws": [c_uint64, c_uint64, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_net_workspace_bytes": [c_int, c_int, c_int, c_int],
+    "l2hmc_net_run": [POINTER(NetWeights), POINTER(NetCall), c_void_p],
+    "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
+    "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
+                              c_void_p],
 }
+
+RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 
@@ -70,7 +109,7 @@ def load_library(path=LIB_PATH):
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.argtypes = argtypes
-        fn.restype = c_char_p if name == "l2hmc_last_error" else c_int
+        fn.restype = RESTYPES.get(name, c_int)
     return lib
 
 

@@ -1,0 +1,199 @@
+// K3 conv front-end of ConvNet3D: per input stream
+//   (N,T,X,2,1) -> Conv3D(F, (3,3,2), 'same', relu) -> MaxPool3D(2, 2, 'same')
+//               -> Conv3D(2F, (2,2,2), 'same', relu) -> MaxPool3D(2, 2, 'same') -> flatten
+// in ONE kernel, one chain per CTA pass with everything on-chip.
+//
+// Replaces reference l2hmc/network/conv_net.py:247-260 (+ reshape_5D :283-311, layers :86-168),
+// data_format = channels_last.  TensorFlow 'same' semantics: ZERO padding (not periodic), total
+// pad = k - 1 with the odd cell at the END (so the 2-wide kernels only see pad after), and the
+// pooling windows are clipped at the end (-inf padding).  The lattice's link direction mu is the
+// third spatial axis (size 2); after the first pool it has size 1, so the kd = 1 taps of the
+// second convolution only ever see padding and are skipped.
+//
+// Work split: phase 1 computes pooled conv-1 outputs P1[t1][x1][f] (f fastest: weight reads are
+// conflict-free, input reads are broadcasts) into shared memory; phase 2 computes the four
+// conv-2 positions of a pooling window together from a 3x3 patch of P1 held in registers.
+// relu(max(.)) == max(relu(.)), and max(a_i + b) == max(a_i) + b in floating point (monotone),
+// so bias and relu are applied once per pooled output.
+#include "common.cuh"
+
+namespace l2hmc {
+namespace {
+
+constexpr int kThreads = 256;
+
+struct ConvParams {
+  const float* w1;   // [3][3][2][1][F]
+  const float* b1;   // [F]
+  const float* w2;   // [2][2][2][F][2F]
+  const float* b2;   // [2F]
+  const float* in;   // [N][T][X][2]
+  const float* mask; // nullable [T*X*2]
+  int invert;
+  int N, T, X, F;
+  float* feat;       // [N][T2*X2*2F]
+};
+
+__global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
+  extern __shared__ __align__(16) float sm[];
+  const int T = p.T, X = p.X, F = p.F, C = 2 * p.F;
+  const int T1 = (T + 1) / 2, X1 = (X + 1) / 2, T2 = (T1 + 1) / 2, X2 = (X1 + 1) / 2;
+  const int D = 2 * T * X;
+  float* s_w1 = sm;                       // [18][F]
+  float* s_b1 = s_w1 + 18 * F;            // [F]
+  float* s_w2 = s_b1 + F;                 // [4][F][C]   (kd = 0 taps only)
+  float* s_b2 = s_w2 + 4 * F * C;         // [C]
+  float* s_in = s_b2 + C;                 // [T][X][2]
+  float* s_p1 = s_in + ((D + 3) & ~3);    // [T1][X1][F]
+  const int tid = threadIdx.x;
+
+  for (int i = tid; i < 18 * F; i += kThreads) s_w1[i] = p.w1[i];
+  for (int i = tid; i < F; i += kThreads) s_b1[i] = p.b1[i];
+  for (int i = tid; i < 4 * F * C; i += kThreads) {
+    const int tap = i / (F * C), rest = i % (F * C);        // tap = kt*2 + kx; source index [kt][kx][kd=0][f][c]
+    s_w2[i] = p.w2[static_cast<size_t>(tap) * 2 * F * C + rest];
+  }
+  for (int i = tid; i < C; i += kThreads) s_b2[i] = p.b2[i];
+
+  for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
+    __syncthreads();   // previous chain's phase 2 done with s_p1 / s_in; weights visible on the first pass
+    const float* src = p.in + static_cast<size_t>(n) * D;
+    for (int i = tid; i < D; i += kThreads) {
+      float a = src[i];
+      if (p.mask) {
+        const float m = p.mask[i];
+        a = __fmul_rn(p.invert ? __fsub_rn(1.f, m) : m, a);
+      }
+      s_in[i] = a;
+    }
+    __syncthreads();
+
+    // ---- phase 1: conv (3,3,2) + bias + relu + pool (2,2,2)
+    for (int o = tid; o < T1 * X1 * F; o += kThreads) {
+      const int f = o % F, pos = o / F;
+      const int x1 = pos % X1, t1 = pos / X1;
+      // input patch rows 2*t1-1 .. 2*t1+2, cols 2*x1-1 .. 2*x1+2, both mu (zero outside the lattice)
+      float in[4][4][2];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int t = 2 * t1 - 1 + a, x = 2 * x1 - 1 + b;
+          const bool ok = t >= 0 && t < T && x >= 0 && x < X;
+          const float2 u = ok ? *reinterpret_cast<const float2*>(&s_in[(t * X + x) * 2]) : make_float2(0.f, 0.f);
+          in[a][b][0] = u.x, in[a][b][1] = u.y;
+        }
+      float w[3][3][2];
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+          w[a][b][0] = s_w1[((a * 3 + b) * 2 + 0) * F + f];
+          w[a][b][1] = s_w1[((a * 3 + b) * 2 + 1) * F + f];
+        }
+      float best = -INFINITY;
+#pragma unroll
+      for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx) {
+          if (2 * t1 + dt >= T || 2 * x1 + dx >= X) continue;     // pooling window clipped at the end
+          float s0 = 0.f, s1 = 0.f;                                // outputs at mu = 0 and mu = 1
+#pragma unroll
+          for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+              // mu = 0 sees taps kd = 0 (mu 0) and kd = 1 (mu 1); mu = 1 sees kd = 0 (mu 1), kd = 1 -> pad
+              s0 = fmaf(in[dt + a][dx + b][0], w[a][b][0], s0);
+              s0 = fmaf(in[dt + a][dx + b][1], w[a][b][1], s0);
+              s1 = fmaf(in[dt + a][dx + b][1], w[a][b][0], s1);
+            }
+          best = fmaxf(best, fmaxf(s0, s1));
+        }
+      s_p1[o] = fmaxf(__fadd_rn(best, s_b1[f]), 0.f);
+    }
+    __syncthreads();
+
+    // ---- phase 2: conv (2,2,[2]) + bias + relu + pool (2,2,[1]) -> flattened features
+    float* dst = p.feat + static_cast<size_t>(n) * T2 * X2 * C;
+    for (int o = tid; o < T2 * X2 * C; o += kThreads) {
+      const int c = o % C, pos = o / C;
+      const int x2 = pos % X2, t2 = pos / X2;
+      float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+      const int tb = 2 * t2, xb = 2 * x2;
+      for (int f = 0; f < F; ++f) {
+        float pp[3][3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+          for (int b = 0; b < 3; ++b) {
+            const int t = tb + a, x = xb + b;
+            pp[a][b] = (t < T1 && x < X1) ? s_p1[(t * X1 + x) * F + f] : 0.f;
+          }
+        const float w00 = s_w2[(0 * F + f) * C + c], w01 = s_w2[(1 * F + f) * C + c];
+        const float w10 = s_w2[(2 * F + f) * C + c], w11 = s_w2[(3 * F + f) * C + c];
+#pragma unroll
+        for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            float s = acc[dt][dx];
+            s = fmaf(pp[dt][dx], w00, s);
+            s = fmaf(pp[dt][dx + 1], w01, s);
+            s = fmaf(pp[dt + 1][dx], w10, s);
+            s = fmaf(pp[dt + 1][dx + 1], w11, s);
+            acc[dt][dx] = s;
+          }
+      }
+      float best = -INFINITY;
+#pragma unroll
+      for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+        for (int dx = 0; dx < 2; ++dx)
+          if (tb + dt < T1 && xb + dx < X1) best = fmaxf(best, acc[dt][dx]);
+      dst[o] = fmaxf(__fadd_rn(best, s_b2[c]), 0.f);
+    }
+  }
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+extern "C" int l2hmc_conv3d_num_features(int T, int X, int F) {
+  const int T1 = (T + 1) / 2, X1 = (X + 1) / 2;
+  return ((T1 + 1) / 2) * ((X1 + 1) / 2) * 2 * F;
+}
+
+extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float* in, const float* mask,
+                                     int mask_invert, int N, int T, int X, float* feat, void* stream) {
+  L2HMC_REQUIRE(w, "l2hmc_conv3d_features: null weights");
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(w->w1 && w->b1 && w->w2 && w->b2 && in && feat, "l2hmc_conv3d_features: null pointer");
+  L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0 && w->F > 0, "l2hmc_conv3d_features: bad sizes N=%d T=%d X=%d F=%d", N, T, X,
+                w->F);
+  const int F = w->F, C = 2 * F, D = 2 * T * X, T1 = (T + 1) / 2, X1 = (X + 1) / 2;
+  const size_t smem = sizeof(float) * (18 * F + F + 4 * F * C + C + ((D + 3) & ~3) + T1 * X1 * F);
+  int dev = 0, max_smem = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (smem > static_cast<size_t>(max_smem)) {
+    set_error("l2hmc_conv3d_features: %dx%d lattice with F=%d needs %zu B of shared memory (limit %d)", T, X, F, smem,
+              max_smem);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(conv3d_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(conv3d_kernel): %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+  }
+  int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
+  per_sm = max(1, min(per_sm, 8));
+  const int grid = max(1, min(N, sms * per_sm));
+  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, N, T, X, F, feat};
+  conv3d_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_launch("conv3d_kernel");
+}

@@ -15,31 +15,12 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "update_math.cuh"
 
 namespace l2hmc {
 namespace {
 
 constexpr int kWarps = 8;
-
-__device__ __forceinline__ void flag_nonfinite(int32_t* flag, bool bad) {
-  if (flag != nullptr && __any_sync(0xffffffffu, bad)) {
-    if ((threadIdx.x & 31) == 0) atomicOr(flag, 1);
-  }
-}
-
-// ---- momentum ---------------------------------------------------------------------------
-template <int DIR>
-__device__ __forceinline__ float momentum_elem(float v, float g, float S, float Tr, float Q, float eps, float heps,
-                                               float& logdet, bool& bad) {
-  const float sc = __fmul_rn(S, DIR > 0 ? heps : -heps);
-  const float se = expf(sc);
-  const float te = expf(__fmul_rn(Q, eps));
-  bad |= !(isfinite(se) && isfinite(te));
-  logdet = __fadd_rn(logdet, sc);
-  const float inner = __fsub_rn(__fmul_rn(te, g), Tr);
-  if (DIR > 0) return __fsub_rn(__fmul_rn(v, se), __fmul_rn(heps, inner));
-  return __fmul_rn(se, __fadd_rn(v, __fmul_rn(heps, inner)));
-}
 
 template <int DIR, bool NETS>
 __global__ void __launch_bounds__(kWarps * 32) update_momentum_kernel(
@@ -83,22 +64,6 @@ __global__ void __launch_bounds__(kWarps * 32) update_momentum_kernel(
 }
 
 // ---- position ---------------------------------------------------------------------------
-template <int DIR>
-__device__ __forceinline__ float position_elem(float x, float v, float S, float Tr, float Q, float m, float eps,
-                                               float& logdet, bool& bad) {
-  const float mi = __fsub_rn(1.f, m);
-  const float sc = __fmul_rn(S, DIR > 0 ? eps : -eps);
-  const float se = expf(sc);
-  const float te = expf(__fmul_rn(Q, eps));
-  bad |= !(isfinite(se) && isfinite(te));
-  logdet = __fadd_rn(logdet, __fmul_rn(mi, sc));
-  const float inner = __fadd_rn(__fmul_rn(te, v), Tr);
-  float tmp;
-  if (DIR > 0) tmp = __fadd_rn(__fmul_rn(x, se), __fmul_rn(eps, inner));
-  else tmp = __fmul_rn(se, __fsub_rn(x, __fmul_rn(eps, inner)));
-  return __fadd_rn(__fmul_rn(m, x), __fmul_rn(mi, tmp));
-}
-
 template <int DIR, bool NETS>
 __global__ void __launch_bounds__(kWarps * 32) update_position_kernel(
     const float* x, const float* __restrict__ v, const float* __restrict__ S,

@@ -69,6 +69,7 @@ class GaugeDynamics(object):
         self.seed = 0            # Philox key of the free-running mode
         self.chain_offset = 0    # global index of local chain 0 (chain sharding)
         self.use_fused = True    # one-launch HMC path when the shape has a kernel
+        self.fuse_updates = True # L2HMC: sub-updates run in the head GEMM's epilogue (no S,T,Q in HBM)
         self.weights = None      # optional {'XNet': {...}, 'VNet': {...}} in Keras layouts
         for key, val in kwargs.items():
             if key != 'eps':
@@ -230,12 +231,14 @@ class GaugeDynamics(object):
         x, v = self._x(position), self._x(momentum)
         N, D = x.shape
         grad = self.grad_potential(x, beta)
+        ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
+        if not self.hmc and self.fuse_updates and hasattr(self.momentum_fn, 'momentum_update'):
+            return self.momentum_fn.momentum_update(x, v, grad, t, self._eps(), direction, ld, self._flag), ld
         if self.hmc:
             S = Tr = Q = None
         else:
             S, Tr, Q = self.momentum_fn([x, grad, t])
         out = torch.empty_like(v)
-        ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
         self._lib_call(_lib.get_lib().l2hmc_update_momentum, _lib.dptr(v), _lib.dptr(grad), _lib.dptr(S),
                        _lib.dptr(Tr), _lib.dptr(Q), self._eps(), direction, N, D, _lib.dptr(out), _lib.dptr(ld),
                        _lib.dptr(self._flag, torch.int32))
@@ -244,6 +247,10 @@ class GaugeDynamics(object):
     def _position_update(self, position, momentum, t, mask_row, invert, direction, logdet=None):
         x, v = self._x(position), self._x(momentum)
         N, D = x.shape
+        ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
+        if not self.hmc and self.fuse_updates and hasattr(self.position_fn, 'position_update'):
+            return self.position_fn.position_update(x, v, t, mask_row, invert, self._eps(), direction, ld,
+                                                    self._flag), ld
         if self.hmc:
             S = Tr = Q = None
         else:
@@ -252,7 +259,6 @@ class GaugeDynamics(object):
                            _lib.dptr(mx))
             S, Tr, Q = self.position_fn([v, mx, t])
         out = torch.empty_like(x)
-        ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
         self._lib_call(_lib.get_lib().l2hmc_update_position, _lib.dptr(x), _lib.dptr(v), _lib.dptr(S),
                        _lib.dptr(Tr), _lib.dptr(Q), _lib.dptr(mask_row), int(invert), self._eps(), direction, N, D,
                        _lib.dptr(out), _lib.dptr(ld), _lib.dptr(self._flag, torch.int32))
@@ -288,7 +294,7 @@ class GaugeDynamics(object):
         x, v = self._x(position), self._x(momentum)
         step = int(step.item() if isinstance(step, torch.Tensor) else step)
         idx = step if direction > 0 else self.num_steps - step - 1
-        t = self.ts[idx][None, :].expand(x.shape[0], 2).contiguous() if not self.hmc else None
+        t = (float(self._ts_host[idx, 0]), float(self._ts_host[idx, 1]))   # host floats: no sync per launch
         row = self.mask[idx]
         if ld is None:
             ld = torch.zeros(x.shape[0], dtype=torch.float32, device=x.device)

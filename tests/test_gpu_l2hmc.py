@@ -1,0 +1,190 @@
+"""L2HMC path with S/T/Q networks on the GPU (K3 + fused K2 epilogues) against the reference's
+golden vectors (tests/golden/l2hmc_cases.npz, produced by the unmodified reference) and the oracle.
+
+Tolerances: north_star asks 1e-5 relative in fp32 for links / log-dets; the `atol` terms are a few
+fp32 ulps of the value range (links ~ 2 pi, momenta ~ 3, log-dets ~ 1)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import u1_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def close(a, b, rtol=1e-5, atol=2e-5):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+    b = b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
+    np.testing.assert_allclose(a.astype(np.float64), b.astype(np.float64), rtol=rtol, atol=atol)
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import l2hmc_b200
+    return l2hmc_b200
+
+
+def golden_nets(g, tag):
+    nets = {}
+    for net in ("XNet", "VNet"):
+        pre = f"{tag}.{net}."
+        nets[net] = {k[len(pre):]: v for k, v in g.items() if k.startswith(pre) and ".call." not in k}
+    return nets
+
+
+def make_dyn(pkg, g, tag, arch, **kw):
+    T, X, N, M = (int(v) for v in g[tag + ".meta"])
+    lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
+    np.random.seed(42)
+    dyn = pkg.GaugeDynamics(lat, lat.get_energy_function(), hmc=False, network_arch=arch, num_steps=M,
+                            eps=float(g[tag + ".eps"]), weights=golden_nets(g, tag), **kw)
+    assert np.array_equal(dyn.mask.cpu().numpy(), g[tag + ".mask"])
+    return dyn, (T, X, N, M)
+
+
+CASES = [("generic.4x4", "generic"), ("conv3D.4x4", "conv3D"), ("conv3D.8x8", "conv3D")]
+
+
+@pytest.mark.parametrize("tag,arch", CASES)
+@pytest.mark.parametrize("fuse", [True, False])
+def test_l2hmc_against_reference_goldens(pkg, golden, tag, arch, fuse):
+    g = golden("l2hmc_cases")
+    dyn, (T, X, N, M) = make_dyn(pkg, g, tag, arch, fuse_updates=fuse)
+    beta = float(g[tag + ".beta"])
+    x, v = g[tag + ".x"], g[tag + ".v_f"]
+    # bare network calls (generic_net.py:129-146 / conv_net.py:247-280)
+    for name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
+        S, Tr, Q = net([v, x, g[f"{tag}.{name}.call.tvec"]])
+        close(S, g[f"{tag}.{name}.call.S"], atol=2e-6); close(Tr, g[f"{tag}.{name}.call.T"], atol=2e-6)
+        close(Q, g[f"{tag}.{name}.call.Q"], atol=2e-6)
+    # the four sub-updates at step 1 (gauge_dynamics.py:486-590)
+    tv = dyn._format_time(1, tile=N)
+    m, mi = dyn._get_mask_while(1)
+    for nm, fn in (("vf", dyn._update_momentum_forward), ("vb", dyn._update_momentum_backward)):
+        vv, ld = fn(x, v, beta, tv)
+        close(vv, g[f"{tag}.sub.{nm}.v"]); close(ld, g[f"{tag}.sub.{nm}.logdet"])
+    for nm, fn in (("xf", dyn._update_position_forward), ("xb", dyn._update_position_backward)):
+        xx, ld = fn(x, v, tv, m, mi)
+        close(xx, g[f"{tag}.sub.{nm}.x"]); close(ld, g[f"{tag}.sub.{nm}.logdet"])
+    # one leapfrog step each way (gauge_dynamics.py:412-483)
+    xx, vv, ld = dyn._forward_lf(x, v, beta, 1)
+    close(xx, g[tag + ".lf_f.x"], atol=5e-5); close(vv, g[tag + ".lf_f.v"], atol=5e-5)
+    close(ld, g[tag + ".lf_f.logdet"], atol=5e-5)
+    xx, vv, ld = dyn._backward_lf(x, v, beta, 1)
+    close(xx, g[tag + ".lf_b.x"], atol=5e-5); close(vv, g[tag + ".lf_b.v"], atol=5e-5)
+    close(ld, g[tag + ".lf_b.logdet"], atol=5e-5)
+    # whole transitions and the MC step
+    for fwd, vk, sfx in ((True, ".v_f", "f"), (False, ".v_b", "b")):
+        xs, vs, ps = dyn.transition_kernel(x, beta, forward=fwd, momentum=g[tag + vk])
+        close(xs, g[f"{tag}.x_{sfx}"], rtol=1e-4, atol=2e-4); close(vs, g[f"{tag}.v_{sfx}_out"], rtol=1e-4, atol=2e-4)
+        close(ps, g[f"{tag}.p_{sfx}"], rtol=1e-3, atol=1e-6)
+    xp, vp, p, xo = dyn.apply_transition(x, beta, momentum_f=g[tag + ".v_f"], momentum_b=g[tag + ".v_b"],
+                                         direction_uniform=g[tag + ".u_dir"], accept_uniform=g[tag + ".u_acc"])
+    close(xp, g[tag + ".x_post"], rtol=1e-4, atol=2e-4); close(vp, g[tag + ".v_post"], rtol=1e-4, atol=2e-4)
+    close(p, g[tag + ".accept_prob"], rtol=1e-3, atol=1e-6)
+    acc_ref = g[tag + ".accept_prob"] > g[tag + ".u_acc"]
+    assert np.array_equal(dyn.last_accepted.cpu().numpy().astype(bool), acc_ref)     # accept decisions bit-exact
+    close(xo, g[tag + ".x_out"], rtol=1e-4, atol=2e-4)
+    dyn.raise_if_nonfinite()
+
+
+def _oracle_weights(arch, T, X, rng, gain=None):
+    gain = gain if gain is not None else (1.0 if arch == "generic" else 5.0)   # S,T,Q = O(0.3): p_acc stays > 0
+    ws = {}
+    for net, factor in (("XNet", 2.), ("VNet", 1.)):
+        w = orc.init_net_weights(arch, T, X, factor, rng)
+        for k in ("scale_layer", "translation_layer", "transformation_layer"):
+            w[k + ".kernel"] *= gain                                       # trained-like heads: S,T,Q = O(0.1)
+            w[k + ".bias"] = rng.normal(0, 0.02, w[k + ".bias"].shape).astype(np.float32)
+        for k in ("x_layer", "v_layer", "t_layer", "h_layer"):
+            w[k + ".bias"] = rng.normal(0, 0.05, w[k + ".bias"].shape).astype(np.float32)
+        w["coeff_scale"] = rng.normal(0, 0.1, w["coeff_scale"].shape).astype(np.float32)
+        w["coeff_transformation"] = rng.normal(0, 0.1, w["coeff_transformation"].shape).astype(np.float32)
+        ws[net] = w
+    return ws
+
+
+@pytest.mark.parametrize("arch,T,X,N,M", [("generic", 8, 8, 128, 5), ("generic", 6, 10, 37, 2), ("generic", 3, 5, 70, 2),
+                                          ("generic", 16, 16, 200, 2), ("conv3D", 16, 16, 33, 2),
+                                          ("conv3D", 6, 10, 9, 2), ("conv3D", 8, 4, 130, 3)])
+def test_l2hmc_transition_against_oracle(pkg, arch, T, X, N, M):
+    """Config-2 size (8x8 generic, N=128, M=5) and ragged shapes: fused and unfused paths vs the oracle."""
+    rng = np.random.default_rng(100 + T * X + N)
+    D, eps, beta = 2 * T * X, 0.2, 2.5
+    ws = _oracle_weights(arch, T, X, rng)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    vf, vb = (rng.standard_normal((N, D)).astype(np.float32) for _ in range(2))
+    ud, ua = (rng.uniform(size=N).astype(np.float32) for _ in range(2))
+    lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
+    np.random.seed(42)
+    mask = orc.construct_masks(D, M, seed=42)
+    od = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch=arch, mask=mask, xnet=ws["XNet"], vnet=ws["VNet"])
+    od64 = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch=arch, mask=mask, xnet=ws["XNet"],
+                              vnet=ws["VNet"], dtype=torch.float64)
+    rxp, rvp, rp, rxo = od.apply_transition(x, beta, vf, vb, ud, ua)
+    dxp, dvp, dp, _ = od64.apply_transition(x, beta, vf, vb, ud, ua)
+    # the fp32 oracle's own distance from fp64 sets the scale of a fair tolerance
+    noise = max(float((rxp.double() - dxp).abs().max()), 1e-6)
+    outs = []
+    for fuse in (True, False):
+        np.random.seed(42)
+        dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M, eps=eps, weights=ws, fuse_updates=fuse)
+        xp, vp, p, xo = dyn.apply_transition(x, beta, momentum_f=vf, momentum_b=vb, direction_uniform=ud,
+                                             accept_uniform=ua)
+        assert float((xp.cpu().double() - dxp).abs().max()) < 4 * noise + 2e-5
+        assert float((vp.cpu().double() - dvp).abs().max()) < 4 * noise + 2e-5
+        close(xp, rxp, rtol=1e-5, atol=4 * noise + 2e-5); close(vp, rvp, rtol=1e-5, atol=4 * noise + 2e-5)
+        close(p, rp, rtol=2e-3, atol=1e-6)
+        safe = np.abs(dp.numpy() - ua) > 1e-3
+        assert np.array_equal(dyn.last_accepted.cpu().numpy().astype(bool)[safe], (dp.numpy() > ua)[safe])
+        dyn.raise_if_nonfinite()
+        outs.append((xp, vp, p))
+    close(outs[0][0], outs[1][0], rtol=0, atol=1e-5)        # fused epilogue == separate S,T,Q + K2 kernels
+    close(outs[0][1], outs[1][1], rtol=0, atol=1e-5)
+    assert float(np.abs(rp.numpy() - 1).max()) > 1e-3        # the nets actually moved the accept probability
+
+
+def test_net_reversibility_on_device(pkg):
+    """_backward_lf(step = M-1-k) undoes _forward_lf(step = k), log-dets opposite (SURVEY 8c iii)."""
+    rng = np.random.default_rng(8)
+    T = X = 8
+    N, M, D = 64, 3, 128
+    ws = _oracle_weights("generic", T, X, rng)
+    lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
+    dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch="generic", num_steps=M, eps=0.2, weights=ws)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    v = rng.standard_normal((N, D)).astype(np.float32)
+    for k in range(M):
+        x1, v1, ld = dyn._forward_lf(x, v, 2.0, k)
+        x2, v2, ldb = dyn._backward_lf(x1, v1, 2.0, M - 1 - k)
+        close(x2, x, rtol=0, atol=3e-5); close(v2, v, rtol=0, atol=3e-5)
+        close(ldb, -ld, rtol=1e-4, atol=2e-5)
+        assert float(ld.abs().max()) > 1e-3
+
+
+def test_net_errors(pkg):
+    from l2hmc_b200 import _lib
+    from l2hmc_b200.network import GenericNet
+    net = GenericNet(model_name="XNet", x_dim=32, links_shape=(4, 4, 2), num_hidden=64, name_scope="position",
+                     factor=2.)
+    with pytest.raises(KeyError):
+        net.load_weights({"x_layer.kernel": np.zeros((32, 64), np.float32)})
+    w = net.state_dict()
+    w["h_layer.kernel"] = np.zeros((3, 3), np.float32)
+    with pytest.raises(ValueError):
+        net.load_weights(w)
+    lib = _lib.get_lib()
+    assert lib.l2hmc_net_run(None, None, None) == _lib.L2HMC_ERR_INVALID
+    # zero-initialised heads => S = T = Q = 0 exactly like the reference's freshly built nets are ~1e-3
+    S, Tr, Q = net([np.zeros((5, 32), np.float32), np.zeros((5, 32), np.float32), np.array([[1.0, 0.0]], np.float32)])
+    assert S.shape == (5, 32) and float(S.abs().max()) < 0.05
+    # check_numerics mirror: huge scale head -> exp overflow -> flag
+    w = net.state_dict()
+    w["scale_layer.bias"] = np.full((32,), 50.0, np.float32)
+    w["coeff_scale"] = np.full((1, 32), 8.0, np.float32)
+    net.load_weights(w)
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ld = torch.zeros(5, device="cuda")
+    z = torch.zeros(5, 32, device="cuda")
+    net.momentum_update(z, z + 1, z, (1.0, 0.0), 1.0, 1, ld, flag)
+    assert int(flag.item()) == 1
