@@ -231,10 +231,27 @@ typedef struct {
   int32_t* nonfinite_flag;
   void* workspace;       /* >= l2hmc_net_workspace_bytes(...) bytes of device memory */
   size_t workspace_bytes;
+  int path;              /* L2HMC_NET_PATH_*: AUTO picks tcgen05 when the shapes are dense contractions */
 } l2hmc_net_call;
+
+#define L2HMC_NET_PATH_AUTO 0
+#define L2HMC_NET_PATH_FFMA 1
+#define L2HMC_NET_PATH_TCGEN05 2 /* L2HMC_ERR_UNSUPPORTED if the shape / missing `packed` rules it out */
 
 size_t l2hmc_net_workspace_bytes(int K, int H, int D, int N);
 int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* call, void* stream);
+
+/* Pre-tiled, TF32-split copy of the dense weights for the tcgen05 path (3xTF32: hi.lo + lo.hi + hi.hi,
+ * fp32 accumulation in TMEM).  `packed` is caller-owned device memory of l2hmc_net_pack_bytes(K,H,D)
+ * bytes; re-pack after the weights change.  w->packed is ignored by l2hmc_net_pack itself. */
+size_t l2hmc_net_pack_bytes(int K, int H, int D);
+int l2hmc_net_pack(const l2hmc_net_weights* w, void* packed, size_t packed_bytes, void* stream);
+
+/* Diagnostic: C[M,Nc] = relu(A[M,K] . W[K,Nc]) through the tcgen05 layer kernel and its operand
+ * converters (row-major fp32 in / out; bn = 128 or 256 selects the N tile). */
+size_t l2hmc_tc_selftest_bytes(int M, int Nc, int K);
+int l2hmc_tc_selftest(const float* A, const float* W, int M, int Nc, int K, int bn, float* C, void* scratch,
+                      void* stream);
 
 /* Conv front-end of ConvNet3D for one input stream (network/conv_net.py:247-260, reshape_5D
  * :283-311; channels_last): (N,T,X,2,1) -> Conv3D(F,(3,3,2),same,relu) -> MaxPool3D(2,2,same)

@@ -50,7 +50,7 @@ class NetCall(Structure):
         ("eps", c_float), ("dir", c_int),
         ("x", c_void_p), ("v", c_void_p), ("g", c_void_p), ("mask", c_void_p), ("mask_invert", c_int),
         ("out", c_void_p), ("logdet", c_void_p), ("nonfinite_flag", c_void_p),
-        ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("workspace", c_void_p), ("workspace_bytes", c_size_t), ("path", c_int),
     ]
 
 
@@ -60,6 +60,7 @@ class Conv3dWeights(Structure):
 
 
 NET_STQ, NET_MOMENTUM, NET_POSITION = 0, 1, 2
+NET_PATH_AUTO, NET_PATH_FFMA, NET_PATH_TCGEN05 = 0, 1, 2
 
 # name -> argtypes; every function returns int status except the two noted below.
 SIGNATURES = {
@@ -83,12 +84,17 @@ SIGNATURES = {
     "l2hmc_philox_draws": [c_uint64, c_uint64, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
     "l2hmc_net_workspace_bytes": [c_int, c_int, c_int, c_int],
     "l2hmc_net_run": [POINTER(NetWeights), POINTER(NetCall), c_void_p],
+    "l2hmc_net_pack_bytes": [c_int, c_int, c_int],
+    "l2hmc_net_pack": [POINTER(NetWeights), c_void_p, c_size_t, c_void_p],
+    "l2hmc_tc_selftest_bytes": [c_int, c_int, c_int],
+    "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],
 }
 
-RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t}
+RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
+            "l2hmc_tc_selftest_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

@@ -1,0 +1,620 @@
+// K3 (tensor-core path): the S/T/Q networks' dense layers on tcgen05 with 3xTF32 split precision.
+//
+// Replaces the same reference code as nets.cu (network/generic_net.py:129-146,
+// network/conv_net.py:262-280, and -- in the head epilogue -- dynamics/gauge_dynamics.py:486-590)
+// for the shapes where the layers are dense contractions (chains >= 256, K and H in the hundreds:
+// BASELINE configs 3 and 4).
+//
+// Precision.  The north star asks links / log-dets within 1e-5 of the fp32 reference, which plain
+// TF32 (10-bit mantissa) misses by two orders of magnitude.  Every operand is therefore split as
+// a = hi + lo (hi = a rounded to TF32, lo = a - hi rounded to TF32) and the product is
+// formed from three tensor-core MMAs accumulating in fp32 in TMEM:
+//       A.B  ~=  A_hi.B_lo + A_lo.B_hi + A_hi.B_hi          (error ~ 2^-22 relative per term)
+//
+// Layout ("TS32").  Operands live in HBM already in the shared-memory image the MMA consumes, so a
+// tile is ONE contiguous 1-D bulk copy (cp.async.bulk, no tensor map):
+//   element (r, k) of a K-major matrix with R rows:
+//     float offset = ((kb*RG + rg)*2 + part)*256 + kc*32 + (r%8)*4 + k%4
+//     kb = k/32, kc = (k%32)/4, rg = r/8, RG = R/8, part = 0 (hi) / 1 (lo)
+//   i.e. 8-row x 16-byte core matrices (128 B, contiguous), K-chunks 128 B apart (LBO), hi and lo
+//   of a row group 1 KB apart, row groups 2 KB apart (SBO), one 32-wide K block after the other.
+//   UMMA descriptors: K-major, SWIZZLE_NONE.
+// Weights are packed once (l2hmc_net_pack); activations are written in this form by the producing
+// kernel's epilogue (hidden layers) or by a small converter (network inputs, mask folded in).
+//
+// Kernel.  Persistent, one CTA per SM, 192 threads, warp-specialised:
+//   warps 0-3  epilogue: tcgen05.ld accumulator rows (thread = chain) -> bias/relu -> hi/lo split ->
+//              TS32 store; or, for the heads, tanh/exp + the leapfrog sub-update + log-det
+//   warp 4     bulk-copy producer (one lane) + TMEM allocation
+//   warp 5     MMA issuer (one lane): per 32-wide K block 4 K-steps x 3 products of
+//              tcgen05.mma.cta_group::1.kind::tf32, M = 128, N = BN
+//   smem ring of 2-3 stages (A 32 KB + B BN*256 B), full/empty mbarriers; two accumulator stages in
+//   TMEM (tmem_full / tmem_empty) so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "common.cuh"
+#include "nets.cuh"
+#include "update_math.cuh"
+
+namespace l2hmc {
+namespace {
+
+constexpr int kTcThreads = 192;
+constexpr int TC_BM = 128;
+constexpr uint32_t kATileBytes = TC_BM * 32 * 4 * 2;   // 128 rows x 32 k x (hi, lo)
+
+enum TcMode { kTcLayer = 0, kTcHeadsStq = 1, kTcHeadsMomentum = 2, kTcHeadsPosition = 3 };
+
+struct TcParams {
+  const float* A;      // TS32, a_rg row groups
+  const float* B;      // TS32 (weights^T), b_rg row groups
+  int a_rg, b_rg, KB;
+  int m_tiles, n_tiles;
+  int rows;            // valid chains
+  int cols;            // valid outputs (H for layers, D per head)
+  // layer epilogue
+  const float* bias;   // [cols] effective bias
+  float* out_ts;       // next layer's A operand (TS32), out_rg row groups, out_kb K blocks
+  int out_rg, out_kb;
+  // heads epilogue
+  const float* b_s;
+  const float* b_tr;
+  const float* b_q;
+  const float* coeff_s;
+  const float* coeff_q;
+  int tanh_on_q;
+  float* S;
+  float* T;
+  float* Q;
+  const float* ux;
+  const float* uv;
+  const float* ug;
+  const float* umask;
+  int uinvert;
+  float eps;
+  int dir;
+  float* uout;
+  float* ld_part;
+  int32_t* flag;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, no swizzle: start address, LBO = 128 B (next 16-byte K chunk), SBO = 2048 B (next 8-row group)
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+  return static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu) | (static_cast<uint64_t>(128u >> 4) << 16) |
+         (static_cast<uint64_t>(2048u >> 4) << 32) | (1ULL << 46);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
+      "[%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// round-to-nearest TF32 (10-bit mantissa, low 13 bits zero): |a - tf32_rn(a)| <= 2^-11 |a|
+__device__ __forceinline__ float tf32_rn(float a) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(a));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float tf32_hi(float a) { return tf32_rn(a); }
+// lo = a - hi is exact in fp32; rounding it to TF32 here (instead of the MMA truncating it) halves its error
+__device__ __forceinline__ float tf32_lo(float a, float hi) { return tf32_rn(__fsub_rn(a, hi)); }
+
+// ------------------------------------------------------------------ the GEMM kernel
+template <int BN, int MODE>
+__global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p) {
+  constexpr int NSTAGE = (BN <= 128) ? 3 : 2;
+  constexpr uint32_t kBTileBytes = BN * 32 * 4 * 2;
+  constexpr uint32_t kStageBytes = kATileBytes + kBTileBytes;
+  constexpr uint32_t kAccCols = 256;                       // column offset of the second accumulator stage
+  // instruction descriptor: D = f32, A = B = tf32, both K-major, N = BN, M = 128
+  constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                              (static_cast<uint32_t>(TC_BM >> 4) << 24);
+  extern __shared__ __align__(1024) uint8_t tc_smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tc_smem + NSTAGE * kStageBytes);
+  uint64_t* full = bars;                 // [NSTAGE]
+  uint64_t* empty = bars + NSTAGE;       // [NSTAGE]
+  uint64_t* tmem_full = bars + 2 * NSTAGE;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1), mbar_init(&empty[s], 1);
+    for (int s = 0; s < 2; ++s) mbar_init(&tmem_full[s], 1), mbar_init(&tmem_empty[s], 128);
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int num_tiles = p.m_tiles * p.n_tiles;
+
+  if (warp == 4) {
+    // ===== producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sa = tc_smem + stage * kStageBytes;
+          mbar_arrive_expect_tx(&full[stage], kStageBytes);
+          bulk_g2s(sa, p.A + (static_cast<size_t>(kb) * p.a_rg + static_cast<size_t>(m_blk) * (TC_BM / 8)) * 512,
+                   kATileBytes, &full[stage]);
+          bulk_g2s(sa + kATileBytes,
+                   p.B + (static_cast<size_t>(kb) * p.b_rg + static_cast<size_t>(n_blk) * (BN / 8)) * 512, kBTileBytes,
+                   &full[stage]);
+          if (++stage == NSTAGE) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0, acc = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kAccCols;
+        for (int kb = 0; kb < p.KB; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(tc_smem + stage * kStageBytes);
+          const uint32_t sb = sa + kATileBytes;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            const uint64_t a_hi = make_desc(sa + ks * 256), a_lo = make_desc(sa + 1024 + ks * 256);
+            const uint64_t b_hi = make_desc(sb + ks * 256), b_lo = make_desc(sb + 1024 + ks * 256);
+            umma_tf32(d_tmem, a_hi, b_lo, kIdesc, (kb | ks) != 0);
+            umma_tf32(d_tmem, a_lo, b_hi, kIdesc, 1);
+            umma_tf32(d_tmem, a_hi, b_hi, kIdesc, 1);
+          }
+          umma_commit(&empty[stage]);          // smem slot free once these MMAs have read it
+          if (++stage == NSTAGE) stage = 0, phase ^= 1;
+        }
+        umma_commit(&tmem_full[acc]);          // accumulator complete
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===== epilogue (warps 0-3: TMEM lanes 32*warp ..) =====
+    uint32_t acc = 0, acc_phase = 0;
+    const int row_in_tile = warp * 32 + lane;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+      const int r = m_blk * TC_BM + row_in_tile;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kAccCols;
+      if (MODE == kTcLayer) {
+        const int rg = r >> 3, r8 = r & 7;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+          const int kb = n_blk * (BN / 32) + c;           // K block of the NEXT layer
+          if (kb < p.out_kb) {
+            const int n0 = kb * 32;
+            float* dst = p.out_ts + ((static_cast<size_t>(kb) * p.out_rg + rg) * 2) * 256 + r8 * 4;
+#pragma unroll
+            for (int kc = 0; kc < 8; ++kc) {
+              float o[4], h[4], l[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int n = n0 + kc * 4 + j;
+                const float b = n < p.cols ? __ldg(p.bias + n) : 0.f;
+                o[j] = fmaxf(__fadd_rn(v[kc * 4 + j], b), 0.f);
+                h[j] = tf32_hi(o[j]);
+                l[j] = tf32_lo(o[j], h[j]);
+              }
+              *reinterpret_cast<float4*>(dst + kc * 32) = make_float4(h[0], h[1], h[2], h[3]);
+              *reinterpret_cast<float4*>(dst + 256 + kc * 32) = make_float4(l[0], l[1], l[2], l[3]);
+            }
+          }
+        }
+      } else {
+        // heads: columns [0,64) = S, [64,128) = T, [128,192) = Q pre-activations of d = 64*n_blk + ..
+        const bool rok = r < p.rows;
+        const float heps = __fmul_rn(0.5f, p.eps);
+        float ld = 0.f;
+        bool bad = false;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          float s[16], t[16], q[16];
+          tmem_ld16(taddr + c * 16, s);
+          tmem_ld16(taddr + 64 + c * 16, t);
+          tmem_ld16(taddr + 128 + c * 16, q);
+          tmem_ld_wait();
+          const int d0 = n_blk * 64 + c * 16;
+          if (rok && d0 < p.cols) {       // cols is a multiple of 16 on this path
+            const size_t at = static_cast<size_t>(r) * p.cols + d0;
+            float a0[16], a1[16], o[16];
+            if (MODE == kTcHeadsMomentum) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 4) {
+                *reinterpret_cast<float4*>(a0 + j) = *reinterpret_cast<const float4*>(p.uv + at + j);
+                *reinterpret_cast<float4*>(a1 + j) = *reinterpret_cast<const float4*>(p.ug + at + j);
+              }
+            } else if (MODE == kTcHeadsPosition) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 4) {
+                *reinterpret_cast<float4*>(a0 + j) = *reinterpret_cast<const float4*>(p.ux + at + j);
+                *reinterpret_cast<float4*>(a1 + j) = *reinterpret_cast<const float4*>(p.uv + at + j);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int d = d0 + j;
+              const float S = __fmul_rn(tanhf(__fadd_rn(s[j], __ldg(p.b_s + d))), expf(__ldg(p.coeff_s + d)));
+              const float Tr = __fadd_rn(t[j], __ldg(p.b_tr + d));
+              float Q = __fadd_rn(q[j], __ldg(p.b_q + d));
+              if (p.tanh_on_q) Q = tanhf(Q);
+              Q = __fmul_rn(Q, expf(__ldg(p.coeff_q + d)));
+              if (MODE == kTcHeadsStq) {
+                s[j] = S, t[j] = Tr, q[j] = Q;
+              } else if (MODE == kTcHeadsMomentum) {
+                o[j] = p.dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
+                                 : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
+              } else {
+                float m = __ldg(p.umask + d);
+                if (p.uinvert) m = __fsub_rn(1.f, m);
+                o[j] = p.dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
+                                 : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+              if (MODE == kTcHeadsStq) {
+                *reinterpret_cast<float4*>(p.S + at + j) = *reinterpret_cast<float4*>(s + j);
+                *reinterpret_cast<float4*>(p.T + at + j) = *reinterpret_cast<float4*>(t + j);
+                *reinterpret_cast<float4*>(p.Q + at + j) = *reinterpret_cast<float4*>(q + j);
+              } else {
+                *reinterpret_cast<float4*>(p.uout + at + j) = *reinterpret_cast<float4*>(o + j);
+              }
+            }
+          }
+        }
+        if (MODE != kTcHeadsStq) {
+          if (rok && p.ld_part) p.ld_part[static_cast<size_t>(n_blk) * p.rows + r] = ld;
+          flag_nonfinite(p.flag, bad);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------ format kernels
+// row-major fp32 [rows, K] (leading dimension ld, optional 0/1 mask row) -> TS32 K blocks
+// [kb0, kb0 + ceil(K/32)) of a buffer with `rg_total` row groups; rows >= `rows` and k >= K are zero.
+__global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __restrict__ src, int ld, int rows, int K,
+                                                                 const float* __restrict__ mask, int invert,
+                                                                 float* dst, int rg_total, int kb0, int nkb) {
+  // one thread per (kb, rg, kc, r8): consecutive threads write consecutive 16 B
+  const size_t total = static_cast<size_t>(nkb) * rg_total * 64;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int r8 = static_cast<int>(i & 7), kc = static_cast<int>((i >> 3) & 7);
+    const size_t blk = i >> 6;
+    const int rg = static_cast<int>(blk % rg_total), kb = static_cast<int>(blk / rg_total);
+    const int r = rg * 8 + r8, k = kb * 32 + kc * 4;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (r < rows) {
+      const float* s = src + static_cast<size_t>(r) * ld + k;
+      if (k + 3 < K && ((reinterpret_cast<uintptr_t>(s) & 15u) == 0)) {
+        const float4 t = *reinterpret_cast<const float4*>(s);
+        a[0] = t.x, a[1] = t.y, a[2] = t.z, a[3] = t.w;
+      } else {
+        for (int j = 0; j < 4; ++j)
+          if (k + j < K) a[j] = s[j];
+      }
+      if (mask) {
+        for (int j = 0; j < 4; ++j)
+          if (k + j < K) {
+            const float m = mask[k + j];
+            a[j] = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a[j]);
+          }
+      }
+    }
+    float h[4], l[4];
+    for (int j = 0; j < 4; ++j) h[j] = tf32_hi(a[j]), l[j] = tf32_lo(a[j], h[j]);
+    float* d = dst + ((static_cast<size_t>(kb0 + kb) * rg_total + rg) * 2) * 256 + kc * 32 + r8 * 4;
+    *reinterpret_cast<float4*>(d) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(d + 256) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+// Keras kernel W [K, cols] (row-major) -> TS32 of W^T: packed row `prow(n)` = output feature n, K blocks
+// [kb0, kb0 + ceil(K/32)).  heads != 0: n = output d of head `head`, packed row = (d/64)*192 + head*64 + d%64.
+__global__ void __launch_bounds__(256) ts32_pack_weight_kernel(const float* __restrict__ W, int K, int cols, float* dst,
+                                                               int rg_total, int kb0, int heads, int head) {
+  const int nkb = (K + 31) / 32;
+  const size_t total = static_cast<size_t>(nkb) * 32 * cols;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int n = static_cast<int>(i % cols);
+    const int k = static_cast<int>(i / cols);
+    const float a = k < K ? W[static_cast<size_t>(k) * cols + n] : 0.f;
+    const int pr = heads ? (n / 64) * 192 + head * 64 + (n % 64) : n;
+    const int kb = k / 32, kc = (k % 32) / 4, k4 = k % 4;
+    float* d = dst + ((static_cast<size_t>(kb0 + kb) * rg_total + pr / 8) * 2) * 256 + kc * 32 + (pr % 8) * 4 + k4;
+    const float h = tf32_hi(a);
+    d[0] = h;
+    d[256] = tf32_lo(a, h);
+  }
+}
+
+// TS32 (hi + lo) -> row-major fp32 (diagnostics)
+__global__ void __launch_bounds__(256) ts32_to_rowmajor_kernel(const float* __restrict__ src, int rg_total, int rows,
+                                                               int K, float* dst) {
+  const size_t total = static_cast<size_t>(rows) * K;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % K), r = static_cast<int>(i / K);
+    const float* s = src + ((static_cast<size_t>(k / 32) * rg_total + r / 8) * 2) * 256 + ((k % 32) / 4) * 32 +
+                     (r % 8) * 4 + k % 4;
+    dst[i] = __fadd_rn(s[0], s[256]);
+  }
+}
+
+// bias_eff[n] = b0[n] + b1[n] + (tau0*wt[0][n] + tau1*wt[1][n] + b2[n])   (first layer)
+__global__ void bias_eff_kernel(const float* b0, const float* b1, const float* b2, const float* wt, float tau0,
+                                float tau1, int H, float* out) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= H) return;
+  const float tt = __fadd_rn(__fadd_rn(__fmul_rn(tau0, wt[n]), __fmul_rn(tau1, wt[H + n])), b2[n]);
+  out[n] = __fadd_rn(__fadd_rn(b0[n], b1[n]), tt);
+}
+
+__global__ void logdet_reduce_tc_kernel(const float* __restrict__ part, int tiles, int N, float* logdet) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float s = 0.f;
+  for (int j = 0; j < tiles; ++j) s = __fadd_rn(s, part[static_cast<size_t>(j) * N + n]);
+  logdet[n] = __fadd_rn(logdet[n], s);
+}
+
+inline int ew_grid(size_t total) { return static_cast<int>(std::min<size_t>((total + 255) / 256, 148 * 32)); }
+
+template <int BN, int MODE>
+int launch_tc(const TcParams& p, cudaStream_t st) {
+  constexpr int NSTAGE = (BN <= 128) ? 3 : 2;
+  constexpr size_t smem = static_cast<size_t>(NSTAGE) * (kATileBytes + BN * 256) + (2 * NSTAGE + 4) * 8 + 16;
+  auto kern = gemm_tc_kernel<BN, MODE>;
+  static bool opted = false;
+  if (!opted) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(gemm_tc_kernel, %zu B): %s", smem, cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+    opted = true;
+  }
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  const int tiles = p.m_tiles * p.n_tiles;
+  if (tiles == 0) return L2HMC_OK;
+  kern<<<std::min(tiles, sms), kTcThreads, smem, st>>>(p);
+  return check_launch("gemm_tc_kernel");
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ sizes shared with the pack / workspace API
+TcDims tc_dims(int K, int H, int D, int N) {
+  TcDims d;
+  d.kbK = (K + 31) / 32;
+  d.kbH = (H + 31) / 32;
+  d.h_rows = (H + 255) / 256 * 256;            // packed rows of W1^T / W2^T (covers BN = 128 and 256)
+  d.d_tiles = (D + 63) / 64;
+  d.rows_p = (N + 127) / 128 * 128;
+  d.w1_floats = static_cast<size_t>(2 * d.kbK) * d.h_rows * 64;     // rows * kb * 32 k * 2 parts
+  d.w2_floats = static_cast<size_t>(d.kbH) * d.h_rows * 64;
+  d.w3_floats = static_cast<size_t>(d.kbH) * (d.d_tiles * 192) * 64;
+  d.acat_floats = static_cast<size_t>(2 * d.kbK) * d.rows_p * 64;
+  d.h_floats = static_cast<size_t>(d.kbH) * d.rows_p * 64;
+  return d;
+}
+
+bool tc_eligible(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
+  if (w->packed == nullptr) return false;
+  // dense-contraction shapes only (north star): enough chains to fill 128-row MMA tiles, D a multiple
+  // of the head tile's 16-column epilogue chunks, 16-byte aligned rows for the update operands
+  return c->N >= 256 && w->K >= 64 && w->H >= 128 && w->D >= 64 && (w->D % 16) == 0;
+}
+
+int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
+  const int N = c->N, K = w->K, H = w->H, D = w->D;
+  const TcDims d = tc_dims(K, H, D, N);
+  const float* packed = static_cast<const float*>(w->packed);
+  const float* W1 = packed;
+  const float* W2 = W1 + d.w1_floats;
+  const float* W3 = W2 + d.w2_floats;
+  float* ws = static_cast<float*>(c->workspace);
+  float* acat = ws;
+  float* h1 = acat + d.acat_floats;
+  float* h2 = h1 + d.h_floats;
+  float* bias_eff = h2 + d.h_floats;
+  float* ld_part = bias_eff + d.h_rows;
+  const int rg = d.rows_p / 8;
+
+  // network inputs -> TS32 (mask folded into the second input)
+  ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
+      c->in0, K, N, K, nullptr, 0, acat, rg, 0, d.kbK);
+  ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
+      c->in1, K, N, K, c->in1_mask, c->in1_mask_invert, acat, rg, d.kbK, d.kbK);
+  bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos, c->tau_sin, H,
+                                                    bias_eff);
+  int rc = check_launch("ts32_from_rowmajor_kernel");
+  if (rc) return rc;
+
+  const int m_tiles = d.rows_p / 128;
+  // few tiles: halve the N tile so more SMs take part
+  const bool narrow = m_tiles * ((H + 255) / 256) < 120;
+  TcParams p{};
+  p.A = acat, p.a_rg = rg, p.B = W1, p.b_rg = d.h_rows / 8, p.KB = 2 * d.kbK;
+  p.m_tiles = m_tiles, p.n_tiles = narrow ? (H + 127) / 128 : (H + 255) / 256;
+  p.rows = N, p.cols = H, p.bias = bias_eff;
+  p.out_ts = h1, p.out_rg = rg, p.out_kb = d.kbH;
+  rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
+  if (rc) return rc;
+
+  p.A = h1, p.B = W2, p.KB = d.kbH, p.bias = w->b_h, p.out_ts = h2;
+  rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
+  if (rc) return rc;
+
+  p = TcParams{};
+  p.A = h2, p.a_rg = rg, p.B = W3, p.b_rg = d.d_tiles * 192 / 8, p.KB = d.kbH;
+  p.m_tiles = m_tiles, p.n_tiles = d.d_tiles;
+  p.rows = N, p.cols = D;
+  p.b_s = w->b_s, p.b_tr = w->b_tr, p.b_q = w->b_q, p.coeff_s = w->coeff_s, p.coeff_q = w->coeff_q;
+  p.tanh_on_q = w->tanh_on_q;
+  p.S = c->S, p.T = c->T, p.Q = c->Q;
+  p.ux = c->x, p.uv = c->v, p.ug = c->g, p.umask = c->mask, p.uinvert = c->mask_invert;
+  p.eps = c->eps, p.dir = c->dir, p.uout = c->out, p.flag = c->nonfinite_flag;
+  p.ld_part = c->logdet ? ld_part : nullptr;
+  if (c->mode == L2HMC_NET_STQ) rc = launch_tc<192, kTcHeadsStq>(p, st);
+  else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_tc<192, kTcHeadsMomentum>(p, st);
+  else rc = launch_tc<192, kTcHeadsPosition>(p, st);
+  if (rc) return rc;
+  if (c->mode != L2HMC_NET_STQ && c->logdet) {
+    logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, d.d_tiles, N, c->logdet);
+    rc = check_launch("logdet_reduce_tc_kernel");
+  }
+  return rc;
+}
+
+size_t tc_workspace_floats(int K, int H, int D, int N) {
+  const TcDims d = tc_dims(K, H, D, N);
+  return d.acat_floats + 2 * d.h_floats + d.h_rows + static_cast<size_t>(d.d_tiles) * d.rows_p;
+}
+
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+extern "C" size_t l2hmc_net_pack_bytes(int K, int H, int D) {
+  if (K <= 0 || H <= 0 || D <= 0) return 0;
+  const TcDims d = tc_dims(K, H, D, 128);
+  return sizeof(float) * (d.w1_floats + d.w2_floats + d.w3_floats);
+}
+
+extern "C" int l2hmc_net_pack(const l2hmc_net_weights* w, void* packed, size_t packed_bytes, void* stream) {
+  L2HMC_REQUIRE(w && packed, "l2hmc_net_pack: null argument");
+  L2HMC_REQUIRE(w->K > 0 && w->H > 0 && w->D > 0, "l2hmc_net_pack: bad sizes");
+  L2HMC_REQUIRE(w->w_in0 && w->w_in1 && w->w_h && w->w_s && w->w_tr && w->w_q, "l2hmc_net_pack: null weight pointer");
+  L2HMC_REQUIRE(packed_bytes >= l2hmc_net_pack_bytes(w->K, w->H, w->D), "l2hmc_net_pack: buffer too small");
+  L2HMC_REQUIRE(aligned16(packed), "l2hmc_net_pack: buffer must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const TcDims d = tc_dims(w->K, w->H, w->D, 128);
+  float* W1 = static_cast<float*>(packed);
+  float* W2 = W1 + d.w1_floats;
+  float* W3 = W2 + d.w2_floats;
+  cudaError_t e = cudaMemsetAsync(packed, 0, l2hmc_net_pack_bytes(w->K, w->H, w->D), st);   // zero padding rows / k
+  if (e != cudaSuccess) {
+    set_error("l2hmc_net_pack: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return L2HMC_ERR_CUDA;
+  }
+  const int K = w->K, H = w->H, D = w->D;
+  const size_t t1 = static_cast<size_t>(d.kbK) * 32 * H, t2 = static_cast<size_t>(d.kbH) * 32 * H;
+  const size_t t3 = static_cast<size_t>(d.kbH) * 32 * D;
+  ts32_pack_weight_kernel<<<ew_grid(t1), 256, 0, st>>>(w->w_in0, K, H, W1, d.h_rows / 8, 0, 0, 0);
+  ts32_pack_weight_kernel<<<ew_grid(t1), 256, 0, st>>>(w->w_in1, K, H, W1, d.h_rows / 8, d.kbK, 0, 0);
+  ts32_pack_weight_kernel<<<ew_grid(t2), 256, 0, st>>>(w->w_h, H, H, W2, d.h_rows / 8, 0, 0, 0);
+  ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_s, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 0);
+  ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_tr, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 1);
+  ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_q, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 2);
+  return check_launch("ts32_pack_weight_kernel");
+}
+
+// Diagnostic: C = relu(A . W) through the tensor-core layer kernel and the TS32 converters
+// (A [M,K] and W [K,Nc] row-major fp32 in, C [M,Nc] row-major out; scratch >= l2hmc_tc_selftest_bytes).
+extern "C" size_t l2hmc_tc_selftest_bytes(int M, int Nc, int K) {
+  const size_t rows_p = (M + 127) / 128 * 128, n_p = (Nc + 255) / 256 * 256, kb = (K + 31) / 32, kbn = (Nc + 31) / 32;
+  return sizeof(float) * (kb * rows_p * 64 + kb * n_p * 64 + kbn * rows_p * 64 + n_p);
+}
+
+extern "C" int l2hmc_tc_selftest(const float* A, const float* W, int M, int Nc, int K, int bn, float* C, void* scratch,
+                                 void* stream) {
+  L2HMC_REQUIRE(A && W && C && scratch, "l2hmc_tc_selftest: null pointer");
+  L2HMC_REQUIRE(M > 0 && Nc > 0 && K > 0 && (bn == 128 || bn == 256), "l2hmc_tc_selftest: bad sizes");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int rows_p = (M + 127) / 128 * 128, n_p = (Nc + 255) / 256 * 256, kb = (K + 31) / 32, kbn = (Nc + 31) / 32;
+  float* a_ts = static_cast<float*>(scratch);
+  float* w_ts = a_ts + static_cast<size_t>(kb) * rows_p * 64;
+  float* c_ts = w_ts + static_cast<size_t>(kb) * n_p * 64;
+  float* bias = c_ts + static_cast<size_t>(kbn) * rows_p * 64;
+  cudaMemsetAsync(w_ts, 0, sizeof(float) * static_cast<size_t>(kb) * n_p * 64, st);
+  cudaMemsetAsync(bias, 0, sizeof(float) * n_p, st);
+  ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(kb) * (rows_p / 8) * 64), 256, 0, st>>>(
+      A, K, M, K, nullptr, 0, a_ts, rows_p / 8, 0, kb);
+  ts32_pack_weight_kernel<<<ew_grid(static_cast<size_t>(kb) * 32 * Nc), 256, 0, st>>>(W, K, Nc, w_ts, n_p / 8, 0, 0, 0);
+  TcParams p{};
+  p.A = a_ts, p.a_rg = rows_p / 8, p.B = w_ts, p.b_rg = n_p / 8, p.KB = kb;
+  p.m_tiles = rows_p / 128, p.n_tiles = (Nc + bn - 1) / bn;
+  p.rows = M, p.cols = Nc, p.bias = bias, p.out_ts = c_ts, p.out_rg = rows_p / 8, p.out_kb = kbn;
+  int rc = bn == 128 ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
+  if (rc) return rc;
+  ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(M) * Nc), 256, 0, st>>>(c_ts, rows_p / 8, M, Nc, C);
+  return check_launch("l2hmc_tc_selftest");
+}

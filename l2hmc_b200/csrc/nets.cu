@@ -18,6 +18,7 @@
 // is fmaf in K order (fp32); this path serves the shapes too small or ragged for the tcgen05
 // kernel in gemm_tc.cu (config 2: 128 chains x 512 hidden; tail rows).
 #include "common.cuh"
+#include "nets.cuh"
 #include "update_math.cuh"
 
 namespace l2hmc {
@@ -290,8 +291,6 @@ int launch_dense(const DenseParams& p, cudaStream_t st) {
   return check_launch("dense_kernel");
 }
 
-inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-
 }  // namespace
 
 int heads_col_tiles(int D) { return (D + 31) / 32; }
@@ -381,17 +380,23 @@ int net_validate(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
 using namespace l2hmc;
 
 extern "C" size_t l2hmc_net_workspace_bytes(int K, int H, int D, int N) {
-  (void)K;
-  if (H <= 0 || D <= 0 || N <= 0) return 16;
+  if (K <= 0 || H <= 0 || D <= 0 || N <= 0) return 16;
   // h1, h2 [N,H] (fp32 row-major on the FFMA path; tiled hi/lo pairs on the tcgen05 path need
   // 2x and 128-row padding) + log-det partials [D/32][N]
-  const size_t rows = align_up(static_cast<size_t>(N), 128);
-  const size_t hcols = align_up(static_cast<size_t>(H), 32);
-  return sizeof(float) * (4 * rows * hcols + static_cast<size_t>(heads_col_tiles(D)) * rows) + 256;
+  const size_t simt = 2 * static_cast<size_t>(N) * H + static_cast<size_t>(heads_col_tiles(D)) * N;
+  return sizeof(float) * std::max(simt, tc_workspace_floats(K, H, D, N)) + 256;
 }
 
 extern "C" int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* c, void* stream) {
   const int rc = net_validate(w, c);
   if (rc != L2HMC_OK || c->N == 0) return rc;
-  return net_run_simt(w, c, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (c->path == L2HMC_NET_PATH_FFMA) return net_run_simt(w, c, st);
+  const bool tc = tc_eligible(w, c);
+  if (c->path == L2HMC_NET_PATH_TCGEN05 && !tc) {
+    set_error("l2hmc_net_run: shape K=%d H=%d D=%d N=%d (packed=%p) has no tcgen05 path", w->K, w->H, w->D, c->N,
+              w->packed);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
+  return tc ? net_run_tc(w, c, st) : net_run_simt(w, c, st);
 }

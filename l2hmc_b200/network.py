@@ -43,6 +43,8 @@ class _StqNet(object):
     """Dense trunk + heads shared by both architectures."""
 
     tanh_on_q = 0
+    use_tensor_cores = True      # pack weights for the tcgen05 path (taken when N >= 256 and the trunk is wide)
+    path = _lib.NET_PATH_AUTO    # NET_PATH_FFMA / NET_PATH_TCGEN05 force one path (tests, benchmarks)
 
     def _init_dense(self, feat, rng):
         """`_custom_dense` initialisers (generic_net.py:149-161): truncated normal with
@@ -131,7 +133,23 @@ class _StqNet(object):
         return self._struct
 
     def _packed_ptr(self):
-        return None
+        """Pre-tiled TF32-split weight copy for the tcgen05 path (packed lazily, re-packed by
+        load_weights); only built when the trunk is wide enough to ever take that path."""
+        K, H, D = int(self.num_features), int(self.num_hidden), int(self.x_dim)
+        if not self.use_tensor_cores or K < 64 or H < 128 or D < 64 or D % 16:
+            self._packed = None
+            return None
+        lib = _lib.get_lib()
+        nbytes = int(lib.l2hmc_net_pack_bytes(K, H, D))
+        self._packed = torch.empty((nbytes + 3) // 4, dtype=torch.float32, device=self.device)
+        s = _lib.NetWeights()
+        s.K, s.H, s.D = K, H, D
+        p = lambda k: _lib.dptr(self.weights[k])
+        s.w_in0, s.w_in1, s.w_h = p("v_layer.kernel"), p("x_layer.kernel"), p("h_layer.kernel")
+        s.w_s, s.w_tr, s.w_q = p("scale_layer.kernel"), p("translation_layer.kernel"), p("transformation_layer.kernel")
+        with torch.cuda.device(self.device):
+            _lib.check(lib.l2hmc_net_pack(s, _lib.dptr(self._packed), nbytes, _lib.stream_ptr()))
+        return _lib.dptr(self._packed)
 
     def _workspace(self, N):
         need = int(_lib.get_lib().l2hmc_net_workspace_bytes(int(self.num_features), int(self.num_hidden),
@@ -161,6 +179,7 @@ class _StqNet(object):
         call.tau_cos, call.tau_sin = self._tau(t)
         call.N = int(N)
         call.workspace, call.workspace_bytes = _lib.dptr(ws), need
+        call.path = int(self.path)
         with torch.cuda.device(self.device):
             _lib.check(_lib.get_lib().l2hmc_net_run(self._weights_struct(), call, _lib.stream_ptr()))
 

@@ -188,3 +188,70 @@ def test_net_errors(pkg):
     z = torch.zeros(5, 32, device="cuda")
     net.momentum_update(z, z + 1, z, (1.0, 0.0), 1.0, 1, ld, flag)
     assert int(flag.item()) == 1
+
+
+# ------------------------------------------------------------------ tcgen05 path
+@pytest.mark.parametrize("M,Nc,K,bn", [(128, 256, 32, 256), (128, 128, 64, 128), (256, 512, 512, 256),
+                                       (300, 200, 100, 128), (1000, 1024, 1024, 256), (130, 70, 40, 256)])
+def test_tc_selftest_gemm(pkg, M, Nc, K, bn):
+    """relu(A.W) through the tcgen05 3xTF32 layer kernel + TS32 converters vs float64."""
+    from l2hmc_b200 import _lib
+    lib = _lib.get_lib()
+    rng = np.random.default_rng(M + Nc + K)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    W = (rng.standard_normal((K, Nc)) / np.sqrt(K)).astype(np.float32)
+    dA, dW = torch.as_tensor(A).cuda(), torch.as_tensor(W).cuda()
+    C = torch.empty(M, Nc, device="cuda")
+    scratch = torch.empty(int(lib.l2hmc_tc_selftest_bytes(M, Nc, K)) // 4 + 64, device="cuda")
+    _lib.check(lib.l2hmc_tc_selftest(_lib.dptr(dA), _lib.dptr(dW), M, Nc, K, bn, _lib.dptr(C), _lib.dptr(scratch), None))
+    torch.cuda.synchronize()
+    ref = np.maximum(A.astype(np.float64) @ W.astype(np.float64), 0)
+    err = np.abs(C.cpu().numpy() - ref).max()
+    fp32 = np.abs(np.maximum(A @ W, 0) - ref).max()               # what plain fp32 accumulation achieves
+    assert err < max(2e-6, 4 * fp32), f"max abs err {err}, fp32 matmul {fp32} (plain TF32 would be ~1e-3)"
+
+
+@pytest.mark.parametrize("arch,T,X,N,M", [("generic", 8, 8, 256, 2), ("generic", 16, 16, 300, 2),
+                                          ("conv3D", 16, 16, 512, 2), ("generic", 6, 8, 257, 1)])
+def test_tc_path_equals_ffma_path_and_oracle(pkg, arch, T, X, N, M):
+    from l2hmc_b200 import _lib
+    rng = np.random.default_rng(7 + T * X + N)
+    D, eps, beta = 2 * T * X, 0.2, 2.5
+    ws = _oracle_weights(arch, T, X, rng)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    vf, vb = (rng.standard_normal((N, D)).astype(np.float32) for _ in range(2))
+    ud, ua = (rng.uniform(size=N).astype(np.float32) for _ in range(2))
+    lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
+    mask = orc.construct_masks(D, M, seed=42)
+    od = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch=arch, mask=mask, xnet=ws["XNet"], vnet=ws["VNet"])
+    rxp, rvp, rp, _ = od.apply_transition(x, beta, vf, vb, ud, ua)
+    res = {}
+    for path in (_lib.NET_PATH_TCGEN05, _lib.NET_PATH_FFMA):
+        np.random.seed(42)
+        dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M, eps=eps, weights=ws)
+        dyn.position_fn.path = dyn.momentum_fn.path = path
+        # bare S,T,Q through each path
+        S, Tr, Q = dyn.position_fn([vf, x, (1.0, 0.0)], mask=dyn.mask[0], mask_invert=True)
+        xp, vp, p, xo = dyn.apply_transition(x, beta, momentum_f=vf, momentum_b=vb, direction_uniform=ud,
+                                             accept_uniform=ua)
+        res[path] = (S, Tr, Q, xp, vp, p)
+        close(xp, rxp, rtol=1e-5, atol=5e-5); close(vp, rvp, rtol=1e-5, atol=5e-5)
+        close(p, rp, rtol=2e-3, atol=1e-6)
+        dyn.raise_if_nonfinite()
+    a, b = res[_lib.NET_PATH_TCGEN05], res[_lib.NET_PATH_FFMA]
+    for i in range(3):
+        close(a[i], b[i], rtol=1e-5, atol=2e-6)          # 3xTF32 == fp32 FFMA to ~1e-6
+    close(a[3], b[3], rtol=0, atol=3e-5); close(a[4], b[4], rtol=0, atol=3e-5)
+    tS, tT, tQ = od.position_fn(torch.as_tensor(vf), (1 - torch.as_tensor(mask[0])) * torch.as_tensor(x),
+                                torch.tensor([[1.0, 0.0]]).repeat(N, 1))
+    close(a[0], tS, rtol=1e-5, atol=2e-6); close(a[1], tT, rtol=1e-5, atol=2e-6); close(a[2], tQ, rtol=1e-5, atol=2e-6)
+
+
+def test_tc_path_refuses_small_shapes(pkg):
+    from l2hmc_b200 import _lib
+    from l2hmc_b200.network import GenericNet
+    net = GenericNet(model_name="XNet", x_dim=32, links_shape=(4, 4, 2), num_hidden=64, name_scope="position",
+                     factor=2.)
+    net.path = _lib.NET_PATH_TCGEN05
+    with pytest.raises(_lib.L2hmcError, match="no tcgen05 path"):
+        net([np.zeros((5, 32), np.float32), np.zeros((5, 32), np.float32), (1.0, 0.0)])
