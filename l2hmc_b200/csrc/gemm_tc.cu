@@ -22,14 +22,15 @@
 // Weights are packed once (l2hmc_net_pack); activations are written in this form by the producing
 // kernel's epilogue (hidden layers) or by a small converter (network inputs, mask folded in).
 //
-// Kernel.  Persistent, one CTA per SM, 192 threads, warp-specialised:
-//   warps 0-3  epilogue: tcgen05.ld accumulator rows (thread = chain) -> bias/relu -> hi/lo split ->
-//              TS32 store; or, for the heads, tanh/exp + the leapfrog sub-update + log-det
-//   warp 4     bulk-copy producer (one lane) + TMEM allocation
-//   warp 5     MMA issuer (one lane): per 32-wide K block 4 K-steps x 3 products of
+// Kernel.  Persistent, one CTA per SM, 320 threads, warp-specialised:
+//   warps 0-7  epilogue: tcgen05.ld finished K chunks (thread = chain, half the tile's columns) and
+//              add them into fp32 running sums in registers; at the end of the tile bias/relu ->
+//              hi/lo split -> TS32 store, or, for the heads, tanh/exp + the leapfrog sub-update
+//   warp 8     bulk-copy producer (one lane) + TMEM allocation
+//   warp 9     MMA issuer (one lane): per 32-wide K block 4 K-steps x 3 products of
 //              tcgen05.mma.cta_group::1.kind::tf32, M = 128, N = BN
 //   smem ring of 2-3 stages (A 32 KB + B BN*256 B), full/empty mbarriers; two accumulator stages in
-//   TMEM (tmem_full / tmem_empty) so the epilogue of tile i overlaps the MMAs of tile i+1.
+//   TMEM (tmem_full / tmem_empty), one per in-flight 128-wide K chunk.
 #include "common.cuh"
 #include "nets.cuh"
 #include "update_math.cuh"
@@ -37,7 +38,8 @@
 namespace l2hmc {
 namespace {
 
-constexpr int kTcThreads = 192;
+constexpr int kEpiWarps = 8, kProducerWarp = 8, kMmaWarp = 9;
+constexpr int kTcThreads = (kEpiWarps + 2) * 32;
 constexpr int TC_BM = 128;
 constexpr uint32_t kATileBytes = TC_BM * 32 * 4 * 2;   // 128 rows x 32 k x (hi, lo)
 
@@ -142,6 +144,13 @@ __device__ __forceinline__ float tf32_hi(float a) { return tf32_rn(a); }
 __device__ __forceinline__ float tf32_lo(float a, float hi) { return tf32_rn(__fsub_rn(a, hi)); }
 
 // ------------------------------------------------------------------ the GEMM kernel
+// Tensor-core accumulation truncates (round-toward-zero) every time an MMA adds into the TMEM
+// accumulator; over K/8 x 3 dependent adds that bias reaches ~1e-5 relative at K = 512 (measured).
+// The accumulator is therefore flushed every kChunkKB K blocks (K = 128): the MMA warp starts a
+// fresh accumulator stage per chunk, and the epilogue warps add each finished chunk into fp32
+// running sums in REGISTERS with round-to-nearest adds while the next chunk's MMAs run.
+constexpr int kChunkKB = 4;
+
 template <int BN, int MODE>
 __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p) {
   constexpr int NSTAGE = (BN <= 128) ? 3 : 2;
@@ -153,8 +162,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
                               (static_cast<uint32_t>(TC_BM >> 4) << 24);
   extern __shared__ __align__(1024) uint8_t tc_smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(tc_smem + NSTAGE * kStageBytes);
-  uint64_t* full = bars;                 // [NSTAGE]
-  uint64_t* empty = bars + NSTAGE;       // [NSTAGE]
+  uint64_t* full = bars;                     // [NSTAGE]
+  uint64_t* empty = bars + NSTAGE;           // [NSTAGE]
   uint64_t* tmem_full = bars + 2 * NSTAGE;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
@@ -162,17 +171,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < NSTAGE; ++s) mbar_init(&full[s], 1), mbar_init(&empty[s], 1);
-    for (int s = 0; s < 2; ++s) mbar_init(&tmem_full[s], 1), mbar_init(&tmem_empty[s], 128);
+    for (int s = 0; s < 2; ++s) mbar_init(&tmem_full[s], 1), mbar_init(&tmem_empty[s], kEpiWarps * 32);
     mbar_fence_init();
   }
-  if (warp == 4) tmem_alloc(tmem_slot, 512);
+  if (warp == kProducerWarp) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const int num_tiles = p.m_tiles * p.n_tiles;
+  const int num_chunks = (p.KB + kChunkKB - 1) / kChunkKB;
 
-  if (warp == 4) {
+  if (warp == kProducerWarp) {
     // ===== producer =====
     if (lane == 0) {
       int stage = 0;
@@ -192,16 +202,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == kMmaWarp) {
     // ===== MMA issuer =====
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0, acc = 0, acc_phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * kAccCols;
         for (int kb = 0; kb < p.KB; ++kb) {
+          const int in_chunk = kb % kChunkKB;
+          if (in_chunk == 0) {                   // fresh accumulator stage for this K chunk
+            mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+            tc_fence_after();
+          }
+          const uint32_t d_tmem = tmem_base + acc * kAccCols;
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(tc_smem + stage * kStageBytes);
@@ -210,49 +223,70 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
           for (int ks = 0; ks < 4; ++ks) {
             const uint64_t a_hi = make_desc(sa + ks * 256), a_lo = make_desc(sa + 1024 + ks * 256);
             const uint64_t b_hi = make_desc(sb + ks * 256), b_lo = make_desc(sb + 1024 + ks * 256);
-            umma_tf32(d_tmem, a_hi, b_lo, kIdesc, (kb | ks) != 0);
+            umma_tf32(d_tmem, a_hi, b_lo, kIdesc, (in_chunk | ks) != 0);
             umma_tf32(d_tmem, a_lo, b_hi, kIdesc, 1);
             umma_tf32(d_tmem, a_hi, b_hi, kIdesc, 1);
           }
-          umma_commit(&empty[stage]);          // smem slot free once these MMAs have read it
+          umma_commit(&empty[stage]);            // smem slot free once these MMAs have read it
           if (++stage == NSTAGE) stage = 0, phase ^= 1;
+          if (in_chunk == kChunkKB - 1 || kb == p.KB - 1) {
+            umma_commit(&tmem_full[acc]);        // chunk complete
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+          }
         }
-        umma_commit(&tmem_full[acc]);          // accumulator complete
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
       }
     }
   } else {
-    // ===== epilogue (warps 0-3: TMEM lanes 32*warp ..) =====
+    // ===== epilogue (8 warps: TMEM lane quadrant = warp % 4, column half = warp / 4) =====
+    constexpr int NG = (MODE == kTcLayer) ? BN / 64 : 3;     // 32-column groups owned by this thread
+    const int quad = warp & 3, half = warp >> 2;
     uint32_t acc = 0, acc_phase = 0;
-    const int row_in_tile = warp * 32 + lane;
+    const int row_in_tile = quad * 32 + lane;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
       const int r = m_blk * TC_BM + row_in_tile;
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16) + acc * kAccCols;
+      float sum[NG][32];
+#pragma unroll
+      for (int g = 0; g < NG; ++g)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) sum[g][j] = 0.f;
+      for (int chunk = 0; chunk < num_chunks; ++chunk) {
+        mbar_wait(&tmem_full[acc], acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kAccCols;
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+          const int col = (MODE == kTcLayer) ? half * (BN / 2) + g * 32 : g * 64 + half * 32;
+          float v[32];
+          tmem_ld32(taddr + col, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sum[g][j] = __fadd_rn(sum[g][j], v[j]);
+        }
+        tc_fence_before();
+        mbar_arrive(&tmem_empty[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
       if (MODE == kTcLayer) {
         const int rg = r >> 3, r8 = r & 7;
-#pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          float v[32];
-          tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          const int kb = n_blk * (BN / 32) + c;           // K block of the NEXT layer
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+          const int kb = n_blk * (BN / 32) + half * (BN / 64) + g;     // K block of the NEXT layer
           if (kb < p.out_kb) {
             const int n0 = kb * 32;
             float* dst = p.out_ts + ((static_cast<size_t>(kb) * p.out_rg + rg) * 2) * 256 + r8 * 4;
 #pragma unroll
             for (int kc = 0; kc < 8; ++kc) {
-              float o[4], h[4], l[4];
+              float h[4], l[4];
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int n = n0 + kc * 4 + j;
                 const float b = n < p.cols ? __ldg(p.bias + n) : 0.f;
-                o[j] = fmaxf(__fadd_rn(v[kc * 4 + j], b), 0.f);
-                h[j] = tf32_hi(o[j]);
-                l[j] = tf32_lo(o[j], h[j]);
+                const float o = fmaxf(__fadd_rn(sum[g][kc * 4 + j], b), 0.f);
+                h[j] = tf32_hi(o);
+                l[j] = tf32_lo(o, h[j]);
               }
               *reinterpret_cast<float4*>(dst + kc * 32) = make_float4(h[0], h[1], h[2], h[3]);
               *reinterpret_cast<float4*>(dst + 256 + kc * 32) = make_float4(l[0], l[1], l[2], l[3]);
@@ -260,22 +294,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
           }
         }
       } else {
-        // heads: columns [0,64) = S, [64,128) = T, [128,192) = Q pre-activations of d = 64*n_blk + ..
+        // heads: sum[0] = S, sum[1] = T, sum[2] = Q pre-activations of d = 64*n_blk + 32*half + j
         const bool rok = r < p.rows;
         const float heps = __fmul_rn(0.5f, p.eps);
         float ld = 0.f;
         bool bad = false;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          float s[16], t[16], q[16];
-          tmem_ld16(taddr + c * 16, s);
-          tmem_ld16(taddr + 64 + c * 16, t);
-          tmem_ld16(taddr + 128 + c * 16, q);
-          tmem_ld_wait();
-          const int d0 = n_blk * 64 + c * 16;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int d0 = n_blk * 64 + half * 32 + c * 16;
           if (rok && d0 < p.cols) {       // cols is a multiple of 16 on this path
             const size_t at = static_cast<size_t>(r) * p.cols + d0;
-            float a0[16], a1[16], o[16];
+            float a0[16], a1[16], o0[16], o1[16], o2[16];
             if (MODE == kTcHeadsMomentum) {
 #pragma unroll
               for (int j = 0; j < 16; j += 4) {
@@ -292,49 +321,47 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const int d = d0 + j;
-              const float S = __fmul_rn(tanhf(__fadd_rn(s[j], __ldg(p.b_s + d))), expf(__ldg(p.coeff_s + d)));
-              const float Tr = __fadd_rn(t[j], __ldg(p.b_tr + d));
-              float Q = __fadd_rn(q[j], __ldg(p.b_q + d));
+              const float S = __fmul_rn(tanhf(__fadd_rn(sum[0][c * 16 + j], __ldg(p.b_s + d))),
+                                        expf(__ldg(p.coeff_s + d)));
+              const float Tr = __fadd_rn(sum[1][c * 16 + j], __ldg(p.b_tr + d));
+              float Q = __fadd_rn(sum[2][c * 16 + j], __ldg(p.b_q + d));
               if (p.tanh_on_q) Q = tanhf(Q);
               Q = __fmul_rn(Q, expf(__ldg(p.coeff_q + d)));
               if (MODE == kTcHeadsStq) {
-                s[j] = S, t[j] = Tr, q[j] = Q;
+                o0[j] = S, o1[j] = Tr, o2[j] = Q;
               } else if (MODE == kTcHeadsMomentum) {
-                o[j] = p.dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
-                                 : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
+                o0[j] = p.dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
+                                  : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
               } else {
                 float m = __ldg(p.umask + d);
                 if (p.uinvert) m = __fsub_rn(1.f, m);
-                o[j] = p.dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
-                                 : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
+                o0[j] = p.dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
+                                  : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
               }
             }
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
               if (MODE == kTcHeadsStq) {
-                *reinterpret_cast<float4*>(p.S + at + j) = *reinterpret_cast<float4*>(s + j);
-                *reinterpret_cast<float4*>(p.T + at + j) = *reinterpret_cast<float4*>(t + j);
-                *reinterpret_cast<float4*>(p.Q + at + j) = *reinterpret_cast<float4*>(q + j);
+                *reinterpret_cast<float4*>(p.S + at + j) = *reinterpret_cast<float4*>(o0 + j);
+                *reinterpret_cast<float4*>(p.T + at + j) = *reinterpret_cast<float4*>(o1 + j);
+                *reinterpret_cast<float4*>(p.Q + at + j) = *reinterpret_cast<float4*>(o2 + j);
               } else {
-                *reinterpret_cast<float4*>(p.uout + at + j) = *reinterpret_cast<float4*>(o + j);
+                *reinterpret_cast<float4*>(p.uout + at + j) = *reinterpret_cast<float4*>(o0 + j);
               }
             }
           }
         }
         if (MODE != kTcHeadsStq) {
-          if (rok && p.ld_part) p.ld_part[static_cast<size_t>(n_blk) * p.rows + r] = ld;
+          // one partial per (64-wide head tile, column half): [2*n_blk + half][rows]
+          if (rok && p.ld_part) p.ld_part[static_cast<size_t>(2 * n_blk + half) * p.rows + r] = ld;
           flag_nonfinite(p.flag, bad);
         }
       }
-      tc_fence_before();
-      mbar_arrive(&tmem_empty[acc]);
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kProducerWarp) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }
@@ -476,11 +503,16 @@ TcDims tc_dims(int K, int H, int D, int N) {
   return d;
 }
 
+// structural requirements of the tcgen05 path: packed weights, D a multiple of the head epilogue's
+// 16-column chunks (16-byte aligned rows for the update operands); rows / K / H are padded
+bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
+  (void)c;
+  return w->packed != nullptr && (w->D % 16) == 0;
+}
+
+// AUTO: dense-contraction shapes only (north star) -- enough chains to fill 128-row MMA tiles
 bool tc_eligible(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
-  if (w->packed == nullptr) return false;
-  // dense-contraction shapes only (north star): enough chains to fill 128-row MMA tiles, D a multiple
-  // of the head tile's 16-column epilogue chunks, 16-byte aligned rows for the update operands
-  return c->N >= 256 && w->K >= 64 && w->H >= 128 && w->D >= 64 && (w->D % 16) == 0;
+  return tc_supported(w, c) && c->N >= 256 && w->K >= 64 && w->H >= 128 && w->D >= 64;
 }
 
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
@@ -538,7 +570,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   else rc = launch_tc<192, kTcHeadsPosition>(p, st);
   if (rc) return rc;
   if (c->mode != L2HMC_NET_STQ && c->logdet) {
-    logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, d.d_tiles, N, c->logdet);
+    logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, 2 * d.d_tiles, N, c->logdet);
     rc = check_launch("logdet_reduce_tc_kernel");
   }
   return rc;
@@ -546,7 +578,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
 
 size_t tc_workspace_floats(int K, int H, int D, int N) {
   const TcDims d = tc_dims(K, H, D, N);
-  return d.acat_floats + 2 * d.h_floats + d.h_rows + static_cast<size_t>(d.d_tiles) * d.rows_p;
+  return d.acat_floats + 2 * d.h_floats + d.h_rows + 2 * static_cast<size_t>(d.d_tiles) * d.rows_p;
 }
 
 }  // namespace l2hmc

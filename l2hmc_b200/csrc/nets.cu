@@ -392,7 +392,7 @@ extern "C" int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* c
   if (rc != L2HMC_OK || c->N == 0) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (c->path == L2HMC_NET_PATH_FFMA) return net_run_simt(w, c, st);
-  const bool tc = tc_eligible(w, c);
+  const bool tc = c->path == L2HMC_NET_PATH_TCGEN05 ? tc_supported(w, c) : tc_eligible(w, c);
   if (c->path == L2HMC_NET_PATH_TCGEN05 && !tc) {
     set_error("l2hmc_net_run: shape K=%d H=%d D=%d N=%d (packed=%p) has no tcgen05 path", w->K, w->H, w->D, c->N,
               w->packed);
