@@ -282,6 +282,82 @@ def run_e2e(r):
             "plaq": float(res.plaqs.mean()), "charge_diff": res.charge_diff}
 
 
+def run_l2hmc(r, steps):
+    """Second leg: the L2HMC path with S/T/Q networks (BASELINE config 3: 16x16, conv3D front-end,
+    2048 chains per GPU, M = 5) -- MC-step throughput, and the tensor-pipe roofline of the network
+    GEMMs (tcgen05, 3xTF32) at the config-3 and config-4 (32x32 generic, H = 8192) shapes."""
+    import numpy as np
+    c = r["ctx"]
+    torch, dev, world = c["torch"], c["dev"], c["world"]
+    from l2hmc_b200 import GaugeDynamics, GaugeLattice, _lib
+    peaks = {}
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            peaks = json.load(f)
+    bf16_peak, peak_kind = float(peaks.get("bf16_tflops", 1590.0)), ("measured" if peaks else "fallback")
+    tf32_peak = bf16_peak / 2.0           # kind::tf32 runs at half the bf16 rate (1.1 vs 2.25 PF nominal)
+    out = {}
+
+    def events_ms(fn, iters, warm=2):
+        for _ in range(warm):
+            fn()
+        c["barrier"]()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        ev[0].record()
+        for _ in range(iters):
+            fn()
+        ev[1].record()
+        c["barrier"]()
+        return c["max_over_ranks"](ev[0].elapsed_time(ev[1])) / iters
+
+    for tag, arch, T_, N, M_, eps, do_mc in (("config3_16x16_conv3D", "conv3D", 16, 2048, 5, 0.25, True),
+                                              ("config4_32x32_generic_nets", "generic", 32, 2048, 10, 0.1, False)):
+        D_ = 2 * T_ * T_
+        lat = GaugeLattice(T_, T_, 2, "U1", num_samples=1)
+        np.random.seed(42)
+        dyn = GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M_, eps=eps, seed=7,
+                            chain_offset=c["dyn"].chain_offset // 32, device=dev)
+        net = dyn.position_fn
+        K_, H_ = net.num_features, net.num_hidden
+        gen = torch.Generator(device=dev).manual_seed(5)
+        x = torch.rand(N, D_, device=dev, generator=gen) * (2 * np.pi)
+        v = torch.randn(N, D_, device=dev, generator=gen)
+        ld = torch.zeros(N, device=dev)
+        flop = 2.0 * N * (2 * K_ * H_ + 2 * H_ + H_ * H_ + 3 * H_ * D_)
+        feats = net._features(v, x, dyn.mask[0], False)       # conv features (or the inputs) outside the GEMM timing
+        call = _lib.NetCall()
+        call.mode, call.eps, call.dir = _lib.NET_POSITION, eps, 1
+        call.in1_mask, call.in1_mask_invert = _lib.dptr(feats[2]), 0
+        x_new, mask0 = torch.empty_like(x), dyn.mask[0].contiguous()
+        call.x, call.v, call.mask, call.out = _lib.dptr(x), _lib.dptr(v), _lib.dptr(mask0), _lib.dptr(x_new)
+        call.logdet, call.nonfinite_flag = _lib.dptr(ld), _lib.dptr(dyn._flag, torch.int32)
+        ms = events_ms(lambda: net._run(call, feats[0], feats[1], N, (1.0, 0.0)), max(5, steps // 2))
+        tf = flop / ms / 1e9
+        entry = {"chains_per_gpu": N, "K": K_, "H": H_, "D": D_, "lf_steps": M_,
+                 "net_call": {"what": "3 tcgen05 GEMMs (two-input layer, hidden layer, 3 heads with the position "
+                                      "update + log-det in the epilogue) + operand converters, one position_fn call",
+                              "ms": ms, "gflop_algorithmic": flop / 1e9},
+                 "roofline": {"bound": "tensor", "achieved": tf, "unit": "TFLOP/s",
+                              "tensor_pipe_tflops": 3 * tf, "peak": tf32_peak, "peak_kind": peak_kind + " bf16 / 2",
+                              "frac": 3 * tf / tf32_peak,
+                              "note": "achieved = algorithmic fp32 flops / time; every product is 3 TF32 MMAs "
+                                      "(hi.lo + lo.hi + hi.hi), so the tensor pipe runs at 3x that rate"}}
+        if do_mc:
+            x_mc = [x]
+
+            def mc():
+                x_mc[0] = dyn.apply_transition(x_mc[0], 3.0, wrap=True)[3]
+            step_ms = events_ms(mc, max(3, steps // 4), warm=2)
+            entry["mc_step_ms"] = step_ms
+            entry["link_updates_per_s"] = world * N * D_ * M_ / (step_ms * 1e-3)
+            dyn.raise_if_nonfinite()
+        out[tag] = entry
+        del dyn, net, x, v
+        torch.cuda.empty_cache()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -292,6 +368,7 @@ def main():
     ap.add_argument("--cpu-chains", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-l2hmc", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -303,6 +380,7 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
     r = run_gpu(args, rank, local_rank, world)
     e2e = None if args.no_e2e else run_e2e(r)
+    l2hmc = None if args.no_l2hmc else run_l2hmc(r, args.steps)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         v, per_step, threads = cpu_reference_run(steps=5, warmup=1, chains=args.cpu_chains)
@@ -333,7 +411,7 @@ def main():
                         "achieved": r["mc"]["gbs"], "peak": r["peak"], "unit": "GB/s",
                         "frac": r["mc"]["gbs"] / r["peak"], "algorithmic_bytes": r["mc"]["bytes"],
                         "ms_per_step": r["mc"]["ms"]},
-        "cpu_baseline": cpu, "observables": r["obs"],
+        "l2hmc": l2hmc, "cpu_baseline": cpu, "observables": r["obs"],
     }
     print(json.dumps(line))
 
