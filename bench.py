@@ -155,7 +155,10 @@ def run_gpu(args, rank, local_rank, world):
     N = args.chains_per_gpu
     K, W = args.steps, max(args.warmup, 3)
     lat = GaugeLattice(T, X, 2, "U1", num_samples=1)
-    dyn = GaugeDynamics(lat, hmc=True, num_steps=M, eps=EPS, seed=2024, chain_offset=rank * N, device=dev)
+    from l2hmc_b200.sharding import shard_range
+    chain_lo, chain_hi = shard_range(world * N, rank, world)          # contiguous block of the global batch
+    assert chain_hi - chain_lo == N
+    dyn = GaugeDynamics(lat, hmc=True, num_steps=M, eps=EPS, seed=2024, chain_offset=chain_lo, device=dev)
     gen = torch.Generator(device=dev).manual_seed(1000 + rank)
     x = torch.rand(N, D, device=dev, generator=gen) * (2 * np.pi)      # synthetic hot start
 
