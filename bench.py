@@ -43,6 +43,16 @@ def measured_peaks():
     return 6650.0, "fallback"
 
 
+def ncu_traffic(kernel):
+    """dram bytes per launch from the committed ncu capture (profiles/r1_traffic.json), or None."""
+    path = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)[kernel])
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons while the timed region runs (B200_PROFILING.md)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -406,7 +416,7 @@ def main():
         "clocks": r["clk"], "gpu_launches": launches, "e2e": e2e,
         "roofline": {"bound": "hbm", "kernel": "hmc_kernel<32,32,false> (fused leapfrog step, one launch per LF step)",
                      "achieved": r["lf"]["gbs"], "peak": r["peak"], "peak_kind": r["peak_kind"], "unit": "GB/s",
-                     "frac": r["lf"]["gbs"] / r["peak"], "traffic": None, "algorithmic_bytes": r["lf"]["bytes"],
+                     "frac": r["lf"]["gbs"] / r["peak"], "traffic": ncu_traffic("hmc_kernel<32,32,false>"), "algorithmic_bytes": r["lf"]["bytes"],
                      "ms_per_launch": r["lf"]["ms"],
                      "link_updates_per_s": args.chains_per_gpu * D / (r["lf"]["ms"] * 1e-3)},
         "roofline_mc": {"bound": "hbm", "kernel": "hmc_kernel<32,32,true> (one launch = one MC step incl. observables; M LF steps "
