@@ -118,6 +118,7 @@ def reshape(x, shape, name=None):
 
 
 def cast(x, dtype, name=None):
+    x = _t(x)
     if dtype in (torch.int32, torch.int64):
         return torch.trunc(x).to(dtype) if x.is_floating_point() else x.to(dtype)
     return x.to(dtype)
@@ -168,6 +169,8 @@ def is_finite(x, name=None):
 
 
 def where(cond, x, y, name=None):
+    if cond.dim() == 1 and _t(x).dim() > 1:        # TF-1: a vector condition selects whole rows
+        cond = cond.reshape((-1,) + (1,) * (_t(x).dim() - 1))
     return torch.where(cond, x, y)
 
 
@@ -403,3 +406,77 @@ contrib = types.SimpleNamespace(
     eager=types.SimpleNamespace(),
 )
 logging = types.SimpleNamespace(set_verbosity=lambda *_a: None, INFO=0)
+
+
+# --------------------------------------------------------------------------- MoG path additions
+# Symbols used by the reference's utils/{dynamics,sampler,network,distributions}.py (config 5).
+import sys as _sys
+
+
+def placeholder(dtype=torch.float32, shape=None, name=None):
+    """A feedable scalar: the golden script sets it in place (`.fill_`).  Starts at 1."""
+    return torch.ones(tuple(shape or ()), dtype=dtype)
+
+
+@contextlib.contextmanager
+def variable_scope(*_a, **_k):
+    yield types.SimpleNamespace(reuse_variables=lambda: None)
+
+
+def get_variable(name, shape=None, initializer=None, trainable=True, dtype=None):
+    if isinstance(initializer, torch.Tensor):
+        return initializer.clone()
+    if callable(initializer):
+        return initializer(list(shape)).clone()
+    return torch.zeros(tuple(shape))
+
+
+def log(x, name=None):
+    return torch.log(_t(x))
+
+
+def sqrt(x, name=None):
+    return torch.sqrt(_t(x))
+
+
+def matmul(a, b, name=None):
+    return torch.matmul(_t(a), _t(b))
+
+
+def add(a, b, name=None):
+    return _t(a) + _t(b)
+
+
+def diag_part(x, name=None):
+    return torch.diagonal(x)
+
+
+def concat(values, axis=0, name=None):
+    return torch.cat(list(values), dim=axis)
+
+
+def reduce_logsumexp(x, axis=None, name=None, keepdims=False):
+    return torch.logsumexp(x, dim=axis, keepdim=keepdims)
+
+
+def reduce_max(x, axis=None, name=None):
+    return x.max() if axis is None else x.max(dim=axis).values
+
+
+def reduce_min(x, axis=None, name=None):
+    return x.min() if axis is None else x.min(dim=axis).values
+
+
+def stop_gradient(x, name=None):
+    return x.detach()
+
+
+summary = types.SimpleNamespace(scalar=lambda *_a, **_k: None, histogram=lambda *_a, **_k: None)
+pi = _pymath.pi
+
+for _name in ("tensorflow.python", "tensorflow.python.ops", "tensorflow.python.ops.variable_scope",
+              "tensorflow.python.ops.array_ops", "tensorflow.python.ops.math_ops", "tensorflow.python.ops.nn_ops"):
+    _sys.modules.setdefault(_name, types.ModuleType(_name))
+_sys.modules["tensorflow.python"].ops = _sys.modules["tensorflow.python.ops"]
+for _sub in ("variable_scope", "array_ops", "math_ops", "nn_ops"):
+    setattr(_sys.modules["tensorflow.python.ops"], _sub, _sys.modules["tensorflow.python.ops." + _sub])

@@ -162,3 +162,77 @@ def test_misc_host_helpers():
     assert abs(orc.update_beta(0, 2., 4., 100) - 2.) < 1e-12 and abs(orc.update_beta(100, 2., 4., 100) - 4.) < 1e-12
     w = orc.wrap_2pi(np.array([-0.5, 7.0, 0.0, 6.2831855], np.float32))
     assert (w >= 0).all() and (w < np.float32(2 * np.pi) + 1e-6).all()
+
+
+# --------------------------------------------------------------------------- MoG path (config 5)
+MOG_TAGS = ["mog2.L2", "mog2.L5.T2", "ring4.L3", "mog2.hmc", "gmm6.L2"]
+
+
+def mog_dyn_from(g, tag, dtype=torch.float32):
+    from oracle import mog_oracle as mog
+    x_dim, L, H, N, hmc, nb = (int(v) for v in g[tag + ".meta"])
+    nets = {}
+    if not hmc:
+        for net in ("XNet", "VNet"):
+            pre = f"{tag}.{net}."
+            nets[net] = {k[len(pre):]: v for k, v in g.items() if k.startswith(pre) and ".call." not in k}
+    target = mog.GMMTarget(g[tag + ".mus"], g[tag + ".i_sigmas"], g[tag + ".constants"], dtype)
+    dyn = mog.OracleMogDynamics(target, x_dim, L, float(g[tag + ".eps"]), hmc=bool(hmc), mask=g[tag + ".mask"],
+                                xnet=nets.get("XNet"), vnet=nets.get("VNet"),
+                                temperature=float(g[tag + ".temperature"]), dtype=dtype)
+    return dyn, (x_dim, L, H, N, bool(hmc))
+
+
+@pytest.mark.parametrize("tag", MOG_TAGS)
+def test_mog_oracle_against_reference_goldens(golden, tag):
+    from oracle import mog_oracle as mog
+    g = golden("mog_cases")
+    dyn, (x_dim, L, H, N, hmc) = mog_dyn_from(g, tag)
+    assert np.array_equal(mog.init_masks(x_dim, L, seed=42), g[tag + ".mask"])
+    x, vf, vb = t32(g[tag + ".x"]), t32(g[tag + ".v_f"]), t32(g[tag + ".v_b"])
+    close(dyn.energy(x), g[tag + ".energy"], rtol=1e-5, atol=1e-5)
+    close(dyn.grad_energy(x), g[tag + ".grad"], rtol=1e-5, atol=2e-5)
+    if not hmc:
+        tv = t32(g[tag + ".call.tvec"])
+        for name, fn in (("XNet", dyn.XNet), ("VNet", dyn.VNet)):
+            S, Tr, Q = fn(vf, x, tv)
+            close(S, g[f"{tag}.{name}.call.S"], atol=2e-6); close(Tr, g[f"{tag}.{name}.call.T"], atol=2e-6)
+            close(Q, g[f"{tag}.{name}.call.Q"], atol=2e-6)
+    step = 1 if L > 1 else 0
+    xo, vo, lj = dyn.forward_step(x, vf, step)
+    close(xo, g[tag + ".fstep.x"], atol=1e-5); close(vo, g[tag + ".fstep.v"], rtol=1e-5, atol=2e-5)
+    close(lj, g[tag + ".fstep.logjac"], atol=1e-5)
+    xo, vo, lj = dyn.backward_step(x, vf, step)
+    close(xo, g[tag + ".bstep.x"], atol=1e-5); close(vo, g[tag + ".bstep.v"], rtol=1e-5, atol=2e-5)
+    close(lj, g[tag + ".bstep.logjac"], atol=1e-5)
+    X, V, p = dyn.forward(x, vf)
+    close(X, g[tag + ".fwd.x"], rtol=1e-5, atol=2e-5); close(V, g[tag + ".fwd.v"], rtol=1e-4, atol=1e-4)
+    close(p, g[tag + ".fwd.p"], rtol=2e-3, atol=1e-6)
+    X, V, p = dyn.backward(x, vb)
+    close(X, g[tag + ".bwd.x"], rtol=1e-5, atol=2e-5); close(V, g[tag + ".bwd.v"], rtol=1e-4, atol=1e-4)
+    close(p, g[tag + ".bwd.p"], rtol=2e-3, atol=1e-6)
+    Lx, Lv, px, xout, acc = dyn.propose(x, vf, vb, g[tag + ".dir_mask"], g[tag + ".u_acc"])
+    close(Lx, g[tag + ".propose.Lx"], rtol=1e-5, atol=2e-5); close(px, g[tag + ".propose.px"], rtol=2e-3, atol=1e-6)
+    assert np.array_equal(acc.numpy(), (g[tag + ".propose.px"] - g[tag + ".u_acc"]) >= 0)
+    close(xout, g[tag + ".propose.x_out"], rtol=1e-5, atol=2e-5)
+
+
+def test_mog_step_reversibility_and_tunneling_rate():
+    from oracle import mog_oracle as mog
+    rng = np.random.default_rng(2)
+    target = mog.GMMTarget.from_params([[1., 0.], [-1., 0.]], [0.05 * np.eye(2)] * 2, [0.5, 0.5], torch.float64)
+    xw, vw = mog.init_mog_net(2, 2., rng), mog.init_mog_net(2, 1., rng)
+    for w in (xw, vw):
+        for k in ("scale_layer", "translation_layer", "transformation_layer"):
+            w[k + ".kernel"] *= 100
+    dyn = mog.OracleMogDynamics(target, 2, 3, 0.1, xnet=xw, vnet=vw, dtype=torch.float64)
+    x = torch.as_tensor(rng.standard_normal((6, 2)) * 0.3 + np.array([1., 0.]))
+    v = torch.as_tensor(rng.standard_normal((6, 2)))
+    for k in range(3):
+        x1, v1, lj = dyn.forward_step(x, v, k)
+        x2, v2, ljb = dyn.backward_step(x1, v1, k)
+        close(x2, x, rtol=1e-9, atol=1e-9); close(v2, v, rtol=1e-9, atol=1e-9); close(ljb, -lj, rtol=1e-9, atol=1e-9)
+    traj = np.zeros((5, 2, 2))
+    traj[:, 0, 0] = [1, -1, -1, 1, 1]        # three switches in four steps
+    traj[:, 1, 0] = [1, 1, 1, 1, 1]
+    assert np.allclose(mog.calc_tunneling_rate(traj, [[1., 0.], [-1., 0.]], 2), [0.5, 0.0])
