@@ -269,6 +269,62 @@ int l2hmc_conv3d_num_features(int T, int X, int F);
 int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float* in, const float* mask, int mask_invert,
                           int N, int T, int X, float* feat, void* stream);
 
+/* ------------------------------------------------------------------ MoG / generic-target path (config 5)
+ * Gaussian-mixture target of utils/distributions.py:124-158:
+ *     E(x) = -logsumexp_i( -0.5 (x-mu_i)^T S_i (x-mu_i) + log c_i ) / temperature
+ * computed row-wise (the reference forms an N x N product and takes its diagonal, :32-39).
+ * mus [m,k], i_sigmas [m,k,k] (= inv(sigma_i)), log_consts [m] (= log(pi_i / sqrt((2pi)^k det sigma_i))),
+ * all device fp32.  k <= 8, m <= 16. */
+typedef struct {
+  int k, m;
+  const float* mus;
+  const float* i_sigmas;
+  const float* log_consts;
+} l2hmc_gmm;
+
+/* energy [N] and force = dE/dx [N,k] (each nullable): Dynamics.energy / grad_energy
+ * (utils/dynamics.py:227-242). */
+int l2hmc_gmm_energy_force(const l2hmc_gmm* gmm, const float* x, float temperature, int N, float* energy,
+                           float* force, void* stream);
+
+/* One MC step of the MoG sampler in ONE launch, one thread per chain, both networks' weights in
+ * shared memory: utils/sampler.py:28-59 propose(do_mh_step=True) over
+ * Dynamics.forward / backward (utils/dynamics.py:120-319), integrating only the direction each
+ * chain selects.  Nets are utils/network.py:89-114 (tanh on both S and F heads): pass
+ * l2hmc_net_weights with K = D = k, H <= 64, tanh_on_q = 1 (xnet / vnet NULL when hmc != 0).
+ *   v_f / v_b [N,k]: momentum draws of forward / backward (v_b NULL -> v_f); v_f NULL -> Philox
+ *   dir_mask [N]: 1 = forward, 0 = backward (the reference's random {0,1} mask); NULL -> Philox
+ *                 uniform >= 0.5, or all forward when momenta are injected; ignored (forward) for hmc
+ *   u_acc [N]: accept if p - u >= 0; NULL -> Philox when v_f is NULL, else no accept step
+ *   mask [L,k]: Dynamics.mask (:85-100)
+ * outputs (each nullable): Lx, Lv [N,k], px [N], x_out [N,k], accepted [N] uint8, mode [N] int32 =
+ * index of the mixture mean nearest to x_out (utils/trajectories.py:39-60, for the tunneling rate). */
+typedef struct {
+  const float* x;
+  const float* v_f;
+  const float* v_b;
+  const float* dir_mask;
+  const float* u_acc;
+  const float* mask;
+  float eps;
+  float temperature;
+  int L;
+  int hmc;
+  int N;
+  uint64_t seed, mc_step, chain0;
+  const l2hmc_net_weights* xnet;
+  const l2hmc_net_weights* vnet;
+  float* Lx;
+  float* Lv;
+  float* px;
+  float* x_out;
+  uint8_t* accepted;
+  int32_t* mode;
+  int32_t* nonfinite_flag;
+} l2hmc_mog_args;
+
+int l2hmc_mog_mc_step(const l2hmc_gmm* gmm, const l2hmc_mog_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

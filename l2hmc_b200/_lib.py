@@ -59,6 +59,23 @@ class Conv3dWeights(Structure):
     _fields_ = [("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p), ("F", c_int)]
 
 
+class Gmm(Structure):
+    """l2hmc_gmm (include/l2hmc_b200.h)."""
+    _fields_ = [("k", c_int), ("m", c_int), ("mus", c_void_p), ("i_sigmas", c_void_p), ("log_consts", c_void_p)]
+
+
+class MogArgs(Structure):
+    """l2hmc_mog_args (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("x", c_void_p), ("v_f", c_void_p), ("v_b", c_void_p), ("dir_mask", c_void_p), ("u_acc", c_void_p),
+        ("mask", c_void_p), ("eps", c_float), ("temperature", c_float), ("L", c_int), ("hmc", c_int), ("N", c_int),
+        ("seed", c_uint64), ("mc_step", c_uint64), ("chain0", c_uint64),
+        ("xnet", POINTER(NetWeights)), ("vnet", POINTER(NetWeights)),
+        ("Lx", c_void_p), ("Lv", c_void_p), ("px", c_void_p), ("x_out", c_void_p), ("accepted", c_void_p),
+        ("mode", c_void_p), ("nonfinite_flag", c_void_p),
+    ]
+
+
 NET_STQ, NET_MOMENTUM, NET_POSITION = 0, 1, 2
 NET_PATH_AUTO, NET_PATH_FFMA, NET_PATH_TCGEN05 = 0, 1, 2
 
@@ -88,6 +105,8 @@ SIGNATURES = {
     "l2hmc_net_pack": [POINTER(NetWeights), c_void_p, c_size_t, c_void_p],
     "l2hmc_tc_selftest_bytes": [c_int, c_int, c_int],
     "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_gmm_energy_force": [POINTER(Gmm), c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_mog_mc_step": [POINTER(Gmm), POINTER(MogArgs), c_void_p],
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],
