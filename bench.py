@@ -368,7 +368,35 @@ def run_l2hmc(r, steps):
         out[tag] = entry
         del dyn, net, x, v
         torch.cuda.empty_cache()
+    out["config5_mog"] = run_mog(c, events_ms, steps)
     return out
+
+
+def run_mog(c, events_ms, steps):
+    """BASELINE config 5: two-mode Gaussian mixture, k = 2, M = 2 leapfrog steps, H = 50, 2^20 chains
+    per GPU; one launch of mog_mc_kernel = one MC step (both nets evaluated in shared memory)."""
+    import numpy as np
+    from l2hmc_b200 import mog
+    torch, dev, world = c["torch"], c["dev"], c["world"]
+    N, k, L, H = 1 << 20, 2, 2, 50
+    gmm = mog.GMM([[1., 0.], [-1., 0.]], [0.05 * np.eye(2)] * 2, [0.5, 0.5], device=dev)
+    np.random.seed(42)
+    dyn = mog.Dynamics(k, gmm, trajectory_length=L, eps=0.1, seed=11, device=dev,
+                       chain_offset=c["dyn"].chain_offset // 32 * 512,
+                       net_factory=lambda d, scope, factor: mog.network(d, scope, factor, num_nodes=H, device=dev))
+    gen = torch.Generator(device=dev).manual_seed(3)
+    x = [torch.randn(N, k, device=dev, generator=gen) * 0.2 + torch.tensor([1.0, 0.0], device=dev)]
+
+    def mc():
+        x[0] = dyn.mc_step(x[0])["x_out"]
+    ms = events_ms(mc, max(5, steps))
+    # per chain per step: 3 V-net + 2 X-net calls per LF step, each 2(kH + kH + 2H + HH + 3Hk) flops
+    flop = N * L * 5 * 2.0 * (2 * k * H + 2 * H + H * H + 3 * H * k)
+    return {"chains_per_gpu": N, "k": k, "lf_steps": L, "H": H, "mc_step_ms": ms,
+            "chain_updates_per_s": world * N / (ms * 1e-3), "lf_steps_per_s": world * N * L / (ms * 1e-3),
+            "ffma_tflops": flop / ms / 1e9,
+            "algorithmic_bytes": N * (4 * k * 4 + 4 + 1 + 4), "hbm_gbs": N * (4 * k * 4 + 9) / ms / 1e6,
+            "note": "compute-bound: 50x50 hidden layer per net call per chain on the FFMA pipe, nets in shared memory"}
 
 
 def main():
