@@ -154,6 +154,181 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Register-tiled variant for F in {8, 16, 32} (F = X for the lattices of BASELINE configs 2-4):
+// kChains chains per CTA pass.
+//   phase 1: a thread keeps the 18 taps of ITS filter f = tid % F in registers for the whole kernel
+//            and computes two neighbouring pooled outputs from one 4x6 input patch
+//            (24 LDS.64 per 216 FFMA).
+//   phase 2: a thread owns one pooled output position x four output channels: per block of four
+//            input filters it reads the 3x3 P1 patch as float4 over f (9 LDS.128) and the weights as
+//            float4 over c (16 LDS.128) for 256 FFMA; the P1 rows are padded to F + 4 floats so the
+//            four positions a warp reads side by side fall into different banks.
+// The arithmetic per output (tap order, bias after max, relu last) is the generic kernel's.
+constexpr int kChains = 2;
+
+template <int F>
+__global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams p) {
+  extern __shared__ __align__(16) float sm[];
+  constexpr int C = 2 * F, FP = F + 4, CG = C / 4, G = kThreads / F;
+  const int T = p.T, X = p.X;
+  const int T1 = (T + 1) / 2, X1 = (X + 1) / 2, T2 = (T1 + 1) / 2, X2 = (X1 + 1) / 2;
+  const int D = 2 * T * X, Dp = (D + 3) & ~3, P1 = T1 * X1 * FP;
+  float* s_w2 = sm;                        // [4][F][C]   (kd = 0 taps only)
+  float* s_b2 = s_w2 + 4 * F * C;          // [C]
+  float* s_in = s_b2 + C;                  // [kChains][Dp]
+  float* s_p1 = s_in + kChains * Dp;       // [kChains][T1*X1][FP]
+  const int tid = threadIdx.x;
+
+  for (int i = tid; i < 4 * F * C; i += kThreads) {
+    const int tap = i / (F * C), rest = i % (F * C);
+    s_w2[i] = p.w2[static_cast<size_t>(tap) * 2 * F * C + rest];
+  }
+  for (int i = tid; i < C; i += kThreads) s_b2[i] = p.b2[i];
+  const int f = tid % F, grp = tid / F;
+  float w[3][3][2];
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int b = 0; b < 3; ++b) {
+      w[a][b][0] = p.w1[((a * 3 + b) * 2 + 0) * F + f];
+      w[a][b][1] = p.w1[((a * 3 + b) * 2 + 1) * F + f];
+    }
+  const float bias1 = p.b1[f];
+  const int XP = (X1 + 1) / 2;             // pairs of pooled columns
+
+  for (int n0 = blockIdx.x * kChains; n0 < p.N; n0 += gridDim.x * kChains) {
+    const int nch = min(kChains, p.N - n0);
+    __syncthreads();
+    for (int i = tid; i < nch * D; i += kThreads) {
+      const int ch = i / D, j = i - ch * D;
+      float a = p.in[static_cast<size_t>(n0 + ch) * D + j];
+      if (p.mask) {
+        const float m = p.mask[j];
+        a = __fmul_rn(p.invert ? __fsub_rn(1.f, m) : m, a);
+      }
+      s_in[ch * Dp + j] = a;
+    }
+    __syncthreads();
+
+    // ---- phase 1
+    for (int item = grp; item < nch * T1 * XP; item += G) {
+      const int xp = item % XP, rest = item / XP, t1 = rest % T1, ch = rest / T1;
+      const float* in_c = s_in + ch * Dp;
+      float in[4][6][2];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 6; ++b) {
+          const int t = 2 * t1 - 1 + a, x = 4 * xp - 1 + b;
+          const bool ok = t >= 0 && t < T && x >= 0 && x < X;
+          const float2 u = ok ? *reinterpret_cast<const float2*>(&in_c[(t * X + x) * 2]) : make_float2(0.f, 0.f);
+          in[a][b][0] = u.x, in[a][b][1] = u.y;
+        }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int x1 = 2 * xp + h;
+        if (x1 >= X1) break;
+        float best = -INFINITY;
+#pragma unroll
+        for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx) {
+            if (2 * t1 + dt >= T || 2 * x1 + dx >= X) continue;
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+            for (int a = 0; a < 3; ++a)
+#pragma unroll
+              for (int b = 0; b < 3; ++b) {
+                s0 = fmaf(in[dt + a][2 * h + dx + b][0], w[a][b][0], s0);
+                s0 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][1], s0);
+                s1 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][0], s1);
+              }
+            best = fmaxf(best, fmaxf(s0, s1));
+          }
+        s_p1[ch * P1 + (t1 * X1 + x1) * FP + f] = fmaxf(__fadd_rn(best, bias1), 0.f);
+      }
+    }
+    __syncthreads();
+
+    // ---- phase 2
+    const int cg = tid % CG;
+    for (int item = tid / CG; item < nch * T2 * X2; item += kThreads / CG) {
+      const int x2 = item % X2, rest = item / X2, t2 = rest % T2, ch = rest / T2;
+      const float* p1 = s_p1 + ch * P1;
+      const int tb = 2 * t2, xb = 2 * x2;
+      float acc[2][2][4];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) (&acc[0][0][0])[i] = 0.f;
+#pragma unroll 1
+      for (int f4 = 0; f4 < F; f4 += 4) {
+        float4 pp[3][3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+          for (int b = 0; b < 3; ++b) {
+            const int t = tb + a, x = xb + b;
+            pp[a][b] = (t < T1 && x < X1) ? *reinterpret_cast<const float4*>(&p1[(t * X1 + x) * FP + f4])
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+        for (int fi = 0; fi < 4; ++fi) {
+          float4 wt[4];
+#pragma unroll
+          for (int tap = 0; tap < 4; ++tap)
+            wt[tap] = *reinterpret_cast<const float4*>(&s_w2[(tap * F + f4 + fi) * C + 4 * cg]);
+#pragma unroll
+          for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+              for (int tap = 0; tap < 4; ++tap) {
+                const float4 q = pp[dt + (tap >> 1)][dx + (tap & 1)];
+                const float a = fi == 0 ? q.x : fi == 1 ? q.y : fi == 2 ? q.z : q.w;
+                acc[dt][dx][0] = fmaf(a, wt[tap].x, acc[dt][dx][0]);
+                acc[dt][dx][1] = fmaf(a, wt[tap].y, acc[dt][dx][1]);
+                acc[dt][dx][2] = fmaf(a, wt[tap].z, acc[dt][dx][2]);
+                acc[dt][dx][3] = fmaf(a, wt[tap].w, acc[dt][dx][3]);
+              }
+        }
+      }
+      float o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float best = -INFINITY;
+#pragma unroll
+        for (int dt = 0; dt < 2; ++dt)
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx)
+            if (tb + dt < T1 && xb + dx < X1) best = fmaxf(best, acc[dt][dx][j]);
+        o[j] = fmaxf(__fadd_rn(best, s_b2[4 * cg + j]), 0.f);
+      }
+      float* dst = p.feat + static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
+      *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+template <int F>
+int launch_tiled(const ConvParams& p, int sms, int max_smem, cudaStream_t stream) {
+  const int T1 = (p.T + 1) / 2, X1 = (p.X + 1) / 2, D = 2 * p.T * p.X;
+  const size_t smem = sizeof(float) * (4 * F * 2 * F + 2 * F + kChains * ((D + 3) & ~3) + kChains * T1 * X1 * (F + 4));
+  if (smem > static_cast<size_t>(max_smem)) return -1;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(conv3d_tiled_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(conv3d_tiled_kernel): %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+  }
+  int per_sm = max(1, min(static_cast<int>((200 * 1024) / (smem + 1024)), 2));
+  const int grid = max(1, min((p.N + kChains - 1) / kChains, sms * per_sm));
+  conv3d_tiled_kernel<F><<<grid, kThreads, smem, stream>>>(p);
+  return check_launch("conv3d_tiled_kernel");
+}
+
 }  // namespace
 }  // namespace l2hmc
 
@@ -177,6 +352,12 @@ extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float*
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, N, T, X, F, feat};
+  int rc = -1;
+  if (F == 8) rc = launch_tiled<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+  else if (F == 16) rc = launch_tiled<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+  else if (F == 32) rc = launch_tiled<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+  if (rc >= 0) return rc;                 // -1: not covered by the tiled kernel, use the generic one
   if (smem > static_cast<size_t>(max_smem)) {
     set_error("l2hmc_conv3d_features: %dx%d lattice with F=%d needs %zu B of shared memory (limit %d)", T, X, F, smem,
               max_smem);
@@ -193,7 +374,6 @@ extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float*
   int per_sm = static_cast<int>((200 * 1024) / (smem + 1024));
   per_sm = max(1, min(per_sm, 8));
   const int grid = max(1, min(N, sms * per_sm));
-  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, N, T, X, F, feat};
   conv3d_kernel<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_launch("conv3d_kernel");
 }

@@ -61,6 +61,13 @@ __device__ __forceinline__ float fast_sin(float x) {
   return sin_poly(sin_reduce(x).r);
 }
 
+__device__ __forceinline__ float fast_cos(float x) {
+  if (__builtin_expect(fabsf(x) > 40000.f, 0)) return cosf(x);
+  const SinReduce q = sin_reduce(x);
+  const float c = cos_poly(q.a);
+  return q.fold ? -c : c;
+}
+
 __device__ __forceinline__ void fast_sincos(float x, float* sn, float* cs) {
   if (__builtin_expect(fabsf(x) > 40000.f, 0)) {
     sincosf(x, sn, cs);

@@ -13,6 +13,7 @@
 // lane-strided partials closed by a shuffle tree (deterministic).  Only __syncwarp is needed.
 // HBM traffic: 4 B/link read (+ 4 B/link written when the force is requested).
 #include "common.cuh"
+#include "fast_sin.cuh"
 
 namespace l2hmc {
 namespace {
@@ -53,14 +54,14 @@ __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int
           __fadd_rn(__fsub_rn(__fsub_rn(sx[2 * s], sx[2 * s + 1]), sx[2 * sr]), sx[2 * sd + 1]);
       if (want_force && want_cos) {
         float sn, cs;
-        sincosf(P, &sn, &cs);
+        fast_sincos(P, &sn, &cs);
         sb[s] = __fmul_rn(p.beta, sn);
         act = __fadd_rn(act, __fsub_rn(1.f, cs));
         csum = __fadd_rn(csum, cs);
       } else if (want_force) {
-        sb[s] = __fmul_rn(p.beta, sinf(P));
+        sb[s] = __fmul_rn(p.beta, fast_sin(P));
       } else if (want_cos) {
-        const float cs = cosf(P);
+        const float cs = fast_cos(P);
         act = __fadd_rn(act, __fsub_rn(1.f, cs));
         csum = __fadd_rn(csum, cs);
       }
@@ -103,6 +104,121 @@ __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int
   }
 }
 
+
+// Register-resident variant for X in {8, 16, 32} and T*X = 32*I sites: a warp holds one chain in
+// registers (lane l owns sites l, l+32, ...: row i*(32/X) + l/X, column l%X), all 2*I float2 loads of
+// a chain are in flight at once, neighbours come from warp shuffles (x +- 1) and the adjacent
+// register (t +- 1; a second shuffle when a warp pass spans several rows).  No shared memory, so
+// occupancy is set by registers alone.  Summation order is the generic kernel's (lane-strided
+// partials, then the shuffle tree), hence bit-identical results.
+template <int X, int I, bool FORCE, bool COS, bool QSUM, bool HAMIL>
+__global__ void __launch_bounds__(256) stencil_reg_kernel(const StencilParams p) {
+  constexpr int SITES = 32 * I, D = 2 * SITES;
+  constexpr unsigned kFull = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int warps = (blockDim.x >> 5) * gridDim.x;
+  const int right = (lane & ~(X - 1)) | ((lane + 1) & (X - 1));
+  const int left = (lane & ~(X - 1)) | ((lane - 1) & (X - 1));
+  const int down = (lane + X) & 31, up = (lane - X) & 31;
+  const bool down_wraps = lane + X >= 32, up_wraps = lane < X;   // neighbour row lives in register i+1 / i-1
+  for (int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); n < p.N; n += warps) {
+    const float2* gx = reinterpret_cast<const float2*>(p.x + static_cast<size_t>(n) * D);
+    float2 u[I];
+#pragma unroll
+    for (int i = 0; i < I; ++i) u[i] = __ldcs(gx + lane + 32 * i);
+    float ke = 0.f;
+    if (HAMIL) {
+      const float2* gv = reinterpret_cast<const float2*>(p.v + static_cast<size_t>(n) * D);
+      float2 w[I];
+#pragma unroll
+      for (int i = 0; i < I; ++i) w[i] = __ldcs(gv + lane + 32 * i);
+#pragma unroll
+      for (int i = 0; i < I; ++i)
+        ke = __fadd_rn(ke, __fadd_rn(__fmul_rn(w[i].x, w[i].x), __fmul_rn(w[i].y, w[i].y)));
+    }
+    float b[FORCE ? I : 1];
+    float act = 0.f, csum = 0.f, qsum = 0.f;
+#pragma unroll
+    for (int i = 0; i < I; ++i) {
+      const int in = (i + 1 == I) ? 0 : i + 1;
+      const float xr = __shfl_sync(kFull, u[i].x, right);              // x0 at (t, x+1)
+      float yd;                                                        // x1 at (t+1, x)
+      if (X == 32) {
+        yd = u[in].y;
+      } else {
+        const float same = __shfl_sync(kFull, u[i].y, down), next = __shfl_sync(kFull, u[in].y, down);
+        yd = down_wraps ? next : same;
+      }
+      const float P = __fadd_rn(__fsub_rn(__fsub_rn(u[i].x, u[i].y), xr), yd);
+      if (FORCE && COS) {
+        float sn, cs;
+        fast_sincos(P, &sn, &cs);
+        b[i] = __fmul_rn(p.beta, sn);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+      } else if (FORCE) {
+        b[i] = __fmul_rn(p.beta, fast_sin(P));
+      } else if (COS) {
+        const float cs = fast_cos(P);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+      }
+      if (QSUM) qsum = __fadd_rn(qsum, project_angle(P));
+    }
+    if (FORCE) {
+      float2* gf = reinterpret_cast<float2*>(p.force + static_cast<size_t>(n) * D);
+#pragma unroll
+      for (int i = 0; i < I; ++i) {
+        const int ip = (i == 0) ? I - 1 : i - 1;
+        const float bl = __shfl_sync(kFull, b[i], left);               // b at (t, x-1)
+        float bu;                                                      // b at (t-1, x)
+        if (X == 32) {
+          bu = b[ip];
+        } else {
+          const float same = __shfl_sync(kFull, b[i], up), prev = __shfl_sync(kFull, b[ip], up);
+          bu = up_wraps ? prev : same;
+        }
+        __stcs(gf + lane + 32 * i, make_float2(__fsub_rn(b[i], bl), __fsub_rn(bu, b[i])));
+      }
+    }
+    if (COS) {
+      act = warp_sum(act);
+      csum = warp_sum(csum);
+    }
+    if (QSUM) qsum = warp_sum(qsum);
+    if (HAMIL) {
+      ke = warp_sum(ke);
+      if (lane == 0) p.hamil[n] = __fadd_rn(__fmul_rn(p.beta, act), __fmul_rn(0.5f, ke));
+    }
+    if (lane == 0) {
+      if (p.action) p.action[n] = act;
+      if (p.avg_plaq) p.avg_plaq[n] = __fdiv_rn(csum, static_cast<float>(SITES));
+      if (QSUM) {
+        const float qf = __fdiv_rn(qsum, kTwoPi);
+        if (p.q_float) p.q_float[n] = qf;
+        if (p.q_int) p.q_int[n] = static_cast<int32_t>(floorf(__fadd_rn(0.1f, qf)));
+      }
+    }
+  }
+}
+
+template <int X, int I>
+bool launch_reg(const StencilParams& p, int sms, cudaStream_t stream) {
+  const bool force = p.force != nullptr, hamil = p.hamil != nullptr;
+  const bool cosv = p.action != nullptr || p.avg_plaq != nullptr || hamil;
+  const bool q = p.q_float != nullptr || p.q_int != nullptr;
+  const int blocks = min((p.N + 7) / 8, sms * 16);
+  // the combinations the API can ask for: force [+ action]; action / plaq / Q observables; Hamiltonian
+  if (force && cosv && !q && !hamil) stencil_reg_kernel<X, I, true, true, false, false><<<blocks, 256, 0, stream>>>(p);
+  else if (force && !cosv && !q) stencil_reg_kernel<X, I, true, false, false, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && cosv && !q && !hamil) stencil_reg_kernel<X, I, false, true, false, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && cosv && q && !hamil) stencil_reg_kernel<X, I, false, true, true, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && !cosv && q) stencil_reg_kernel<X, I, false, false, true, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && hamil && !q) stencil_reg_kernel<X, I, false, true, false, true><<<blocks, 256, 0, stream>>>(p);
+  else return false;
+  return true;
+}
+
 int launch_stencil(const StencilParams& p, cudaStream_t stream) {
   if (p.N == 0) return L2HMC_OK;
   const size_t per_warp = sizeof(float) * ((3u * p.T * p.X + 1u) & ~1u);
@@ -110,6 +226,11 @@ int launch_stencil(const StencilParams& p, cudaStream_t stream) {
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  bool done = false;
+  if (p.T == 32 && p.X == 32) done = launch_reg<32, 32>(p, sms, stream);
+  else if (p.T == 16 && p.X == 16) done = launch_reg<16, 8>(p, sms, stream);
+  else if (p.T == 8 && p.X == 8) done = launch_reg<8, 2>(p, sms, stream);
+  if (done) return check_launch("stencil_reg_kernel");
   int warps = 8;
   while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
   const size_t smem = per_warp * warps;

@@ -144,15 +144,21 @@ __global__ void accept_prob_kernel(const float* __restrict__ h_old, const float*
   p[n] = prob;
 }
 
+template <int VEC> struct RawVec { using type = float; };
+template <> struct RawVec<4> { using type = float4; };
+
+// VEC = 4: D % 4 == 0 and 16-byte aligned arrays (every lattice here), one float4 per lane per pass.
+template <int VEC>
 __global__ void __launch_bounds__(kWarps * 32) mh_select_kernel(
     const float* __restrict__ x, const float* __restrict__ x_f, const float* __restrict__ x_b,
     const float* __restrict__ v_f, const float* __restrict__ v_b, const float* __restrict__ p_f,
     const float* __restrict__ p_b, const float* __restrict__ u_dir, const float* __restrict__ u_acc, int N, int D,
     int wrap, float* x_post, float* v_post, float* p, float* x_out, uint8_t* accepted) {
+  struct alignas(4 * VEC) Vec { float e[VEC]; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool both = x_b != nullptr;
   for (int n = blockIdx.x * kWarps + warp; n < N; n += gridDim.x * kWarps) {
     const size_t base = static_cast<size_t>(n) * D;
-    const bool both = x_b != nullptr;
     const float fm = (both && u_dir) ? (u_dir[n] > 0.5f ? 1.f : 0.f) : 1.f;
     const float bm = __fsub_rn(1.f, fm);
     float prob = p_f[n];
@@ -163,19 +169,41 @@ __global__ void __launch_bounds__(kWarps * 32) mh_select_kernel(
       if (p) p[n] = prob;
       if (accepted) accepted[n] = am != 0.f;
     }
-    for (int i = lane; i < D; i += 32) {
-      float xp = x_f[base + i];
-      if (both) xp = __fadd_rn(__fmul_rn(fm, xp), __fmul_rn(bm, x_b[base + i]));
-      if (x_post) x_post[base + i] = xp;
+    using Raw = typename RawVec<VEC>::type;
+    auto ld = [&](const float* a, int i) {
+      const Raw r = __ldcs(reinterpret_cast<const Raw*>(a + base + i));
+      return *reinterpret_cast<const Vec*>(&r);
+    };
+    auto st = [&](float* a, int i, const Vec& w) {
+      __stcs(reinterpret_cast<Raw*>(a + base + i), *reinterpret_cast<const Raw*>(&w));
+    };
+#pragma unroll 2
+    for (int i = lane * VEC; i < D; i += 32 * VEC) {
+      Vec xp = ld(x_f, i);
+      if (both) {
+        const Vec xb = ld(x_b, i);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) xp.e[j] = __fadd_rn(__fmul_rn(fm, xp.e[j]), __fmul_rn(bm, xb.e[j]));
+      }
+      if (x_post) st(x_post, i, xp);
       if (v_post) {
-        float vp = v_f[base + i];
-        if (both) vp = __fadd_rn(__fmul_rn(fm, vp), __fmul_rn(bm, v_b[base + i]));
-        v_post[base + i] = vp;
+        Vec vp = ld(v_f, i);
+        if (both) {
+          const Vec vb = ld(v_b, i);
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) vp.e[j] = __fadd_rn(__fmul_rn(fm, vp.e[j]), __fmul_rn(bm, vb.e[j]));
+        }
+        st(v_post, i, vp);
       }
       if (x_out) {
-        float o = __fadd_rn(__fmul_rn(am, xp), __fmul_rn(rm, x[base + i]));
-        if (wrap) o = wrap_2pi(o);
-        x_out[base + i] = o;
+        const Vec x0 = ld(x, i);
+        Vec o;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          o.e[j] = __fadd_rn(__fmul_rn(am, xp.e[j]), __fmul_rn(rm, x0.e[j]));
+          if (wrap) o.e[j] = wrap_2pi(o.e[j]);
+        }
+        st(x_out, i, o);
       }
     }
   }
@@ -305,8 +333,15 @@ extern "C" int l2hmc_mh_select(const float* x, const float* x_f, const float* x_
   L2HMC_REQUIRE(!x_b || (p_b && (!v_post || v_b)), "l2hmc_mh_select: backward arrays must be given together");
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_mh_select: bad sizes");
   if (N == 0) return L2HMC_OK;
-  mh_select_kernel<<<chain_grid(N), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, wrap_2pi, x_post, v_post, p, x_out, accepted);
+  const auto misaligned = [](const void* a) { return (reinterpret_cast<uintptr_t>(a) & 15u) != 0; };
+  const bool vec4 = D % 4 == 0 && !(misaligned(x) || misaligned(x_f) || misaligned(x_b) || misaligned(v_f) ||
+                                    misaligned(v_b) || misaligned(x_post) || misaligned(v_post) || misaligned(x_out));
+  if (vec4)
+    mh_select_kernel<4><<<chain_grid(N), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, wrap_2pi, x_post, v_post, p, x_out, accepted);
+  else
+    mh_select_kernel<1><<<chain_grid(N), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
+        x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, wrap_2pi, x_post, v_post, p, x_out, accepted);
   return check_launch("mh_select_kernel");
 }
 

@@ -255,3 +255,32 @@ def test_tc_path_refuses_small_shapes(pkg):
     net.path = _lib.NET_PATH_TCGEN05
     with pytest.raises(_lib.L2hmcError, match="no tcgen05 path"):
         net([np.zeros((5, 32), np.float32), np.zeros((5, 32), np.float32), (1.0, 0.0)])
+
+
+@pytest.mark.parametrize("T,X,F,N", [(16, 16, 16, 67), (8, 8, 8, 3), (7, 9, 8, 5), (32, 32, 32, 6), (5, 6, 16, 4),
+                                     (6, 10, 10, 9), (4, 4, 4, 2), (16, 16, 16, 1)])
+def test_conv3d_features_against_oracle(T, X, F, N):
+    """l2hmc_conv3d_features (register-tiled kernel for F in {8,16,32}, generic otherwise) against the oracle's
+    Conv3D/MaxPool3D 'same' stack (network/conv_net.py:247-260), with and without the mask on load."""
+    from l2hmc_b200 import _lib
+    rng = np.random.default_rng(T * 100 + X + F)
+    w1 = rng.normal(0, 0.4, (3, 3, 2, 1, F)).astype(np.float32)
+    w2 = rng.normal(0, 0.2, (2, 2, 2, F, 2 * F)).astype(np.float32)
+    b1, b2 = rng.normal(0, 0.1, F).astype(np.float32), rng.normal(0, 0.1, 2 * F).astype(np.float32)
+    x = rng.uniform(0, 2 * np.pi, (N, 2 * T * X)).astype(np.float32)
+    mask = (rng.uniform(size=2 * T * X) > 0.5).astype(np.float32)
+    dev = [torch.as_tensor(a).cuda().contiguous() for a in (w1, b1, w2, b2, x, mask)]
+    c = _lib.Conv3dWeights()
+    c.w1, c.b1, c.w2, c.b2, c.F = _lib.dptr(dev[0]), _lib.dptr(dev[1]), _lib.dptr(dev[2]), _lib.dptr(dev[3]), F
+    lib = _lib.get_lib()
+    nf = lib.l2hmc_conv3d_num_features(T, X, F)
+    for m, inv in ((None, 0), (dev[5], 0), (dev[5], 1)):
+        out = torch.full((N, nf), float("nan"), device="cuda")
+        _lib.check(lib.l2hmc_conv3d_features(c, _lib.dptr(dev[4]), _lib.dptr(m), inv, N, T, X, _lib.dptr(out), None))
+        xin = torch.as_tensor(x) if m is None else torch.as_tensor(x * (1 - mask if inv else mask))
+        ref = xin.reshape(N, T, X, 2, 1)
+        ref = orc._maxpool3d_same(orc._conv3d_same_relu(ref, torch.as_tensor(w1), torch.as_tensor(b1)))
+        ref = orc._maxpool3d_same(orc._conv3d_same_relu(ref, torch.as_tensor(w2), torch.as_tensor(b2)))
+        ref = ref.reshape(N, -1)
+        assert ref.shape[1] == nf
+        close(out, ref, rtol=1e-5, atol=3e-5)
