@@ -232,6 +232,17 @@ typedef struct {
   void* workspace;       /* >= l2hmc_net_workspace_bytes(...) bytes of device memory */
   size_t workspace_bytes;
   int path;              /* L2HMC_NET_PATH_*: AUTO picks tcgen05 when the shapes are dense contractions */
+  /* Mixed-direction batches.  The reference integrates every chain forward AND backward and blends
+     the two with exact 0/1 masks (dynamics/gauge_dynamics.py:211-241); here a chain runs only the
+     direction it selected, and both kinds share one launch: row_set[n] in {0,1} picks, per chain,
+     between the fields above (0) and the *_alt fields (1).  NULL: every chain uses set 0. */
+  const uint8_t* row_set;      /* nullable [N] */
+  float tau_cos_alt, tau_sin_alt;
+  const float* in1_mask_alt;   /* nullable [K] */
+  int in1_mask_invert_alt;
+  int dir_alt;                 /* +1 / -1 */
+  const float* mask_alt;       /* POSITION: mask row [D] */
+  int mask_invert_alt;
 } l2hmc_net_call;
 
 #define L2HMC_NET_PATH_AUTO 0
@@ -268,6 +279,11 @@ typedef struct {
 int l2hmc_conv3d_num_features(int T, int X, int F);
 int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float* in, const float* mask, int mask_invert,
                           int N, int T, int X, float* feat, void* stream);
+/* Same, for mixed-direction batches: chain n uses (mask_alt, mask_invert_alt) when row_set[n] != 0
+ * (see l2hmc_net_call.row_set); row_set == NULL is l2hmc_conv3d_features. */
+int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const float* in, const float* mask, int mask_invert,
+                               const float* mask_alt, int mask_invert_alt, const uint8_t* row_set, int N, int T,
+                               int X, float* feat, void* stream);
 
 /* ------------------------------------------------------------------ MoG / generic-target path (config 5)
  * Gaussian-mixture target of utils/distributions.py:124-158:

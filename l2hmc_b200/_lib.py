@@ -51,6 +51,9 @@ class NetCall(Structure):
         ("x", c_void_p), ("v", c_void_p), ("g", c_void_p), ("mask", c_void_p), ("mask_invert", c_int),
         ("out", c_void_p), ("logdet", c_void_p), ("nonfinite_flag", c_void_p),
         ("workspace", c_void_p), ("workspace_bytes", c_size_t), ("path", c_int),
+        ("row_set", c_void_p), ("tau_cos_alt", c_float), ("tau_sin_alt", c_float),
+        ("in1_mask_alt", c_void_p), ("in1_mask_invert_alt", c_int), ("dir_alt", c_int),
+        ("mask_alt", c_void_p), ("mask_invert_alt", c_int),
     ]
 
 
@@ -110,6 +113,8 @@ SIGNATURES = {
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],
+    "l2hmc_conv3d_features_sets": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                                   c_int, c_int, c_int, c_void_p, c_void_p],
 }
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,

@@ -30,6 +30,9 @@ struct ConvParams {
   const float* in;   // [N][T][X][2]
   const float* mask; // nullable [T*X*2]
   int invert;
+  const float* mask_alt;     // chains with row_set[n] != 0 use this pair instead
+  int invert_alt;
+  const uint8_t* row_set;    // nullable [N]
   int N, T, X, F;
   float* feat;       // [N][T2*X2*2F]
 };
@@ -58,11 +61,14 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
   for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
     __syncthreads();   // previous chain's phase 2 done with s_p1 / s_in; weights visible on the first pass
     const float* src = p.in + static_cast<size_t>(n) * D;
+    const bool alt = p.row_set != nullptr && p.row_set[n] != 0;
+    const float* mask = alt ? p.mask_alt : p.mask;
+    const int invert = alt ? p.invert_alt : p.invert;
     for (int i = tid; i < D; i += kThreads) {
       float a = src[i];
-      if (p.mask) {
-        const float m = p.mask[i];
-        a = __fmul_rn(p.invert ? __fsub_rn(1.f, m) : m, a);
+      if (mask) {
+        const float m = mask[i];
+        a = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a);
       }
       s_in[i] = a;
     }
@@ -204,9 +210,11 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
     for (int i = tid; i < nch * D; i += kThreads) {
       const int ch = i / D, j = i - ch * D;
       float a = p.in[static_cast<size_t>(n0 + ch) * D + j];
-      if (p.mask) {
-        const float m = p.mask[j];
-        a = __fmul_rn(p.invert ? __fsub_rn(1.f, m) : m, a);
+      const bool alt = p.row_set != nullptr && p.row_set[n0 + ch] != 0;
+      const float* mask = alt ? p.mask_alt : p.mask;
+      if (mask) {
+        const float m = mask[j];
+        a = __fmul_rn((alt ? p.invert_alt : p.invert) ? __fsub_rn(1.f, m) : m, a);
       }
       s_in[ch * Dp + j] = a;
     }
@@ -341,6 +349,12 @@ extern "C" int l2hmc_conv3d_num_features(int T, int X, int F) {
 
 extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float* in, const float* mask,
                                      int mask_invert, int N, int T, int X, float* feat, void* stream) {
+  return l2hmc_conv3d_features_sets(w, in, mask, mask_invert, nullptr, 0, nullptr, N, T, X, feat, stream);
+}
+
+extern "C" int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const float* in, const float* mask,
+                                          int mask_invert, const float* mask_alt, int mask_invert_alt,
+                                          const uint8_t* row_set, int N, int T, int X, float* feat, void* stream) {
   L2HMC_REQUIRE(w, "l2hmc_conv3d_features: null weights");
   if (N == 0) return L2HMC_OK;
   L2HMC_REQUIRE(w->w1 && w->b1 && w->w2 && w->b2 && in && feat, "l2hmc_conv3d_features: null pointer");
@@ -352,7 +366,7 @@ extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float*
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, N, T, X, F, feat};
+  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, mask_alt, mask_invert_alt, row_set, N, T, X, F, feat};
   int rc = -1;
   if (F == 8) rc = launch_tiled<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
   else if (F == 16) rc = launch_tiled<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));

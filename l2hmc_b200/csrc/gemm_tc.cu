@@ -54,6 +54,8 @@ struct TcParams {
   int cols;            // valid outputs (H for layers, D per head)
   // layer epilogue
   const float* bias;   // [cols] effective bias
+  const float* bias_alt;   // rows with row_set != 0 (first layer of a mixed-direction batch)
+  const uint8_t* row_set;  // nullable [rows]
   float* out_ts;       // next layer's A operand (TS32), out_rg row groups, out_kb K blocks
   int out_rg, out_kb;
   // heads epilogue
@@ -71,8 +73,10 @@ struct TcParams {
   const float* ug;
   const float* umask;
   int uinvert;
+  const float* umask_alt;
+  int uinvert_alt;
   float eps;
-  int dir;
+  int dir, dir_alt;
   float* uout;
   float* ld_part;
   int32_t* flag;
@@ -269,8 +273,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
+      const bool alt = p.row_set != nullptr && r < p.rows && p.row_set[r] != 0;
       if (MODE == kTcLayer) {
         const int rg = r >> 3, r8 = r & 7;
+        const float* bias = alt ? p.bias_alt : p.bias;
 #pragma unroll
         for (int g = 0; g < NG; ++g) {
           const int kb = n_blk * (BN / 32) + half * (BN / 64) + g;     // K block of the NEXT layer
@@ -283,7 +289,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int n = n0 + kc * 4 + j;
-                const float b = n < p.cols ? __ldg(p.bias + n) : 0.f;
+                const float b = n < p.cols ? __ldg(bias + n) : 0.f;
                 const float o = fmaxf(__fadd_rn(sum[g][kc * 4 + j], b), 0.f);
                 h[j] = tf32_hi(o);
                 l[j] = tf32_lo(o, h[j]);
@@ -297,6 +303,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         // heads: sum[0] = S, sum[1] = T, sum[2] = Q pre-activations of d = 64*n_blk + 32*half + j
         const bool rok = r < p.rows;
         const float heps = __fmul_rn(0.5f, p.eps);
+        const int dir = alt ? p.dir_alt : p.dir;
+        const float* umask = alt ? p.umask_alt : p.umask;
+        const int uinvert = alt ? p.uinvert_alt : p.uinvert;
         float ld = 0.f;
         bool bad = false;
 #pragma unroll
@@ -330,13 +339,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
               if (MODE == kTcHeadsStq) {
                 o0[j] = S, o1[j] = Tr, o2[j] = Q;
               } else if (MODE == kTcHeadsMomentum) {
-                o0[j] = p.dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
-                                  : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
+                o0[j] = dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
+                                : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
               } else {
-                float m = __ldg(p.umask + d);
-                if (p.uinvert) m = __fsub_rn(1.f, m);
-                o0[j] = p.dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
-                                  : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
+                float m = __ldg(umask + d);
+                if (uinvert) m = __fsub_rn(1.f, m);
+                o0[j] = dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
+                                : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
               }
             }
 #pragma unroll
@@ -372,6 +381,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
 // [kb0, kb0 + ceil(K/32)) of a buffer with `rg_total` row groups; rows >= `rows` and k >= K are zero.
 __global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __restrict__ src, int ld, int rows, int K,
                                                                  const float* __restrict__ mask, int invert,
+                                                                 const float* __restrict__ mask_alt, int invert_alt,
+                                                                 const uint8_t* __restrict__ row_set,
                                                                  float* dst, int rg_total, int kb0, int nkb) {
   // one thread per (kb, rg, kc, r8): consecutive threads write consecutive 16 B
   const size_t total = static_cast<size_t>(nkb) * rg_total * 64;
@@ -391,11 +402,14 @@ __global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __
         for (int j = 0; j < 4; ++j)
           if (k + j < K) a[j] = s[j];
       }
-      if (mask) {
+      const bool alt = row_set != nullptr && row_set[r] != 0;
+      const float* mrow = alt ? mask_alt : mask;
+      if (mrow) {
+        const int inv = alt ? invert_alt : invert;
         for (int j = 0; j < 4; ++j)
           if (k + j < K) {
-            const float m = mask[k + j];
-            a[j] = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a[j]);
+            const float m = mrow[k + j];
+            a[j] = __fmul_rn(inv ? __fsub_rn(1.f, m) : m, a[j]);
           }
       }
     }
@@ -527,16 +541,20 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   float* h1 = acat + d.acat_floats;
   float* h2 = h1 + d.h_floats;
   float* bias_eff = h2 + d.h_floats;
-  float* ld_part = bias_eff + d.h_rows;
+  float* ld_part = bias_eff + 2 * d.h_rows;       // [2][h_rows]: second row for the *_alt time embedding
   const int rg = d.rows_p / 8;
 
   // network inputs -> TS32 (mask folded into the second input)
   ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
-      c->in0, K, N, K, nullptr, 0, acat, rg, 0, d.kbK);
+      c->in0, K, N, K, nullptr, 0, nullptr, 0, nullptr, acat, rg, 0, d.kbK);
   ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
-      c->in1, K, N, K, c->in1_mask, c->in1_mask_invert, acat, rg, d.kbK, d.kbK);
+      c->in1, K, N, K, c->in1_mask, c->in1_mask_invert, c->in1_mask_alt, c->in1_mask_invert_alt, c->row_set, acat, rg,
+      d.kbK, d.kbK);
   bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos, c->tau_sin, H,
                                                     bias_eff);
+  if (c->row_set)
+    bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos_alt, c->tau_sin_alt,
+                                                      H, bias_eff + d.h_rows);
   int rc = check_launch("ts32_from_rowmajor_kernel");
   if (rc) return rc;
 
@@ -546,12 +564,12 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   TcParams p{};
   p.A = acat, p.a_rg = rg, p.B = W1, p.b_rg = d.h_rows / 8, p.KB = 2 * d.kbK;
   p.m_tiles = m_tiles, p.n_tiles = narrow ? (H + 127) / 128 : (H + 255) / 256;
-  p.rows = N, p.cols = H, p.bias = bias_eff;
+  p.rows = N, p.cols = H, p.bias = bias_eff, p.bias_alt = bias_eff + d.h_rows, p.row_set = c->row_set;
   p.out_ts = h1, p.out_rg = rg, p.out_kb = d.kbH;
   rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
   if (rc) return rc;
 
-  p.A = h1, p.B = W2, p.KB = d.kbH, p.bias = w->b_h, p.out_ts = h2;
+  p.A = h1, p.B = W2, p.KB = d.kbH, p.bias = w->b_h, p.bias_alt = nullptr, p.row_set = nullptr, p.out_ts = h2;
   rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
   if (rc) return rc;
 
@@ -564,6 +582,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   p.S = c->S, p.T = c->T, p.Q = c->Q;
   p.ux = c->x, p.uv = c->v, p.ug = c->g, p.umask = c->mask, p.uinvert = c->mask_invert;
   p.eps = c->eps, p.dir = c->dir, p.uout = c->out, p.flag = c->nonfinite_flag;
+  p.row_set = c->row_set, p.umask_alt = c->mask_alt, p.uinvert_alt = c->mask_invert_alt, p.dir_alt = c->dir_alt;
   p.ld_part = c->logdet ? ld_part : nullptr;
   if (c->mode == L2HMC_NET_STQ) rc = launch_tc<192, kTcHeadsStq>(p, st);
   else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_tc<192, kTcHeadsMomentum>(p, st);
@@ -578,7 +597,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
 
 size_t tc_workspace_floats(int K, int H, int D, int N) {
   const TcDims d = tc_dims(K, H, D, N);
-  return d.acat_floats + 2 * d.h_floats + d.h_rows + 2 * static_cast<size_t>(d.d_tiles) * d.rows_p;
+  return d.acat_floats + 2 * d.h_floats + 2 * d.h_rows + 2 * static_cast<size_t>(d.d_tiles) * d.rows_p;
 }
 
 }  // namespace l2hmc
@@ -639,7 +658,7 @@ extern "C" int l2hmc_tc_selftest(const float* A, const float* W, int M, int Nc, 
   cudaMemsetAsync(w_ts, 0, sizeof(float) * static_cast<size_t>(kb) * n_p * 64, st);
   cudaMemsetAsync(bias, 0, sizeof(float) * n_p, st);
   ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(kb) * (rows_p / 8) * 64), 256, 0, st>>>(
-      A, K, M, K, nullptr, 0, a_ts, rows_p / 8, 0, kb);
+      A, K, M, K, nullptr, 0, nullptr, 0, nullptr, a_ts, rows_p / 8, 0, kb);
   ts32_pack_weight_kernel<<<ew_grid(static_cast<size_t>(kb) * 32 * Nc), 256, 0, st>>>(W, K, Nc, w_ts, n_p / 8, 0, 0, 0);
   TcParams p{};
   p.A = a_ts, p.a_rg = rows_p / 8, p.B = w_ts, p.b_rg = n_p / 8, p.KB = kb;

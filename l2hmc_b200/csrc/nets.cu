@@ -33,6 +33,8 @@ struct Seg {
   int lda;
   const float* mask;   // nullable [K]
   int invert;
+  const float* mask_alt;   // rows with row_set != 0
+  int invert_alt;
   const float* W[3];   // [K, cols] row-major, leading dimension ldb (three for the heads)
   int ldb;
   int K;
@@ -45,6 +47,10 @@ struct DenseParams {
   const float* bias[3]; // layers: up to three biases summed; heads: b_s, b_tr, b_q
   const float* wt;      // t_layer kernel [2, cols] (nullable)
   float tau0, tau1;
+  const uint8_t* row_set;   // nullable [rows]: 1 -> the *_alt parameters (mixed-direction batches)
+  float tau0_alt, tau1_alt;
+  const float* umask_alt;
+  int uinvert_alt, dir_alt;
   const float* coeff_s; // heads
   const float* coeff_q;
   int tanh_on_q;
@@ -85,6 +91,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 
   // A: one float4 along K per thread
   const int ar = tid >> 2, ak = (tid & 3) * 4;
+  const bool a_alt = p.row_set != nullptr && m0 + ar < p.rows && p.row_set[m0 + ar] != 0;
   float a_reg[4];
   float b_reg[BV][4];
 
@@ -102,12 +109,14 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
         for (int i = 0; i < 4; ++i)
           if (k0 + ak + i < s.K) a_reg[i] = src[i];
       }
-      if (s.mask != nullptr) {
+      const float* mask = a_alt ? s.mask_alt : s.mask;
+      if (mask != nullptr) {
+        const int invert = a_alt ? s.invert_alt : s.invert;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           if (k0 + ak + i < s.K) {
-            const float m = s.mask[k0 + ak + i];
-            a_reg[i] = __fmul_rn(s.invert ? __fsub_rn(1.f, m) : m, a_reg[i]);
+            const float m = mask[k0 + ak + i];
+            a_reg[i] = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a_reg[i]);
           }
       }
     }
@@ -187,7 +196,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
   // ------------------------------------------------------------------ epilogue
   const int c0 = n0 + CW * tx;       // first owned column (per group)
   if (MODE == kBiasRelu) {
-    float add[CW];
+    float add[2][CW];
 #pragma unroll
     for (int j = 0; j < CW; ++j) {
       const int c = c0 + j;
@@ -195,21 +204,22 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
       if (c < p.cols) {
         s = p.bias[0][c];
         if (p.bias[1]) s = __fadd_rn(s, p.bias[1][c]);
-        if (p.wt) {
-          const float tt = __fadd_rn(__fadd_rn(__fmul_rn(p.tau0, p.wt[c]), __fmul_rn(p.tau1, p.wt[p.cols + c])),
-                                     p.bias[2][c]);
-          s = __fadd_rn(s, tt);
-        }
       }
-      add[j] = s;
+      add[0][j] = add[1][j] = s;
+      if (c < p.cols && p.wt) {
+        const float w0 = p.wt[c], w1 = p.wt[p.cols + c], b2 = p.bias[2][c];
+        add[0][j] = __fadd_rn(s, __fadd_rn(__fadd_rn(__fmul_rn(p.tau0, w0), __fmul_rn(p.tau1, w1)), b2));
+        add[1][j] = __fadd_rn(s, __fadd_rn(__fadd_rn(__fmul_rn(p.tau0_alt, w0), __fmul_rn(p.tau1_alt, w1)), b2));
+      }
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int r = m0 + 4 * ty + i;
       if (r >= p.rows) continue;
+      const int set = (p.row_set != nullptr && p.row_set[r] != 0) ? 1 : 0;
       float o[CW];
 #pragma unroll
-      for (int j = 0; j < CW; ++j) o[j] = fmaxf(__fadd_rn(acc[i][j], add[j]), 0.f);
+      for (int j = 0; j < CW; ++j) o[j] = fmaxf(__fadd_rn(acc[i][j], set ? add[1][j] : add[0][j]), 0.f);
       float* dst = p.out[0] + static_cast<size_t>(r) * p.cols + c0;
       if (CW == 4 && c0 + 3 < p.cols && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
         *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
@@ -221,7 +231,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
     }
   } else {
     // heads: acc[i][0..1] = S, [2..3] = T, [4..5] = Q pre-activations of outputs d = c0, c0 + 1
-    float bs[CW], bt[CW], bq[CW], es[CW], eq[CW], um[CW];
+    float bs[CW], bt[CW], bq[CW], es[CW], eq[CW], um[CW], um_alt[CW];
 #pragma unroll
     for (int j = 0; j < CW; ++j) {
       const int d = c0 + j;
@@ -231,8 +241,11 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
       bq[j] = ok ? p.bias[2][d] : 0.f;
       es[j] = ok ? expf(p.coeff_s[d]) : 1.f;
       eq[j] = ok ? expf(p.coeff_q[d]) : 1.f;
-      um[j] = 0.f;
-      if (MODE == kHeadsPosition && ok) um[j] = p.uinvert ? __fsub_rn(1.f, p.umask[d]) : p.umask[d];
+      um[j] = um_alt[j] = 0.f;
+      if (MODE == kHeadsPosition && ok) {
+        um[j] = p.uinvert ? __fsub_rn(1.f, p.umask[d]) : p.umask[d];
+        if (p.row_set) um_alt[j] = p.uinvert_alt ? __fsub_rn(1.f, p.umask_alt[d]) : p.umask_alt[d];
+      }
     }
     const float heps = __fmul_rn(0.5f, p.eps);
     bool bad = false;
@@ -240,6 +253,8 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
     for (int i = 0; i < 4; ++i) {
       const int r = m0 + 4 * ty + i;
       const bool rok = r < p.rows;
+      const bool alt = p.row_set != nullptr && rok && p.row_set[r] != 0;
+      const int dir = alt ? p.dir_alt : p.dir;
       float ld = 0.f;
 #pragma unroll
       for (int j = 0; j < CW; ++j) {
@@ -255,12 +270,13 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
           p.out[0][at] = S, p.out[1][at] = Tr, p.out[2][at] = Q;
         } else if (MODE == kHeadsMomentum) {
           const float v = p.uv[at], g = p.ug[at];
-          p.uout[at] = p.dir > 0 ? momentum_elem<1>(v, g, S, Tr, Q, p.eps, heps, ld, bad)
-                                 : momentum_elem<-1>(v, g, S, Tr, Q, p.eps, heps, ld, bad);
+          p.uout[at] = dir > 0 ? momentum_elem<1>(v, g, S, Tr, Q, p.eps, heps, ld, bad)
+                               : momentum_elem<-1>(v, g, S, Tr, Q, p.eps, heps, ld, bad);
         } else {
           const float x = p.ux[at], v = p.uv[at];
-          p.uout[at] = p.dir > 0 ? position_elem<1>(x, v, S, Tr, Q, um[j], p.eps, ld, bad)
-                                 : position_elem<-1>(x, v, S, Tr, Q, um[j], p.eps, ld, bad);
+          const float m = alt ? um_alt[j] : um[j];
+          p.uout[at] = dir > 0 ? position_elem<1>(x, v, S, Tr, Q, m, p.eps, ld, bad)
+                               : position_elem<-1>(x, v, S, Tr, Q, m, p.eps, ld, bad);
         }
       }
       if (MODE != kHeadsStq) {
@@ -304,18 +320,20 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
 
   DenseParams p{};
   p.nseg = 2;
-  p.seg[0] = Seg{c->in0, K, nullptr, 0, {w->w_in0, nullptr, nullptr}, H, K};
-  p.seg[1] = Seg{c->in1, K, c->in1_mask, c->in1_mask_invert, {w->w_in1, nullptr, nullptr}, H, K};
+  p.seg[0] = Seg{c->in0, K, nullptr, 0, nullptr, 0, {w->w_in0, nullptr, nullptr}, H, K};
+  p.seg[1] = Seg{c->in1, K, c->in1_mask, c->in1_mask_invert, c->in1_mask_alt, c->in1_mask_invert_alt,
+                 {w->w_in1, nullptr, nullptr}, H, K};
   p.rows = N, p.cols = H;
   p.bias[0] = w->b_in0, p.bias[1] = w->b_in1, p.bias[2] = w->b_t;
   p.wt = w->w_t, p.tau0 = c->tau_cos, p.tau1 = c->tau_sin;
+  p.row_set = c->row_set, p.tau0_alt = c->tau_cos_alt, p.tau1_alt = c->tau_sin_alt;
   p.out[0] = h1;
   int rc = launch_dense<1, 4, kBiasRelu>(p, st);
   if (rc) return rc;
 
   p = DenseParams{};
   p.nseg = 1;
-  p.seg[0] = Seg{h1, H, nullptr, 0, {w->w_h, nullptr, nullptr}, H, H};
+  p.seg[0] = Seg{h1, H, nullptr, 0, nullptr, 0, {w->w_h, nullptr, nullptr}, H, H};
   p.rows = N, p.cols = H;
   p.bias[0] = w->b_h;
   p.out[0] = h2;
@@ -324,13 +342,14 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
 
   p = DenseParams{};
   p.nseg = 1;
-  p.seg[0] = Seg{h2, H, nullptr, 0, {w->w_s, w->w_tr, w->w_q}, D, H};
+  p.seg[0] = Seg{h2, H, nullptr, 0, nullptr, 0, {w->w_s, w->w_tr, w->w_q}, D, H};
   p.rows = N, p.cols = D;
   p.bias[0] = w->b_s, p.bias[1] = w->b_tr, p.bias[2] = w->b_q;
   p.coeff_s = w->coeff_s, p.coeff_q = w->coeff_q, p.tanh_on_q = w->tanh_on_q;
   p.out[0] = c->S, p.out[1] = c->T, p.out[2] = c->Q;
   p.ux = c->x, p.uv = c->v, p.ug = c->g, p.umask = c->mask, p.uinvert = c->mask_invert;
   p.eps = c->eps, p.dir = c->dir, p.uout = c->out, p.flag = c->nonfinite_flag;
+  p.row_set = c->row_set, p.umask_alt = c->mask_alt, p.uinvert_alt = c->mask_invert_alt, p.dir_alt = c->dir_alt;
   p.ld_part = c->logdet ? ld_part : nullptr;
   if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 2, kHeadsStq>(p, st);
   else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 2, kHeadsMomentum>(p, st);
@@ -371,6 +390,13 @@ int net_validate(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
     default:
       set_error("l2hmc_net_run: unknown mode %d", c->mode);
       return L2HMC_ERR_INVALID;
+  }
+  if (c->row_set != nullptr) {
+    L2HMC_REQUIRE((c->in1_mask == nullptr) == (c->in1_mask_alt == nullptr),
+                  "l2hmc_net_run: in1_mask and in1_mask_alt must be given together");
+    if (c->mode != L2HMC_NET_STQ)
+      L2HMC_REQUIRE(c->dir_alt == 1 || c->dir_alt == -1, "l2hmc_net_run: dir_alt must be +1 or -1");
+    if (c->mode == L2HMC_NET_POSITION) L2HMC_REQUIRE(c->mask_alt, "l2hmc_net_run: row_set given without mask_alt");
   }
   return L2HMC_OK;
 }

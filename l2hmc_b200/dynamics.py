@@ -227,13 +227,15 @@ class GaugeDynamics(object):
         return self.lattice.grad_action(self._x(position), self._beta(beta))
 
     # ------------------------------------------------------------------ the four sub-updates
-    def _momentum_update(self, position, momentum, beta, t, direction, logdet=None):
+    def _momentum_update(self, position, momentum, beta, t, direction, logdet=None, alt=None):
         x, v = self._x(position), self._x(momentum)
         N, D = x.shape
         grad = self.grad_potential(x, beta)
         ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
         if not self.hmc and self.fuse_updates and hasattr(self.momentum_fn, 'momentum_update'):
-            return self.momentum_fn.momentum_update(x, v, grad, t, self._eps(), direction, ld, self._flag), ld
+            return self.momentum_fn.momentum_update(x, v, grad, t, self._eps(), direction, ld, self._flag,
+                                                    alt=alt), ld
+        assert alt is None, "mixed-direction batches need the fused network updates"
         if self.hmc:
             S = Tr = Q = None
         else:
@@ -244,13 +246,14 @@ class GaugeDynamics(object):
                        _lib.dptr(self._flag, torch.int32))
         return out, ld
 
-    def _position_update(self, position, momentum, t, mask_row, invert, direction, logdet=None):
+    def _position_update(self, position, momentum, t, mask_row, invert, direction, logdet=None, alt=None):
         x, v = self._x(position), self._x(momentum)
         N, D = x.shape
         ld = torch.zeros(N, dtype=torch.float32, device=x.device) if logdet is None else logdet
         if not self.hmc and self.fuse_updates and hasattr(self.position_fn, 'position_update'):
             return self.position_fn.position_update(x, v, t, mask_row, invert, self._eps(), direction, ld,
-                                                    self._flag), ld
+                                                    self._flag, alt=alt), ld
+        assert alt is None, "mixed-direction batches need the fused network updates"
         if self.hmc:
             S = Tr = Q = None
         else:
@@ -303,6 +306,21 @@ class GaugeDynamics(object):
         x, ld = self._position_update(x, v, t, row, first_inv, direction, ld)
         x, ld = self._position_update(x, v, t, row, second_inv, direction, ld)
         v, ld = self._momentum_update(x, v, beta, t, direction, ld)
+        return x, v, ld
+
+    def _lf_mixed(self, x, v, beta, step, backward_rows, ld):
+        """One leapfrog step of a batch whose chains run in different directions: chains with
+        backward_rows[n] == 0 take the forward step `step`, the others the backward step (reversed
+        index, inverse mask first) -- both kinds in the same launches (l2hmc_net_call.row_set)."""
+        from .network import AltSet
+        ib = self.num_steps - step - 1
+        tf_ = (float(self._ts_host[step, 0]), float(self._ts_host[step, 1]))
+        tb_ = (float(self._ts_host[ib, 0]), float(self._ts_host[ib, 1]))
+        row_f, row_b = self.mask[step], self.mask[ib]
+        v, ld = self._momentum_update(x, v, beta, tf_, +1, ld, alt=AltSet(backward_rows, tb_, -1))
+        x, ld = self._position_update(x, v, tf_, row_f, 0, +1, ld, alt=AltSet(backward_rows, tb_, -1, row_b, 1))
+        x, ld = self._position_update(x, v, tf_, row_f, 1, +1, ld, alt=AltSet(backward_rows, tb_, -1, row_b, 0))
+        v, ld = self._momentum_update(x, v, beta, tf_, +1, ld, alt=AltSet(backward_rows, tb_, -1))
         return x, v, ld
 
     def _forward_lf(self, position, momentum, beta, step):
@@ -426,7 +444,24 @@ class GaugeDynamics(object):
             z, u_dir, u_acc = self._draws(N)
             self._mc_step += 1
             v_f = v_b = z
-        # run each chain only in the direction it selects: gather, integrate, scatter
+        if self.fuse_updates and not self.hmc and hasattr(self.position_fn, 'position_update'):
+            # every chain runs only the direction it selects, all of them in the same launches
+            lib = _lib.get_lib()
+            if v_b is v_f:
+                v0 = v_f
+            else:                      # injected, distinct draws: v0 = v_f where u_dir > 0.5 else v_b (exact 0/1 blend)
+                v0, ones = torch.empty_like(x), torch.ones(N, dtype=torch.float32, device=x.device)
+                self._lib_call(lib.l2hmc_mh_select, _lib.dptr(v_f), _lib.dptr(v_f), _lib.dptr(v_b), None, None,
+                               _lib.dptr(ones), _lib.dptr(ones), _lib.dptr(u_dir), None, N, D, 0, _lib.dptr(v0),
+                               None, None, None, None)
+            backward_rows = (u_dir <= 0.5).to(torch.uint8)
+            x_post, v_post = x, v0
+            sumlogdet = torch.zeros(N, dtype=torch.float32, device=x.device)
+            for step in range(self.num_steps):
+                x_post, v_post, sumlogdet = self._lf_mixed(x_post, v_post, beta, step, backward_rows, sumlogdet)
+            p_post = self._compute_accept_prob(x, v0, x_post, v_post, sumlogdet, beta)
+            return self._finish_transition(x, x_post, v_post, p_post, u_acc, wrap, observables)
+        # unfused K2 composition: gather the chains of each direction, integrate, scatter
         fwd = u_dir > 0.5
         idx_f = torch.nonzero(fwd, as_tuple=False).reshape(-1)
         idx_b = torch.nonzero(~fwd, as_tuple=False).reshape(-1)
@@ -440,6 +475,11 @@ class GaugeDynamics(object):
             x_post.index_copy_(0, idx, xs)
             v_post.index_copy_(0, idx, vs)
             p_post.index_copy_(0, idx, ps)
+        return self._finish_transition(x, x_post, v_post, p_post, u_acc, wrap, observables)
+
+    def _finish_transition(self, x, x_post, v_post, p_post, u_acc, wrap, observables):
+        """Metropolis-Hastings select (gauge_dynamics.py:243-259) [+ np.mod 2 pi] [+ observables]."""
+        N, D = x.shape
         x_out = torch.empty_like(x)
         acc = torch.empty(N, dtype=torch.uint8, device=x.device)
         self._lib_call(_lib.get_lib().l2hmc_mh_select, _lib.dptr(x), _lib.dptr(x_post), None, None, None,

@@ -112,9 +112,9 @@ class MogNet(_StqNet):
         rng = np.random.default_rng([int(seed), sum(map(ord, scope))])
         self.load_weights(self._init_dense(self.num_features, rng))
 
-    def _features(self, in0, in1, mask, invert):
+    def _features(self, in0, in1, mask, invert, alt=None):
         m = None if mask is None else mask.reshape(-1).contiguous()
-        return in0, in1, m
+        return in0, in1, m, None
 
     def __call__(self, inputs, **kw):
         return self.call(list(inputs[:3]), **kw)        # the 4th entry is `aux` (always None for the MoG model)

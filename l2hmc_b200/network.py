@@ -173,10 +173,14 @@ class _StqNet(object):
         t = to_device(a, self.device)
         return t.reshape(t.shape[0], -1)
 
-    def _run(self, call, feats0, feats1, N, t):
+    def _run(self, call, feats0, feats1, N, t, alt=None):
         ws, need = self._workspace(N)
         call.in0, call.in1 = _lib.dptr(feats0), _lib.dptr(feats1)
         call.tau_cos, call.tau_sin = self._tau(t)
+        if alt is not None:
+            call.row_set = _lib.dptr(alt.row_set, torch.uint8)
+            call.tau_cos_alt, call.tau_sin_alt = self._tau(alt.t)
+            call.dir_alt = int(alt.direction)
         call.N = int(N)
         call.workspace, call.workspace_bytes = _lib.dptr(ws), need
         call.path = int(self.path)
@@ -193,7 +197,7 @@ class _StqNet(object):
         N, D = in0.shape[0], int(self.x_dim)
         if mask is not None:
             mask = self._dev(mask).reshape(-1)
-        f0, f1, fmask = self._features(in0, in1, mask, mask_invert)
+        f0, f1, fmask, _ = self._features(in0, in1, mask, mask_invert)
         S, Tr, Q = (torch.empty(N, D, dtype=torch.float32, device=self.device) for _ in range(3))
         c = _lib.NetCall()
         c.mode = _lib.NET_STQ
@@ -205,33 +209,46 @@ class _StqNet(object):
     __call__ = call
 
     # ------------------------------------------------------------------ fused sub-updates
-    def momentum_update(self, x, v, g, t, eps, direction, logdet, flag, out=None):
+    def momentum_update(self, x, v, g, t, eps, direction, logdet, flag, out=None, alt=None):
         """v' and log-det of _update_momentum_{forward,backward} (gauge_dynamics.py:486-508,
-        537-561): S,T,Q = momentum_fn([x, g, t]) consumed in the head GEMM's epilogue."""
+        537-561): S,T,Q = momentum_fn([x, g, t]) consumed in the head GEMM's epilogue.
+        `alt` (an AltSet) gives the chains flagged in alt.row_set their own time row / direction."""
         N = x.shape[0]
-        f0, f1, _ = self._features(x, g, None, False)
+        f0, f1, _, _ = self._features(x, g, None, False)
         out = torch.empty_like(v) if out is None else out
         c = _lib.NetCall()
         c.mode, c.eps, c.dir = _lib.NET_MOMENTUM, float(eps), int(direction)
         c.v, c.g, c.out = _lib.dptr(v), _lib.dptr(g), _lib.dptr(out)
         c.logdet, c.nonfinite_flag = _lib.dptr(logdet), _lib.dptr(flag, torch.int32)
-        self._run(c, f0, f1, N, t)
+        self._run(c, f0, f1, N, t, alt)
         return out
 
-    def position_update(self, x, v, t, mask_row, invert, eps, direction, logdet, flag, out=None):
+    def position_update(self, x, v, t, mask_row, invert, eps, direction, logdet, flag, out=None, alt=None):
         """x' and log-det of _update_position_{forward,backward} (gauge_dynamics.py:511-534,
         565-590): S,T,Q = position_fn([v, m*x, t]); the update keeps m*x and moves mbar*x."""
         N = x.shape[0]
-        f0, f1, fmask = self._features(v, x, mask_row, invert)
+        f0, f1, fmask, fmask_alt = self._features(v, x, mask_row, invert, alt)
         out = torch.empty_like(x) if out is None else out
         c = _lib.NetCall()
         c.mode, c.eps, c.dir = _lib.NET_POSITION, float(eps), int(direction)
         c.in1_mask, c.in1_mask_invert = _lib.dptr(fmask), int(bool(invert))
         c.x, c.v, c.mask, c.mask_invert, c.out = _lib.dptr(x), _lib.dptr(v), _lib.dptr(mask_row), int(bool(invert)), \
             _lib.dptr(out)
+        if alt is not None:
+            c.in1_mask_alt, c.in1_mask_invert_alt = _lib.dptr(fmask_alt), int(bool(alt.invert))
+            c.mask_alt, c.mask_invert_alt = _lib.dptr(alt.mask_row), int(bool(alt.invert))
         c.logdet, c.nonfinite_flag = _lib.dptr(logdet), _lib.dptr(flag, torch.int32)
-        self._run(c, f0, f1, N, t)
+        self._run(c, f0, f1, N, t, alt)
         return out
+
+
+class AltSet(object):
+    """Second parameter set of a mixed-direction batch (l2hmc_net_call.row_set and *_alt): chains with
+    row_set[n] != 0 use time row `t`, `direction` and (for position updates) `mask_row` / `invert`."""
+
+    def __init__(self, row_set, t, direction, mask_row=None, invert=False):
+        self.row_set, self.t, self.direction = row_set, t, int(direction)
+        self.mask_row, self.invert = mask_row, bool(invert)
 
 
 class GenericNet(_StqNet):
@@ -257,9 +274,10 @@ class GenericNet(_StqNet):
         rng = np.random.default_rng([int(self.seed), sum(map(ord, model_name))])
         self.load_weights(self._init_dense(self.num_features, rng))
 
-    def _features(self, in0, in1, mask, invert):
+    def _features(self, in0, in1, mask, invert, alt=None):
         m = None if mask is None else mask.reshape(-1).contiguous()
-        return in0, in1, m
+        ma = None if alt is None or alt.mask_row is None else alt.mask_row.reshape(-1).contiguous()
+        return in0, in1, m, ma
 
 
 class ConvNet3D(_StqNet):
@@ -332,7 +350,7 @@ class ConvNet3D(_StqNet):
                 self._conv_structs[s] = c
         return self._conv_structs[which]
 
-    def _features(self, in0, in1, mask, invert):
+    def _features(self, in0, in1, mask, invert, alt=None):
         """Conv features of both streams: the first input through conv_v*, the second (masked on
         load) through conv_x* (conv_net.py:252-260)."""
         N = in0.shape[0]
@@ -344,7 +362,15 @@ class ConvNet3D(_StqNet):
             f = self._feat[i][:N]
             mm = None if m is None else m.reshape(-1).contiguous()
             with torch.cuda.device(self.device):
-                _lib.check(lib.l2hmc_conv3d_features(self._conv(which), _lib.dptr(a), _lib.dptr(mm), int(bool(invert)),
-                                                     N, self.T, self.X, _lib.dptr(f), _lib.stream_ptr()))
+                if m is not None and alt is not None:
+                    ma = alt.mask_row.reshape(-1).contiguous()
+                    _lib.check(lib.l2hmc_conv3d_features_sets(
+                        self._conv(which), _lib.dptr(a), _lib.dptr(mm), int(bool(invert)), _lib.dptr(ma),
+                        int(bool(alt.invert)), _lib.dptr(alt.row_set, torch.uint8), N, self.T, self.X, _lib.dptr(f),
+                        _lib.stream_ptr()))
+                else:
+                    _lib.check(lib.l2hmc_conv3d_features(self._conv(which), _lib.dptr(a), _lib.dptr(mm),
+                                                         int(bool(invert)), N, self.T, self.X, _lib.dptr(f),
+                                                         _lib.stream_ptr()))
             feats.append(f)
-        return feats[0], feats[1], None
+        return feats[0], feats[1], None, None

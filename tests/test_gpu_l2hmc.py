@@ -284,3 +284,32 @@ def test_conv3d_features_against_oracle(T, X, F, N):
         ref = ref.reshape(N, -1)
         assert ref.shape[1] == nf
         close(out, ref, rtol=1e-5, atol=3e-5)
+
+
+@pytest.mark.parametrize("arch,T,N,path", [("generic", 8, 300, "ffma"), ("generic", 8, 300, "tc"), ("conv3D", 8, 70, "ffma"),
+                                           ("conv3D", 16, 260, "tc")])
+def test_mixed_direction_batch_equals_per_direction_runs(arch, T, N, path):
+    """apply_transition runs forward and backward chains in the same launches (l2hmc_net_call.row_set);
+    every chain must come out bit-identical to the one-direction transition_kernel of its own direction
+    (the reference computes both for all chains and blends with 0/1 masks, gauge_dynamics.py:211-241)."""
+    from l2hmc_b200 import _lib
+    M, eps, beta = 3, 0.15, 2.5
+    D = 2 * T * T
+    rng = np.random.default_rng(T + N)
+    ws = _oracle_weights(arch, T, T, rng)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    vf, vb = (rng.standard_normal((N, D)).astype(np.float32) for _ in range(2))
+    ud, ua = (rng.uniform(size=N).astype(np.float32) for _ in range(2))
+    lat = pkg.GaugeLattice(T, T, 2, "U1", num_samples=N)
+    np.random.seed(42)
+    dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M, eps=eps, weights=ws)
+    dyn.position_fn.path = dyn.momentum_fn.path = _lib.NET_PATH_TCGEN05 if path == "tc" else _lib.NET_PATH_FFMA
+    xp, vp, p, xo = dyn.apply_transition(x, beta, momentum_f=vf, momentum_b=vb, direction_uniform=ud, accept_uniform=ua)
+    xf, vfo, pf = dyn.transition_kernel(x, beta, forward=True, momentum=vf)
+    xb, vbo, pb = dyn.transition_kernel(x, beta, forward=False, momentum=vb)
+    fwd = torch.as_tensor(ud > 0.5).cuda()
+    assert 0 < int(fwd.sum()) < N
+    assert torch.equal(xp, torch.where(fwd[:, None], xf, xb))
+    assert torch.equal(vp, torch.where(fwd[:, None], vfo, vbo))
+    assert torch.equal(p, torch.where(fwd, pf, pb))
+    dyn.raise_if_nonfinite()
