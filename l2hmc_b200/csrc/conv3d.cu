@@ -162,29 +162,34 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
 
 
 // ---------------------------------------------------------------------------------------------
-// Register-tiled variant for F in {8, 16, 32} (F = X for the lattices of BASELINE configs 2-4):
-// kChains chains per CTA pass.
+// Register-tiled variant for F in {8, 16, 32} and T, X multiples of 4 (BASELINE configs 2-4 have
+// F = X = T): kChains chains per CTA pass, no boundary logic in the arithmetic.
+//   staging: the NEXT pass's links are fetched into registers (PF float4 per thread) before this
+//            pass computes, and written -- mask applied -- into a zero-bordered (T+2) x (X+2) plane,
+//            so TF's 'same' zero padding is a plain load.
 //   phase 1: a thread keeps the 18 taps of ITS filter f = tid % F in registers for the whole kernel
 //            and computes two neighbouring pooled outputs from one 4x6 input patch
 //            (24 LDS.64 per 216 FFMA).
 //   phase 2: a thread owns one pooled output position x four output channels: per block of four
 //            input filters it reads the 3x3 P1 patch as float4 over f (9 LDS.128) and the weights as
-//            float4 over c (16 LDS.128) for 256 FFMA; the P1 rows are padded to F + 4 floats so the
-//            four positions a warp reads side by side fall into different banks.
+//            float4 over c (16 LDS.128) for 256 FFMA.  P1 has a zero row/column at the end (the
+//            2-wide kernel's padding) and rows padded to F + 4 floats, so the four positions a warp
+//            reads side by side fall into different banks.
 // The arithmetic per output (tap order, bias after max, relu last) is the generic kernel's.
 constexpr int kChains = 2;
 
-template <int F>
-__global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams p) {
+template <int F, int PF>
+__global__ void __launch_bounds__(kThreads, 2) conv3d_tiled_kernel(const ConvParams p) {
   extern __shared__ __align__(16) float sm[];
   constexpr int C = 2 * F, FP = F + 4, CG = C / 4, G = kThreads / F;
   const int T = p.T, X = p.X;
-  const int T1 = (T + 1) / 2, X1 = (X + 1) / 2, T2 = (T1 + 1) / 2, X2 = (X1 + 1) / 2;
-  const int D = 2 * T * X, Dp = (D + 3) & ~3, P1 = T1 * X1 * FP;
+  const int T1 = T / 2, X1 = X / 2, T2 = T1 / 2, X2 = X1 / 2;
+  const int D = 2 * T * X, XB = X + 2, IN = (T + 2) * XB * 2;          // bordered input plane (floats)
+  const int X1B = X1 + 1, P1 = (T1 + 1) * X1B * FP;                   // P1 with a zero end row / column
   float* s_w2 = sm;                        // [4][F][C]   (kd = 0 taps only)
   float* s_b2 = s_w2 + 4 * F * C;          // [C]
-  float* s_in = s_b2 + C;                  // [kChains][Dp]
-  float* s_p1 = s_in + kChains * Dp;       // [kChains][T1*X1][FP]
+  float* s_in = s_b2 + C;                  // [kChains][T+2][X+2][2]
+  float* s_p1 = s_in + kChains * IN;       // [kChains][T1+1][X1+1][FP]
   const int tid = threadIdx.x;
 
   for (int i = tid; i < 4 * F * C; i += kThreads) {
@@ -192,6 +197,8 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
     s_w2[i] = p.w2[static_cast<size_t>(tap) * 2 * F * C + rest];
   }
   for (int i = tid; i < C; i += kThreads) s_b2[i] = p.b2[i];
+  for (int i = tid; i < kChains * IN; i += kThreads) s_in[i] = 0.f;    // borders stay zero for the whole kernel
+  for (int i = tid; i < kChains * P1; i += kThreads) s_p1[i] = 0.f;
   const int f = tid % F, grp = tid / F;
   float w[3][3][2];
 #pragma unroll
@@ -202,60 +209,88 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
       w[a][b][1] = p.w1[((a * 3 + b) * 2 + 1) * F + f];
     }
   const float bias1 = p.b1[f];
-  const int XP = (X1 + 1) / 2;             // pairs of pooled columns
+  const int XPR = X1 / 2;                  // pairs of pooled columns
+  const int quads = D / 4;                 // float4 per chain
 
-  for (int n0 = blockIdx.x * kChains; n0 < p.N; n0 += gridDim.x * kChains) {
-    const int nch = min(kChains, p.N - n0);
-    __syncthreads();
-    for (int i = tid; i < nch * D; i += kThreads) {
-      const int ch = i / D, j = i - ch * D;
-      float a = p.in[static_cast<size_t>(n0 + ch) * D + j];
+  float4 pre[PF];
+  auto fetch = [&](int n0) {               // links of chains n0 .. n0 + kChains - 1 -> registers
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i4 = tid + q * kThreads;
+      const int ch = i4 / quads;
+      pre[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ch < kChains && n0 + ch < p.N)
+        pre[q] = __ldcs(reinterpret_cast<const float4*>(p.in + static_cast<size_t>(n0 + ch) * D) + (i4 - ch * quads));
+    }
+  };
+  auto stage = [&](int n0) {               // registers -> bordered plane, mask applied
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i4 = tid + q * kThreads;
+      const int ch = i4 / quads;
+      if (ch >= kChains || n0 + ch >= p.N) continue;
+      const int j = (i4 - ch * quads) * 4;
+      float4 a = pre[q];
       const bool alt = p.row_set != nullptr && p.row_set[n0 + ch] != 0;
       const float* mask = alt ? p.mask_alt : p.mask;
       if (mask) {
-        const float m = mask[j];
-        a = __fmul_rn((alt ? p.invert_alt : p.invert) ? __fsub_rn(1.f, m) : m, a);
+        float4 m = *reinterpret_cast<const float4*>(mask + j);
+        if (alt ? p.invert_alt : p.invert)
+          m = make_float4(__fsub_rn(1.f, m.x), __fsub_rn(1.f, m.y), __fsub_rn(1.f, m.z), __fsub_rn(1.f, m.w));
+        a = make_float4(__fmul_rn(m.x, a.x), __fmul_rn(m.y, a.y), __fmul_rn(m.z, a.z), __fmul_rn(m.w, a.w));
       }
-      s_in[ch * Dp + j] = a;
+      const int site = j >> 1, t = site / X, x = site - t * X;       // two sites (x, x + 1) of one row
+      float* dst = s_in + ch * IN + ((t + 1) * XB + x + 1) * 2;
+      *reinterpret_cast<float2*>(dst) = make_float2(a.x, a.y);
+      *reinterpret_cast<float2*>(dst + 2) = make_float2(a.z, a.w);
     }
+  };
+
+  int n0 = blockIdx.x * kChains;
+  if (n0 < p.N) fetch(n0);
+  for (; n0 < p.N; n0 += gridDim.x * kChains) {
+    const int nch = min(kChains, p.N - n0);
+    __syncthreads();                       // previous pass done with s_in / s_p1 (and the zero fill on the first)
+    stage(n0);
+    const int n_next = n0 + gridDim.x * kChains;
+    if (n_next < p.N) fetch(n_next);       // in flight while this pass computes
     __syncthreads();
 
     // ---- phase 1
-    for (int item = grp; item < nch * T1 * XP; item += G) {
-      const int xp = item % XP, rest = item / XP, t1 = rest % T1, ch = rest / T1;
-      const float* in_c = s_in + ch * Dp;
+    for (int item = grp; item < nch * T1 * XPR; item += G) {
+      const int xp = item % XPR, rest = item / XPR, t1 = rest % T1, ch = rest / T1;
+      const float* in_c = s_in + ch * IN + (2 * t1 * XB + 4 * xp) * 2;   // bordered coords of (2 t1 - 1, 4 xp - 1)
       float in[4][6][2];
 #pragma unroll
       for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int b = 0; b < 6; ++b) {
-          const int t = 2 * t1 - 1 + a, x = 4 * xp - 1 + b;
-          const bool ok = t >= 0 && t < T && x >= 0 && x < X;
-          const float2 u = ok ? *reinterpret_cast<const float2*>(&in_c[(t * X + x) * 2]) : make_float2(0.f, 0.f);
+          const float2 u = *reinterpret_cast<const float2*>(&in_c[(a * XB + b) * 2]);
           in[a][b][0] = u.x, in[a][b][1] = u.y;
         }
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        const int x1 = 2 * xp + h;
-        if (x1 >= X1) break;
         float best = -INFINITY;
 #pragma unroll
         for (int dt = 0; dt < 2; ++dt)
 #pragma unroll
           for (int dx = 0; dx < 2; ++dx) {
-            if (2 * t1 + dt >= T || 2 * x1 + dx >= X) continue;
-            float s0 = 0.f, s1 = 0.f;
+            // first tap as a product: fmaf(a, b, 0) == a * b
+            float s0 = __fmul_rn(in[dt][2 * h + dx][0], w[0][0][0]);
+            s0 = fmaf(in[dt][2 * h + dx][1], w[0][0][1], s0);
+            float s1 = __fmul_rn(in[dt][2 * h + dx][1], w[0][0][0]);
 #pragma unroll
             for (int a = 0; a < 3; ++a)
 #pragma unroll
               for (int b = 0; b < 3; ++b) {
+                if (a == 0 && b == 0) continue;
                 s0 = fmaf(in[dt + a][2 * h + dx + b][0], w[a][b][0], s0);
                 s0 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][1], s0);
                 s1 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][0], s1);
               }
             best = fmaxf(best, fmaxf(s0, s1));
           }
-        s_p1[ch * P1 + (t1 * X1 + x1) * FP + f] = fmaxf(__fadd_rn(best, bias1), 0.f);
+        s_p1[ch * P1 + (t1 * X1B + 2 * xp + h) * FP + f] = fmaxf(__fadd_rn(best, bias1), 0.f);
       }
     }
     __syncthreads();
@@ -264,8 +299,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
     const int cg = tid % CG;
     for (int item = tid / CG; item < nch * T2 * X2; item += kThreads / CG) {
       const int x2 = item % X2, rest = item / X2, t2 = rest % T2, ch = rest / T2;
-      const float* p1 = s_p1 + ch * P1;
-      const int tb = 2 * t2, xb = 2 * x2;
+      const float* p1 = s_p1 + ch * P1 + (2 * t2 * X1B + 2 * x2) * FP;
       float acc[2][2][4];
 #pragma unroll
       for (int i = 0; i < 16; ++i) (&acc[0][0][0])[i] = 0.f;
@@ -275,11 +309,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
 #pragma unroll
         for (int a = 0; a < 3; ++a)
 #pragma unroll
-          for (int b = 0; b < 3; ++b) {
-            const int t = tb + a, x = xb + b;
-            pp[a][b] = (t < T1 && x < X1) ? *reinterpret_cast<const float4*>(&p1[(t * X1 + x) * FP + f4])
-                                          : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
+          for (int b = 0; b < 3; ++b) pp[a][b] = *reinterpret_cast<const float4*>(&p1[(a * X1B + b) * FP + f4]);
 #pragma unroll
         for (int fi = 0; fi < 4; ++fi) {
           float4 wt[4];
@@ -304,37 +334,47 @@ __global__ void __launch_bounds__(kThreads) conv3d_tiled_kernel(const ConvParams
       float o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float best = -INFINITY;
-#pragma unroll
-        for (int dt = 0; dt < 2; ++dt)
-#pragma unroll
-          for (int dx = 0; dx < 2; ++dx)
-            if (tb + dt < T1 && xb + dx < X1) best = fmaxf(best, acc[dt][dx][j]);
+        const float best = fmaxf(fmaxf(acc[0][0][j], acc[0][1][j]), fmaxf(acc[1][0][j], acc[1][1][j]));
         o[j] = fmaxf(__fadd_rn(best, s_b2[4 * cg + j]), 0.f);
       }
       float* dst = p.feat + static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
-      *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+      __stcs(reinterpret_cast<float4*>(dst), make_float4(o[0], o[1], o[2], o[3]));
     }
   }
 }
 
-template <int F>
-int launch_tiled(const ConvParams& p, int sms, int max_smem, cudaStream_t stream) {
-  const int T1 = (p.T + 1) / 2, X1 = (p.X + 1) / 2, D = 2 * p.T * p.X;
-  const size_t smem = sizeof(float) * (4 * F * 2 * F + 2 * F + kChains * ((D + 3) & ~3) + kChains * T1 * X1 * (F + 4));
-  if (smem > static_cast<size_t>(max_smem)) return -1;
+template <int F, int PF>
+int launch_tiled_pf(const ConvParams& p, int sms, size_t smem, cudaStream_t stream) {
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(conv3d_tiled_kernel<F>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(conv3d_tiled_kernel<F, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv3d_tiled_kernel): %s", cudaGetErrorString(e));
       return L2HMC_ERR_CUDA;
     }
   }
-  int per_sm = max(1, min(static_cast<int>((200 * 1024) / (smem + 1024)), 2));
+  const int per_sm = max(1, min(static_cast<int>((200 * 1024) / (smem + 1024)), 2));
   const int grid = max(1, min((p.N + kChains - 1) / kChains, sms * per_sm));
-  conv3d_tiled_kernel<F><<<grid, kThreads, smem, stream>>>(p);
+  conv3d_tiled_kernel<F, PF><<<grid, kThreads, smem, stream>>>(p);
   return check_launch("conv3d_tiled_kernel");
+}
+
+// -1: shape not covered (odd extents, misaligned arrays, too large for shared memory) -> generic kernel
+template <int F>
+int launch_tiled(const ConvParams& p, int sms, int max_smem, cudaStream_t stream) {
+  const auto misaligned = [](const void* a) { return (reinterpret_cast<uintptr_t>(a) & 15u) != 0; };
+  if (p.T % 4 != 0 || p.X % 4 != 0 || misaligned(p.in) || misaligned(p.feat) || misaligned(p.mask) ||
+      misaligned(p.mask_alt))
+    return -1;
+  const int T1 = p.T / 2, X1 = p.X / 2, D = 2 * p.T * p.X;
+  const size_t smem = sizeof(float) * (4 * F * 2 * F + 2 * F + kChains * (p.T + 2) * (p.X + 2) * 2 +
+                                       kChains * (T1 + 1) * (X1 + 1) * (F + 4));
+  if (smem > static_cast<size_t>(max_smem)) return -1;
+  const int pf = (kChains * D / 4 + kThreads - 1) / kThreads;
+  if (pf <= 1) return launch_tiled_pf<F, 1>(p, sms, smem, stream);
+  if (pf <= 2) return launch_tiled_pf<F, 2>(p, sms, smem, stream);
+  if (pf <= 4) return launch_tiled_pf<F, 4>(p, sms, smem, stream);
+  return -1;
 }
 
 }  // namespace

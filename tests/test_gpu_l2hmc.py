@@ -258,7 +258,8 @@ def test_tc_path_refuses_small_shapes(pkg):
 
 
 @pytest.mark.parametrize("T,X,F,N", [(16, 16, 16, 67), (8, 8, 8, 3), (7, 9, 8, 5), (32, 32, 32, 6), (5, 6, 16, 4),
-                                     (6, 10, 10, 9), (4, 4, 4, 2), (16, 16, 16, 1)])
+                                     (6, 10, 10, 9), (4, 4, 4, 2), (16, 16, 16, 1), (12, 8, 8, 11), (16, 32, 16, 7),
+                                     (8, 8, 8, 1000)])
 def test_conv3d_features_against_oracle(T, X, F, N):
     """l2hmc_conv3d_features (register-tiled kernel for F in {8,16,32}, generic otherwise) against the oracle's
     Conv3D/MaxPool3D 'same' stack (network/conv_net.py:247-260), with and without the mask on load."""
@@ -288,7 +289,7 @@ def test_conv3d_features_against_oracle(T, X, F, N):
 
 @pytest.mark.parametrize("arch,T,N,path", [("generic", 8, 300, "ffma"), ("generic", 8, 300, "tc"), ("conv3D", 8, 70, "ffma"),
                                            ("conv3D", 16, 260, "tc")])
-def test_mixed_direction_batch_equals_per_direction_runs(arch, T, N, path):
+def test_mixed_direction_batch_equals_per_direction_runs(pkg, arch, T, N, path):
     """apply_transition runs forward and backward chains in the same launches (l2hmc_net_call.row_set);
     every chain must come out bit-identical to the one-direction transition_kernel of its own direction
     (the reference computes both for all chains and blends with 0/1 masks, gauge_dynamics.py:211-241)."""
