@@ -147,29 +147,24 @@ __global__ void accept_prob_kernel(const float* __restrict__ h_old, const float*
 template <int VEC> struct RawVec { using type = float; };
 template <> struct RawVec<4> { using type = float4; };
 
-// VEC = 4: D % 4 == 0 and 16-byte aligned arrays (every lattice here), one float4 per lane per pass.
-template <int VEC>
+// One warp per chain.  The output arrays may alias the inputs, so the compiler cannot move the next
+// iteration's loads above this iteration's stores: UNR vectors per stream are therefore loaded
+// explicitly before any of them is consumed (bytes in flight = what keeps HBM busy).
+// VEC = 4: D % 4 == 0 and 16-byte aligned arrays (every lattice here).  FULL: blends of both
+// directions and / or the momenta are requested too (more streams, fewer vectors each).
+template <int VEC, bool FULL>
 __global__ void __launch_bounds__(kWarps * 32) mh_select_kernel(
     const float* __restrict__ x, const float* __restrict__ x_f, const float* __restrict__ x_b,
     const float* __restrict__ v_f, const float* __restrict__ v_b, const float* __restrict__ p_f,
     const float* __restrict__ p_b, const float* __restrict__ u_dir, const float* __restrict__ u_acc, int N, int D,
     int wrap, float* x_post, float* v_post, float* p, float* x_out, uint8_t* accepted) {
+  constexpr int UNR = FULL ? 2 : 4;
   struct alignas(4 * VEC) Vec { float e[VEC]; };
+  using Raw = typename RawVec<VEC>::type;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool both = x_b != nullptr;
+  const bool both = FULL && x_b != nullptr;
   for (int n = blockIdx.x * kWarps + warp; n < N; n += gridDim.x * kWarps) {
     const size_t base = static_cast<size_t>(n) * D;
-    const float fm = (both && u_dir) ? (u_dir[n] > 0.5f ? 1.f : 0.f) : 1.f;
-    const float bm = __fsub_rn(1.f, fm);
-    float prob = p_f[n];
-    if (both) prob = __fadd_rn(__fmul_rn(fm, p_f[n]), __fmul_rn(bm, p_b[n]));
-    const float am = u_acc ? (prob > u_acc[n] ? 1.f : 0.f) : 1.f;
-    const float rm = __fsub_rn(1.f, am);
-    if (lane == 0) {
-      if (p) p[n] = prob;
-      if (accepted) accepted[n] = am != 0.f;
-    }
-    using Raw = typename RawVec<VEC>::type;
     auto ld = [&](const float* a, int i) {
       const Raw r = __ldcs(reinterpret_cast<const Raw*>(a + base + i));
       return *reinterpret_cast<const Vec*>(&r);
@@ -177,33 +172,61 @@ __global__ void __launch_bounds__(kWarps * 32) mh_select_kernel(
     auto st = [&](float* a, int i, const Vec& w) {
       __stcs(reinterpret_cast<Raw*>(a + base + i), *reinterpret_cast<const Raw*>(&w));
     };
-#pragma unroll 2
-    for (int i = lane * VEC; i < D; i += 32 * VEC) {
-      Vec xp = ld(x_f, i);
-      if (both) {
-        const Vec xb = ld(x_b, i);
+    float fm = 1.f, bm = 0.f, am = 1.f, rm = 0.f;
+    for (int i0 = lane * VEC; i0 < D; i0 += 32 * VEC * UNR) {
+      Vec xf[UNR], xb[UNR], x0[UNR], vf[UNR], vb[UNR];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) xp.e[j] = __fadd_rn(__fmul_rn(fm, xp.e[j]), __fmul_rn(bm, xb.e[j]));
+      for (int u = 0; u < UNR; ++u) {
+        const int i = i0 + u * 32 * VEC;
+        if (i < D) {
+          xf[u] = ld(x_f, i);
+          if (x_out) x0[u] = ld(x, i);
+          if (both) xb[u] = ld(x_b, i);
+          if (FULL && v_post) {
+            vf[u] = ld(v_f, i);
+            if (both) vb[u] = ld(v_b, i);
+          }
+        }
       }
-      if (x_post) st(x_post, i, xp);
-      if (v_post) {
-        Vec vp = ld(v_f, i);
+      if (i0 == lane * VEC) {          // the chain's scalars, requested after the first vectors
+        fm = (both && u_dir) ? (u_dir[n] > 0.5f ? 1.f : 0.f) : 1.f;
+        bm = __fsub_rn(1.f, fm);
+        float prob = p_f[n];
+        if (both) prob = __fadd_rn(__fmul_rn(fm, prob), __fmul_rn(bm, p_b[n]));
+        am = u_acc ? (prob > u_acc[n] ? 1.f : 0.f) : 1.f;
+        rm = __fsub_rn(1.f, am);
+        if (lane == 0) {
+          if (p) p[n] = prob;
+          if (accepted) accepted[n] = am != 0.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNR; ++u) {
+        const int i = i0 + u * 32 * VEC;
+        if (i >= D) continue;
+        Vec xp = xf[u];
         if (both) {
-          const Vec vb = ld(v_b, i);
 #pragma unroll
-          for (int j = 0; j < VEC; ++j) vp.e[j] = __fadd_rn(__fmul_rn(fm, vp.e[j]), __fmul_rn(bm, vb.e[j]));
+          for (int j = 0; j < VEC; ++j) xp.e[j] = __fadd_rn(__fmul_rn(fm, xp.e[j]), __fmul_rn(bm, xb[u].e[j]));
         }
-        st(v_post, i, vp);
-      }
-      if (x_out) {
-        const Vec x0 = ld(x, i);
-        Vec o;
+        if (x_post) st(x_post, i, xp);
+        if (FULL && v_post) {
+          Vec vp = vf[u];
+          if (both) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          o.e[j] = __fadd_rn(__fmul_rn(am, xp.e[j]), __fmul_rn(rm, x0.e[j]));
-          if (wrap) o.e[j] = wrap_2pi(o.e[j]);
+            for (int j = 0; j < VEC; ++j) vp.e[j] = __fadd_rn(__fmul_rn(fm, vp.e[j]), __fmul_rn(bm, vb[u].e[j]));
+          }
+          st(v_post, i, vp);
         }
-        st(x_out, i, o);
+        if (x_out) {
+          Vec o;
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            o.e[j] = __fadd_rn(__fmul_rn(am, xp.e[j]), __fmul_rn(rm, x0[u].e[j]));
+            if (wrap) o.e[j] = wrap_2pi(o.e[j]);
+          }
+          st(x_out, i, o);
+        }
       }
     }
   }
@@ -336,12 +359,16 @@ extern "C" int l2hmc_mh_select(const float* x, const float* x_f, const float* x_
   const auto misaligned = [](const void* a) { return (reinterpret_cast<uintptr_t>(a) & 15u) != 0; };
   const bool vec4 = D % 4 == 0 && !(misaligned(x) || misaligned(x_f) || misaligned(x_b) || misaligned(v_f) ||
                                     misaligned(v_b) || misaligned(x_post) || misaligned(v_post) || misaligned(x_out));
-  if (vec4)
-    mh_select_kernel<4><<<chain_grid(N), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, wrap_2pi, x_post, v_post, p, x_out, accepted);
-  else
-    mh_select_kernel<1><<<chain_grid(N), kWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(
-        x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, wrap_2pi, x_post, v_post, p, x_out, accepted);
+  const bool full = x_b != nullptr || v_post != nullptr;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define L2HMC_MH(V, F)                                                                                          \
+  mh_select_kernel<V, F><<<chain_grid(N), kWarps * 32, 0, st>>>(x, x_f, x_b, v_f, v_b, p_f, p_b, u_dir, u_acc, N, D, \
+                                                                wrap_2pi, x_post, v_post, p, x_out, accepted)
+  if (vec4 && full) L2HMC_MH(4, true);
+  else if (vec4) L2HMC_MH(4, false);
+  else if (full) L2HMC_MH(1, true);
+  else L2HMC_MH(1, false);
+#undef L2HMC_MH
   return check_launch("mh_select_kernel");
 }
 

@@ -18,6 +18,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--chains", type=int, default=65536)
     ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--warm", type=int, default=3)
     args = ap.parse_args()
     T = X = 32
     N, D = args.chains, 2 * T * X
@@ -64,7 +65,7 @@ def main():
     if os.path.exists(pk):
         peak = float(json.load(open(pk))["hbm_gbs"])
     for name, nbytes, fn in cases:
-        for _ in range(3):
+        for _ in range(args.warm):
             _lib.check(fn())
         torch.cuda.synchronize()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
