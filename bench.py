@@ -24,6 +24,16 @@ import sys
 import threading
 import time
 
+# Only the JSON line may reach stdout: libraries (NCCL prints its version banner there) write to fd 1
+# directly, so fd 1 is pointed at stderr for the whole run and the line goes to a saved copy.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -129,7 +139,7 @@ def run_reference(args, rank):
     value, per_step, threads = cpu_reference_run(args.steps, args.warmup, chains)
     sample = (f"{chains} chains of the 32x32 workload per step (the GPU arm runs {args.chains_per_gpu} per GPU); "
               f"torch-CPU fp32 restatement of the TF graph, both directions integrated like the reference")
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "link-updates/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -406,7 +416,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--chains-per-gpu", type=int, default=65536)
-    ap.add_argument("--cpu-chains", type=int, default=256)
+    ap.add_argument("--cpu-chains", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-l2hmc", action="store_true")
@@ -424,9 +434,9 @@ def main():
     l2hmc = None if args.no_l2hmc else run_l2hmc(r, args.steps)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, per_step, threads = cpu_reference_run(steps=5, warmup=1, chains=args.cpu_chains)
+        v, per_step, threads = cpu_reference_run(steps=10, warmup=1, chains=args.cpu_chains)
         cpu = {"value": v, "unit": "link-updates/s", "cores": threads, "kind": "port",
-               "sample": f"{args.cpu_chains} chains of the same 32x32 M=10 workload, 5 MC steps after 1 warm-up, "
+               "sample": f"{args.cpu_chains} chains of the same 32x32 M=10 workload, 10 MC steps after 1 warm-up, "
                          f"{per_step:.3f} s/step; oracle restatement of the TF graph (TF 1.x not installable)"}
     if world > 1:
         import torch.distributed as dist
@@ -454,7 +464,7 @@ def main():
                         "ms_per_step": r["mc"]["ms"]},
         "l2hmc": l2hmc, "cpu_baseline": cpu, "observables": r["obs"],
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":
