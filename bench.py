@@ -335,7 +335,7 @@ def run_l2hmc(r, steps):
         return c["max_over_ranks"](ev[0].elapsed_time(ev[1])) / iters
 
     for tag, arch, T_, N, M_, eps, do_mc in (("config3_16x16_conv3D", "conv3D", 16, 2048, 5, 0.25, True),
-                                              ("config4_32x32_generic_nets", "generic", 32, 2048, 10, 0.1, False)):
+                                              ("config4_32x32_generic_nets", "generic", 32, 2048, 10, 0.1, True)):
         D_ = 2 * T_ * T_
         lat = GaugeLattice(T_, T_, 2, "U1", num_samples=1)
         np.random.seed(42)
@@ -371,7 +371,7 @@ def run_l2hmc(r, steps):
 
             def mc():
                 x_mc[0] = dyn.apply_transition(x_mc[0], 3.0, wrap=True)[3]
-            step_ms = events_ms(mc, max(3, steps // 4), warm=2)
+            step_ms = events_ms(mc, max(3, steps // 4), warm=1 if T_ >= 32 else 2)
             entry["mc_step_ms"] = step_ms
             entry["link_updates_per_s"] = world * N * D_ * M_ / (step_ms * 1e-3)
             dyn.raise_if_nonfinite()

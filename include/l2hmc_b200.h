@@ -341,6 +341,54 @@ typedef struct {
 
 int l2hmc_mog_mc_step(const l2hmc_gmm* gmm, const l2hmc_mog_args* args, void* stream);
 
+/* ------------------------------------------------------------------ loss value, run statistics
+ * Training loss VALUE of gauge_model.py:728-803 (_calc_loss) given the two chains' transitions
+ * (x --dynamics--> x_prop, px, x_out;  z ~ N(0,1) --dynamics--> pz): per chain
+ *   x_std = sum_d metric(x, x_prop) * px + 1e-3,  z_std = aux * (sum_d metric(z, x_prop) * pz + 1e-3)
+ *   std   = (ls * (1/x_std + 1/z_std) - (x_std + z_std) / ls) * std_weight
+ *   chg   = charge_weight * ((px |Qfft(x) - Qfft(x_prop)| + 1e-3) + aux * (pz |Qfft(z) - Qfft(x_prop)| + 1e-3))
+ * with Qfft = sum project_angle_approx(P) / 2pi (gauge_model.py:94-108, harmonics 1..4); loss[0] = mean over the
+ * chains (fixed summation tree); x_dq[n] = int32(|Q(x) - Q(x_out)|) with the exact projection (:761-762).
+ * The backward pass (tf.gradients, :805-832) is not part of this library yet. */
+#define L2HMC_METRIC_L1 0
+#define L2HMC_METRIC_L2 1
+#define L2HMC_METRIC_COS 2
+#define L2HMC_METRIC_COS2 3
+#define L2HMC_METRIC_COS_DIFF 4 /* gauge_model.py:631-657 */
+
+typedef struct {
+  int metric; /* L2HMC_METRIC_* */
+  float loss_scale, aux_weight, std_weight, charge_weight;
+} l2hmc_loss_params;
+
+int l2hmc_u1_loss(const l2hmc_loss_params* prm, const float* x, const float* x_prop, const float* z,
+                  const float* x_out, const float* px, const float* pz, int N, int T, int X,
+                  float* per_chain /* [N] */, int32_t* x_dq /* [N], nullable */, float* loss /* [1], nullable */,
+                  void* stream);
+/* _calc_top_charges(x, fft=True), gauge_model.py:699-713: q [N] float. */
+int l2hmc_u1_top_charges_fft(const float* x, int N, int T, int X, float* q, void* stream);
+
+/* Streaming form of calc_observables_stats (gauge_model.py:1473-1533).  sum / sumsq: [4][N] fp64 zero-initialised by
+ * the caller, rows = action, plaquette, charge, charge^2; hist: [2*qmax + 2] zero-initialised counts of the charges
+ * -qmax..qmax (+ one overflow slot), nullable.  Per MC step call l2hmc_stats_update with counted = 0 for the
+ * thermalisation steps (the first num_steps // therm_frac; only charge^2 accumulates there, the reference squares
+ * before it cuts) and 1 afterwards; charges are truncated toward zero like np.array(..., dtype=int).
+ * l2hmc_stats_finalize writes mean and scipy.stats.sem (ddof = 1), both [4][N] fp64. */
+typedef struct {
+  int N;
+  int qmax;
+  double* sum;
+  double* sumsq;
+  unsigned long long* hist;
+} l2hmc_run_stats;
+
+int l2hmc_stats_update(const l2hmc_run_stats* s, const float* action, const float* plaq, const float* charge,
+                       int counted, void* stream);
+int l2hmc_stats_finalize(const l2hmc_run_stats* s, long long n_counted, long long n_total, double* mean, double* err,
+                         void* stream);
+/* utils/trajectories.py:63-95: switches[n] += (mode[n] != prev[n]) when have_prev; prev[n] = mode[n]. */
+int l2hmc_mode_switches(const int32_t* mode, int32_t* prev, uint32_t* switches, int have_prev, int N, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -6,7 +6,7 @@ torch.distributed.
 """
 import ctypes
 import os
-from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_size_t, c_uint64, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_longlong, c_size_t, c_uint64, c_void_p
 
 import torch
 
@@ -67,6 +67,20 @@ class Gmm(Structure):
     _fields_ = [("k", c_int), ("m", c_int), ("mus", c_void_p), ("i_sigmas", c_void_p), ("log_consts", c_void_p)]
 
 
+class LossParams(Structure):
+    """l2hmc_loss_params (include/l2hmc_b200.h)."""
+    _fields_ = [("metric", c_int), ("loss_scale", c_float), ("aux_weight", c_float), ("std_weight", c_float),
+                ("charge_weight", c_float)]
+
+
+class RunStats(Structure):
+    """l2hmc_run_stats (include/l2hmc_b200.h)."""
+    _fields_ = [("N", c_int), ("qmax", c_int), ("sum", c_void_p), ("sumsq", c_void_p), ("hist", c_void_p)]
+
+
+METRICS = {"l1": 0, "l2": 1, "cos": 2, "cos2": 3, "cos_diff": 4}
+
+
 class MogArgs(Structure):
     """l2hmc_mog_args (include/l2hmc_b200.h)."""
     _fields_ = [
@@ -110,6 +124,12 @@ SIGNATURES = {
     "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_gmm_energy_force": [POINTER(Gmm), c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_mog_mc_step": [POINTER(Gmm), POINTER(MogArgs), c_void_p],
+    "l2hmc_u1_loss": [POINTER(LossParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                      c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_u1_top_charges_fft": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p],
+    "l2hmc_stats_update": [POINTER(RunStats), c_void_p, c_void_p, c_void_p, c_int, c_void_p],
+    "l2hmc_stats_finalize": [POINTER(RunStats), c_longlong, c_longlong, c_void_p, c_void_p, c_void_p],
+    "l2hmc_mode_switches": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p],
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],

@@ -1,0 +1,187 @@
+"""Host-side mirror of the parts of the reference's GaugeModel that sit next to the hot path
+(SURVEY section 8(f)): the training loss VALUE, the observable ops and the run-loop statistics.
+
+Mirrors, with the same names and argument meaning (reference l2hmc/gauge_model.py):
+  :585-613    _create_lattice / _create_dynamics (from the params dict of globals.py:22-47)
+  :631-657    _create_metric_fn  (here: the metric's name selects the kernel's formula)
+  :683-725    _calc_total_actions / _calc_avg_plaqs / _calc_top_charges(fft) / _calc_top_charges_diff
+  :728-803    _calc_loss(x, beta, **weights) -> (loss, x_out, px, x_dq)
+  :1039-1046  update_beta (1/beta-linear annealing)
+  :1473-1533  calc_observables_stats(observables, therm_frac)
+All arithmetic runs in csrc/loss.cu, csrc/stats.cu and the path's own kernels; there is no CPU fallback.
+The backward pass (_calc_loss_and_grads, :805-832), the optimiser and checkpointing are not built yet.
+"""
+import collections
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from .dynamics import GaugeDynamics
+from .lattice import GaugeLattice, to_device
+
+PARAMS = {  # globals.py:22-47 (the keys this mirror reads)
+    'time_size': 8, 'space_size': 8, 'link_type': 'U1', 'dim': 2, 'num_samples': 128, 'rand': False,
+    'num_steps': 5, 'eps': 0.25, 'loss_scale': 1., 'beta_init': 2., 'beta_final': 4., 'train_steps': 10000,
+    'hmc': False, 'network_arch': 'generic', 'metric': 'cos_diff', 'std_weight': 1., 'aux_weight': 1.,
+    'charge_weight': 1., 'annealing': True, 'data_format': 'channels_last',
+}
+
+
+class RunStats(object):
+    """Streaming calc_observables_stats (gauge_model.py:1473-1533): fold each MC step's (N,) observables into
+    device accumulators; nothing but the final statistics leaves the GPU.  `num_steps` is the planned run length
+    (the thermalisation cut is its first num_steps // therm_frac steps)."""
+
+    def __init__(self, num_chains, num_steps, therm_frac=10, qmax=64, device="cuda"):
+        _lib.require_cuda()
+        self.N, self.num_steps, self.therm_steps = int(num_chains), int(num_steps), int(num_steps) // int(therm_frac)
+        self.device, self.qmax, self.step = torch.device(device), int(qmax), 0
+        self.sum = torch.zeros(4, self.N, dtype=torch.float64, device=self.device)
+        self.sumsq = torch.zeros(4, self.N, dtype=torch.float64, device=self.device)
+        self.hist = torch.zeros(2 * self.qmax + 2, dtype=torch.int64, device=self.device)
+        s = _lib.RunStats()
+        s.N, s.qmax = self.N, self.qmax
+        s.sum, s.sumsq = _lib.dptr(self.sum, torch.float64), _lib.dptr(self.sumsq, torch.float64)
+        s.hist = _lib.dptr(self.hist, torch.int64)        # non-negative counts: same bits as unsigned long long
+        self._s = s
+
+    def update(self, actions, plaqs, charges):
+        """One MC step's observables, (N,) each (device tensors or arrays; charges float or int32)."""
+        a, p = to_device(actions, self.device).reshape(-1), to_device(plaqs, self.device).reshape(-1)
+        q = charges if isinstance(charges, torch.Tensor) else torch.as_tensor(np.asarray(charges))
+        q = q.to(device=self.device, dtype=torch.float32).reshape(-1).contiguous()
+        counted = int(self.step >= self.therm_steps)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.get_lib().l2hmc_stats_update(ctypes.byref(self._s), _lib.dptr(a), _lib.dptr(p), _lib.dptr(q),
+                                                         counted, _lib.stream_ptr()))
+        self.step += 1
+
+    def finalize(self):
+        """((mean, err) of actions, plaqs, charges, suscept -- (N,) fp64 host arrays each -- , charge_probabilities)."""
+        counted = self.step - min(self.step, self.therm_steps)
+        mean = torch.empty(4, self.N, dtype=torch.float64, device=self.device)
+        err = torch.empty_like(mean)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.get_lib().l2hmc_stats_finalize(ctypes.byref(self._s), counted, self.step,
+                                                           _lib.dptr(mean, torch.float64), _lib.dptr(err, torch.float64),
+                                                           _lib.stream_ptr()))
+        mean, err, hist = mean.cpu().numpy(), err.cpu().numpy(), self.hist.cpu().numpy()
+        if hist[-1]:
+            raise OverflowError(f"{int(hist[-1])} charges outside [-{self.qmax}, {self.qmax}]: raise qmax")
+        total = hist[:-1].sum()
+        probs = collections.OrderedDict((int(i) - self.qmax, hist[i] / total) for i in np.nonzero(hist[:-1])[0])
+        return tuple((mean[i], err[i]) for i in range(4)) + (probs,)
+
+
+class GaugeModel(object):
+    def __init__(self, params=None, lattice=None, dynamics=None, device="cuda"):
+        _lib.require_cuda()
+        self.params = dict(PARAMS)
+        self.params.update(params or {})
+        for key, val in self.params.items():
+            setattr(self, key, val)
+        self.device = torch.device(device)
+        self.lattice = lattice if lattice is not None else self._create_lattice()
+        self.batch_size = self.num_samples = self.lattice.samples.shape[0] if lattice is not None else self.num_samples
+        self.x_dim = self.lattice.num_links
+        self.dynamics = dynamics if dynamics is not None else self._create_dynamics(self.lattice)
+        self.loss_weights = {k: getattr(self, k) for k in ('std_weight', 'aux_weight', 'charge_weight')}
+        self.metric_fn = self._create_metric_fn(self.metric)
+        self.beta = self.beta_init
+        self._z_step = 0
+
+    # ------------------------------------------------------------------ construction (:585-613)
+    def _create_lattice(self):
+        return GaugeLattice(time_size=self.time_size, space_size=self.space_size, dim=self.dim,
+                            link_type=self.link_type, num_samples=self.num_samples, rand=self.rand)
+
+    def _create_dynamics(self, lattice, **kwargs):
+        kw = dict(num_steps=self.num_steps, eps=self.eps, network_arch=self.network_arch, hmc=self.hmc,
+                  eps_trainable=True, data_format=self.data_format, device=self.device)
+        kw.update(kwargs)
+        return GaugeDynamics(lattice=lattice, potential_fn=lattice.get_energy_function(), **kw)
+
+    @staticmethod
+    def _create_metric_fn(metric):
+        """(:631-657) The returned object only names the formula; the kernel evaluates it."""
+        if metric not in _lib.METRICS:
+            raise AttributeError(f"metric={metric}. Expected one of: 'l1', 'l2', 'cos', 'cos2', or 'cos_diff'.")
+        return metric
+
+    def update_beta(self, step):
+        """(:1039-1046) 1/beta-linear annealing from beta_init to beta_final over train_steps."""
+        temp = ((1. / self.beta_init - 1. / self.beta_final) * (1. - step / float(self.train_steps))
+                + 1. / self.beta_final)
+        return 1. / temp
+
+    # ------------------------------------------------------------------ observable ops (:683-725)
+    def _x(self, x):
+        return to_device(x, self.device).reshape(-1, self.x_dim)
+
+    def _calc_total_actions(self, x):
+        return self.lattice.observables(self._x(x))[0]
+
+    def _calc_avg_plaqs(self, x):
+        return self.lattice.observables(self._x(x))[1]
+
+    def _calc_top_charges(self, x, fft=False):
+        x = self._x(x)
+        if not fft:
+            return self.lattice.observables(x)[2]
+        q = torch.empty(x.shape[0], dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.get_lib().l2hmc_u1_top_charges_fft(_lib.dptr(x), x.shape[0], self.lattice.time_size,
+                                                               self.lattice.space_size, _lib.dptr(q), _lib.stream_ptr()))
+        return q
+
+    # ------------------------------------------------------------------ loss value (:728-803)
+    def _calc_loss(self, x, beta, draws_x=None, z=None, draws_z=None, **weights):
+        """(loss, x_out, px, x_dq).  draws_x / draws_z = (v_f, v_b, u_dir, u_acc) and `z` inject the reference's
+        in-graph draws (:754-758 over gauge_dynamics.py:211-248); all-None runs on the Philox stream."""
+        x = self._x(x)
+        N, D = x.shape
+        w = dict(self.loss_weights)
+        w.update(weights)
+        dyn = self.dynamics
+        inj = lambda d: {} if d is None else dict(momentum_f=d[0], momentum_b=d[1], direction_uniform=d[2],
+                                                  accept_uniform=d[3])
+        x_prop, _, px, x_out = dyn(x, beta, **inj(draws_x))
+        if z is None:
+            z = torch.empty_like(x)
+            with torch.cuda.device(x.device):                  # z ~ N(0,1): its own Philox substream
+                _lib.check(_lib.get_lib().l2hmc_philox_draws(int(dyn.seed) ^ 0x5A5A5A5A, self._z_step, int(dyn.chain_offset), N, D,
+                                                             _lib.dptr(z), None, None, _lib.stream_ptr()))
+            self._z_step += 1
+        z = self._x(z)
+        _, _, pz, _ = dyn(z, beta, **inj(draws_z))
+        prm = _lib.LossParams()
+        prm.metric, prm.loss_scale = _lib.METRICS[self.metric_fn], float(self.loss_scale)
+        prm.aux_weight, prm.std_weight, prm.charge_weight = (float(w[k]) for k in ('aux_weight', 'std_weight',
+                                                                                   'charge_weight'))
+        per_chain = torch.empty(N, dtype=torch.float32, device=x.device)
+        x_dq = torch.empty(N, dtype=torch.int32, device=x.device)
+        loss = torch.empty(1, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.get_lib().l2hmc_u1_loss(
+                ctypes.byref(prm), _lib.dptr(x), _lib.dptr(x_prop), _lib.dptr(z), _lib.dptr(x_out), _lib.dptr(px),
+                _lib.dptr(pz), N, self.lattice.time_size, self.lattice.space_size, _lib.dptr(per_chain),
+                _lib.dptr(x_dq, torch.int32), _lib.dptr(loss), _lib.stream_ptr()))
+        self.last_per_chain_loss = per_chain
+        return loss[0], x_out, px, x_dq
+
+    def _calc_loss_and_grads(self, x, beta, **weights):
+        raise NotImplementedError("the backward pass (tf.gradients of the loss, gauge_model.py:805-832) is the next "
+                                  "row of SURVEY section 8(f); only the loss value is built")
+
+    # ------------------------------------------------------------------ statistics (:1473-1533)
+    def calc_observables_stats(self, observables, therm_frac=10):
+        """observables = (actions_dict, plaqs_dict, charges_dict) of {step: (N,) array}; returns
+        (actions_stats, plaqs_stats, charges_stats, suscept_stats, charge_probabilities)."""
+        actions, plaqs, charges = (list(d.values()) for d in observables[:3])
+        stats = RunStats(len(np.asarray(actions[0]).reshape(-1)) if not isinstance(actions[0], torch.Tensor)
+                         else actions[0].numel(), len(actions), therm_frac, device=self.device)
+        for a, p, q in zip(actions, plaqs, charges):
+            stats.update(a, p, q)
+        return stats.finalize()

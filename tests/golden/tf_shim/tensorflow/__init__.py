@@ -228,7 +228,9 @@ def mod(x, y):
 def random_normal(shape, mean=0.0, stddev=1.0, dtype=torch.float32, name=None):
     out = _STATE["normals"].pop(0)
     assert list(out.shape) == _shape_list(shape), (out.shape, shape)
-    return out
+    # a graph node other ops may differentiate with respect to (the auxiliary z-chain of
+    # gauge_model.py:757-758 feeds a drawn tensor into grad_potential)
+    return torch.as_tensor(out).detach().clone().requires_grad_(True)
 
 
 def random_uniform(shape, minval=0, maxval=None, dtype=torch.float32, name=None):
@@ -480,3 +482,23 @@ for _name in ("tensorflow.python", "tensorflow.python.ops", "tensorflow.python.o
 _sys.modules["tensorflow.python"].ops = _sys.modules["tensorflow.python.ops"]
 for _sub in ("variable_scope", "array_ops", "math_ops", "nn_ops"):
     setattr(_sys.modules["tensorflow.python.ops"], _sub, _sys.modules["tensorflow.python.ops." + _sub])
+
+
+# ---- what `import gauge_model` touches at module level (gauge_model.py:52-66): never executed as TF
+__version__ = "1.13.1-shim"
+logging = types.SimpleNamespace(INFO=20, set_verbosity=lambda *_a, **_k: None, info=lambda *_a, **_k: None)
+
+
+def set_random_seed(seed):
+    set_init_seed(int(seed))
+
+
+for _name in ("tensorflow.python.debug", "tensorflow.python.client", "tensorflow.python.client.timeline",
+              "tensorflow.core", "tensorflow.core.protobuf", "tensorflow.core.protobuf.rewriter_config_pb2"):
+    _sys.modules.setdefault(_name, types.ModuleType(_name))
+_sys.modules["tensorflow.python"].debug = _sys.modules["tensorflow.python.debug"]
+_sys.modules["tensorflow.python"].client = _sys.modules["tensorflow.python.client"]
+_sys.modules["tensorflow.python.client"].timeline = _sys.modules["tensorflow.python.client.timeline"]
+_sys.modules["tensorflow.core"].protobuf = _sys.modules["tensorflow.core.protobuf"]
+_sys.modules["tensorflow.core.protobuf"].rewriter_config_pb2 = \
+    _sys.modules["tensorflow.core.protobuf.rewriter_config_pb2"]

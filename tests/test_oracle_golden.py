@@ -236,3 +236,68 @@ def test_mog_step_reversibility_and_tunneling_rate():
     traj[:, 0, 0] = [1, -1, -1, 1, 1]        # three switches in four steps
     traj[:, 1, 0] = [1, 1, 1, 1, 1]
     assert np.allclose(mog.calc_tunneling_rate(traj, [[1., 0.], [-1., 0.]], 2), [0.5, 0.0])
+
+
+# ----------------------------------------------------------------------------- section 8(f) rows: loss value, run statistics
+def _train_tags(g, prefix):
+    return sorted({k.rsplit(".meta", 1)[0] for k in g if k.startswith(prefix) and k.endswith(".meta")})
+
+
+def train_dyn_from(g, tag):
+    T, X, N, M, hmc = (int(v) for v in g[tag + ".meta"])
+    arch = tag.split(".")[1]
+    nets = {}
+    if not hmc:
+        for net in ("XNet", "VNet"):
+            pre = f"{tag}.{net}."
+            nets[net] = {k[len(pre):]: v for k, v in g.items() if k.startswith(pre)}
+    dyn = orc.OracleDynamics(T, X, M, float(g[tag + ".eps"]), hmc=bool(hmc), network_arch="generic" if hmc else arch,
+                             mask=g[tag + ".mask"], xnet=nets.get("XNet"), vnet=nets.get("VNet"))
+    return dyn, (T, X, N, M, bool(hmc))
+
+
+def test_loss_value_against_reference_goldens(golden):
+    """gauge_model.py:728-803 (_calc_loss) restated in oracle/train_oracle.py vs the unmodified reference."""
+    from oracle import train_oracle as tro
+    g = golden("train_cases")
+    tags = _train_tags(g, "loss")
+    assert len(tags) == 6
+    for tag in tags:
+        dyn, (T, X, N, M, hmc) = train_dyn_from(g, tag)
+        metric = tag.split(".")[-1]
+        aux, std, chg = (float(v) for v in g[tag + ".weights"])
+        beta, ls = float(g[tag + ".beta"]), float(g[tag + ".loss_scale"])
+        for nm in ("x", "x_prop", "z"):
+            close(tro.top_charges(g[f"{tag}.{nm}"], T, X, fft=True), g[f"{tag}.qfft.{nm}"], rtol=1e-5, atol=2e-5)
+            close(tro.top_charges(g[f"{tag}.{nm}"], T, X, fft=False), g[f"{tag}.q.{nm}"], rtol=1e-5, atol=2e-5)
+        # the loss terms on the reference's own proposals: isolates the loss arithmetic
+        loss, per_chain, x_dq = tro.loss_terms(g[tag + ".x"], g[tag + ".x_prop"], g[tag + ".z"], g[tag + ".px"],
+                                               g[tag + ".pz"], g[tag + ".x_out"], T, X, metric, ls, aux, std, chg)
+        scale = float(per_chain.abs().max())
+        close(loss, g[tag + ".loss"], rtol=2e-5, atol=2e-5 * scale)
+        assert np.array_equal(x_dq.numpy(), g[tag + ".x_dq"])
+        # end to end through the oracle dynamics (both chains)
+        loss2, x_out, px, x_dq2 = tro.calc_loss(
+            dyn, g[tag + ".x"], beta, (g[tag + ".v_f"], g[tag + ".v_b"], g[tag + ".u_dir"], g[tag + ".u_acc"]),
+            g[tag + ".z"], (g[tag + ".vz_f"], g[tag + ".vz_b"], g[tag + ".uz_dir"], g[tag + ".uz_acc"]),
+            metric=metric, loss_scale=ls, aux_weight=aux, std_weight=std, charge_weight=chg)
+        close(px, g[tag + ".px"], rtol=1e-3, atol=1e-6)
+        close(x_out, g[tag + ".x_out"], rtol=1e-4, atol=2e-4)
+        close(loss2, g[tag + ".loss"], rtol=5e-3, atol=5e-3 * scale)     # 1/x_std amplifies the proposals' rounding
+        assert np.array_equal(x_dq2.numpy(), g[tag + ".x_dq"])
+
+
+def test_observables_stats_against_reference_goldens(golden):
+    """gauge_model.py:1473-1533 (calc_observables_stats) restated vs the unmodified reference."""
+    from oracle import train_oracle as tro
+    g = golden("train_cases")
+    tags = _train_tags(g, "stats")
+    assert len(tags) == 4
+    for tag in tags:
+        steps, N, tf_ = (int(v) for v in g[tag + ".meta"])
+        st = tro.calc_observables_stats(g[tag + ".actions"], g[tag + ".plaqs"], g[tag + ".charges"], therm_frac=tf_)
+        for nm in ("actions", "plaqs", "charges", "suscept"):
+            np.testing.assert_allclose(st[nm][0], g[f"{tag}.{nm}.mean"], rtol=1e-6, atol=1e-7)
+            np.testing.assert_allclose(st[nm][1], g[f"{tag}.{nm}.err"], rtol=1e-5, atol=1e-7)
+        assert list(st["charge_probabilities"].keys()) == list(g[tag + ".prob.keys"])
+        np.testing.assert_allclose(list(st["charge_probabilities"].values()), g[tag + ".prob.vals"], rtol=1e-12)
