@@ -4,6 +4,8 @@
 
   gauge_model.py:728-803    GaugeModel._calc_loss  (std loss on the metric, Fourier-smoothed charge loss, the x- and the
                             auxiliary z-chain; :94-108 project_angle_approx, :631-657 metric functions, :692-725 charges)
+  gauge_model.py:805-832    tf.gradients(loss, dynamics.variables): d loss / d eps and d loss / d weights, stored for
+                            the backward kernels of the next round (keys `<tag>.grad.*`)
   gauge_model.py:1473-1533  GaugeModel.calc_observables_stats (thermalisation cut, mean / scipy sem, charge histogram)
 
 Run in the build container only:  python tests/golden/make_golden_train.py  -> tests/golden/train_cases.npz
@@ -86,12 +88,24 @@ def gen_loss_cases(out):
             mg.dump_net(dyn.position_fn, tag + ".XNet", out)
             mg.dump_net(dyn.momentum_fn, tag + ".VNet", out)
         model = bare_model(lat, dyn, N, metric, ls)
+        named = {"eps": dyn.eps}
+        if not hmc:
+            for net_name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
+                for nm in mg.net_layers(net):
+                    named[f"{net_name}.{nm}.kernel"], named[f"{net_name}.{nm}.bias"] = getattr(net, nm).kernel, getattr(net, nm).bias
+                named[f"{net_name}.coeff_scale"] = net.coeff_scale
+                named[f"{net_name}.coeff_transformation"] = net.coeff_transformation
+        for v in named.values():
+            v.requires_grad_(True)
         # draw order inside _calc_loss (gauge_model.py:754-760 over gauge_dynamics.py:211-248):
         #   x-chain: v_f, v_b | u_dir, u_acc ; z ; z-chain: vz_f, vz_b | uz_dir, uz_acc
         tf.inject_randoms(normals=[v_f, v_b, z, vz_f, vz_b], uniforms=[u_dir, u_acc, uz_dir, uz_acc])
         loss, x_out, px, x_dq = model._calc_loss(leaf(x), tf.constant(beta, dtype=tf.float32), **wts)
         out[tag + ".loss"], out[tag + ".x_out"], out[tag + ".px"] = npf(loss), npf(x_out), npf(px)
         out[tag + ".x_dq"] = x_dq.detach().cpu().numpy().astype(np.int32)
+        grads = tf.gradients(loss, list(named.values()))          # gauge_model.py:823
+        for (nm, v), gr in zip(named.items(), grads):
+            out[f"{tag}.grad.{nm}"] = npf(torch.zeros_like(v) if gr is None else gr)
         # the pieces, for localising a mismatch
         tf.inject_randoms(normals=[v_f, v_b], uniforms=[u_dir, u_acc])
         x_, _, px2, _ = dyn(leaf(x), tf.constant(beta, dtype=tf.float32))

@@ -242,7 +242,9 @@ def random_uniform(shape, minval=0, maxval=None, dtype=torch.float32, name=None)
 def gradients(ys, xs, name=None):
     single = not isinstance(xs, (list, tuple))
     xs_l = [xs] if single else list(xs)
-    g = torch.autograd.grad(ys.sum(), xs_l, retain_graph=True, allow_unused=True)
+    # create_graph: the loss gradient (gauge_model.py:823) differentiates THROUGH the force, itself a
+    # tf.gradients node (gauge_dynamics.py:707); TF keeps every gradient op differentiable
+    g = torch.autograd.grad(ys.sum(), xs_l, retain_graph=True, create_graph=True, allow_unused=True)
     return list(g)
 
 
