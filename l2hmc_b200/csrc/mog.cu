@@ -35,7 +35,7 @@ struct MogParams {
   l2hmc_net_weights net[2];
 };
 
-// shared-memory image of one network, padded: W1[HP][2*KD] (in0 | in1 columns), b1e[L][HP] (bias with the
+// shared-memory image of one network, padded: W1[HP/2][2*KD][2] (in0 | in1 columns, unit pairs interleaved), b1e[L][HP] (bias with the
 // time embedding folded in, one row per step), W2t[HP][HP] (row j = weights INTO unit j), b2[HP],
 // W3[HP][3*KD] (S | T | F columns per hidden unit), b3[3*KD], escale[2*KD] = exp(coeff_s | coeff_f)
 template <int KD, int HP>
@@ -58,8 +58,9 @@ __device__ void load_net(float* s, const l2hmc_net_weights& w, int k, int H, int
   __syncthreads();
   for (int i = tid; i < H * k; i += nt) {
     const int j = i / k, c = i % k;                       // hidden unit j, input component c
-    s[NS::W1 + j * 2 * KD + c] = w.w_in0[c * H + j];      // Keras (in, out)
-    s[NS::W1 + j * 2 * KD + KD + c] = w.w_in1[c * H + j];
+    // pairs of hidden units (2q, 2q+1) interleaved per input component: [q][c'][parity]
+    s[NS::W1 + ((j >> 1) * 2 * KD + c) * 2 + (j & 1)] = w.w_in0[c * H + j];      // Keras (in, out)
+    s[NS::W1 + ((j >> 1) * 2 * KD + KD + c) * 2 + (j & 1)] = w.w_in1[c * H + j];
     s[NS::W3 + j * 3 * KD + c] = w.w_s[j * k + c];
     s[NS::W3 + j * 3 * KD + KD + c] = w.w_tr[j * k + c];
     s[NS::W3 + j * 3 * KD + 2 * KD + c] = w.w_q[j * k + c];
@@ -87,45 +88,55 @@ __device__ void load_net(float* s, const l2hmc_net_weights& w, int k, int H, int
 }
 
 // S, T, F = net([in0, in1, t(step)])   (network.py:89-114)
+// Packed fp32x2 arithmetic (FFMA2: two FMAs per lane per instruction -- the only way to the full FP32 rate
+// on sm_100): layer 1 pairs two hidden units, layer 2 pairs two consecutive inputs of one unit (even / odd
+// partial sums, added at the end), the heads pair two outputs.  Each lane of a pair is an ordinary fmaf.
 template <int KD, int HP>
 __device__ __forceinline__ void net_eval(const float* __restrict__ s, int step, const float* in0, const float* in1,
                                          float* S, float* Tr, float* F) {
   using NS = NetSmem<KD, HP>;
-  float h1[HP];
+  f32x2 in0p[KD], in1p[KD];
 #pragma unroll
-  for (int j = 0; j < HP; ++j) {
-    float acc = s[NS::B1E + step * HP + j];
+  for (int c = 0; c < KD; ++c) in0p[c] = pack2(in0[c], in0[c]), in1p[c] = pack2(in1[c], in1[c]);
+  f32x2 h1[HP / 2];                       // (h1[2q], h1[2q+1])
+#pragma unroll
+  for (int q = 0; q < HP / 2; ++q) {
+    f32x2 acc = *reinterpret_cast<const f32x2*>(s + NS::B1E + step * HP + 2 * q);
+    const f32x2* w = reinterpret_cast<const f32x2*>(s + NS::W1 + q * 4 * KD);   // [c' = 0 .. 2KD) pairs over (2q, 2q+1)
 #pragma unroll
     for (int c = 0; c < KD; ++c) {
-      acc = fmaf(in0[c], s[NS::W1 + j * 2 * KD + c], acc);
-      acc = fmaf(in1[c], s[NS::W1 + j * 2 * KD + KD + c], acc);
+      acc = fma2(in0p[c], w[c], acc);
+      acc = fma2(in1p[c], w[KD + c], acc);
     }
-    h1[j] = fmaxf(acc, 0.f);
+    h1[q] = pack2(fmaxf(lo2(acc), 0.f), fmaxf(hi2(acc), 0.f));
   }
-  float o[3 * KD];
+  f32x2 o[3 * KD / 2];
 #pragma unroll
-  for (int c = 0; c < 3 * KD; ++c) o[c] = s[NS::B3 + c];
+  for (int c = 0; c < 3 * KD / 2; ++c) o[c] = *reinterpret_cast<const f32x2*>(s + NS::B3 + 2 * c);
 #pragma unroll 2
   for (int j = 0; j < HP; ++j) {
-    float acc = s[NS::B2 + j];
-    const float4* wrow = reinterpret_cast<const float4*>(s + NS::W2 + j * HP);
+    f32x2 acc = pack2(s[NS::B2 + j], 0.f);
+    const ulonglong2* wrow = reinterpret_cast<const ulonglong2*>(s + NS::W2 + j * HP);
 #pragma unroll
     for (int q = 0; q < HP / 4; ++q) {
-      const float4 w4 = wrow[q];
-      acc = fmaf(h1[4 * q + 0], w4.x, acc);
-      acc = fmaf(h1[4 * q + 1], w4.y, acc);
-      acc = fmaf(h1[4 * q + 2], w4.z, acc);
-      acc = fmaf(h1[4 * q + 3], w4.w, acc);
+      const ulonglong2 w4 = wrow[q];
+      acc = fma2(h1[2 * q], w4.x, acc);
+      acc = fma2(h1[2 * q + 1], w4.y, acc);
     }
-    const float h2 = fmaxf(acc, 0.f);
+    const float h2 = fmaxf(__fadd_rn(lo2(acc), hi2(acc)), 0.f);
+    const f32x2 h2p = pack2(h2, h2);
+    const f32x2* w3 = reinterpret_cast<const f32x2*>(s + NS::W3 + j * 3 * KD);
 #pragma unroll
-    for (int c = 0; c < 3 * KD; ++c) o[c] = fmaf(h2, s[NS::W3 + j * 3 * KD + c], o[c]);
+    for (int c = 0; c < 3 * KD / 2; ++c) o[c] = fma2(h2p, w3[c], o[c]);
   }
+  float of[3 * KD];
+#pragma unroll
+  for (int c = 0; c < 3 * KD / 2; ++c) of[2 * c] = lo2(o[c]), of[2 * c + 1] = hi2(o[c]);
 #pragma unroll
   for (int c = 0; c < KD; ++c) {
-    S[c] = __fmul_rn(s[NS::ESC + c], tanhf(o[c]));
-    Tr[c] = o[KD + c];
-    F[c] = __fmul_rn(s[NS::ESC + KD + c], tanhf(o[2 * KD + c]));
+    S[c] = __fmul_rn(s[NS::ESC + c], tanhf(of[c]));
+    Tr[c] = of[KD + c];
+    F[c] = __fmul_rn(s[NS::ESC + KD + c], tanhf(of[2 * KD + c]));
   }
 }
 
