@@ -162,73 +162,71 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
 
 
 // ---------------------------------------------------------------------------------------------
-// Register-tiled variant for F in {8, 16, 32} and T, X multiples of 4 (BASELINE configs 2-4 have
-// F = X = T): kChains chains per CTA pass, no boundary logic in the arithmetic.
+// Register-tiled, packed-fp32x2 variant for F in {8, 16, 32} and T, X multiples of 4 (BASELINE configs
+// 2-4 have F = X = T): kChains chains per CTA pass, no boundary logic in the arithmetic, and every
+// multiply-add is one lane of an FFMA2 (two FMAs per thread per instruction: the plain FFMA pipe tops
+// out at half the FP32 rate on sm_100).
 //   staging: the NEXT pass's links are fetched into registers (PF float4 per thread) before this
-//            pass computes, and written -- mask applied -- into a zero-bordered (T+2) x (X+2) plane,
-//            so TF's 'same' zero padding is a plain load.
-//   phase 1: a thread keeps the 18 taps of ITS filter f = tid % F in registers for the whole kernel
-//            and computes two neighbouring pooled outputs from one 4x6 input patch
-//            (24 LDS.64 per 216 FFMA).
-//   phase 2: a thread owns one pooled output position x four output channels: per block of four
-//            input filters it reads the 3x3 P1 patch as float4 over f (9 LDS.128) and the weights as
-//            float4 over c (16 LDS.128) for 256 FFMA.  P1 has a zero row/column at the end (the
-//            2-wide kernel's padding) and rows padded to F + 4 floats, so the four positions a warp
-//            reads side by side fall into different banks.
-// The arithmetic per output (tap order, bias after max, relu last) is the generic kernel's.
-constexpr int kChains = 2;
-
-template <int F, int PF>
-__global__ void __launch_bounds__(kThreads, 2) conv3d_tiled_kernel(const ConvParams p) {
+//            pass computes, and written -- mask applied, each value DUPLICATED (a, a) so a 64-bit load is a
+//            ready broadcast operand -- into a zero-bordered (T+2) x (X+2) plane: TF's 'same' zero
+//            padding is a plain load.
+//   phase 1: a thread keeps the 18 taps of TWO neighbouring filters (f, f+1) as pairs in registers for
+//            the whole kernel and streams the 4x4 input patch of one pooled output row by row
+//            (16 LDS.128 per 108 FFMA2); the pooled value goes to P1, duplicated.
+//   phase 2: a thread owns one pooled output position x four output channels (two pairs): per pair of
+//            input filters it reads the 3x3 P1 patch (9 LDS.128) and the weights as channel pairs
+//            (8 LDS.128) for 64 FFMA2.  P1 has a zero row / column at the end (the 2-wide kernel's padding).
+// Per output the taps are accumulated in the generic kernel's order, so the results are bit-identical to it.
+template <int F, int PF, int CH, int TH>
+__global__ void __launch_bounds__(TH, 512 / TH) conv3d_tiled_kernel(const ConvParams p) {
   extern __shared__ __align__(16) float sm[];
-  constexpr int C = 2 * F, FP = F + 4, CG = C / 4, G = kThreads / F;
+  constexpr int C = 2 * F, FPD = 2 * F + 8, CG = C / 4, FH = F / 2, G = TH / FH;
   const int T = p.T, X = p.X;
   const int T1 = T / 2, X1 = X / 2, T2 = T1 / 2, X2 = X1 / 2;
-  const int D = 2 * T * X, XB = X + 2, IN = (T + 2) * XB * 2;          // bordered input plane (floats)
-  const int X1B = X1 + 1, P1 = (T1 + 1) * X1B * FP;                   // P1 with a zero end row / column
+  const int D = 2 * T * X, XB = X + 2, IN = (T + 2) * XB * 4;          // bordered plane: [t][x][mu][dup]
+  const int X1B = X1 + 1, P1 = (T1 + 1) * X1B * FPD;                  // P1: [t1][x1][f][dup] + zero end row / column
   float* s_w2 = sm;                        // [4][F][C]   (kd = 0 taps only)
   float* s_b2 = s_w2 + 4 * F * C;          // [C]
-  float* s_in = s_b2 + C;                  // [kChains][T+2][X+2][2]
-  float* s_p1 = s_in + kChains * IN;       // [kChains][T1+1][X1+1][FP]
+  float* s_in = s_b2 + C;                  // [CH][IN]
+  float* s_p1 = s_in + CH * IN;       // [CH][P1]
   const int tid = threadIdx.x;
 
-  for (int i = tid; i < 4 * F * C; i += kThreads) {
+  for (int i = tid; i < 4 * F * C; i += TH) {
     const int tap = i / (F * C), rest = i % (F * C);
     s_w2[i] = p.w2[static_cast<size_t>(tap) * 2 * F * C + rest];
   }
-  for (int i = tid; i < C; i += kThreads) s_b2[i] = p.b2[i];
-  for (int i = tid; i < kChains * IN; i += kThreads) s_in[i] = 0.f;    // borders stay zero for the whole kernel
-  for (int i = tid; i < kChains * P1; i += kThreads) s_p1[i] = 0.f;
-  const int f = tid % F, grp = tid / F;
-  float w[3][3][2];
+  for (int i = tid; i < C; i += TH) s_b2[i] = p.b2[i];
+  for (int i = tid; i < CH * IN; i += TH) s_in[i] = 0.f;    // borders stay zero for the whole kernel
+  for (int i = tid; i < CH * P1; i += TH) s_p1[i] = 0.f;
+  const int fp = tid % FH, grp = tid / FH;                             // filters 2 fp, 2 fp + 1
+  f32x2 w[3][3][2];
 #pragma unroll
   for (int a = 0; a < 3; ++a)
 #pragma unroll
-    for (int b = 0; b < 3; ++b) {
-      w[a][b][0] = p.w1[((a * 3 + b) * 2 + 0) * F + f];
-      w[a][b][1] = p.w1[((a * 3 + b) * 2 + 1) * F + f];
-    }
-  const float bias1 = p.b1[f];
-  const int XPR = X1 / 2;                  // pairs of pooled columns
+    for (int b = 0; b < 3; ++b)
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+        w[a][b][m] = pack2(p.w1[((a * 3 + b) * 2 + m) * F + 2 * fp], p.w1[((a * 3 + b) * 2 + m) * F + 2 * fp + 1]);
+  const float bias1a = p.b1[2 * fp], bias1b = p.b1[2 * fp + 1];
   const int quads = D / 4;                 // float4 per chain
 
   float4 pre[PF];
-  auto fetch = [&](int n0) {               // links of chains n0 .. n0 + kChains - 1 -> registers
+  auto fetch = [&](int n0) {               // links of chains n0 .. n0 + CH - 1 -> registers
 #pragma unroll
     for (int q = 0; q < PF; ++q) {
-      const int i4 = tid + q * kThreads;
+      const int i4 = tid + q * TH;
       const int ch = i4 / quads;
       pre[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (ch < kChains && n0 + ch < p.N)
+      if (ch < CH && n0 + ch < p.N)
         pre[q] = __ldcs(reinterpret_cast<const float4*>(p.in + static_cast<size_t>(n0 + ch) * D) + (i4 - ch * quads));
     }
   };
-  auto stage = [&](int n0) {               // registers -> bordered plane, mask applied
+  auto stage = [&](int n0) {               // registers -> bordered plane, mask applied, values duplicated
 #pragma unroll
     for (int q = 0; q < PF; ++q) {
-      const int i4 = tid + q * kThreads;
+      const int i4 = tid + q * TH;
       const int ch = i4 / quads;
-      if (ch >= kChains || n0 + ch >= p.N) continue;
+      if (ch >= CH || n0 + ch >= p.N) continue;
       const int j = (i4 - ch * quads) * 4;
       float4 a = pre[q];
       const bool alt = p.row_set != nullptr && p.row_set[n0 + ch] != 0;
@@ -240,101 +238,105 @@ __global__ void __launch_bounds__(kThreads, 2) conv3d_tiled_kernel(const ConvPar
         a = make_float4(__fmul_rn(m.x, a.x), __fmul_rn(m.y, a.y), __fmul_rn(m.z, a.z), __fmul_rn(m.w, a.w));
       }
       const int site = j >> 1, t = site / X, x = site - t * X;       // two sites (x, x + 1) of one row
-      float* dst = s_in + ch * IN + ((t + 1) * XB + x + 1) * 2;
-      *reinterpret_cast<float2*>(dst) = make_float2(a.x, a.y);
-      *reinterpret_cast<float2*>(dst + 2) = make_float2(a.z, a.w);
+      float* dst = s_in + ch * IN + ((t + 1) * XB + x + 1) * 4;
+      *reinterpret_cast<float4*>(dst) = make_float4(a.x, a.x, a.y, a.y);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(a.z, a.z, a.w, a.w);
     }
   };
 
-  int n0 = blockIdx.x * kChains;
+  int n0 = blockIdx.x * CH;
   if (n0 < p.N) fetch(n0);
-  for (; n0 < p.N; n0 += gridDim.x * kChains) {
-    const int nch = min(kChains, p.N - n0);
+  for (; n0 < p.N; n0 += gridDim.x * CH) {
+    const int nch = min(CH, p.N - n0);
     __syncthreads();                       // previous pass done with s_in / s_p1 (and the zero fill on the first)
     stage(n0);
-    const int n_next = n0 + gridDim.x * kChains;
+    const int n_next = n0 + gridDim.x * CH;
     if (n_next < p.N) fetch(n_next);       // in flight while this pass computes
     __syncthreads();
 
-    // ---- phase 1
-    for (int item = grp; item < nch * T1 * XPR; item += G) {
-      const int xp = item % XPR, rest = item / XPR, t1 = rest % T1, ch = rest / T1;
-      const float* in_c = s_in + ch * IN + (2 * t1 * XB + 4 * xp) * 2;   // bordered coords of (2 t1 - 1, 4 xp - 1)
-      float in[4][6][2];
+    // ---- phase 1: one pooled output (t1, x1) of filters (2 fp, 2 fp + 1) per item
+    for (int item = grp; item < nch * T1 * X1; item += G) {
+      const int x1 = item % X1, rest = item / X1, t1 = rest % T1, ch = rest / T1;
+      const float* in_c = s_in + ch * IN + (2 * t1 * XB + 2 * x1) * 4;   // bordered coords of (2 t1 - 1, 2 x1 - 1)
+      f32x2 s0[2][2], s1[2][2];            // conv outputs at mu = 0 / mu = 1 of the four window positions
 #pragma unroll
-      for (int a = 0; a < 4; ++a)
+      for (int i = 0; i < 4; ++i) (&s0[0][0])[i] = 0ull, (&s1[0][0])[i] = 0ull;
 #pragma unroll
-        for (int b = 0; b < 6; ++b) {
-          const float2 u = *reinterpret_cast<const float2*>(&in_c[(a * XB + b) * 2]);
-          in[a][b][0] = u.x, in[a][b][1] = u.y;
+      for (int r = 0; r < 4; ++r) {        // patch row r feeds window row dt through tap row a = r - dt
+        ulonglong2 row[4];                 // .x = (mu0, mu0), .y = (mu1, mu1)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) row[b] = *reinterpret_cast<const ulonglong2*>(&in_c[(r * XB + b) * 4]);
+#pragma unroll
+        for (int dt = 0; dt < 2; ++dt) {
+          const int a = r - dt;
+          if (a < 0 || a > 2) continue;
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+              // mu = 0 sees taps kd = 0 (mu 0) and kd = 1 (mu 1); mu = 1 sees kd = 0 (mu 1), kd = 1 -> pad
+              s0[dt][dx] = fma2(row[dx + b].x, w[a][b][0], s0[dt][dx]);
+              s0[dt][dx] = fma2(row[dx + b].y, w[a][b][1], s0[dt][dx]);
+              s1[dt][dx] = fma2(row[dx + b].y, w[a][b][0], s1[dt][dx]);
+            }
         }
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        float best = -INFINITY;
-#pragma unroll
-        for (int dt = 0; dt < 2; ++dt)
-#pragma unroll
-          for (int dx = 0; dx < 2; ++dx) {
-            // first tap as a product: fmaf(a, b, 0) == a * b
-            float s0 = __fmul_rn(in[dt][2 * h + dx][0], w[0][0][0]);
-            s0 = fmaf(in[dt][2 * h + dx][1], w[0][0][1], s0);
-            float s1 = __fmul_rn(in[dt][2 * h + dx][1], w[0][0][0]);
-#pragma unroll
-            for (int a = 0; a < 3; ++a)
-#pragma unroll
-              for (int b = 0; b < 3; ++b) {
-                if (a == 0 && b == 0) continue;
-                s0 = fmaf(in[dt + a][2 * h + dx + b][0], w[a][b][0], s0);
-                s0 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][1], s0);
-                s1 = fmaf(in[dt + a][2 * h + dx + b][1], w[a][b][0], s1);
-              }
-            best = fmaxf(best, fmaxf(s0, s1));
-          }
-        s_p1[ch * P1 + (t1 * X1B + 2 * xp + h) * FP + f] = fmaxf(__fadd_rn(best, bias1), 0.f);
       }
+      float ba = -INFINITY, bb = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ba = fmaxf(ba, fmaxf(lo2((&s0[0][0])[i]), lo2((&s1[0][0])[i])));
+        bb = fmaxf(bb, fmaxf(hi2((&s0[0][0])[i]), hi2((&s1[0][0])[i])));
+      }
+      ba = fmaxf(__fadd_rn(ba, bias1a), 0.f);
+      bb = fmaxf(__fadd_rn(bb, bias1b), 0.f);
+      *reinterpret_cast<float4*>(&s_p1[ch * P1 + (t1 * X1B + x1) * FPD + 4 * fp]) = make_float4(ba, ba, bb, bb);
     }
     __syncthreads();
 
     // ---- phase 2
     const int cg = tid % CG;
-    for (int item = tid / CG; item < nch * T2 * X2; item += kThreads / CG) {
+    for (int item = tid / CG; item < nch * T2 * X2; item += TH / CG) {
       const int x2 = item % X2, rest = item / X2, t2 = rest % T2, ch = rest / T2;
-      const float* p1 = s_p1 + ch * P1 + (2 * t2 * X1B + 2 * x2) * FP;
-      float acc[2][2][4];
+      const float* p1 = s_p1 + ch * P1 + (2 * t2 * X1B + 2 * x2) * FPD;
+      f32x2 acc[2][2][2];                  // [dt][dx][channel pair]
 #pragma unroll
-      for (int i = 0; i < 16; ++i) (&acc[0][0][0])[i] = 0.f;
-#pragma unroll 1
-      for (int f4 = 0; f4 < F; f4 += 4) {
-        float4 pp[3][3];
+      for (int i = 0; i < 8; ++i) (&acc[0][0][0])[i] = 0ull;
+#pragma unroll 2
+      for (int f2 = 0; f2 < FH; ++f2) {
+        ulonglong2 pp[3][3];               // .x = (P1[f], P1[f]) of f = 2 f2, .y of f = 2 f2 + 1
 #pragma unroll
         for (int a = 0; a < 3; ++a)
 #pragma unroll
-          for (int b = 0; b < 3; ++b) pp[a][b] = *reinterpret_cast<const float4*>(&p1[(a * X1B + b) * FP + f4]);
+          for (int b = 0; b < 3; ++b) pp[a][b] = *reinterpret_cast<const ulonglong2*>(&p1[(a * X1B + b) * FPD + 4 * f2]);
 #pragma unroll
-        for (int fi = 0; fi < 4; ++fi) {
-          float4 wt[4];
+        for (int fi = 0; fi < 2; ++fi) {
+          ulonglong2 wt[4];                // .x = channels (4 cg, 4 cg + 1), .y = (4 cg + 2, 4 cg + 3)
 #pragma unroll
           for (int tap = 0; tap < 4; ++tap)
-            wt[tap] = *reinterpret_cast<const float4*>(&s_w2[(tap * F + f4 + fi) * C + 4 * cg]);
+            wt[tap] = *reinterpret_cast<const ulonglong2*>(&s_w2[(tap * F + 2 * f2 + fi) * C + 4 * cg]);
 #pragma unroll
           for (int dt = 0; dt < 2; ++dt)
 #pragma unroll
             for (int dx = 0; dx < 2; ++dx)
 #pragma unroll
               for (int tap = 0; tap < 4; ++tap) {
-                const float4 q = pp[dt + (tap >> 1)][dx + (tap & 1)];
-                const float a = fi == 0 ? q.x : fi == 1 ? q.y : fi == 2 ? q.z : q.w;
-                acc[dt][dx][0] = fmaf(a, wt[tap].x, acc[dt][dx][0]);
-                acc[dt][dx][1] = fmaf(a, wt[tap].y, acc[dt][dx][1]);
-                acc[dt][dx][2] = fmaf(a, wt[tap].z, acc[dt][dx][2]);
-                acc[dt][dx][3] = fmaf(a, wt[tap].w, acc[dt][dx][3]);
+                const ulonglong2 q = pp[dt + (tap >> 1)][dx + (tap & 1)];
+                const f32x2 a = fi == 0 ? q.x : q.y;
+                acc[dt][dx][0] = fma2(a, wt[tap].x, acc[dt][dx][0]);
+                acc[dt][dx][1] = fma2(a, wt[tap].y, acc[dt][dx][1]);
               }
         }
       }
       float o[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float best = fmaxf(fmaxf(acc[0][0][j], acc[0][1][j]), fmaxf(acc[1][0][j], acc[1][1][j]));
+        float v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const f32x2 a = (&acc[0][0][0])[2 * i + (j >> 1)];
+          v[i] = (j & 1) ? hi2(a) : lo2(a);
+        }
+        const float best = fmaxf(fmaxf(v[0], v[1]), fmaxf(v[2], v[3]));
         o[j] = fmaxf(__fadd_rn(best, s_b2[4 * cg + j]), 0.f);
       }
       float* dst = p.feat + static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
@@ -343,20 +345,29 @@ __global__ void __launch_bounds__(kThreads, 2) conv3d_tiled_kernel(const ConvPar
   }
 }
 
-template <int F, int PF>
+template <int F, int PF, int CH, int TH>
 int launch_tiled_pf(const ConvParams& p, int sms, size_t smem, cudaStream_t stream) {
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(conv3d_tiled_kernel<F, PF>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(conv3d_tiled_kernel<F, PF, CH, TH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv3d_tiled_kernel): %s", cudaGetErrorString(e));
       return L2HMC_ERR_CUDA;
     }
   }
-  const int per_sm = max(1, min(static_cast<int>((200 * 1024) / (smem + 1024)), 2));
-  const int grid = max(1, min((p.N + kChains - 1) / kChains, sms * per_sm));
-  conv3d_tiled_kernel<F, PF><<<grid, kThreads, smem, stream>>>(p);
+  const int per_sm = max(1, min(static_cast<int>((200 * 1024) / (smem + 1024)), 512 / TH));
+  const int grid = max(1, min((p.N + CH - 1) / CH, sms * per_sm));
+  conv3d_tiled_kernel<F, PF, CH, TH><<<grid, TH, smem, stream>>>(p);
   return check_launch("conv3d_tiled_kernel");
+}
+
+template <int F, int CH, int TH>
+int launch_tiled_ch(const ConvParams& p, int sms, size_t smem, cudaStream_t stream) {
+  const int pf = (CH * 2 * p.T * p.X / 4 + TH - 1) / TH;
+  if (pf <= 1) return launch_tiled_pf<F, 1, CH, TH>(p, sms, smem, stream);
+  if (pf <= 2) return launch_tiled_pf<F, 2, CH, TH>(p, sms, smem, stream);
+  if (pf <= 4) return launch_tiled_pf<F, 4, CH, TH>(p, sms, smem, stream);
+  return -1;
 }
 
 // -1: shape not covered (odd extents, misaligned arrays, too large for shared memory) -> generic kernel
@@ -366,14 +377,15 @@ int launch_tiled(const ConvParams& p, int sms, int max_smem, cudaStream_t stream
   if (p.T % 4 != 0 || p.X % 4 != 0 || misaligned(p.in) || misaligned(p.feat) || misaligned(p.mask) ||
       misaligned(p.mask_alt))
     return -1;
-  const int T1 = p.T / 2, X1 = p.X / 2, D = 2 * p.T * p.X;
-  const size_t smem = sizeof(float) * (4 * F * 2 * F + 2 * F + kChains * (p.T + 2) * (p.X + 2) * 2 +
-                                       kChains * (T1 + 1) * (X1 + 1) * (F + 4));
-  if (smem > static_cast<size_t>(max_smem)) return -1;
-  const int pf = (kChains * D / 4 + kThreads - 1) / kThreads;
-  if (pf <= 1) return launch_tiled_pf<F, 1>(p, sms, smem, stream);
-  if (pf <= 2) return launch_tiled_pf<F, 2>(p, sms, smem, stream);
-  if (pf <= 4) return launch_tiled_pf<F, 4>(p, sms, smem, stream);
+  const int T1 = p.T / 2, X1 = p.X / 2;
+  const auto smem_for = [&](int ch) {
+    return sizeof(float) * (4 * F * 2 * F + 2 * F + static_cast<size_t>(ch) * (p.T + 2) * (p.X + 2) * 4 +
+                            static_cast<size_t>(ch) * (T1 + 1) * (X1 + 1) * (2 * F + 8));
+  };
+  // two chains per pass while two CTAs still fit an SM, one chain per pass for the large lattices
+  // (four 128-thread CTAs per SM with one chain each measured the same: the FMA pipe is the limit)
+  if (smem_for(2) <= 100 * 1024) return launch_tiled_ch<F, 2, 256>(p, sms, smem_for(2), stream);
+  if (smem_for(1) <= static_cast<size_t>(max_smem)) return launch_tiled_ch<F, 1, 256>(p, sms, smem_for(1), stream);
   return -1;
 }
 
