@@ -31,6 +31,8 @@
 //              tcgen05.mma.cta_group::1.kind::tf32, M = 128, N = BN
 //   smem ring of 2-3 stages (A 32 KB + B BN*256 B), full/empty mbarriers; two accumulator stages in
 //   TMEM (tmem_full / tmem_empty), one per in-flight 128-wide K chunk.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "nets.cuh"
 #include "update_math.cuh"
@@ -80,6 +82,8 @@ struct TcParams {
   float* uout;
   float* ld_part;
   int32_t* flag;
+  int debug_noload;    // diagnostics (L2HMC_TC_DEBUG_NOLOAD=1): operand tiles are fetched only while the ring first
+                       // fills; later K blocks re-use stale shared memory -> wrong numbers, pure MMA / epilogue timing
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -189,12 +193,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
   if (warp == kProducerWarp) {
     // ===== producer =====
     if (lane == 0) {
-      int stage = 0;
+      int stage = 0, issued = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
         for (int kb = 0; kb < p.KB; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
+          if (p.debug_noload && issued++ >= NSTAGE) {
+            mbar_arrive(&full[stage]);
+            if (++stage == NSTAGE) stage = 0, phase ^= 1;
+            continue;
+          }
           uint8_t* sa = tc_smem + stage * kStageBytes;
           mbar_arrive_expect_tx(&full[stage], kStageBytes);
           bulk_g2s(sa, p.A + (static_cast<size_t>(kb) * p.a_rg + static_cast<size_t>(m_blk) * (TC_BM / 8)) * 512,
@@ -558,12 +567,14 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   int rc = check_launch("ts32_from_rowmajor_kernel");
   if (rc) return rc;
 
+  static const int debug_noload = getenv("L2HMC_TC_DEBUG_NOLOAD") ? atoi(getenv("L2HMC_TC_DEBUG_NOLOAD")) : 0;
   const int m_tiles = d.rows_p / 128;
   // few tiles: halve the N tile so more SMs take part
   const bool narrow = m_tiles * ((H + 255) / 256) < 120;
   TcParams p{};
   p.A = acat, p.a_rg = rg, p.B = W1, p.b_rg = d.h_rows / 8, p.KB = 2 * d.kbK;
   p.m_tiles = m_tiles, p.n_tiles = narrow ? (H + 127) / 128 : (H + 255) / 256;
+  p.debug_noload = debug_noload;
   p.rows = N, p.cols = H, p.bias = bias_eff, p.bias_alt = bias_eff + d.h_rows, p.row_set = c->row_set;
   p.out_ts = h1, p.out_rg = rg, p.out_kb = d.kbH;
   rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
@@ -574,6 +585,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   if (rc) return rc;
 
   p = TcParams{};
+  p.debug_noload = debug_noload;
   p.A = h2, p.a_rg = rg, p.B = W3, p.b_rg = d.d_tiles * 192 / 8, p.KB = d.kbH;
   p.m_tiles = m_tiles, p.n_tiles = d.d_tiles;
   p.rows = N, p.cols = D;

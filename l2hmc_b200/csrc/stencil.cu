@@ -18,6 +18,30 @@
 namespace l2hmc {
 namespace {
 
+// cos P and project_angle(P) from ONE range reduction.  With j = rint(P / 2pi) and r = P - j 2pi (Cody-Waite,
+// |r| <= pi), the reference's q = floor((P + pi) / 2pi) equals j whenever r is not within 1e-4 of +-pi (the
+// quotient's fractional part is then in (1.5e-5, 1 - 1.5e-5), far outside any rounding), and
+// proj = P - 2pi q is formed with the reference's own two roundings -- bit-identical to project_angle().
+// Near the branch cut (probability ~3e-5) and for |P| > 4e4 the exact division is taken.
+__device__ __forceinline__ void cos_and_project(float P, float* cs, float* proj) {
+  if (__builtin_expect(fabsf(P) > 40000.f, 0)) {
+    *cs = cosf(P);
+    *proj = project_angle(P);
+    return;
+  }
+  const float magic = 12582912.0f;
+  const float j = __fsub_rn(fmaf(P, 0.15915494309189535f, magic), magic);
+  float r = fmaf(j, -6.28125f, P);
+  r = fmaf(j, -0.0019350051879882812f, r);
+  r = fmaf(j, -3.019916050561733e-07f, r);
+  const float a = fabsf(r);
+  const bool fold = a > 1.57079637050628662f;
+  const float folded = __fadd_rn(__fsub_rn(3.14159274101257324f, a), -8.742277657347586e-08f);
+  const float c = cos_poly(fold ? folded : a);
+  *cs = fold ? -c : c;
+  *proj = a < 3.1415f ? __fsub_rn(P, __fmul_rn(kTwoPi, j)) : project_angle(P);
+}
+
 struct StencilParams {
   const float* x;
   float beta;
@@ -60,12 +84,18 @@ __global__ void __launch_bounds__(256) stencil_kernel(const StencilParams p, int
         csum = __fadd_rn(csum, cs);
       } else if (want_force) {
         sb[s] = __fmul_rn(p.beta, fast_sin(P));
+      } else if (want_cos && want_q) {
+        float cs, pr;
+        cos_and_project(P, &cs, &pr);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+        qsum = __fadd_rn(qsum, pr);
       } else if (want_cos) {
         const float cs = fast_cos(P);
         act = __fadd_rn(act, __fsub_rn(1.f, cs));
         csum = __fadd_rn(csum, cs);
       }
-      if (want_q) qsum = __fadd_rn(qsum, project_angle(P));
+      if (want_q && !(want_cos && !want_force)) qsum = __fadd_rn(qsum, project_angle(P));
     }
     if (want_force) {
       __syncwarp();
@@ -158,12 +188,18 @@ __global__ void __launch_bounds__(256) stencil_reg_kernel(const StencilParams p)
         csum = __fadd_rn(csum, cs);
       } else if (FORCE) {
         b[i] = __fmul_rn(p.beta, fast_sin(P));
+      } else if (COS && QSUM) {
+        float cs, pr;
+        cos_and_project(P, &cs, &pr);
+        act = __fadd_rn(act, __fsub_rn(1.f, cs));
+        csum = __fadd_rn(csum, cs);
+        qsum = __fadd_rn(qsum, pr);
       } else if (COS) {
         const float cs = fast_cos(P);
         act = __fadd_rn(act, __fsub_rn(1.f, cs));
         csum = __fadd_rn(csum, cs);
       }
-      if (QSUM) qsum = __fadd_rn(qsum, project_angle(P));
+      if (QSUM && !(COS && !FORCE)) qsum = __fadd_rn(qsum, project_angle(P));
     }
     if (FORCE) {
       float2* gf = reinterpret_cast<float2*>(p.force + static_cast<size_t>(n) * D);
