@@ -487,21 +487,23 @@ int launch_tc(const TcParams& p, cudaStream_t st) {
   constexpr int NSTAGE = (BN <= 128) ? 3 : 2;
   constexpr size_t smem = static_cast<size_t>(NSTAGE) * (kATileBytes + BN * 256) + (2 * NSTAGE + 4) * 8 + 16;
   auto kern = gemm_tc_kernel<BN, MODE>;
-  static bool opted = false;
-  if (!opted) {
+  // per device: the opt-in shared-memory size and the SM count (one process may drive several GPUs)
+  constexpr int kMaxDevices = 64;
+  static bool opted[kMaxDevices] = {};
+  static int sm_count[kMaxDevices] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const int slot = dev < kMaxDevices ? dev : 0;
+  if (dev >= kMaxDevices || !opted[slot]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(gemm_tc_kernel, %zu B): %s", smem, cudaGetErrorString(e));
       return L2HMC_ERR_CUDA;
     }
-    opted = true;
+    cudaDeviceGetAttribute(&sm_count[slot], cudaDevAttrMultiProcessorCount, dev);
+    opted[slot] = dev < kMaxDevices;
   }
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int sms = sm_count[slot];
   const int tiles = p.m_tiles * p.n_tiles;
   if (tiles == 0) return L2HMC_OK;
   kern<<<std::min(tiles, sms), kTcThreads, smem, st>>>(p);

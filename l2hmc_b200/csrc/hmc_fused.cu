@@ -399,14 +399,18 @@ int launch(const HmcParams& p_in, cudaStream_t stream) {
   p.off_bar = p.off_red + 64;
   const size_t smem_bytes = sizeof(float) * static_cast<size_t>(p.off_bar) + 2 * sizeof(uint64_t);
 
-  static int sm_count = 0;
-  static size_t smem_opted = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev);
-  }
-  if (smem_bytes > smem_opted) {
+  // per device (one process may drive several GPUs): SM count and the opted-in shared-memory size
+  constexpr int kMaxDevices = 64;
+  static int sm_counts[kMaxDevices] = {};
+  static size_t smem_opts[kMaxDevices] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const int slot = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+  if (sm_counts[slot] == 0 || slot != dev)
+    cudaDeviceGetAttribute(&sm_counts[slot], cudaDevAttrMultiProcessorCount, dev);
+  const int sm_count = sm_counts[slot];
+  size_t& smem_opted = smem_opts[slot];
+  if (smem_bytes > smem_opted || slot != dev) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem_bytes));
     if (e != cudaSuccess) {

@@ -109,3 +109,24 @@ def calc_observables_stats(actions, plaqs, charges, therm_frac=10):
     stats["charge_probabilities"] = collections.OrderedDict(sorted(((k, v / total) for k, v in counts.items()),
                                                                 key=lambda kv: kv[0]))
     return stats
+
+
+def loss_and_grads(dyn, x, beta, draws_x, z, draws_z, metric="cos_diff", loss_scale=1., **weights):
+    """gauge_model.py:805-832 (tf.gradients(loss, dynamics.variables)) by reverse-mode autodiff THROUGH the oracle's
+    own transition (both chains, both directions, the analytic force included).  Returns (loss, {name: grad}) with
+    names 'eps', 'XNet.<layer>.kernel', ... as in the golden fixtures.  This is the reference the backward kernels
+    of the next round are checked against."""
+    named = {"eps": dyn.eps}
+    for net_name, w in (("XNet", dyn.xnet), ("VNet", dyn.vnet)):
+        if w is not None:
+            for k, v in w.items():
+                named[f"{net_name}.{k}"] = v
+    for v in named.values():
+        v.requires_grad_(True)
+    try:
+        loss, _, _, _ = calc_loss(dyn, x, beta, draws_x, z, draws_z, metric=metric, loss_scale=loss_scale, **weights)
+        grads = torch.autograd.grad(loss, list(named.values()), allow_unused=True)
+    finally:
+        for v in named.values():
+            v.requires_grad_(False)
+    return loss.detach(), {k: (torch.zeros_like(v) if g is None else g.detach()) for (k, v), g in zip(named.items(), grads)}

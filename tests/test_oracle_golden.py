@@ -301,3 +301,25 @@ def test_observables_stats_against_reference_goldens(golden):
             np.testing.assert_allclose(st[nm][1], g[f"{tag}.{nm}.err"], rtol=1e-5, atol=1e-7)
         assert list(st["charge_probabilities"].keys()) == list(g[tag + ".prob.keys"])
         np.testing.assert_allclose(list(st["charge_probabilities"].values()), g[tag + ".prob.vals"], rtol=1e-12)
+
+
+def test_loss_gradients_against_reference_goldens(golden):
+    """d loss / d eps and d loss / d weights (gauge_model.py:805-832) from autodiff through the oracle vs the
+    reference's tf.gradients (run on the stand-in): pins the backward reference for the next round's kernels."""
+    from oracle import train_oracle as tro
+    g = golden("train_cases")
+    for tag in _train_tags(g, "loss"):
+        dyn, (T, X, N, M, hmc) = train_dyn_from(g, tag)
+        aux, std, chg = (float(v) for v in g[tag + ".weights"])
+        loss, grads = tro.loss_and_grads(
+            dyn, g[tag + ".x"], float(g[tag + ".beta"]),
+            (g[tag + ".v_f"], g[tag + ".v_b"], g[tag + ".u_dir"], g[tag + ".u_acc"]), g[tag + ".z"],
+            (g[tag + ".vz_f"], g[tag + ".vz_b"], g[tag + ".uz_dir"], g[tag + ".uz_acc"]),
+            metric=tag.split(".")[-1], loss_scale=float(g[tag + ".loss_scale"]), aux_weight=aux, std_weight=std,
+            charge_weight=chg)
+        names = [k[len(tag) + 6:] for k in g if k.startswith(tag + ".grad.")]
+        assert set(names) == set(grads), (sorted(names)[:3], sorted(grads)[:3])
+        for nm in names:
+            ref = g[f"{tag}.grad.{nm}"]
+            scale = max(float(np.abs(ref).max()), 1e-12)
+            np.testing.assert_allclose(grads[nm].numpy(), ref, rtol=2e-2, atol=2e-3 * scale, err_msg=f"{tag} {nm}")
