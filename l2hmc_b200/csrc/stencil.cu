@@ -238,6 +238,76 @@ __global__ void __launch_bounds__(256) stencil_reg_kernel(const StencilParams p)
   }
 }
 
+// Reduce-only variant (action / plaquette / charge, no force): the chain streams through a ring of PD row
+// registers instead of living in registers whole -- ~40 registers instead of ~90, three times the resident
+// warps, and PD - 1 loads in flight per lane all the time.  Same lane -> site map, same summation order and
+// therefore the same bits as stencil_reg_kernel.
+template <int X, int I, bool COS, bool QSUM>
+__global__ void __launch_bounds__(256) stencil_roll_kernel(const StencilParams p) {
+  constexpr int SITES = 32 * I, D = 2 * SITES, PD = I < 8 ? I : 8;
+  static_assert(I % PD == 0, "row count must be a multiple of the ring depth");
+  constexpr unsigned kFull = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int warps = (blockDim.x >> 5) * gridDim.x;
+  const int right = (lane & ~(X - 1)) | ((lane + 1) & (X - 1));
+  const int down = (lane + X) & 31;
+  const bool down_wraps = lane + X >= 32;
+  for (int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); n < p.N; n += warps) {
+    const float2* gx = reinterpret_cast<const float2*>(p.x + static_cast<size_t>(n) * D) + lane;
+    float2 ring[PD];
+#pragma unroll
+    for (int k = 0; k < PD; ++k) ring[k] = __ldcs(gx + 32 * k);
+    const float2 first = ring[0];
+    float act = 0.f, csum = 0.f, qsum = 0.f;
+#pragma unroll 1
+    for (int i0 = 0; i0 < I; i0 += PD) {
+#pragma unroll
+      for (int k = 0; k < PD; ++k) {
+        const int i = i0 + k;
+        const float2 cur = ring[k];
+        if (i + PD < I) ring[k] = __ldcs(gx + 32 * (i + PD));          // row i + PD takes the slot just consumed
+        const float2 nxt = (i + 1 == I) ? first : ring[(k + 1) % PD];  // row i + 1 (slot k + 1, or the reloaded slot 0)
+        const float xr = __shfl_sync(kFull, cur.x, right);
+        float yd;
+        if (X == 32) {
+          yd = nxt.y;
+        } else {
+          const float same = __shfl_sync(kFull, cur.y, down), next = __shfl_sync(kFull, nxt.y, down);
+          yd = down_wraps ? next : same;
+        }
+        const float P = __fadd_rn(__fsub_rn(__fsub_rn(cur.x, cur.y), xr), yd);
+        if (COS && QSUM) {
+          float cs, pr;
+          cos_and_project(P, &cs, &pr);
+          act = __fadd_rn(act, __fsub_rn(1.f, cs));
+          csum = __fadd_rn(csum, cs);
+          qsum = __fadd_rn(qsum, pr);
+        } else if (COS) {
+          const float cs = fast_cos(P);
+          act = __fadd_rn(act, __fsub_rn(1.f, cs));
+          csum = __fadd_rn(csum, cs);
+        } else {
+          qsum = __fadd_rn(qsum, project_angle(P));
+        }
+      }
+    }
+    if (COS) {
+      act = warp_sum(act);
+      csum = warp_sum(csum);
+    }
+    if (QSUM) qsum = warp_sum(qsum);
+    if (lane == 0) {
+      if (p.action) p.action[n] = act;
+      if (p.avg_plaq) p.avg_plaq[n] = __fdiv_rn(csum, static_cast<float>(SITES));
+      if (QSUM) {
+        const float qf = __fdiv_rn(qsum, kTwoPi);
+        if (p.q_float) p.q_float[n] = qf;
+        if (p.q_int) p.q_int[n] = static_cast<int32_t>(floorf(__fadd_rn(0.1f, qf)));
+      }
+    }
+  }
+}
+
 template <int X, int I>
 bool launch_reg(const StencilParams& p, int sms, cudaStream_t stream) {
   const bool force = p.force != nullptr, hamil = p.hamil != nullptr;
@@ -247,9 +317,9 @@ bool launch_reg(const StencilParams& p, int sms, cudaStream_t stream) {
   // the combinations the API can ask for: force [+ action]; action / plaq / Q observables; Hamiltonian
   if (force && cosv && !q && !hamil) stencil_reg_kernel<X, I, true, true, false, false><<<blocks, 256, 0, stream>>>(p);
   else if (force && !cosv && !q) stencil_reg_kernel<X, I, true, false, false, false><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && cosv && !q && !hamil) stencil_reg_kernel<X, I, false, true, false, false><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && cosv && q && !hamil) stencil_reg_kernel<X, I, false, true, true, false><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && !cosv && q) stencil_reg_kernel<X, I, false, false, true, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && cosv && !q && !hamil) stencil_roll_kernel<X, I, true, false><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && cosv && q && !hamil) stencil_roll_kernel<X, I, true, true><<<blocks, 256, 0, stream>>>(p);
+  else if (!force && !cosv && q) stencil_roll_kernel<X, I, false, true><<<blocks, 256, 0, stream>>>(p);
   else if (!force && hamil && !q) stencil_reg_kernel<X, I, false, true, false, true><<<blocks, 256, 0, stream>>>(p);
   else return false;
   return true;
