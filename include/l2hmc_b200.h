@@ -285,6 +285,43 @@ int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const float* in, c
                                const float* mask_alt, int mask_invert_alt, const uint8_t* row_set, int N, int T,
                                int X, float* feat, void* stream);
 
+/* ------------------------------------------------------------------ one host call = one L2HMC MC step
+ * GaugeDynamics.apply_transition WITH the S/T/Q networks (dynamics/gauge_dynamics.py:195-313, 412-483): momentum and
+ * direction draws, M augmented leapfrog steps (each chain in the direction it drew, both kinds in the same
+ * launches), accept probability, Metropolis-Hastings select [+ np.mod 2 pi, gauge_model.py:1180,1388]
+ * [+ observables of the new state, gauge_model.py:683-716].  Only launches kernels of this library, in stream
+ * order; nothing is allocated or synchronised.  v_f == NULL: momenta and uniforms come from the Philox stream
+ * (seed, chain0 + n, mc_step), the same numbers l2hmc_philox_draws returns.  Generic nets: the four conv pointers
+ * NULL.  Conv nets: xconv_in0 / xconv_in1 are position_fn's conv stacks for its first / second input (conv_v*,
+ * conv_x*), vconv_* momentum_fn's; the nets' K is then the conv feature count. */
+typedef struct {
+  int N, T, X, M;
+  float eps, beta;
+  const float* masks;   /* [M][2TX] device */
+  const float* ts;      /* [M][2] HOST array: (cos, sin)(2 pi t / M) rows, dynamics/gauge_dynamics.py:625-633 */
+  const l2hmc_net_weights* xnet; /* position_fn */
+  const l2hmc_net_weights* vnet; /* momentum_fn */
+  const l2hmc_conv3d_weights *xconv_in0, *xconv_in1, *vconv_in0, *vconv_in1; /* nullable (all or none) */
+  int net_path;         /* L2HMC_NET_PATH_* */
+  const float* x;       /* [N,2TX] */
+  const float *v_f, *v_b;     /* [N,2TX] injected momenta, nullable (v_b NULL: v_f both ways) */
+  const float *u_dir, *u_acc; /* [N] injected uniforms (required with v_f) */
+  uint64_t seed, mc_step, chain0;
+  int wrap_2pi;
+  float *x_post, *v_post; /* [N,2TX] proposal (also the in-place working state) */
+  float* accept_prob;     /* [N] */
+  float* x_out;           /* [N,2TX] nullable */
+  uint8_t* accepted;      /* [N] nullable */
+  float *obs_action, *obs_plaq; /* [N] nullable: observables of x_out */
+  int32_t* obs_charge;
+  int32_t* nonfinite_flag;
+  void* workspace;        /* >= l2hmc_u1_l2hmc_mc_workspace_bytes(args), 256-byte aligned */
+  size_t workspace_bytes;
+} l2hmc_l2hmc_mc_args;
+
+size_t l2hmc_u1_l2hmc_mc_workspace_bytes(const l2hmc_l2hmc_mc_args* a);
+int l2hmc_u1_l2hmc_mc_step(const l2hmc_l2hmc_mc_args* a, void* stream);
+
 /* ------------------------------------------------------------------ MoG / generic-target path (config 5)
  * Gaussian-mixture target of utils/distributions.py:124-158:
  *     E(x) = -logsumexp_i( -0.5 (x-mu_i)^T S_i (x-mu_i) + log c_i ) / temperature

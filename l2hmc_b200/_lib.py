@@ -67,6 +67,21 @@ class Gmm(Structure):
     _fields_ = [("k", c_int), ("m", c_int), ("mus", c_void_p), ("i_sigmas", c_void_p), ("log_consts", c_void_p)]
 
 
+class L2hmcMcArgs(Structure):
+    """l2hmc_l2hmc_mc_args (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("N", c_int), ("T", c_int), ("X", c_int), ("M", c_int), ("eps", c_float), ("beta", c_float),
+        ("masks", c_void_p), ("ts", c_void_p), ("xnet", POINTER(NetWeights)), ("vnet", POINTER(NetWeights)),
+        ("xconv_in0", POINTER(Conv3dWeights)), ("xconv_in1", POINTER(Conv3dWeights)),
+        ("vconv_in0", POINTER(Conv3dWeights)), ("vconv_in1", POINTER(Conv3dWeights)), ("net_path", c_int),
+        ("x", c_void_p), ("v_f", c_void_p), ("v_b", c_void_p), ("u_dir", c_void_p), ("u_acc", c_void_p),
+        ("seed", c_uint64), ("mc_step", c_uint64), ("chain0", c_uint64), ("wrap_2pi", c_int),
+        ("x_post", c_void_p), ("v_post", c_void_p), ("accept_prob", c_void_p), ("x_out", c_void_p),
+        ("accepted", c_void_p), ("obs_action", c_void_p), ("obs_plaq", c_void_p), ("obs_charge", c_void_p),
+        ("nonfinite_flag", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+    ]
+
+
 class LossParams(Structure):
     """l2hmc_loss_params (include/l2hmc_b200.h)."""
     _fields_ = [("metric", c_int), ("loss_scale", c_float), ("aux_weight", c_float), ("std_weight", c_float),
@@ -124,6 +139,8 @@ SIGNATURES = {
     "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_gmm_energy_force": [POINTER(Gmm), c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_mog_mc_step": [POINTER(Gmm), POINTER(MogArgs), c_void_p],
+    "l2hmc_u1_l2hmc_mc_workspace_bytes": [POINTER(L2hmcMcArgs)],
+    "l2hmc_u1_l2hmc_mc_step": [POINTER(L2hmcMcArgs), c_void_p],
     "l2hmc_u1_loss": [POINTER(LossParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                       c_int, c_void_p, c_void_p, c_void_p, c_void_p],
     "l2hmc_u1_top_charges_fft": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p],
@@ -138,7 +155,7 @@ SIGNATURES = {
 }
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
-            "l2hmc_tc_selftest_bytes": c_size_t}
+            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

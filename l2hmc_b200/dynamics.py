@@ -68,6 +68,8 @@ class GaugeDynamics(object):
         self.data_format = 'channels_last'
         self.seed = 0            # Philox key of the free-running mode
         self.chain_offset = 0    # global index of local chain 0 (chain sharding)
+        self.native_step = True  # nets: one C call enqueues the whole MC step (csrc/l2hmc_step.cu)
+        self._step_ws = None
         self.use_fused = True    # one-launch HMC path when the shape has a kernel
         self.fuse_updates = True # L2HMC: sub-updates run in the head GEMM's epilogue (no S,T,Q in HBM)
         self.weights = None      # optional {'XNet': {...}, 'VNet': {...}} in Keras layouts
@@ -440,6 +442,9 @@ class GaugeDynamics(object):
                 self._mc_step += 1
             return x_post, v_post, p, x_out
 
+        if self.fuse_updates and self.native_step and not self.hmc and hasattr(self.position_fn, '_weights_struct'):
+            return self._native_mc_step(x, beta, v_f if inject else None, v_b if inject else None,
+                                        u_dir if inject else None, u_acc if inject else None, wrap, observables)
         if not inject:
             z, u_dir, u_acc = self._draws(N)
             self._mc_step += 1
@@ -476,6 +481,50 @@ class GaugeDynamics(object):
             v_post.index_copy_(0, idx, vs)
             p_post.index_copy_(0, idx, ps)
         return self._finish_transition(x, x_post, v_post, p_post, u_acc, wrap, observables)
+
+    def _native_mc_step(self, x, beta, v_f, v_b, u_dir, u_acc, wrap, observables):
+        """The whole MC step enqueued by one C call (csrc/l2hmc_step.cu: l2hmc_u1_l2hmc_mc_step)."""
+        N, D = x.shape
+        dev = x.device
+        new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+        x_post, v_post, x_out, p = new(N, D), new(N, D), new(N, D), new(N)
+        acc = torch.empty(N, dtype=torch.uint8, device=dev)
+        a = _lib.L2hmcMcArgs()
+        a.N, a.T, a.X, a.M = N, self.T, self.X, int(self.num_steps)
+        a.eps, a.beta = self._eps(), self._beta(beta)
+        mask = self.mask if self.mask.is_contiguous() else self.mask.contiguous()
+        a.masks = _lib.dptr(mask)
+        ts = np.ascontiguousarray(self._ts_host, dtype=np.float32)
+        a.ts = ts.ctypes.data_as(ctypes.c_void_p)
+        xs, vs = self.position_fn._weights_struct(), self.momentum_fn._weights_struct()
+        a.xnet, a.vnet = ctypes.pointer(xs), ctypes.pointer(vs)
+        if hasattr(self.position_fn, '_conv'):
+            convs = [self.position_fn._conv("v"), self.position_fn._conv("x"), self.momentum_fn._conv("v"),
+                     self.momentum_fn._conv("x")]
+            a.xconv_in0, a.xconv_in1, a.vconv_in0, a.vconv_in1 = (ctypes.pointer(c) for c in convs)
+        a.net_path = int(self.position_fn.path)
+        a.x, a.v_f, a.v_b = _lib.dptr(x), _lib.dptr(v_f), _lib.dptr(None if v_b is v_f else v_b)
+        a.u_dir, a.u_acc = _lib.dptr(u_dir), _lib.dptr(u_acc)
+        a.seed, a.mc_step, a.chain0 = int(self.seed), int(self._mc_step), int(self.chain_offset)
+        a.wrap_2pi = int(bool(wrap))
+        a.x_post, a.v_post, a.accept_prob, a.x_out = _lib.dptr(x_post), _lib.dptr(v_post), _lib.dptr(p), _lib.dptr(x_out)
+        a.accepted = _lib.dptr(acc, torch.uint8)
+        if observables:
+            self.last_observables = (new(N), new(N), torch.empty(N, dtype=torch.int32, device=dev))
+            a.obs_action, a.obs_plaq = _lib.dptr(self.last_observables[0]), _lib.dptr(self.last_observables[1])
+            a.obs_charge = _lib.dptr(self.last_observables[2], torch.int32)
+        a.nonfinite_flag = _lib.dptr(self._flag, torch.int32)
+        lib = _lib.get_lib()
+        need = int(lib.l2hmc_u1_l2hmc_mc_workspace_bytes(ctypes.byref(a)))
+        if self._step_ws is None or self._step_ws.numel() < need:
+            self._step_ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        a.workspace, a.workspace_bytes = ctypes.c_void_p(self._step_ws.data_ptr()), need
+        with torch.cuda.device(dev):
+            self._lib_call(lib.l2hmc_u1_l2hmc_mc_step, ctypes.byref(a))
+        if v_f is None:
+            self._mc_step += 1
+        self.last_accepted = acc
+        return x_post, v_post, p, x_out
 
     def _finish_transition(self, x, x_post, v_post, p_post, u_acc, wrap, observables):
         """Metropolis-Hastings select (gauge_dynamics.py:243-259) [+ np.mod 2 pi] [+ observables]."""

@@ -314,3 +314,38 @@ def test_mixed_direction_batch_equals_per_direction_runs(pkg, arch, T, N, path):
     assert torch.equal(vp, torch.where(fwd[:, None], vfo, vbo))
     assert torch.equal(p, torch.where(fwd, pf, pb))
     dyn.raise_if_nonfinite()
+
+
+@pytest.mark.parametrize("arch,T,N,path,inject", [("generic", 8, 150, "ffma", True), ("generic", 8, 300, "tc", True),
+                                                  ("conv3D", 8, 70, "ffma", True), ("conv3D", 16, 260, "tc", False),
+                                                  ("generic", 4, 9, "ffma", False)])
+def test_native_mc_step_equals_python_composition(pkg, arch, T, N, path, inject):
+    """l2hmc_u1_l2hmc_mc_step (one C call enqueues the whole MC step) against the same kernels driven one by one from
+    Python: identical bits, injected or Philox draws, with the mod 2 pi and the observables."""
+    from l2hmc_b200 import _lib
+    M, eps, beta = 3, 0.15, 2.5
+    D = 2 * T * T
+    rng = np.random.default_rng(T * N)
+    ws = _oracle_weights(arch, T, T, rng)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    kw = {}
+    if inject:
+        kw = dict(momentum_f=rng.standard_normal((N, D)).astype(np.float32),
+                  momentum_b=rng.standard_normal((N, D)).astype(np.float32),
+                  direction_uniform=rng.uniform(size=N).astype(np.float32),
+                  accept_uniform=rng.uniform(size=N).astype(np.float32))
+    lat = pkg.GaugeLattice(T, T, 2, "U1", num_samples=N)
+    outs = []
+    for native in (True, False):
+        np.random.seed(42)
+        dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M, eps=eps, weights=ws, seed=5, chain_offset=11)
+        dyn.native_step = native
+        dyn.position_fn.path = dyn.momentum_fn.path = _lib.NET_PATH_TCGEN05 if path == "tc" else _lib.NET_PATH_FFMA
+        dyn._mc_step = 4
+        res = dyn.apply_transition(x, beta, wrap=True, observables=True, **kw)
+        outs.append(res + (dyn.last_accepted,) + tuple(dyn.last_observables))
+        assert dyn._mc_step == (4 if inject else 5)
+        dyn.raise_if_nonfinite()
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    assert 0 < int(outs[0][4].sum()) <= N
