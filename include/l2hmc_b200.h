@@ -243,6 +243,10 @@ typedef struct {
   int dir_alt;                 /* +1 / -1 */
   const float* mask_alt;       /* POSITION: mask row [D] */
   int mask_invert_alt;
+  /* Training tape (FFMA path only, L2HMC_ERR_UNSUPPORTED with L2HMC_NET_PATH_TCGEN05): when given, the hidden
+     activations h1 / h2 [N,H] (after the ReLU) are written here instead of the workspace and survive the call,
+     for the backward pass of l2hmc_sgemm / l2hmc_update_bwd.  Nullable, together. */
+  float *h1_out, *h2_out;
 } l2hmc_net_call;
 
 #define L2HMC_NET_PATH_AUTO 0
@@ -425,6 +429,106 @@ int l2hmc_stats_finalize(const l2hmc_run_stats* s, long long n_counted, long lon
                          void* stream);
 /* utils/trajectories.py:63-95: switches[n] += (mode[n] != prev[n]) when have_prev; prev[n] = mode[n]. */
 int l2hmc_mode_switches(const int32_t* mode, int32_t* prev, uint32_t* switches, int have_prev, int N, void* stream);
+
+/* ------------------------------------------------------------------ training: backward pass + optimiser
+ * SURVEY section 8(f) ranks 1-2.  The reference obtains every gradient from tf.gradients(loss, dynamics.variables)
+ * (gauge_model.py:805-832); here each adjoint is an explicit kernel and the host (l2hmc_b200/training.py) walks the
+ * tape the forward pass recorded.  Everything is deterministic (no atomics; split-K sums in fixed order). */
+
+/* fp32 GEMM with general strides (NN / NT / TN without copies), up to three K segments summed into one product:
+ *     C[m,n] (=|+=) scale[n] * gate[m,n] * sum_seg sum_k A_seg(m,k) * B_seg(k,n)
+ *   A_seg(m,k) = A[m*a_rs + k*a_cs],  B_seg(k,n) = B[k*b_rs + n*b_cs]
+ *   relu_gate (nullable): the product is zeroed where gate[m*ldg + n] <= 0   (d relu: dZ = dH * [h > 0])
+ *   col_scale (nullable [N]): multiplies column n by scale[n] (or 1 - scale[n]); rows with row_set[m] != 0 use
+ *   col_scale_alt / col_scale_invert_alt  (the `mask * x` input of position_fn, dynamics/gauge_dynamics.py:515-517)
+ * ksplit > 1 splits K over grid.z into `workspace` and sums the slices in order (one segment, no epilogue): the
+ * deferred weight-gradient GEMMs, whose K is the whole tape. */
+typedef struct {
+  const float* A;
+  long long a_rs, a_cs;
+  const float* B;
+  long long b_rs, b_cs;
+  int K;
+} l2hmc_gemm_seg;
+
+typedef struct {
+  int M, N, nseg;
+  l2hmc_gemm_seg seg[3];
+  float* C;
+  long long ldc;
+  int accumulate;
+  const float* relu_gate;
+  long long ldg;
+  const float* col_scale;
+  int col_scale_invert;
+  const uint8_t* row_set;
+  const float* col_scale_alt;
+  int col_scale_invert_alt;
+} l2hmc_gemm_args;
+
+size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit);
+int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t workspace_bytes, void* stream);
+
+/* The four sub-updates (formulas of l2hmc_update_momentum / l2hmc_update_position) with a per-chain parameter set:
+ * chains with row_set[n] != 0 use dir_alt / mask_alt / invert_alt (mixed-direction batches).  S, T, Q nullable
+ * together (plain HMC).  `logdet` [N] is accumulated into. */
+int l2hmc_train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S,
+                           const float* Tr, const float* Q, const float* mask, int invert, const float* mask_alt,
+                           int invert_alt, const uint8_t* row_set, float eps, int dir, int dir_alt, int N, int D,
+                           float* out, float* logdet, int32_t* nonfinite_flag, void* stream);
+/* out[n,:] = m (*) x[n,:] with the chain's mask set (materialised network input for the tape). */
+int l2hmc_mask_mul_sets(const float* x, const float* mask, int invert, const float* mask_alt, int invert_alt,
+                        const uint8_t* row_set, int N, int D, float* out, void* stream);
+
+/* Adjoint of one sub-update (dynamics/gauge_dynamics.py:486-590).  In: the update's inputs from the tape, the
+ * upstream gradients gv (momentum: d loss / d v') or gx (position: d loss / d x') and gld [N] = d loss / d sumlogdet.
+ * Out (in place): momentum: gv <- d loss / d v;  dg [N,D] = the direct part of d loss / d force.
+ *                 position: gx <- direct part of d loss / d x;  gv += d loss / d v (direct part).
+ * With networks: dA [N,3D] = gradients of the three heads' pre-activations (scale | translation | transformation),
+ * ps / pq [N,D] = dS*S / dQ*Q (their column sums are d loss / d coeff_scale / coeff_transformation);
+ * deps [N] += per-chain d loss / d eps. */
+typedef struct {
+  int position; /* 0 = momentum update, 1 = position update */
+  int N, D;
+  float eps;
+  int dir, dir_alt;
+  const uint8_t* row_set;
+  const float *x, *v, *g;
+  const float *S, *T, *Q;
+  const float *coeff_s, *coeff_q;
+  const float *mask, *mask_alt;
+  int invert, invert_alt;
+  float *gx, *gv;
+  const float* gld;
+  float *dA, *dg, *ps, *pq, *deps;
+} l2hmc_update_bwd_args;
+int l2hmc_update_bwd(const l2hmc_update_bwd_args* a, void* stream);
+
+/* out += d/dx [ force(x) . w ]  (force = d(beta*S)/dx): the Hessian-vector product that tf.gradients builds when it
+ * differentiates through grad_potential (dynamics/gauge_dynamics.py:698-709), i.e. the network input `grad`. */
+int l2hmc_u1_force_hvp(const float* x, const float* w, float beta, int N, int T, int X, float* out, void* stream);
+
+/* a[n] = d loss / d (h_old - h_new + sumlogdet) given g_p = d loss / d accept_prob (dynamics/gauge_dynamics.py:592-609). */
+int l2hmc_accept_prob_bwd(const float* h_old, const float* h_new, const float* sumlogdet, const float* g_p, int N,
+                          float* a, void* stream);
+/* Start of a trajectory's backward sweep: gx = gx_post - a * force(x_M), gv = -a * v_M  (gx_post nullable = 0). */
+int l2hmc_traj_bwd_init(const float* a, const float* force, const float* v, const float* gx_post, int N, int D,
+                        float* gx, float* gv, void* stream);
+
+/* d loss / d (x_prop, px, pz) of l2hmc_u1_loss's mean loss (gauge_model.py:762-801). */
+int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, const float* x_prop, const float* z,
+                      const float* px, const float* pz, int N, int T, int X, float* g_xprop /* [N,2TX] */,
+                      float* g_px /* [N] */, float* g_pz /* [N] */, void* stream);
+
+/* out[0] = sum v[i] (square = 0) or sum v[i]^2 (square = 1), fixed two-stage tree; scratch: 1024 floats. */
+int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch, void* stream);
+
+/* tf.train.AdamOptimizer.apply_gradients over a flat parameter arena (gauge_model.py:934-945): lr_t = lr *
+ * sqrt(1 - beta2^t) / (1 - beta1^t) is folded by the caller.  grad_scale multiplies the gradient (1 / world size after
+ * a SUM all-reduce); grad_sumsq (nullable, device [1]) + clip_norm > 0 apply tf.clip_by_global_norm (:826-827). */
+int l2hmc_adam_step(float* param, const float* grad, float* m, float* v, long long n, float lr_t, float beta1,
+                    float beta2, float epsilon, float grad_scale, const float* grad_sumsq, float clip_norm,
+                    void* stream);
 
 #ifdef __cplusplus
 }

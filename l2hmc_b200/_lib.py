@@ -54,7 +54,32 @@ class NetCall(Structure):
         ("row_set", c_void_p), ("tau_cos_alt", c_float), ("tau_sin_alt", c_float),
         ("in1_mask_alt", c_void_p), ("in1_mask_invert_alt", c_int), ("dir_alt", c_int),
         ("mask_alt", c_void_p), ("mask_invert_alt", c_int),
+        ("h1_out", c_void_p), ("h2_out", c_void_p),
     ]
+
+
+class GemmSeg(Structure):
+    """l2hmc_gemm_seg (include/l2hmc_b200.h)."""
+    _fields_ = [("A", c_void_p), ("a_rs", c_longlong), ("a_cs", c_longlong), ("B", c_void_p), ("b_rs", c_longlong),
+                ("b_cs", c_longlong), ("K", c_int)]
+
+
+class GemmArgs(Structure):
+    """l2hmc_gemm_args (include/l2hmc_b200.h)."""
+    _fields_ = [("M", c_int), ("N", c_int), ("nseg", c_int), ("seg", GemmSeg * 3), ("C", c_void_p),
+                ("ldc", c_longlong), ("accumulate", c_int), ("relu_gate", c_void_p), ("ldg", c_longlong),
+                ("col_scale", c_void_p), ("col_scale_invert", c_int), ("row_set", c_void_p),
+                ("col_scale_alt", c_void_p), ("col_scale_invert_alt", c_int)]
+
+
+class UpdateBwdArgs(Structure):
+    """l2hmc_update_bwd_args (include/l2hmc_b200.h)."""
+    _fields_ = [("position", c_int), ("N", c_int), ("D", c_int), ("eps", c_float), ("dir", c_int), ("dir_alt", c_int),
+                ("row_set", c_void_p), ("x", c_void_p), ("v", c_void_p), ("g", c_void_p),
+                ("S", c_void_p), ("T", c_void_p), ("Q", c_void_p), ("coeff_s", c_void_p), ("coeff_q", c_void_p),
+                ("mask", c_void_p), ("mask_alt", c_void_p), ("invert", c_int), ("invert_alt", c_int),
+                ("gx", c_void_p), ("gv", c_void_p), ("gld", c_void_p),
+                ("dA", c_void_p), ("dg", c_void_p), ("ps", c_void_p), ("pq", c_void_p), ("deps", c_void_p)]
 
 
 class Conv3dWeights(Structure):
@@ -150,12 +175,26 @@ SIGNATURES = {
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],
+    "l2hmc_sgemm_workspace_bytes": [POINTER(GemmArgs), c_int],
+    "l2hmc_sgemm": [POINTER(GemmArgs), c_int, c_void_p, c_size_t, c_void_p],
+    "l2hmc_train_update_fwd": [c_int] + [c_void_p] * 7 + [c_int, c_void_p, c_int, c_void_p, c_float, c_int, c_int,
+                                                         c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_mask_mul_sets": [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p],
+    "l2hmc_update_bwd": [POINTER(UpdateBwdArgs), c_void_p],
+    "l2hmc_u1_force_hvp": [c_void_p, c_void_p, c_float, c_int, c_int, c_int, c_void_p, c_void_p],
+    "l2hmc_accept_prob_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p],
+    "l2hmc_traj_bwd_init": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_u1_loss_bwd": [POINTER(LossParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                          c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
+                        c_float, c_void_p, c_float, c_void_p],
     "l2hmc_conv3d_features_sets": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
                                    c_int, c_int, c_int, c_void_p, c_void_p],
 }
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
-            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t}
+            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

@@ -314,9 +314,10 @@ int heads_col_tiles(int D) { return (D + 31) / 32; }
 // Layers 1, 2 and the heads on the FFMA path (also called by gemm_tc.cu for shapes it rejects).
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
   const int N = c->N, K = w->K, H = w->H, D = w->D;
-  float* h1 = static_cast<float*>(c->workspace);
-  float* h2 = h1 + static_cast<size_t>(N) * H;
-  float* ld_part = h2 + static_cast<size_t>(N) * H;
+  float* ws = static_cast<float*>(c->workspace);
+  float* h1 = c->h1_out ? c->h1_out : ws;
+  float* h2 = c->h2_out ? c->h2_out : ws + static_cast<size_t>(N) * H;
+  float* ld_part = ws + 2 * static_cast<size_t>(N) * H;
 
   DenseParams p{};
   p.nseg = 2;
@@ -391,6 +392,11 @@ int net_validate(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
       set_error("l2hmc_net_run: unknown mode %d", c->mode);
       return L2HMC_ERR_INVALID;
   }
+  L2HMC_REQUIRE((c->h1_out == nullptr) == (c->h2_out == nullptr), "l2hmc_net_run: h1_out and h2_out go together");
+  if (c->h1_out != nullptr && c->path == L2HMC_NET_PATH_TCGEN05) {
+    set_error("l2hmc_net_run: the training tape (h1_out / h2_out) is written by the FFMA path only");
+    return L2HMC_ERR_UNSUPPORTED;
+  }
   if (c->row_set != nullptr) {
     L2HMC_REQUIRE((c->in1_mask == nullptr) == (c->in1_mask_alt == nullptr),
                   "l2hmc_net_run: in1_mask and in1_mask_alt must be given together");
@@ -418,6 +424,7 @@ extern "C" int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* c
   if (rc != L2HMC_OK || c->N == 0) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (c->path == L2HMC_NET_PATH_FFMA) return net_run_simt(w, c, st);
+  if (c->h1_out != nullptr) return net_run_simt(w, c, st);
   const bool tc = c->path == L2HMC_NET_PATH_TCGEN05 ? tc_supported(w, c) : tc_eligible(w, c);
   if (c->path == L2HMC_NET_PATH_TCGEN05 && !tc) {
     set_error("l2hmc_net_run: shape K=%d H=%d D=%d N=%d (packed=%p) has no tcgen05 path", w->K, w->H, w->D, c->N,

@@ -1,0 +1,745 @@
+// the backward pass of the training loss and the optimiser step.
+//
+// Replaces (reference l2hmc/...), all of which TensorFlow derives by graph autodiff (`tf.gradients`,
+// gauge_model.py:805-832) -- here every adjoint is written out:
+//   gauge_model.py:762-801                 d loss / d (x_prop, px, pz)            loss_bwd_kernel
+//   dynamics/gauge_dynamics.py:592-609     accept probability                     accept_bwd_kernel, traj_bwd_init_kernel
+//   dynamics/gauge_dynamics.py:486-590     the four augmented-leapfrog updates    momentum_bwd_kernel / position_bwd_kernel
+//   dynamics/gauge_dynamics.py:698-709     force = tf.gradients(beta*S) -> its    force_hvp_kernel (Hessian-vector product,
+//                                          own adjoint is a second derivative     same plaquette stencil applied twice)
+//   network/generic_net.py:129-146         dense trunk + heads                    sgemm_kernel (NT / TN forms, ReLU gate,
+//                                                                                 column-mask and accumulate epilogues)
+//   gauge_model.py:925-945                 tf.train.AdamOptimizer [+ :826-827     adam_kernel (one launch over the flat
+//                                          clip_by_global_norm]                   parameter arena)
+//
+// Design (B200): the forward pass of a training step records a TAPE in HBM (per network call: both inputs, h1, h2,
+// S, T, Q; x- and z-chain stacked into one batch of 2N rows, forward and backward chains in the same launches via
+// row_set).  The backward sweep produces only the per-call activation gradients (dA, dZ2, dZ1) and appends them to
+// the tape; every WEIGHT gradient is one deferred TN GEMM over the whole tape (K = calls x rows instead of `calls`
+// small GEMMs), split along K with a fixed-order second stage, so results are deterministic (no atomics anywhere).
+// Training shapes (configs 2-3) are small: these kernels are FFMA; the tcgen05 path serves inference.
+#include <algorithm>
+
+#include "common.cuh"
+#include "update_math.cuh"
+
+namespace l2hmc {
+namespace {
+
+// =============================================================================================== SGEMM
+constexpr int GBM = 64, GBN = 64, GBK = 16, kGemmThreads = 256;
+
+struct GemmParams {
+  l2hmc_gemm_args a;
+  int ksplit;
+  float* partial;   // [ksplit][M*N] when ksplit > 1
+};
+
+// A_KC / B_KC: the operand's K index is the contiguous one (only affects which threads read neighbouring words)
+template <bool A_KC, bool B_KC>
+__global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p) {
+  __shared__ __align__(16) float As[GBK][GBM + 4];
+  __shared__ __align__(16) float Bs[GBK][GBN + 4];
+  const l2hmc_gemm_args& g = p.a;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * GBM, n0 = blockIdx.x * GBN;
+  const int z = blockIdx.z;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  int am[4], ak[4], bk[4], bn[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int e = tid + i * kGemmThreads;
+    if (A_KC) ak[i] = e & 15, am[i] = e >> 4; else am[i] = e & 63, ak[i] = e >> 6;
+    if (B_KC) bk[i] = e & 15, bn[i] = e >> 4; else bn[i] = e & 63, bk[i] = e >> 6;
+  }
+  float a_reg[4], b_reg[4];
+
+  for (int s = 0; s < g.nseg; ++s) {
+    const l2hmc_gemm_seg& sg = g.seg[s];
+    int kb = 0, ke = sg.K;
+    if (p.ksplit > 1) {
+      int chunk = (sg.K + p.ksplit - 1) / p.ksplit;
+      chunk = (chunk + GBK - 1) / GBK * GBK;
+      kb = min(sg.K, z * chunk);
+      ke = min(sg.K, kb + chunk);
+    }
+    auto load = [&](int k0) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int m = m0 + am[i], k = k0 + ak[i];
+        a_reg[i] = (m < g.M && k < ke) ? sg.A[static_cast<long long>(m) * sg.a_rs + static_cast<long long>(k) * sg.a_cs]
+                                       : 0.f;
+        const int n = n0 + bn[i], k2 = k0 + bk[i];
+        b_reg[i] = (n < g.N && k2 < ke) ? sg.B[static_cast<long long>(k2) * sg.b_rs + static_cast<long long>(n) * sg.b_cs]
+                                        : 0.f;
+      }
+    };
+    if (kb < ke) load(kb);
+    for (int k0 = kb; k0 < ke; k0 += GBK) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) As[ak[i]][am[i]] = a_reg[i], Bs[bk[i]][bn[i]] = b_reg[i];
+      __syncthreads();
+      if (k0 + GBK < ke) load(k0 + GBK);
+#pragma unroll
+      for (int k = 0; k < GBK; ++k) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&As[k][4 * ty]);
+        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][4 * tx]);
+        const float a[4] = {a4.x, a4.y, a4.z, a4.w};
+        const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = m0 + 4 * ty + i;
+    if (r >= g.M) continue;
+    const bool alt = g.row_set != nullptr && g.row_set[r] != 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = n0 + 4 * tx + j;
+      if (c >= g.N) continue;
+      float val = acc[i][j];
+      if (p.ksplit > 1) {
+        p.partial[(static_cast<size_t>(z) * g.M + r) * g.N + c] = val;
+        continue;
+      }
+      if (g.relu_gate != nullptr && !(g.relu_gate[static_cast<long long>(r) * g.ldg + c] > 0.f)) val = 0.f;
+      const float* cs = alt ? g.col_scale_alt : g.col_scale;
+      if (cs != nullptr) {
+        const float sc = cs[c];
+        val = __fmul_rn(val, (alt ? g.col_scale_invert_alt : g.col_scale_invert) ? __fsub_rn(1.f, sc) : sc);
+      }
+      float* dst = g.C + static_cast<long long>(r) * g.ldc + c;
+      if (g.accumulate) val = __fadd_rn(*dst, val);
+      *dst = val;
+    }
+  }
+}
+
+// C[r][c] (+)= sum_z partial[z][r][c], z in fixed order
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int ksplit, int M, int N, float* C,
+                                     long long ldc, int accumulate) {
+  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const size_t total = static_cast<size_t>(M) * N;
+  if (idx >= total) return;
+  float s = 0.f;
+  for (int z = 0; z < ksplit; ++z) s = __fadd_rn(s, partial[static_cast<size_t>(z) * total + idx]);
+  const int r = static_cast<int>(idx / N), c = static_cast<int>(idx % N);
+  float* dst = C + static_cast<long long>(r) * ldc + c;
+  *dst = accumulate ? __fadd_rn(*dst, s) : s;
+}
+
+// =============================================================================================== block helpers
+template <int THREADS>
+__device__ __forceinline__ float block_sum(float v, float* scratch /* >= THREADS/32 floats */) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) scratch[warp] = v;
+  __syncthreads();
+  float s = 0.f;
+  if (warp == 0) {
+    s = lane < THREADS / 32 ? scratch[lane] : 0.f;
+    s = warp_sum(s);
+  }
+  __syncthreads();
+  return s;   // valid in warp 0
+}
+
+constexpr int kRowThreads = 128;
+
+// =============================================================================================== forward updates (tape)
+struct UpdFwdParams {
+  int N, D;
+  float eps;
+  int dir, dir_alt;
+  const uint8_t* row_set;
+  const float *x, *v, *g;
+  const float *S, *T, *Q;
+  const float *mask, *mask_alt;
+  int invert, invert_alt;
+  float* out;
+  float* logdet;
+  int32_t* flag;
+};
+
+// One CTA per chain: the arithmetic of update_math.cuh with per-chain direction / mask set.
+template <bool POSITION>
+__global__ void __launch_bounds__(kRowThreads) train_update_fwd_kernel(const UpdFwdParams p) {
+  __shared__ float scratch[kRowThreads / 32];
+  const int row = blockIdx.x;
+  const bool alt = p.row_set != nullptr && p.row_set[row] != 0;
+  const int dir = alt ? p.dir_alt : p.dir;
+  const float* mask = alt ? p.mask_alt : p.mask;
+  const int invert = alt ? p.invert_alt : p.invert;
+  const float heps = __fmul_rn(0.5f, p.eps);
+  float ld = 0.f;
+  bool bad = false;
+  for (int d = threadIdx.x; d < p.D; d += kRowThreads) {
+    const size_t at = static_cast<size_t>(row) * p.D + d;
+    const float S = p.S ? p.S[at] : 0.f, Tr = p.S ? p.T[at] : 0.f, Q = p.S ? p.Q[at] : 0.f;
+    if (POSITION) {
+      const float m = invert ? __fsub_rn(1.f, mask[d]) : mask[d];
+      p.out[at] = dir > 0 ? position_elem<1>(p.x[at], p.v[at], S, Tr, Q, m, p.eps, ld, bad)
+                          : position_elem<-1>(p.x[at], p.v[at], S, Tr, Q, m, p.eps, ld, bad);
+    } else {
+      p.out[at] = dir > 0 ? momentum_elem<1>(p.v[at], p.g[at], S, Tr, Q, p.eps, heps, ld, bad)
+                          : momentum_elem<-1>(p.v[at], p.g[at], S, Tr, Q, p.eps, heps, ld, bad);
+    }
+  }
+  const float tot = block_sum<kRowThreads>(ld, scratch);
+  if (threadIdx.x == 0 && p.logdet != nullptr) p.logdet[row] = __fadd_rn(p.logdet[row], tot);
+  flag_nonfinite(p.flag, bad);
+}
+
+// out = m (*) x with the per-chain mask set (the second input of position_fn, materialised for the tape)
+__global__ void __launch_bounds__(kRowThreads) mask_mul_sets_kernel(const float* __restrict__ x, const float* mask,
+                                                                    int invert, const float* mask_alt, int invert_alt,
+                                                                    const uint8_t* row_set, int D, float* out) {
+  const int row = blockIdx.x;
+  const bool alt = row_set != nullptr && row_set[row] != 0;
+  const float* m = alt ? mask_alt : mask;
+  const int inv = alt ? invert_alt : invert;
+  for (int d = threadIdx.x; d < D; d += kRowThreads) {
+    const size_t at = static_cast<size_t>(row) * D + d;
+    out[at] = __fmul_rn(inv ? __fsub_rn(1.f, m[d]) : m[d], x[at]);
+  }
+}
+
+// =============================================================================================== backward updates
+struct UpdBwdParams {
+  l2hmc_update_bwd_args a;
+};
+
+__device__ __forceinline__ void heads_bwd(const l2hmc_update_bwd_args& a, int row, int d, size_t at, float S, float Q,
+                                          float dS, float dT, float dQ) {
+  const float es = expf(a.coeff_s[d]);
+  const float t = S / es;
+  float* dst = a.dA + static_cast<size_t>(row) * 3 * a.D;
+  dst[d] = dS * es * (1.f - t * t);
+  dst[a.D + d] = dT;
+  dst[2 * a.D + d] = dQ * expf(a.coeff_q[d]);
+  a.ps[at] = dS * S;
+  a.pq[at] = dQ * Q;
+}
+
+__global__ void __launch_bounds__(kRowThreads) momentum_bwd_kernel(const UpdBwdParams pp) {
+  __shared__ float scratch[kRowThreads / 32];
+  const l2hmc_update_bwd_args& a = pp.a;
+  const int row = blockIdx.x;
+  const bool alt = a.row_set != nullptr && a.row_set[row] != 0;
+  const int dir = alt ? a.dir_alt : a.dir;
+  const float eps = a.eps, heps = 0.5f * a.eps;
+  const float gld = a.gld ? a.gld[row] : 0.f;
+  float de = 0.f;
+  for (int d = threadIdx.x; d < a.D; d += kRowThreads) {
+    const size_t at = static_cast<size_t>(row) * a.D + d;
+    const float gvp = a.gv[at], v = a.v[at], g = a.g[at];
+    if (a.S == nullptr) {               // S = T = Q = 0: v' = v -+ eps/2 g
+      const float sgn = dir > 0 ? -1.f : 1.f;
+      a.dg[at] = sgn * heps * gvp;
+      de += sgn * 0.5f * g * gvp;
+      continue;
+    }
+    const float S = a.S[at], Tr = a.T[at], Q = a.Q[at];
+    const float sc = S * (dir > 0 ? heps : -heps);
+    const float se = expf(sc), te = expf(Q * eps);
+    const float inner = te * g - Tr;
+    float dv, ds, d_inner, dS;
+    if (dir > 0) {
+      dv = gvp * se;
+      ds = gvp * v * se + gld;
+      d_inner = -heps * gvp;
+      de += ds * 0.5f * S - 0.5f * gvp * inner;
+      dS = heps * ds;
+    } else {
+      const float vprime = se * (v + heps * inner);
+      ds = gvp * vprime + gld;
+      const float du = gvp * se;
+      dv = du;
+      d_inner = heps * du;
+      de += -0.5f * ds * S + 0.5f * du * inner;
+      dS = -heps * ds;
+    }
+    const float dq = d_inner * te * g;
+    const float dQ = eps * dq;
+    de += dq * Q;
+    a.gv[at] = dv;
+    a.dg[at] = d_inner * te;
+    heads_bwd(a, row, d, at, S, Q, dS, -d_inner, dQ);
+  }
+  const float tot = block_sum<kRowThreads>(de, scratch);
+  if (threadIdx.x == 0) a.deps[row] += tot;
+}
+
+__global__ void __launch_bounds__(kRowThreads) position_bwd_kernel(const UpdBwdParams pp) {
+  __shared__ float scratch[kRowThreads / 32];
+  const l2hmc_update_bwd_args& a = pp.a;
+  const int row = blockIdx.x;
+  const bool alt = a.row_set != nullptr && a.row_set[row] != 0;
+  const int dir = alt ? a.dir_alt : a.dir;
+  const float* mask = alt ? a.mask_alt : a.mask;
+  const int invert = alt ? a.invert_alt : a.invert;
+  const float eps = a.eps;
+  const float gld = a.gld ? a.gld[row] : 0.f;
+  float de = 0.f;
+  for (int d = threadIdx.x; d < a.D; d += kRowThreads) {
+    const size_t at = static_cast<size_t>(row) * a.D + d;
+    const float gxp = a.gx[at], x = a.x[at], v = a.v[at];
+    const float m = invert ? 1.f - mask[d] : mask[d];
+    const float mi = 1.f - m;
+    if (a.S == nullptr) {               // x' = x +- mbar eps v
+      const float sgn = dir > 0 ? 1.f : -1.f;
+      a.gv[at] += sgn * mi * eps * gxp;
+      de += sgn * mi * v * gxp;
+      continue;
+    }
+    const float S = a.S[at], Tr = a.T[at], Q = a.Q[at];
+    const float sc = S * (dir > 0 ? eps : -eps);
+    const float se = expf(sc), te = expf(Q * eps);
+    const float inner = te * v + Tr;
+    const float dy = mi * gxp;
+    const float dx = m * gxp + dy * se;
+    float ds, d_inner, dS;
+    if (dir > 0) {
+      ds = dy * x * se + gld * mi;
+      dS = eps * ds;
+      d_inner = eps * dy;
+      de += ds * S + dy * inner;
+    } else {
+      const float y = se * (x - eps * inner);
+      ds = dy * y + gld * mi;
+      dS = -eps * ds;
+      const float dw = dy * se;
+      d_inner = -eps * dw;
+      de += -ds * S - dw * inner;
+    }
+    const float dq = d_inner * te * v;
+    const float dQ = eps * dq;
+    de += dq * Q;
+    a.gx[at] = dx;
+    a.gv[at] += d_inner * te;
+    heads_bwd(a, row, d, at, S, Q, dS, d_inner, dQ);
+  }
+  const float tot = block_sum<kRowThreads>(de, scratch);
+  if (threadIdx.x == 0) a.deps[row] += tot;
+}
+
+// =============================================================================================== stencil adjoints
+// One warp per chain, the chain staged in shared memory (any T x X).
+//   HVP: out += d/dx [ g(x) . w ],  g = beta dS/dx:   c(site) = beta cos P(site) * Pw(site),
+//        Pw = the plaquette stencil applied to w;  out0(t,x) += c(t,x) - c(t,x-1);  out1(t,x) += -c(t,x) + c(t-1,x)
+struct HvpParams {
+  const float* x;
+  const float* w;
+  float beta;
+  int N, T, X;
+  float* out;
+};
+
+__device__ __forceinline__ float plaq_at(const float* s, int i, int T, int X) {
+  const int t = i / X, xx = i - t * X;
+  const int sr = t * X + (xx + 1 == X ? 0 : xx + 1);
+  const int sd = (t + 1 == T ? 0 : t + 1) * X + xx;
+  return __fadd_rn(__fsub_rn(__fsub_rn(s[2 * i], s[2 * i + 1]), s[2 * sr]), s[2 * sd + 1]);
+}
+
+// out[link] (+)= stencil adjoint of the per-site coefficients c: (c(t,x) - c(t,x-1), -c(t,x) + c(t-1,x))
+__device__ __forceinline__ void site_adjoint(const float* c, int i, int T, int X, float& o0, float& o1) {
+  const int t = i / X, xx = i - t * X;
+  const int sl = t * X + (xx == 0 ? X - 1 : xx - 1);
+  const int su = (t == 0 ? T - 1 : t - 1) * X + xx;
+  o0 = c[i] - c[sl];
+  o1 = -c[i] + c[su];
+}
+
+__global__ void __launch_bounds__(128) force_hvp_kernel(const HvpParams p, int warps_per_block) {
+  extern __shared__ __align__(16) float s_all[];
+  const int T = p.T, X = p.X, SITES = T * X, D = 2 * SITES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* sx = s_all + static_cast<size_t>(warp) * (2 * D + SITES);
+  float* sw = sx + D;
+  float* sc = sw + D;
+  for (int n = blockIdx.x * warps_per_block + warp; n < p.N; n += gridDim.x * warps_per_block) {
+    const size_t base = static_cast<size_t>(n) * D;
+    for (int i = lane; i < D; i += 32) sx[i] = p.x[base + i], sw[i] = p.w[base + i];
+    __syncwarp();
+    for (int i = lane; i < SITES; i += 32) {
+      const float P = plaq_at(sx, i, T, X);
+      const float Pw = plaq_at(sw, i, T, X);
+      sc[i] = p.beta * cosf(P) * Pw;
+    }
+    __syncwarp();
+    for (int i = lane; i < SITES; i += 32) {
+      float o0, o1;
+      site_adjoint(sc, i, T, X, o0, o1);
+      p.out[base + 2 * i] += o0;
+      p.out[base + 2 * i + 1] += o1;
+    }
+    __syncwarp();
+  }
+}
+
+// a[n] = d loss / d (h_old - h_new + sumlogdet) through p = exp(min(., 0)), non-finite -> 0
+__global__ void accept_bwd_kernel(const float* __restrict__ h_old, const float* __restrict__ h_new,
+                                  const float* __restrict__ sld, const float* __restrict__ gp, int N, float* a) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float arg = __fsub_rn(h_old[n], h_new[n]);
+  if (sld) arg = __fadd_rn(arg, sld[n]);
+  const float pr = expf(fminf(arg, 0.f));
+  a[n] = (arg <= 0.f && isfinite(pr)) ? gp[n] * pr : 0.f;   // tf.minimum routes the tie to its first argument
+}
+
+// gx = gx_post - a * force(x_M),  gv = -a * v_M      (H_new = beta S(x_M) + v_M^2 / 2 enters with a minus sign)
+__global__ void __launch_bounds__(kRowThreads) traj_bwd_init_kernel(const float* __restrict__ a,
+                                                                   const float* __restrict__ force,
+                                                                   const float* __restrict__ v,
+                                                                   const float* __restrict__ gx_post, int D, float* gx,
+                                                                   float* gv) {
+  const int row = blockIdx.x;
+  const float ar = a[row];
+  for (int d = threadIdx.x; d < D; d += kRowThreads) {
+    const size_t at = static_cast<size_t>(row) * D + d;
+    gx[at] = (gx_post ? gx_post[at] : 0.f) - ar * force[at];
+    gv[at] = -ar * v[at];
+  }
+}
+
+// =============================================================================================== loss backward
+struct LossBwdParams {
+  const float *x, *x_prop, *z, *px, *pz;
+  int N, T, X, metric;
+  float loss_scale, aux_weight, std_weight, charge_weight;
+  float *g_xprop, *g_px, *g_pz;
+};
+
+__device__ __forceinline__ float metric_fwd(int metric, float a, float b) {
+  switch (metric) {
+    case L2HMC_METRIC_L1: return fabsf(a - b);
+    case L2HMC_METRIC_L2: return (a - b) * (a - b);
+    case L2HMC_METRIC_COS: return fabsf(cosf(a) - cosf(b));
+    case L2HMC_METRIC_COS2: { const float d = cosf(a) - cosf(b); return d * d; }
+    default: return 1.f - cosf(a - b);
+  }
+}
+__device__ __forceinline__ float sgnf(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
+// d metric(a, b) / d b
+__device__ __forceinline__ float metric_db(int metric, float a, float b) {
+  switch (metric) {
+    case L2HMC_METRIC_L1: return -sgnf(a - b);
+    case L2HMC_METRIC_L2: return -2.f * (a - b);
+    case L2HMC_METRIC_COS: return sgnf(cosf(a) - cosf(b)) * sinf(b);
+    case L2HMC_METRIC_COS2: return 2.f * (cosf(a) - cosf(b)) * sinf(b);
+    default: return -sinf(a - b);
+  }
+}
+__device__ __forceinline__ float proj_approx(float p) {   // gauge_model.py:94-108
+  return 2.f * sinf(p) - sinf(2.f * p) + 0.6666666666666666f * sinf(3.f * p) - 0.5f * sinf(4.f * p);
+}
+__device__ __forceinline__ float proj_approx_d(float p) {
+  return 2.f * (cosf(p) - cosf(2.f * p) + cosf(3.f * p) - cosf(4.f * p));
+}
+__device__ __forceinline__ float charge_fft(const float* s, int T, int X, int lane) {
+  float q = 0.f;
+  for (int i = lane; i < T * X; i += 32) q += proj_approx(plaq_at(s, i, T, X));
+  return warp_sum(q) / kTwoPi;
+}
+
+__global__ void __launch_bounds__(128) loss_bwd_kernel(const LossBwdParams p, int warps_per_block) {
+  extern __shared__ __align__(16) float s_all[];
+  const int T = p.T, X = p.X, SITES = T * X, D = 2 * SITES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* s0 = s_all + static_cast<size_t>(warp) * 3 * D;
+  float* s1 = s0 + D;
+  float* s2 = s1 + D;
+  const float inv_n = 1.f / static_cast<float>(p.N);
+  for (int n = blockIdx.x * warps_per_block + warp; n < p.N; n += gridDim.x * warps_per_block) {
+    const size_t base = static_cast<size_t>(n) * D;
+    float xs = 0.f, zs = 0.f;
+    for (int i = lane; i < D; i += 32) {
+      const float a = p.x[base + i], b = p.x_prop[base + i], c = p.z[base + i];
+      s0[i] = a, s1[i] = b, s2[i] = c;
+      xs += metric_fwd(p.metric, a, b);
+      zs += metric_fwd(p.metric, c, b);
+    }
+    __syncwarp();
+    xs = warp_sum(xs);
+    zs = warp_sum(zs);
+    const float qx = charge_fft(s0, T, X, lane), qp = charge_fft(s1, T, X, lane), qz = charge_fft(s2, T, X, lane);
+    const float e = 1e-3f;
+    const float px = p.px[n], pz = p.pz[n];
+    const float ls = p.loss_scale, aw = p.aux_weight, sw = p.std_weight, cw = p.charge_weight;
+    const float x_std = xs * px + e, z_std = aw * (zs * pz + e);
+    const float dstd_dx = sw * (-ls / (x_std * x_std) - 1.f / ls);
+    const float dstd_dz = sw * (-ls / (z_std * z_std) - 1.f / ls);
+    if (lane == 0) {
+      p.g_px[n] = inv_n * (dstd_dx * xs + cw * fabsf(qx - qp));
+      p.g_pz[n] = inv_n * (dstd_dz * aw * zs + cw * aw * fabsf(qz - qp));
+    }
+    const float kx = inv_n * dstd_dx * px;
+    const float kz = inv_n * dstd_dz * aw * pz;
+    const float kq = inv_n * cw * (-px * sgnf(qx - qp) - aw * pz * sgnf(qz - qp)) / kTwoPi;
+    // metric part (each lane touches only its own entries of s0 / s2)
+    for (int i = lane; i < D; i += 32) {
+      const float b = s1[i];
+      s0[i] = kx * metric_db(p.metric, s0[i], b) + kz * metric_db(p.metric, s2[i], b);
+    }
+    __syncwarp();
+    // charge part: per-site coefficient into s2, then the link stencil
+    for (int i = lane; i < SITES; i += 32) s2[i] = kq * proj_approx_d(plaq_at(s1, i, T, X));
+    __syncwarp();
+    for (int i = lane; i < SITES; i += 32) {
+      float o0, o1;
+      site_adjoint(s2, i, T, X, o0, o1);
+      p.g_xprop[base + 2 * i] = s0[2 * i] + o0;
+      p.g_xprop[base + 2 * i + 1] = s0[2 * i + 1] + o1;
+    }
+    __syncwarp();
+  }
+}
+
+template <typename K>
+int warp_per_chain_launch(K kernel, size_t per_warp_bytes, int N, const char* what, int* grid, int* warps, size_t* smem) {
+  int dev = 0, max_smem = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int w = 4;
+  while (w > 1 && per_warp_bytes * w > 100 * 1024) w >>= 1;
+  const size_t bytes = per_warp_bytes * w;
+  if (bytes > static_cast<size_t>(max_smem)) {
+    set_error("%s: a chain (%zu B staged) does not fit shared memory (%d B)", what, bytes, max_smem);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
+  if (bytes > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(%s): %s", what, cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+  }
+  *grid = max(1, min((N + w - 1) / w, sms * 8));
+  *warps = w;
+  *smem = bytes;
+  return L2HMC_OK;
+}
+
+// =============================================================================================== reductions / Adam
+// stage 1: partial[b] = sum over a grid-stride slice (fixed assignment); stage 2: one block, fixed tree
+template <bool SQUARE>
+__global__ void __launch_bounds__(256) reduce_stage1_kernel(const float* __restrict__ v, long long n, float* partial) {
+  __shared__ float scratch[8];
+  float s = 0.f;
+  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) {
+    const float t = v[i];
+    s += SQUARE ? t * t : t;
+  }
+  const float tot = block_sum<256>(s, scratch);
+  if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(256) reduce_stage2_kernel(const float* __restrict__ partial, int nb, float* out) {
+  __shared__ float scratch[8];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < nb; i += 256) s += partial[i];
+  const float tot = block_sum<256>(s, scratch);
+  if (threadIdx.x == 0) out[0] = tot;
+}
+
+// tf.train.AdamOptimizer (lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) folded on the host):
+//   m = b1 m + (1 - b1) g;  v = b2 v + (1 - b2) g^2;  theta -= lr_t m / (sqrt(v) + eps)
+// with g scaled by clip / max(||g||, clip) when a global-norm clip is given (tf.clip_by_global_norm).
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ param, const float* __restrict__ grad,
+                                                   float* __restrict__ m, float* __restrict__ v, long long n, float lr_t,
+                                                   float b1, float b2, float eps, float grad_scale,
+                                                   const float* sumsq, float clip) {
+  float scale = grad_scale;
+  if (sumsq != nullptr && clip > 0.f) {
+    const float norm = sqrtf(sumsq[0]) * fabsf(grad_scale);
+    scale *= clip / fmaxf(norm, clip);
+  }
+  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256) {
+    const float g = grad[i] * scale;
+    const float mi = b1 * m[i] + (1.f - b1) * g;
+    const float vi = b2 * v[i] + (1.f - b2) * g * g;
+    m[i] = mi, v[i] = vi;
+    param[i] -= lr_t * mi / (sqrtf(vi) + eps);
+  }
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+// =============================================================================================== C ABI
+extern "C" size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {
+  if (!g || ksplit <= 1) return 0;
+  return sizeof(float) * static_cast<size_t>(ksplit) * g->M * g->N;
+}
+
+extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t workspace_bytes, void* stream) {
+  L2HMC_REQUIRE(g, "l2hmc_sgemm: null arguments");
+  L2HMC_REQUIRE(g->M >= 0 && g->N >= 0 && g->nseg >= 1 && g->nseg <= 3, "l2hmc_sgemm: bad sizes M=%d N=%d nseg=%d", g->M,
+                g->N, g->nseg);
+  if (g->M == 0 || g->N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(g->C, "l2hmc_sgemm: null C");
+  for (int s = 0; s < g->nseg; ++s)
+    L2HMC_REQUIRE(g->seg[s].A && g->seg[s].B && g->seg[s].K >= 0, "l2hmc_sgemm: bad segment %d", s);
+  if (ksplit < 1) ksplit = 1;
+  if (ksplit > 1) {
+    L2HMC_REQUIRE(g->nseg == 1 && !g->relu_gate && !g->col_scale && !g->row_set,
+                  "l2hmc_sgemm: split-K takes one segment and no epilogue");
+    L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_sgemm_workspace_bytes(g, ksplit),
+                  "l2hmc_sgemm: split-K workspace too small");
+  }
+  if (g->row_set) L2HMC_REQUIRE(!g->col_scale == !g->col_scale_alt, "l2hmc_sgemm: col_scale and col_scale_alt go together");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GemmParams p{*g, ksplit, static_cast<float*>(workspace)};
+  dim3 grid((g->N + GBN - 1) / GBN, (g->M + GBM - 1) / GBM, ksplit);
+  const bool akc = g->seg[0].a_cs == 1, bkc = g->seg[0].b_rs == 1 && g->seg[0].b_cs != 1;
+  if (akc && bkc) sgemm_kernel<true, true><<<grid, kGemmThreads, 0, st>>>(p);
+  else if (akc) sgemm_kernel<true, false><<<grid, kGemmThreads, 0, st>>>(p);
+  else if (bkc) sgemm_kernel<false, true><<<grid, kGemmThreads, 0, st>>>(p);
+  else sgemm_kernel<false, false><<<grid, kGemmThreads, 0, st>>>(p);
+  int rc = check_launch("sgemm_kernel");
+  if (rc || ksplit == 1) return rc;
+  const size_t total = static_cast<size_t>(g->M) * g->N;
+  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(p.partial, ksplit, g->M, g->N, g->C,
+                                                                                  g->ldc, g->accumulate);
+  return check_launch("splitk_reduce_kernel");
+}
+
+extern "C" int l2hmc_train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S,
+                                      const float* Tr, const float* Q, const float* mask, int invert,
+                                      const float* mask_alt, int invert_alt, const uint8_t* row_set, float eps, int dir,
+                                      int dir_alt, int N, int D, float* out, float* logdet, int32_t* nonfinite_flag,
+                                      void* stream) {
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(N > 0 && D > 0 && v && out, "l2hmc_train_update_fwd: bad arguments");
+  L2HMC_REQUIRE((dir == 1 || dir == -1) && (!row_set || dir_alt == 1 || dir_alt == -1), "l2hmc_train_update_fwd: dir");
+  L2HMC_REQUIRE((S == nullptr) == (Tr == nullptr) && (S == nullptr) == (Q == nullptr),
+                "l2hmc_train_update_fwd: S, T, Q go together");
+  if (position) L2HMC_REQUIRE(x && mask && (!row_set || mask_alt), "l2hmc_train_update_fwd: position needs x and masks");
+  else L2HMC_REQUIRE(g, "l2hmc_train_update_fwd: momentum needs g");
+  UpdFwdParams p{N, D, eps, dir, dir_alt, row_set, x, v, g, S, Tr, Q, mask, mask_alt, invert, invert_alt, out, logdet,
+                 nonfinite_flag};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (position) train_update_fwd_kernel<true><<<N, kRowThreads, 0, st>>>(p);
+  else train_update_fwd_kernel<false><<<N, kRowThreads, 0, st>>>(p);
+  return check_launch("train_update_fwd_kernel");
+}
+
+extern "C" int l2hmc_mask_mul_sets(const float* x, const float* mask, int invert, const float* mask_alt, int invert_alt,
+                                   const uint8_t* row_set, int N, int D, float* out, void* stream) {
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(x && mask && out && N > 0 && D > 0 && (!row_set || mask_alt), "l2hmc_mask_mul_sets: bad arguments");
+  mask_mul_sets_kernel<<<N, kRowThreads, 0, static_cast<cudaStream_t>(stream)>>>(x, mask, invert, mask_alt, invert_alt,
+                                                                               row_set, D, out);
+  return check_launch("mask_mul_sets_kernel");
+}
+
+extern "C" int l2hmc_update_bwd(const l2hmc_update_bwd_args* a, void* stream) {
+  L2HMC_REQUIRE(a, "l2hmc_update_bwd: null arguments");
+  if (a->N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(a->N > 0 && a->D > 0 && a->v && a->gv && a->deps, "l2hmc_update_bwd: bad arguments");
+  L2HMC_REQUIRE((a->dir == 1 || a->dir == -1) && (!a->row_set || a->dir_alt == 1 || a->dir_alt == -1),
+                "l2hmc_update_bwd: dir");
+  if (a->S) L2HMC_REQUIRE(a->T && a->Q && a->coeff_s && a->coeff_q && a->dA && a->ps && a->pq,
+                          "l2hmc_update_bwd: the network outputs need T, Q, coeff_*, dA, ps, pq");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  UpdBwdParams p{*a};
+  if (a->position) {
+    L2HMC_REQUIRE(a->x && a->gx && a->mask && (!a->row_set || a->mask_alt), "l2hmc_update_bwd: position needs x, gx, masks");
+    position_bwd_kernel<<<a->N, kRowThreads, 0, st>>>(p);
+    return check_launch("position_bwd_kernel");
+  }
+  L2HMC_REQUIRE(a->g && a->dg, "l2hmc_update_bwd: momentum needs g and dg");
+  momentum_bwd_kernel<<<a->N, kRowThreads, 0, st>>>(p);
+  return check_launch("momentum_bwd_kernel");
+}
+
+extern "C" int l2hmc_u1_force_hvp(const float* x, const float* w, float beta, int N, int T, int X, float* out,
+                                  void* stream) {
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(x && w && out && N > 0 && T > 0 && X > 0, "l2hmc_u1_force_hvp: bad arguments");
+  int grid, warps;
+  size_t smem;
+  int rc = warp_per_chain_launch(force_hvp_kernel, sizeof(float) * 5u * T * X, N, "force_hvp_kernel", &grid, &warps, &smem);
+  if (rc) return rc;
+  HvpParams p{x, w, beta, N, T, X, out};
+  force_hvp_kernel<<<grid, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p, warps);
+  return check_launch("force_hvp_kernel");
+}
+
+extern "C" int l2hmc_accept_prob_bwd(const float* h_old, const float* h_new, const float* sumlogdet, const float* g_p,
+                                     int N, float* a, void* stream) {
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(h_old && h_new && g_p && a && N > 0, "l2hmc_accept_prob_bwd: bad arguments");
+  accept_bwd_kernel<<<(N + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(h_old, h_new, sumlogdet, g_p, N, a);
+  return check_launch("accept_bwd_kernel");
+}
+
+extern "C" int l2hmc_traj_bwd_init(const float* a, const float* force, const float* v, const float* gx_post, int N, int D,
+                                   float* gx, float* gv, void* stream) {
+  if (N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(a && force && v && gx && gv && N > 0 && D > 0, "l2hmc_traj_bwd_init: bad arguments");
+  traj_bwd_init_kernel<<<N, kRowThreads, 0, static_cast<cudaStream_t>(stream)>>>(a, force, v, gx_post, D, gx, gv);
+  return check_launch("traj_bwd_init_kernel");
+}
+
+extern "C" int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, const float* x_prop, const float* z,
+                                 const float* px, const float* pz, int N, int T, int X, float* g_xprop, float* g_px,
+                                 float* g_pz, void* stream) {
+  L2HMC_REQUIRE(prm, "l2hmc_u1_loss_bwd: null parameters");
+  L2HMC_REQUIRE(N > 0 && T > 0 && X > 0, "l2hmc_u1_loss_bwd: bad sizes N=%d T=%d X=%d", N, T, X);
+  L2HMC_REQUIRE(x && x_prop && z && px && pz && g_xprop && g_px && g_pz, "l2hmc_u1_loss_bwd: null pointer");
+  L2HMC_REQUIRE(prm->metric >= L2HMC_METRIC_L1 && prm->metric <= L2HMC_METRIC_COS_DIFF, "l2hmc_u1_loss_bwd: metric %d",
+                prm->metric);
+  int grid, warps;
+  size_t smem;
+  int rc = warp_per_chain_launch(loss_bwd_kernel, sizeof(float) * 6u * T * X, N, "loss_bwd_kernel", &grid, &warps, &smem);
+  if (rc) return rc;
+  LossBwdParams p{x, x_prop, z, px, pz, N, T, X, prm->metric, prm->loss_scale, prm->aux_weight, prm->std_weight,
+                  prm->charge_weight, g_xprop, g_px, g_pz};
+  loss_bwd_kernel<<<grid, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p, warps);
+  return check_launch("loss_bwd_kernel");
+}
+
+extern "C" int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch /* [1024] */,
+                                void* stream) {
+  L2HMC_REQUIRE(v && out && scratch && n >= 0, "l2hmc_reduce_sum: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = static_cast<int>(std::max<long long>(1, std::min<long long>(1024, (n + 255) / 256)));
+  if (square) reduce_stage1_kernel<true><<<nb, 256, 0, st>>>(v, n, scratch);
+  else reduce_stage1_kernel<false><<<nb, 256, 0, st>>>(v, n, scratch);
+  int rc = check_launch("reduce_stage1_kernel");
+  if (rc) return rc;
+  reduce_stage2_kernel<<<1, 256, 0, st>>>(scratch, nb, out);
+  return check_launch("reduce_stage2_kernel");
+}
+
+extern "C" int l2hmc_adam_step(float* param, const float* grad, float* m, float* v, long long n, float lr_t, float beta1,
+                               float beta2, float epsilon, float grad_scale, const float* grad_sumsq, float clip_norm,
+                               void* stream) {
+  if (n == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(param && grad && m && v && n > 0, "l2hmc_adam_step: bad arguments");
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int nb = static_cast<int>(std::max<long long>(1, std::min<long long>(sms * 8LL, (n + 255) / 256)));
+  adam_kernel<<<nb, 256, 0, static_cast<cudaStream_t>(stream)>>>(param, grad, m, v, n, lr_t, beta1, beta2, epsilon,
+                                                               grad_scale, grad_sumsq, clip_norm);
+  return check_launch("adam_kernel");
+}

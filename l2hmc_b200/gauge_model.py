@@ -8,8 +8,11 @@ Mirrors, with the same names and argument meaning (reference l2hmc/gauge_model.p
   :728-803    _calc_loss(x, beta, **weights) -> (loss, x_out, px, x_dq)
   :1039-1046  update_beta (1/beta-linear annealing)
   :1473-1533  calc_observables_stats(observables, therm_frac)
-All arithmetic runs in csrc/loss.cu, csrc/stats.cu and the path's own kernels; there is no CPU fallback.
-The backward pass (_calc_loss_and_grads, :805-832), the optimiser and checkpointing are not built yet.
+  :805-832    _calc_loss_and_grads(x, beta, **weights) -> (loss, grads, x_out, px, x_dq)   [training.py, csrc/train.cu]
+  :925-945    learning-rate schedule + Adam (train_op)   :1155-1190  one iteration of the training loop (train_step)
+  :519-556    saved state (save_state / restore_state)
+All arithmetic runs in csrc/loss.cu, csrc/stats.cu, csrc/train.cu and the path's own kernels; there is no CPU fallback.
+The backward pass covers network_arch='generic' and hmc=True; the conv3D front-end's backward is not built yet.
 """
 import collections
 import ctypes
@@ -26,6 +29,7 @@ PARAMS = {  # globals.py:22-47 (the keys this mirror reads)
     'num_steps': 5, 'eps': 0.25, 'loss_scale': 1., 'beta_init': 2., 'beta_final': 4., 'train_steps': 10000,
     'hmc': False, 'network_arch': 'generic', 'metric': 'cos_diff', 'std_weight': 1., 'aux_weight': 1.,
     'charge_weight': 1., 'annealing': True, 'data_format': 'channels_last',
+    'lr_init': 1e-3, 'lr_decay_steps': 1000, 'lr_decay_rate': 0.96, 'clip_grads': False, 'clip_value': 1.,
 }
 
 
@@ -91,6 +95,9 @@ class GaugeModel(object):
         self.metric_fn = self._create_metric_fn(self.metric)
         self.beta = self.beta_init
         self._z_step = 0
+        self._engine = self._optimizer = None
+        self.global_step = 0
+        self.using_hvd = False          # set by train(): lr * world size, gradients averaged (gauge_model.py:939-941)
 
     # ------------------------------------------------------------------ construction (:585-613)
     def _create_lattice(self):
@@ -171,9 +178,152 @@ class GaugeModel(object):
         self.last_per_chain_loss = per_chain
         return loss[0], x_out, px, x_dq
 
-    def _calc_loss_and_grads(self, x, beta, **weights):
-        raise NotImplementedError("the backward pass (tf.gradients of the loss, gauge_model.py:805-832) is the next "
-                                  "row of SURVEY section 8(f); only the loss value is built")
+    # ------------------------------------------------------------------ backward pass + optimiser (:805-832, :925-945)
+    @property
+    def engine(self):
+        """Tape / backward engine; created on first use (it re-points the nets' weights into one flat arena, so load
+        weights into the dynamics BEFORE the first training call)."""
+        if self._engine is None:
+            from .training import Adam, TrainEngine
+            self._engine = TrainEngine(self.dynamics, metric=self.metric_fn, loss_scale=self.loss_scale)
+            self._optimizer = Adam(self._engine.params)
+        return self._engine
+
+    def _draws(self, x, draws_x, z, draws_z):
+        """The in-graph draws of _calc_loss (:754-758): injected, or from the Philox stream."""
+        dyn, lib = self.dynamics, _lib.get_lib()
+        N, D = x.shape
+        dev = x.device
+
+        def philox(seed):
+            v = torch.empty(N, D, dtype=torch.float32, device=dev)
+            ud, ua = (torch.empty(N, dtype=torch.float32, device=dev) for _ in range(2))
+            with torch.cuda.device(dev):
+                _lib.check(lib.l2hmc_philox_draws(int(seed), int(dyn._mc_step), int(dyn.chain_offset), N, D,
+                                                  _lib.dptr(v), _lib.dptr(ud), _lib.dptr(ua), _lib.stream_ptr()))
+            return v, ud, ua
+        if draws_x is None:
+            v, ud, ua = philox(dyn.seed)
+            draws_x = (v, v, ud, ua)
+        if z is None:
+            z = philox(int(dyn.seed) ^ 0x5A5A5A5A)[0]
+        if draws_z is None:
+            v, ud, ua = philox(int(dyn.seed) ^ 0x3C3C3C3C)
+            draws_z = (v, v, ud, ua)
+            dyn._mc_step += 1
+        dv = lambda a: to_device(a, self.device).reshape(N, -1).contiguous()
+        d1 = lambda a: to_device(a, self.device).reshape(-1).contiguous()
+        fix = lambda d: (dv(d[0]), dv(d[1] if d[1] is not None else d[0]), d1(d[2]), d1(d[3]))
+        return fix(draws_x), dv(z), fix(draws_z)
+
+    def _calc_loss_and_grads(self, x, beta, draws_x=None, z=None, draws_z=None, **weights):
+        """(loss, grads, x_out, px, x_dq) -- gauge_model.py:805-832.  `grads` is a dict of views into the flat
+        gradient arena keyed 'eps', 'XNet.<layer>.kernel', ... in the order of dynamics.variables."""
+        x = self._x(x).contiguous()
+        w = dict(self.loss_weights)
+        w.update(weights)
+        draws_x, z, draws_z = self._draws(x, draws_x, z, draws_z)
+        eng = self.engine
+        with torch.cuda.device(self.device):
+            fw = eng.forward(x, beta, draws_x, z, draws_z, w)
+            grads = eng.backward(fw)
+        self.last_per_chain_loss, self.last_forward = fw["per_chain"], fw
+        return fw["loss"][0], grads, fw["x_out"], fw["px"], fw["x_dq"]
+
+    def learning_rate(self, global_step=None):
+        """tf.train.exponential_decay(..., staircase=True) (:934-939), times the world size under Horovod (:940)."""
+        from .training import exponential_decay
+        step = self.global_step if global_step is None else global_step
+        lr = exponential_decay(self.lr_init, step, self.lr_decay_steps, self.lr_decay_rate, staircase=True)
+        if self.using_hvd:
+            import torch.distributed as dist
+            lr *= dist.get_world_size()
+        return lr
+
+    def train_step(self, samples, beta=None, **inject):
+        """One iteration of the training loop (:1155-1190): loss + gradients, [all-reduce], Adam, observables of the
+        new samples.  Returns (loss, samples_out, px, eps, actions, plaqs, charges, lr, charge_diff) with
+        samples_out = mod(x_out, 2 pi) as the loop feeds it back (:1180)."""
+        beta = self.beta if beta is None else beta
+        loss, grads, x_out, px, x_dq = self._calc_loss_and_grads(samples, beta, **inject)
+        eng, opt = self.engine, self._optimizer
+        scale = 1.
+        if self.using_hvd:
+            from .sharding import allreduce_mean_
+            allreduce_mean_(eng.params.grad)                      # hvd.DistributedOptimizer: averaged gradients
+        lr = self.learning_rate()
+        with torch.cuda.device(self.device):
+            opt.step(lr, grad_scale=scale, clip_norm=self.clip_value if self.clip_grads else 0.)
+        self.global_step += 1
+        x_new = self._wrap(x_out)
+        actions, plaqs, _, charges = self.lattice.observables(x_new)
+        charge_diff = x_dq.sum().to(torch.float32) / self.num_samples
+        return loss, x_new, px, self.dynamics.eps, actions, plaqs, charges, lr, charge_diff
+
+    def _wrap(self, x):
+        """np.mod(x_out, 2 pi) of the host loop (:1180) on the device (exact, l2hmc_mh_select's wrap)."""
+        N, D = x.shape
+        out = torch.empty_like(x)
+        ones = torch.ones(N, dtype=torch.float32, device=x.device)
+        zeros = torch.zeros(N, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.get_lib().l2hmc_mh_select(_lib.dptr(x), _lib.dptr(x), None, None, None, _lib.dptr(ones), None,
+                                                      None, _lib.dptr(zeros), N, D, 1, None, None, None, _lib.dptr(out),
+                                                      None, _lib.stream_ptr()))
+        return out
+
+    def train(self, train_steps, samples_init=None, beta_init=None, distributed=False, log=None):
+        """The training loop (:1112-1230) without files / TensorBoard: beta annealing (:1158), train_step, feed the
+        wrapped samples back.  distributed=True: one process per GPU, weights broadcast from rank 0 at the start
+        (BroadcastGlobalVariablesHook), lr * world size, gradients averaged, steps // world size (:2085-2096)."""
+        self.using_hvd = bool(distributed)
+        samples = self._x(self.lattice.samples if samples_init is None else samples_init).contiguous()
+        eng = self.engine
+        if self.using_hvd:
+            import torch.distributed as dist
+            from .sharding import broadcast_weights
+            broadcast_weights([eng.params.flat])
+            eng.params.sync_to_dynamics()
+            train_steps = train_steps // dist.get_world_size()
+        history = []
+        for step in range(self.global_step, train_steps):
+            self.beta = self.update_beta(step) if self.annealing else (self.beta_init if beta_init is None else beta_init)
+            out = self.train_step(samples, self.beta)
+            samples = out[1]
+            if log is not None:
+                log(step, out, self.beta)
+            history.append(out[0])
+        self.samples = samples
+        return samples, history
+
+    # ------------------------------------------------------------------ saved state (:519-556, :1104-1110)
+    def save_state(self, path, samples=None):
+        """Weights, eps, Adam moments, masks, step, beta and the current samples in one torch.save file (the
+        reference pickles the same items next to a TF checkpoint; its on-disk format is not kept)."""
+        eng, opt = self.engine, self._optimizer
+        state = {"names": eng.params.names, "shapes": eng.params.shapes, "offsets": eng.params.offsets,
+                 "flat": eng.params.flat.cpu(), "adam_m": opt.m.cpu(), "adam_v": opt.v.cpu(), "adam_t": opt.t,
+                 "global_step": self.global_step, "beta": float(self.beta), "lr": self.learning_rate(),
+                 "mask": self.dynamics.mask.cpu(), "mc_step": self.dynamics._mc_step, "z_step": self._z_step,
+                 "samples": None if samples is None else to_device(samples, self.device).cpu(),
+                 "params": dict(self.params)}
+        torch.save(state, path)
+
+    def restore_state(self, path):
+        """Inverse of save_state; returns the saved samples (or None)."""
+        state = torch.load(path, map_location="cpu", weights_only=False)
+        eng, opt = self.engine, self._optimizer
+        if list(state["names"]) != list(eng.params.names) or list(state["offsets"]) != list(eng.params.offsets):
+            raise ValueError("restore_state: the saved variables do not match this model")
+        eng.params.flat.copy_(state["flat"])
+        opt.m.copy_(state["adam_m"])
+        opt.v.copy_(state["adam_v"])
+        opt.t = int(state["adam_t"])
+        self.global_step, self.beta = int(state["global_step"]), float(state["beta"])
+        self.dynamics.set_masks(state["mask"].numpy())
+        self.dynamics._mc_step, self._z_step = int(state["mc_step"]), int(state["z_step"])
+        eng.params.sync_to_dynamics()
+        return None if state["samples"] is None else state["samples"].to(self.device)
 
     # ------------------------------------------------------------------ statistics (:1473-1533)
     def calc_observables_stats(self, observables, therm_frac=10):

@@ -1,0 +1,448 @@
+"""Training step of the L2HMC sampler: loss, explicit backward pass, Adam -- SURVEY section 8(f) ranks 1, 2 and 4.
+
+Mirrors, with the same meaning (reference l2hmc/gauge_model.py):
+  :728-803    _calc_loss                      (forward: both chains, recorded on a tape)
+  :805-832    _calc_loss_and_grads            tf.gradients(loss, dynamics.variables) [+ clip_by_global_norm]
+  :925-945    exponential_decay (staircase) learning rate, tf.train.AdamOptimizer, Horovod's lr * size / averaged grads
+  :1039-1046  update_beta                     (GaugeModel.update_beta)
+  :519-556, 1104-1110  saved state            (weights, eps, Adam moments, samples, step, beta -> one torch.save file)
+
+TensorFlow derives the gradients by graph autodiff; here every adjoint is a kernel of csrc/train.cu and this module
+only walks the tape (which call, which pointers).  Layout of one training step on the device:
+
+  * the x-chain and the auxiliary z-chain are stacked into ONE batch of R = 2N rows, and chains going forward and
+    backward share every launch (row_set), so a step is 4M network calls regardless of directions;
+  * per network the tape holds, for its 2M calls, both inputs, h1, h2, S, T, Q and -- filled by the backward sweep --
+    the gradients of the head pre-activations and of both hidden layers.  Every weight gradient is then ONE
+    transposed GEMM over the whole tape (K = 2M * R) instead of 2M small ones, split along K in fixed order;
+  * parameters, gradients and Adam moments are three flat arenas; the networks' weight tensors are views into the
+    first, so the optimiser is one launch and the multi-GPU gradient exchange one all-reduce.
+There is no CPU or autograd fallback: every number comes from the sm_100a kernels behind include/l2hmc_b200.h.
+"""
+import ctypes
+import math
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _ptr(t, offset=0):
+    """Device address of element `offset` (in floats) of a CUDA fp32 tensor."""
+    return ctypes.c_void_p(t.data_ptr() + 4 * int(offset))
+
+
+class _Gemm(object):
+    """Thin caller of l2hmc_sgemm with a cached split-K workspace."""
+
+    def __init__(self, device):
+        self.device = device
+        self._ws = None
+        self.launches = 0
+
+    def __call__(self, M, N, segs, C, ldc, accumulate=False, relu_gate=None, ldg=0, col_scale=None, invert=False,
+                 row_set=None, col_scale_alt=None, invert_alt=False, ksplit=1):
+        a = _lib.GemmArgs()
+        a.M, a.N, a.nseg = int(M), int(N), len(segs)
+        for i, (A, a_rs, a_cs, B, b_rs, b_cs, K) in enumerate(segs):
+            s = a.seg[i]
+            s.A, s.a_rs, s.a_cs, s.B, s.b_rs, s.b_cs, s.K = A, int(a_rs), int(a_cs), B, int(b_rs), int(b_cs), int(K)
+        a.C, a.ldc, a.accumulate = C, int(ldc), int(bool(accumulate))
+        a.relu_gate, a.ldg = relu_gate, int(ldg)
+        a.col_scale, a.col_scale_invert = col_scale, int(bool(invert))
+        a.row_set = row_set
+        a.col_scale_alt, a.col_scale_invert_alt = col_scale_alt, int(bool(invert_alt))
+        lib = _lib.get_lib()
+        ws, need = None, 0
+        if ksplit > 1:
+            need = int(lib.l2hmc_sgemm_workspace_bytes(ctypes.byref(a), int(ksplit)))
+            if self._ws is None or self._ws.numel() * 4 < need:
+                self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=self.device)
+            ws = _ptr(self._ws)
+        _lib.check(lib.l2hmc_sgemm(ctypes.byref(a), int(ksplit), ws, need, _lib.stream_ptr()))
+        self.launches += 1 if ksplit <= 1 else 2
+
+
+class _NetTape(object):
+    """Activations and activation gradients of one network's 2M calls (rows = calls * R)."""
+
+    def __init__(self, calls, R, K, H, D, device):
+        f = lambda *s: torch.empty(*s, dtype=torch.float32, device=device)
+        self.calls, self.R, self.K, self.H, self.D = calls, R, K, H, D
+        self.in0, self.in1 = f(calls, R, K), f(calls, R, K)
+        self.h1, self.h2 = f(calls, R, H), f(calls, R, H)
+        self.S, self.T, self.Q = f(calls, R, D), f(calls, R, D), f(calls, R, D)
+        self.dA = f(calls, R, 3 * D)
+        self.dz2, self.dz1 = f(calls, R, H), f(calls, R, H)
+        self.ps, self.pq = f(calls, R, D), f(calls, R, D)
+        self.tau1 = f(calls, R, 3)          # (cos, sin, 1) per row: t_layer's input and the bias "input"
+
+
+class FlatParams(object):
+    """dynamics.variables (gauge_dynamics.py `variables`: eps, then XNet, then VNet) as ONE fp32 arena; the nets'
+    weight tensors are re-pointed to views of it.  `names` follows the golden fixtures ('eps', 'XNet.<key>', ...)."""
+
+    def __init__(self, dynamics):
+        self.dynamics = dynamics
+        dev = dynamics.device
+        entries = [("eps", dynamics.eps.reshape(1))]
+        if not dynamics.hmc:
+            for net_name, net in (("XNet", dynamics.position_fn), ("VNet", dynamics.momentum_fn)):
+                for k in net._weight_keys():
+                    entries.append((f"{net_name}.{k}", net.weights[k]))
+        self.names = [n for n, _ in entries]
+        self.shapes = [tuple(t.shape) for _, t in entries]
+        self.offsets, off = [], 0
+        for _, t in entries:
+            self.offsets.append(off)
+            off += (t.numel() + 3) // 4 * 4                      # 16-byte aligned views
+        self.size = off
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        for (n, t), o in zip(entries, self.offsets):
+            self.flat[o:o + t.numel()].copy_(t.reshape(-1))
+        self.grad = torch.zeros_like(self.flat)
+        dynamics._eps_dev = self.flat[0]
+        self._repoint()
+
+    def view(self, buf, name):
+        i = self.names.index(name)
+        n = int(np.prod(self.shapes[i])) if self.shapes[i] else 1
+        return buf[self.offsets[i]:self.offsets[i] + n].view(self.shapes[i])
+
+    def _repoint(self):
+        dyn = self.dynamics
+        if dyn.hmc:
+            return
+        for net_name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
+            for k in net._weight_keys():
+                net.weights[k] = self.view(self.flat, f"{net_name}.{k}")
+            net._struct = None
+            if hasattr(net, "_conv_structs"):
+                net._conv_structs = None
+
+    def sync_to_dynamics(self):
+        """After an optimiser step: refresh the host copy of eps (one sync, like the reference's fetch of
+        dynamics.eps every step, gauge_model.py:1166) and drop the packed tensor-core weight copies."""
+        dyn = self.dynamics
+        dyn._eps_dev = self.flat[0]
+        dyn._eps_host = float(self.flat[0].item())
+        if not dyn.hmc:
+            for net in (dyn.position_fn, dyn.momentum_fn):
+                net._struct = None
+
+    def grads_dict(self):
+        return {n: self.view(self.grad, n) for n in self.names}
+
+
+class TrainEngine(object):
+    """Forward with tape + backward sweep for one GaugeDynamics (generic nets or plain HMC)."""
+
+    def __init__(self, dynamics, metric="cos_diff", loss_scale=1.):
+        if not dynamics.hmc and dynamics.network_arch != "generic":
+            raise NotImplementedError("the backward pass is built for network_arch='generic' and hmc=True; the conv3D "
+                                      "front-end's backward kernels are not written yet")
+        self.dyn = dynamics
+        self.device = dynamics.device
+        self.metric, self.loss_scale = metric, float(loss_scale)
+        self.params = FlatParams(dynamics)
+        self.gemm = _Gemm(self.device)
+        self._tapes, self._structs = {}, {}
+        self._scratch = torch.empty(1024, dtype=torch.float32, device=self.device)
+        self.launches = 0
+
+    # ------------------------------------------------------------------ small launch helpers
+    def _call(self, fn, *args):
+        _lib.check(fn(*args, _lib.stream_ptr()))
+        self.launches += 1
+
+    def _new(self, *shape):
+        return torch.empty(*shape, dtype=torch.float32, device=self.device)
+
+    def _tape(self, name, R):
+        dyn = self.dyn
+        key = (name, R)
+        if key not in self._tapes:
+            net = dyn.position_fn if name == "XNet" else dyn.momentum_fn
+            self._tapes[key] = _NetTape(2 * dyn.num_steps, R, int(net.num_features), int(net.num_hidden),
+                                        int(net.x_dim), self.device)
+        return self._tapes[key]
+
+    def _net_struct(self, net):
+        """l2hmc_net_weights without the packed tensor-core copy (training runs the FFMA path, whose hidden
+        activations stay on the tape).  The weights are views of the flat arena, updated in place, so the
+        pointers stay valid across optimiser steps."""
+        key = id(net)
+        if key not in self._structs:
+            w, s = net.weights, _lib.NetWeights()
+            s.K, s.H, s.D = int(net.num_features), int(net.num_hidden), int(net.x_dim)
+            p = lambda k: _lib.dptr(w[k])
+            s.w_in0, s.b_in0 = p("v_layer.kernel"), p("v_layer.bias")
+            s.w_in1, s.b_in1 = p("x_layer.kernel"), p("x_layer.bias")
+            s.w_t, s.b_t = p("t_layer.kernel"), p("t_layer.bias")
+            s.w_h, s.b_h = p("h_layer.kernel"), p("h_layer.bias")
+            s.w_s, s.b_s = p("scale_layer.kernel"), p("scale_layer.bias")
+            s.w_tr, s.b_tr = p("translation_layer.kernel"), p("translation_layer.bias")
+            s.w_q, s.b_q = p("transformation_layer.kernel"), p("transformation_layer.bias")
+            s.coeff_s, s.coeff_q = p("coeff_scale"), p("coeff_transformation")
+            s.tanh_on_q, s.packed = 0, None
+            self._structs[key] = s
+        return self._structs[key]
+
+    def _net_forward(self, net, tape, j, R, tau, tau_alt, row_set):
+        lib = _lib.get_lib()
+        c = _lib.NetCall()
+        c.mode = _lib.NET_STQ
+        c.in0, c.in1 = _ptr(tape.in0[j]), _ptr(tape.in1[j])
+        c.tau_cos, c.tau_sin = float(tau[0]), float(tau[1])
+        c.tau_cos_alt, c.tau_sin_alt = float(tau_alt[0]), float(tau_alt[1])
+        c.row_set = _lib.dptr(row_set, torch.uint8)
+        c.dir = c.dir_alt = 1
+        c.N = int(R)
+        c.S, c.T, c.Q = _ptr(tape.S[j]), _ptr(tape.T[j]), _ptr(tape.Q[j])
+        c.h1_out, c.h2_out = _ptr(tape.h1[j]), _ptr(tape.h2[j])
+        ws, need = net._workspace(R)
+        c.workspace, c.workspace_bytes = _lib.dptr(ws), need
+        c.path = _lib.NET_PATH_FFMA
+        _lib.check(lib.l2hmc_net_run(self._net_struct(net), c, _lib.stream_ptr()))
+        self.launches += 3
+        # (cos, sin, 1) rows of this call: the t_layer input of each chain
+        t0 = torch.tensor([tau[0], tau[1], 1.], dtype=torch.float32, device=self.device)
+        t1 = torch.tensor([tau_alt[0], tau_alt[1], 1.], dtype=torch.float32, device=self.device)
+        tape.tau1[j] = torch.where(row_set[:, None] != 0, t1[None, :], t0[None, :])
+
+    # ------------------------------------------------------------------ forward with tape
+    def forward(self, x, beta, draws_x, z, draws_z, weights):
+        """Both chains' transitions + the loss.  draws_* = (v_f, v_b, u_dir, u_acc)."""
+        dyn, lib = self.dyn, _lib.get_lib()
+        N, D = x.shape
+        R, M = 2 * N, int(dyn.num_steps)
+        beta, eps = dyn._beta(beta), dyn._eps()
+        nets = not dyn.hmc
+        X0 = torch.cat([x, z], dim=0)
+        v_f = torch.cat([draws_x[0], draws_z[0]], dim=0)
+        v_b = torch.cat([draws_x[1], draws_z[1]], dim=0)
+        u_dir = torch.cat([draws_x[2], draws_z[2]], dim=0).contiguous()
+        row_set = (u_dir <= 0.5).to(torch.uint8)                    # 1: the chain integrates backward
+        ones = torch.ones(R, dtype=torch.float32, device=self.device)
+        v0 = self._new(R, D)                                        # v_f where u_dir > 0.5 else v_b (exact 0/1 blend)
+        self._call(lib.l2hmc_mh_select, _lib.dptr(v_f), _lib.dptr(v_f), _lib.dptr(v_b), None, None, _lib.dptr(ones),
+                   _lib.dptr(ones), _lib.dptr(u_dir), None, R, D, 0, _lib.dptr(v0), None, None, None, None)
+        tapes = {n: self._tape(n, R) for n in ("XNet", "VNet")} if nets else {}
+        sld = torch.zeros(R, dtype=torch.float32, device=self.device)
+        flag = dyn._flag
+        calls, jx, jv = [], 0, 0
+        xs, vs = X0, v0
+        rs = _lib.dptr(row_set, torch.uint8)
+        for step in range(M):
+            ib = M - step - 1
+            tau, tau_alt = dyn._ts_host[step], dyn._ts_host[ib]
+            row_f, row_b = dyn.mask[step], dyn.mask[ib]
+            for kind, inv, inv_alt in (("m", 0, 0), ("p", 0, 1), ("p", 1, 0), ("m", 0, 0)):
+                if kind == "m":
+                    rec = dict(kind="m", x=xs, v=vs, j=jv)
+                    if nets:
+                        tp = tapes["VNet"]
+                        tp.in0[jv].copy_(xs)
+                        g = tp.in1[jv]
+                    else:
+                        g = self._new(R, D)
+                    self._call(lib.l2hmc_u1_action_force, _lib.dptr(xs), beta, R, dyn.T, dyn.X, None, _ptr(g))
+                    rec["g"] = g
+                    S = Tr = Q = None
+                    if nets:
+                        self._net_forward(dyn.momentum_fn, tp, jv, R, tau, tau_alt, row_set)
+                        S, Tr, Q = _ptr(tp.S[jv]), _ptr(tp.T[jv]), _ptr(tp.Q[jv])
+                        jv += 1
+                    out = self._new(R, D)
+                    self._call(lib.l2hmc_train_update_fwd, 0, None, _lib.dptr(vs), _ptr(g), S, Tr, Q, None, 0, None, 0,
+                               rs, eps, 1, -1, R, D, _lib.dptr(out), _lib.dptr(sld), _lib.dptr(flag, torch.int32))
+                    vs = out
+                else:
+                    rec = dict(kind="p", x=xs, v=vs, j=jx, mask=row_f, inv=inv, mask_alt=row_b, inv_alt=inv_alt)
+                    S = Tr = Q = None
+                    if nets:
+                        tp = tapes["XNet"]
+                        tp.in0[jx].copy_(vs)
+                        self._call(lib.l2hmc_mask_mul_sets, _lib.dptr(xs), _lib.dptr(row_f), inv, _lib.dptr(row_b),
+                                   inv_alt, rs, R, D, _ptr(tp.in1[jx]))
+                        self._net_forward(dyn.position_fn, tp, jx, R, tau, tau_alt, row_set)
+                        S, Tr, Q = _ptr(tp.S[jx]), _ptr(tp.T[jx]), _ptr(tp.Q[jx])
+                        jx += 1
+                    out = self._new(R, D)
+                    self._call(lib.l2hmc_train_update_fwd, 1, _lib.dptr(xs), _lib.dptr(vs), None, S, Tr, Q,
+                               _lib.dptr(row_f), inv, _lib.dptr(row_b), inv_alt, rs, eps, 1, -1, R, D, _lib.dptr(out),
+                               _lib.dptr(sld), _lib.dptr(flag, torch.int32))
+                    xs = out
+                calls.append(rec)
+        h_old, h_new, p = self._new(R), self._new(R), self._new(R)
+        self._call(lib.l2hmc_u1_hamiltonian, _lib.dptr(X0), _lib.dptr(v0), beta, R, dyn.T, dyn.X, _lib.dptr(h_old))
+        self._call(lib.l2hmc_u1_hamiltonian, _lib.dptr(xs), _lib.dptr(vs), beta, R, dyn.T, dyn.X, _lib.dptr(h_new))
+        self._call(lib.l2hmc_accept_prob, _lib.dptr(h_old), _lib.dptr(h_new), _lib.dptr(sld), R, _lib.dptr(p),
+                   _lib.dptr(flag, torch.int32))
+        x_prop, px, pz = xs[:N], p[:N], p[N:]
+        x_out = self._new(N, D)
+        acc = torch.empty(N, dtype=torch.uint8, device=self.device)
+        u_acc = draws_x[3].contiguous()
+        self._call(lib.l2hmc_mh_select, _lib.dptr(x), _lib.dptr(x_prop), None, None, None, _lib.dptr(px), None, None,
+                   _lib.dptr(u_acc), N, D, 0, None, None, None, _lib.dptr(x_out), _lib.dptr(acc, torch.uint8))
+        prm = _lib.LossParams()
+        prm.metric, prm.loss_scale = _lib.METRICS[self.metric], self.loss_scale
+        prm.aux_weight, prm.std_weight, prm.charge_weight = (float(weights[k]) for k in
+                                                             ("aux_weight", "std_weight", "charge_weight"))
+        per_chain = self._new(N)
+        x_dq = torch.empty(N, dtype=torch.int32, device=self.device)
+        loss = self._new(1)
+        self._call(lib.l2hmc_u1_loss, ctypes.byref(prm), _lib.dptr(x), _ptr(x_prop), _lib.dptr(z), _lib.dptr(x_out),
+                   _ptr(px), _ptr(pz), N, dyn.T, dyn.X, _lib.dptr(per_chain), _lib.dptr(x_dq, torch.int32),
+                   _lib.dptr(loss))
+        self.launches += 1
+        return dict(N=N, D=D, R=R, beta=beta, eps=eps, x=x, z=z, xM=xs, vM=vs, h_old=h_old, h_new=h_new, sld=sld, p=p,
+                    x_prop=x_prop, px=px, pz=pz, x_out=x_out, accepted=acc, x_dq=x_dq, loss=loss, per_chain=per_chain,
+                    calls=calls, tapes=tapes, row_set=row_set, prm=prm)
+
+    # ------------------------------------------------------------------ backward sweep
+    def _net_backward(self, net, tp, j, R):
+        """dA[j] -> dz2[j], dz1[j] (activation gradients of one call; weight gradients are deferred)."""
+        w, H, D = net.weights, tp.H, tp.D
+        dA = tp.dA[j]
+        segs = [(_ptr(dA, s * D), 3 * D, 1, _lib.dptr(w[k]), 1, D, D)
+                for s, k in enumerate(("scale_layer.kernel", "translation_layer.kernel", "transformation_layer.kernel"))]
+        self.gemm(R, H, segs, _ptr(tp.dz2[j]), H, relu_gate=_ptr(tp.h2[j]), ldg=H)
+        self.gemm(R, H, [(_ptr(tp.dz2[j]), H, 1, _lib.dptr(w["h_layer.kernel"]), 1, H, H)], _ptr(tp.dz1[j]), H,
+                  relu_gate=_ptr(tp.h1[j]), ldg=H)
+
+    def backward(self, fw):
+        """d loss / d (eps, weights) into self.params.grad; returns its dict of views."""
+        dyn, lib = self.dyn, _lib.get_lib()
+        N, D, R, beta, eps = fw["N"], fw["D"], fw["R"], fw["beta"], fw["eps"]
+        nets = not dyn.hmc
+        rs = _lib.dptr(fw["row_set"], torch.uint8)
+        gx_post = torch.zeros(R, D, dtype=torch.float32, device=self.device)   # z rows: z_prop is not in the loss
+        g_p = self._new(R)
+        self._call(lib.l2hmc_u1_loss_bwd, ctypes.byref(fw["prm"]), _lib.dptr(fw["x"]), _ptr(fw["x_prop"]),
+                   _lib.dptr(fw["z"]), _ptr(fw["px"]), _ptr(fw["pz"]), N, dyn.T, dyn.X, _ptr(gx_post), _ptr(g_p),
+                   _ptr(g_p, N))
+        a = self._new(R)
+        self._call(lib.l2hmc_accept_prob_bwd, _lib.dptr(fw["h_old"]), _lib.dptr(fw["h_new"]), _lib.dptr(fw["sld"]),
+                   _lib.dptr(g_p), R, _lib.dptr(a))
+        force = self._new(R, D)
+        self._call(lib.l2hmc_u1_action_force, _lib.dptr(fw["xM"]), beta, R, dyn.T, dyn.X, None, _lib.dptr(force))
+        gx, gv = self._new(R, D), self._new(R, D)
+        self._call(lib.l2hmc_traj_bwd_init, _lib.dptr(a), _lib.dptr(force), _lib.dptr(fw["vM"]), _lib.dptr(gx_post), R,
+                   D, _lib.dptr(gx), _lib.dptr(gv))
+        deps = torch.zeros(R, dtype=torch.float32, device=self.device)
+        dg = self._new(R, D)
+        for rec in reversed(fw["calls"]):
+            j = rec["j"]
+            u = _lib.UpdateBwdArgs()
+            u.N, u.D, u.eps, u.dir, u.dir_alt, u.row_set = R, D, eps, 1, -1, rs
+            u.v, u.gv, u.gld, u.deps = _lib.dptr(rec["v"]), _lib.dptr(gv), _lib.dptr(a), _lib.dptr(deps)
+            net = tp = None
+            if nets:
+                net = dyn.momentum_fn if rec["kind"] == "m" else dyn.position_fn
+                tp = fw["tapes"]["VNet" if rec["kind"] == "m" else "XNet"]
+                u.S, u.T, u.Q = _ptr(tp.S[j]), _ptr(tp.T[j]), _ptr(tp.Q[j])
+                u.coeff_s, u.coeff_q = _lib.dptr(net.weights["coeff_scale"]), _lib.dptr(net.weights["coeff_transformation"])
+                u.dA, u.ps, u.pq = _ptr(tp.dA[j]), _ptr(tp.ps[j]), _ptr(tp.pq[j])
+            if rec["kind"] == "m":
+                u.position, u.g, u.dg = 0, _ptr(rec["g"]), _lib.dptr(dg)
+                self._call(lib.l2hmc_update_bwd, ctypes.byref(u))
+                if nets:
+                    self._net_backward(net, tp, j, R)
+                    H, K = tp.H, tp.K
+                    dz1 = _ptr(tp.dz1[j])
+                    # momentum_fn([x, grad, t]): first input x, second the force
+                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gx), D,
+                              accumulate=True)
+                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(dg), D,
+                              accumulate=True)
+                self._call(lib.l2hmc_u1_force_hvp, _lib.dptr(rec["x"]), _lib.dptr(dg), beta, R, dyn.T, dyn.X,
+                           _lib.dptr(gx))
+            else:
+                u.position, u.x, u.gx = 1, _lib.dptr(rec["x"]), _lib.dptr(gx)
+                u.mask, u.invert = _lib.dptr(rec["mask"]), int(rec["inv"])
+                u.mask_alt, u.invert_alt = _lib.dptr(rec["mask_alt"]), int(rec["inv_alt"])
+                self._call(lib.l2hmc_update_bwd, ctypes.byref(u))
+                if nets:
+                    self._net_backward(net, tp, j, R)
+                    H, K = tp.H, tp.K
+                    dz1 = _ptr(tp.dz1[j])
+                    # position_fn([v, mask * x, t]): first input v, second the masked links
+                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gv), D,
+                              accumulate=True)
+                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(gx), D,
+                              accumulate=True, col_scale=_lib.dptr(rec["mask"]), invert=rec["inv"], row_set=rs,
+                              col_scale_alt=_lib.dptr(rec["mask_alt"]), invert_alt=rec["inv_alt"])
+        # ---- parameter gradients
+        P = self.params
+        P.grad.zero_()
+        self._call(lib.l2hmc_reduce_sum, _lib.dptr(deps), R, 0, _ptr(P.view(P.grad, "eps")), _lib.dptr(self._scratch))
+        self.launches += 1
+        if nets:
+            for name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
+                self._weight_grads(name, fw["tapes"][name])
+        return P.grads_dict()
+
+    def _ksplit(self, M, N, K):
+        tiles = -(-M // 64) * -(-N // 64)
+        return int(max(1, min(64, -(-296 // tiles), K // 64)))
+
+    def _weight_grads(self, name, tp):
+        """One transposed GEMM over the whole tape per weight tensor (K = calls * R rows)."""
+        P, H, D, Kin = self.params, tp.H, tp.D, tp.K
+        Rt = tp.calls * tp.R
+        g = lambda key: _ptr(P.view(P.grad, f"{name}.{key}"))
+        ones = (_ptr(tp.tau1, 2), 0, 3)                             # A(0, r) = 1
+        dA, dz2, dz1 = _ptr(tp.dA), _ptr(tp.dz2), _ptr(tp.dz1)
+        for s, layer in enumerate(("scale_layer", "translation_layer", "transformation_layer")):
+            B = (_ptr(tp.dA, s * D), 3 * D, 1)
+            self.gemm(H, D, [(_ptr(tp.h2), 1, H) + B + (Rt,)], g(layer + ".kernel"), D, ksplit=self._ksplit(H, D, Rt))
+            self.gemm(1, D, [ones + B + (Rt,)], g(layer + ".bias"), D, ksplit=self._ksplit(1, D, Rt))
+        self.gemm(H, H, [(_ptr(tp.h1), 1, H, dz2, H, 1, Rt)], g("h_layer.kernel"), H, ksplit=self._ksplit(H, H, Rt))
+        self.gemm(1, H, [ones + (dz2, H, 1, Rt)], g("h_layer.bias"), H, ksplit=self._ksplit(1, H, Rt))
+        self.gemm(Kin, H, [(_ptr(tp.in0), 1, Kin, dz1, H, 1, Rt)], g("v_layer.kernel"), H,
+                  ksplit=self._ksplit(Kin, H, Rt))
+        self.gemm(Kin, H, [(_ptr(tp.in1), 1, Kin, dz1, H, 1, Rt)], g("x_layer.kernel"), H,
+                  ksplit=self._ksplit(Kin, H, Rt))
+        self.gemm(2, H, [(_ptr(tp.tau1), 1, 3, dz1, H, 1, Rt)], g("t_layer.kernel"), H, ksplit=self._ksplit(2, H, Rt))
+        for layer in ("v_layer", "x_layer", "t_layer"):
+            self.gemm(1, H, [ones + (dz1, H, 1, Rt)], g(layer + ".bias"), H, ksplit=self._ksplit(1, H, Rt))
+        self.gemm(1, D, [ones + (_ptr(tp.ps), D, 1, Rt)], g("coeff_scale"), D, ksplit=self._ksplit(1, D, Rt))
+        self.gemm(1, D, [ones + (_ptr(tp.pq), D, 1, Rt)], g("coeff_transformation"), D, ksplit=self._ksplit(1, D, Rt))
+
+
+def exponential_decay(lr_init, global_step, decay_steps, decay_rate, staircase=True):
+    """tf.train.exponential_decay (gauge_model.py:925-936)."""
+    e = global_step / float(decay_steps)
+    if staircase:
+        e = math.floor(e)
+    return lr_init * decay_rate ** e
+
+
+class Adam(object):
+    """tf.train.AdamOptimizer over the flat arena (gauge_model.py:937-945): beta1 0.9, beta2 0.999, epsilon 1e-8;
+    clip_norm > 0 applies tf.clip_by_global_norm (:826-827) inside the same launch."""
+
+    def __init__(self, params, beta1=0.9, beta2=0.999, epsilon=1e-8):
+        self.params = params
+        self.beta1, self.beta2, self.epsilon = beta1, beta2, epsilon
+        self.m = torch.zeros_like(params.flat)
+        self.v = torch.zeros_like(params.flat)
+        self.t = 0
+        self._sumsq = torch.zeros(1, dtype=torch.float32, device=params.flat.device)
+        self._scratch = torch.empty(1024, dtype=torch.float32, device=params.flat.device)
+
+    def step(self, lr, grad_scale=1., clip_norm=0.):
+        P, lib = self.params, _lib.get_lib()
+        self.t += 1
+        lr_t = lr * math.sqrt(1. - self.beta2 ** self.t) / (1. - self.beta1 ** self.t)
+        sumsq = None
+        if clip_norm and clip_norm > 0:
+            _lib.check(lib.l2hmc_reduce_sum(_lib.dptr(P.grad), P.size, 1, _lib.dptr(self._sumsq),
+                                            _lib.dptr(self._scratch), _lib.stream_ptr()))
+            sumsq = _lib.dptr(self._sumsq)
+        _lib.check(lib.l2hmc_adam_step(_lib.dptr(P.flat), _lib.dptr(P.grad), _lib.dptr(self.m), _lib.dptr(self.v), P.size,
+                                       float(lr_t), float(self.beta1), float(self.beta2), float(self.epsilon),
+                                       float(grad_scale), sumsq, float(clip_norm or 0.), _lib.stream_ptr()))
+        P.sync_to_dynamics()

@@ -130,3 +130,27 @@ def loss_and_grads(dyn, x, beta, draws_x, z, draws_z, metric="cos_diff", loss_sc
         for v in named.values():
             v.requires_grad_(False)
     return loss.detach(), {k: (torch.zeros_like(v) if g is None else g.detach()) for (k, v), g in zip(named.items(), grads)}
+
+
+def exponential_decay(lr_init, global_step, decay_steps, decay_rate, staircase=True):
+    """tf.train.exponential_decay as called at gauge_model.py:934-939 (TensorFlow 1.x, third party, not vendored:
+    decayed = lr * rate ** (step / decay_steps), the exponent floored when staircase)."""
+    e = global_step / float(decay_steps)
+    return lr_init * decay_rate ** (np.floor(e) if staircase else e)
+
+
+def adam_update(param, grad, m, v, t, lr, beta1=0.9, beta2=0.999, epsilon=1e-8):
+    """tf.train.AdamOptimizer.apply_gradients (gauge_model.py:940-945; TensorFlow 1.x's published update):
+    lr_t = lr sqrt(1 - b2^t) / (1 - b1^t);  m <- b1 m + (1 - b1) g;  v <- b2 v + (1 - b2) g^2;
+    param <- param - lr_t m / (sqrt(v) + epsilon).  float64 NumPy.  Returns (m, v, param)."""
+    lr_t = lr * np.sqrt(1. - beta2 ** t) / (1. - beta1 ** t)
+    m = beta1 * m + (1. - beta1) * grad
+    v = beta2 * v + (1. - beta2) * grad * grad
+    return m, v, param - lr_t * m / (np.sqrt(v) + epsilon)
+
+
+def clip_by_global_norm(grads, clip_norm):
+    """tf.clip_by_global_norm (gauge_model.py:826-827): every tensor scaled by clip_norm / max(global_norm, clip_norm)."""
+    norm = np.sqrt(sum(float((np.asarray(g, np.float64) ** 2).sum()) for g in grads))
+    scale = clip_norm / max(norm, clip_norm)
+    return [np.asarray(g) * scale for g in grads], norm
