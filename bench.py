@@ -379,7 +379,39 @@ def run_l2hmc(r, steps):
         del dyn, net, x, v
         torch.cuda.empty_cache()
     out["config5_mog"] = run_mog(c, events_ms, steps)
+    out["config2_8x8_generic_training"] = run_training(c, events_ms, steps)
     return out
+
+
+def run_training(c, events_ms, steps):
+    """BASELINE config 2: 8x8, generic S/T/Q MLPs (H = 4D = 512), batch 128, M = 5: one training step = loss over
+    the x- and z-chain, explicit backward pass (csrc/train.cu), [gradient all-reduce at N > 1], Adam."""
+    import numpy as np
+    from l2hmc_b200.gauge_model import GaugeModel
+    torch, dev, world = c["torch"], c["dev"], c["world"]
+    np.random.seed(42)
+    model = GaugeModel(dict(time_size=8, space_size=8, num_samples=128, num_steps=5, eps=0.2, network_arch="generic",
+                            rand=True, train_steps=10000), device=dev)
+    model.dynamics.seed, model.dynamics.chain_offset = 13, c["dyn"].chain_offset // 512
+    model.using_hvd = world > 1
+    if world > 1:
+        from l2hmc_b200.sharding import broadcast_weights
+        broadcast_weights([model.engine.params.flat])
+    state = [model._x(model.lattice.samples).contiguous()]
+
+    def step():
+        state[0] = model.train_step(state[0], 2.0)[1]
+    step()
+    eng = model.engine
+    l0 = eng.launches + eng.gemm.launches
+    step()
+    launches = eng.launches + eng.gemm.launches - l0 + 2          # + Adam, + observables
+    ms = events_ms(step, max(5, steps // 2), warm=1)
+    N, D, M = 128, 128, 5
+    return {"chains_per_gpu": N, "H": 512, "D": D, "lf_steps": M, "train_step_ms": ms, "launches_per_step": launches,
+            "params": int(eng.params.size), "link_updates_per_s": world * N * D * M / (ms * 1e-3),
+            "note": "both chains (x, z) forward with tape + backward + Adam; counts the x-chain's advance once; "
+                    "launch-latency bound at this size (Python-driven, ~%d launches per step)" % launches}
 
 
 def run_mog(c, events_ms, steps):
