@@ -520,6 +520,30 @@ int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, const float*
                       const float* px, const float* pz, int N, int T, int X, float* g_xprop /* [N,2TX] */,
                       float* g_px /* [N] */, float* g_pz /* [N] */, void* stream);
 
+/* Backward pass of the conv front-end of ConvNet3D for one input stream (adjoint of l2hmc_conv3d_features[_sets];
+ * network/conv_net.py:247-260 under tf.gradients, gauge_model.py:823).  The forward activations are recomputed
+ * on-chip from `in`.  g_feat [N, l2hmc_conv3d_num_features] is d loss / d features; g_in [N,2TX] is ACCUMULATED into
+ * (+= mask (*) d loss / d masked input); `partial` [l2hmc_conv3d_bwd_rows(N)][l2hmc_conv3d_bwd_cols(F)] is
+ * ACCUMULATED into: each row holds (d w1 [3,3,2,1,F] | d b1 [F] | d w2 [2,2,2,F,2F] | d b2 [2F]) of the chains
+ * n = row mod rows; the caller zeroes it before the first call of a step and sums its rows (fixed order) at the end.
+ * L2HMC_ERR_UNSUPPORTED when a chain's activations do not fit shared memory (32x32 with F = 32). */
+typedef struct {
+  const l2hmc_conv3d_weights* w;
+  const float* in;          /* [N,2TX] the stream's input (before masking) */
+  const float* mask;        /* nullable [2TX] */
+  int mask_invert;
+  const float* mask_alt;    /* rows with row_set != 0 */
+  int mask_invert_alt;
+  const uint8_t* row_set;   /* nullable [N] */
+  int N, T, X;
+  const float* g_feat;
+  float* g_in;
+  float* partial;
+} l2hmc_conv3d_bwd_args;
+int l2hmc_conv3d_bwd_rows(int N);
+int l2hmc_conv3d_bwd_cols(int F);
+int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* stream);
+
 /* out[0] = sum v[i] (square = 0) or sum v[i]^2 (square = 1), fixed two-stage tree; scratch: 1024 floats. */
 int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch, void* stream);
 

@@ -87,6 +87,13 @@ class Conv3dWeights(Structure):
     _fields_ = [("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p), ("F", c_int)]
 
 
+class Conv3dBwdArgs(Structure):
+    """l2hmc_conv3d_bwd_args (include/l2hmc_b200.h)."""
+    _fields_ = [("w", POINTER(Conv3dWeights)), ("in_", c_void_p), ("mask", c_void_p), ("mask_invert", c_int),
+                ("mask_alt", c_void_p), ("mask_invert_alt", c_int), ("row_set", c_void_p), ("N", c_int), ("T", c_int),
+                ("X", c_int), ("g_feat", c_void_p), ("g_in", c_void_p), ("partial", c_void_p)]
+
+
 class Gmm(Structure):
     """l2hmc_gmm (include/l2hmc_b200.h)."""
     _fields_ = [("k", c_int), ("m", c_int), ("mus", c_void_p), ("i_sigmas", c_void_p), ("log_consts", c_void_p)]
@@ -186,6 +193,9 @@ SIGNATURES = {
     "l2hmc_traj_bwd_init": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_u1_loss_bwd": [POINTER(LossParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                           c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_conv3d_bwd_rows": [c_int],
+    "l2hmc_conv3d_bwd_cols": [c_int],
+    "l2hmc_conv3d_backward": [POINTER(Conv3dBwdArgs), c_void_p],
     "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
                         c_float, c_void_p, c_float, c_void_p],

@@ -1,0 +1,273 @@
+// Backward pass of the ConvNet3D front-end (one input stream):
+//   (N,T,X,2,1) -> Conv3D(F,(3,3,2),same,relu) -> MaxPool3D(2,2,same) -> Conv3D(2F,(2,2,2),same,relu)
+//               -> MaxPool3D(2,2,same) -> flatten                       (reference l2hmc/network/conv_net.py:247-260)
+// The reference gets these gradients from tf.gradients (gauge_model.py:823); here the adjoint of each layer is
+// written out.  One chain per CTA pass, everything on-chip: the forward activations are RECOMPUTED from the chain's
+// 2TX inputs (0.4 MFMA) instead of being kept on the tape (36 KB per chain and call at 16x16), then
+//   pool-2 routing -> d conv-2 (weights, bias, input) -> pool-1 routing -> d conv-1 (weights, bias, input).
+// Max-pool routes the gradient to the first maximum of its window; a maximum of 0 (all-ReLU-dead window) gets no
+// gradient because relu'(0) = 0, so ties never matter.  Weight gradients accumulate into a per-CTA row of
+// `partial` (chain n -> row n % rows, calls in stream order) and are summed over rows in fixed order by the caller:
+// deterministic, no atomics.  TF 'same' semantics as in conv3d.cu (zero padding, odd cell at the end, clipped
+// pooling windows; the kd = 1 taps of conv-2 only ever see padding, so their gradient is exactly zero).
+#include "common.cuh"
+
+namespace l2hmc {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxRows = 296;
+
+struct ConvBwdParams {
+  const float *w1, *b1, *w2, *b2;
+  int F;
+  const float* in;
+  const float* mask;
+  int invert;
+  const float* mask_alt;
+  int invert_alt;
+  const uint8_t* row_set;
+  int N, T, X;
+  const float* g_feat;
+  float* g_in;
+  float* partial;
+  int psize;
+};
+
+__global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParams p) {
+  extern __shared__ __align__(16) float sm[];
+  const int T = p.T, X = p.X, F = p.F, C2 = 2 * p.F;
+  const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, T4 = (T2 + 1) / 2, X4 = (X2 + 1) / 2;
+  const int D = 2 * T * X, K = T4 * X4 * C2;
+  float* in_s = sm;                       // [T][X][2] (masked input)
+  float* mk_s = in_s + D;                 // [T][X][2] the mask actually applied (1 if none)
+  float* c1 = mk_s + D;                   // [T][X][2][F]      conv-1 output, later its gradient
+  float* p1 = c1 + D * F;                 // [T2][X2][F]       pool-1 output
+  float* c2 = p1 + T2 * X2 * F;           // [T2][X2][2F]      conv-2 output, later its gradient
+  float* gp1 = c2 + T2 * X2 * C2;         // [T2][X2][F]       gradient of the pool-1 output
+  float* w1s = gp1 + T2 * X2 * F;         // [3][3][2][F]
+  float* w2s = w1s + 18 * F;              // [2][2][F][2F]     (kd = 0 taps)
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 18 * F; i += kThreads) w1s[i] = p.w1[i];
+  for (int i = tid; i < 4 * F * C2; i += kThreads) {
+    const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F);       // kk = kt*2 + kx
+    w2s[i] = p.w2[((kk * 2 + 0) * F + ci) * C2 + co];
+  }
+  float* part = p.partial + static_cast<size_t>(blockIdx.x) * p.psize;
+  const int off_b1 = 18 * F, off_w2 = 19 * F, off_b2 = 19 * F + 8 * F * C2;
+
+  for (int n = blockIdx.x; n < p.N; n += gridDim.x) {
+    const bool alt = p.row_set != nullptr && p.row_set[n] != 0;
+    const float* mask = alt ? p.mask_alt : p.mask;
+    const int invert = alt ? p.invert_alt : p.invert;
+    const float* src = p.in + static_cast<size_t>(n) * D;
+    for (int i = tid; i < D; i += kThreads) {
+      const float m = mask == nullptr ? 1.f : (invert ? 1.f - mask[i] : mask[i]);
+      mk_s[i] = m;
+      in_s[i] = m * src[i];
+    }
+    __syncthreads();
+    // ---- forward, recomputed
+    for (int i = tid; i < D * F; i += kThreads) {
+      const int f = i % F, d = (i / F) & 1, x = (i / (2 * F)) % X, t = i / (2 * F * X);
+      float acc = p.b1[f];
+      for (int kt = 0; kt < 3; ++kt) {
+        const int tt = t + kt - 1;
+        if (tt < 0 || tt >= T) continue;
+        for (int kx = 0; kx < 3; ++kx) {
+          const int xx = x + kx - 1;
+          if (xx < 0 || xx >= X) continue;
+          for (int kd = 0; kd + d < 2; ++kd)
+            acc = fmaf(in_s[(tt * X + xx) * 2 + d + kd], w1s[((kt * 3 + kx) * 2 + kd) * F + f], acc);
+        }
+      }
+      c1[i] = fmaxf(acc, 0.f);
+    }
+    __syncthreads();
+    for (int i = tid; i < T2 * X2 * F; i += kThreads) {
+      const int f = i % F, x2 = (i / F) % X2, t2 = i / (F * X2);
+      float best = -INFINITY;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          const int t = 2 * t2 + a, x = 2 * x2 + b;
+          if (t >= T || x >= X) continue;
+          for (int d = 0; d < 2; ++d) best = fmaxf(best, c1[((t * X + x) * 2 + d) * F + f]);
+        }
+      p1[i] = best;
+    }
+    __syncthreads();
+    for (int i = tid; i < T2 * X2 * C2; i += kThreads) {
+      const int co = i % C2, x = (i / C2) % X2, t = i / (C2 * X2);
+      float acc = p.b2[co];
+      for (int kt = 0; kt < 2; ++kt)
+        for (int kx = 0; kx < 2; ++kx) {
+          const int tt = t + kt, xx = x + kx;
+          if (tt >= T2 || xx >= X2) continue;
+          const float* a = p1 + (tt * X2 + xx) * F;
+          const float* w = w2s + ((kt * 2 + kx) * F) * C2 + co;
+          for (int ci = 0; ci < F; ++ci) acc = fmaf(a[ci], w[ci * C2], acc);
+        }
+      c2[i] = fmaxf(acc, 0.f);
+    }
+    __syncthreads();
+    // ---- pool-2 routing: c2 <- gradient of the conv-2 pre-activation
+    const float* gf = p.g_feat + static_cast<size_t>(n) * K;
+    for (int i = tid; i < T4 * X4 * C2; i += kThreads) {
+      const int co = i % C2, x4 = (i / C2) % X4, t4 = i / (C2 * X4);
+      float best = -INFINITY;
+      int arg = -1;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          const int t = 2 * t4 + a, x = 2 * x4 + b;
+          if (t >= T2 || x >= X2) continue;
+          const int at = (t * X2 + x) * C2 + co;
+          if (c2[at] > best) best = c2[at], arg = at;
+        }
+      const float g = best > 0.f ? gf[i] : 0.f;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          const int t = 2 * t4 + a, x = 2 * x4 + b;
+          if (t >= T2 || x >= X2) continue;
+          const int at = (t * X2 + x) * C2 + co;
+          c2[at] = at == arg ? g : 0.f;
+        }
+    }
+    __syncthreads();
+    // ---- conv-2: weight / bias gradients (kd = 0 taps), input gradient
+    for (int i = tid; i < 4 * F * C2; i += kThreads) {
+      const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F), kt = kk >> 1, kx = kk & 1;
+      float s = 0.f;
+      for (int t = 0; t + kt < T2; ++t)
+        for (int x = 0; x + kx < X2; ++x)
+          s = fmaf(p1[((t + kt) * X2 + x + kx) * F + ci], c2[(t * X2 + x) * C2 + co], s);
+      part[off_w2 + ((kk * 2 + 0) * F + ci) * C2 + co] += s;
+    }
+    for (int co = tid; co < C2; co += kThreads) {
+      float s = 0.f;
+      for (int j = 0; j < T2 * X2; ++j) s += c2[j * C2 + co];
+      part[off_b2 + co] += s;
+    }
+    for (int i = tid; i < T2 * X2 * F; i += kThreads) {
+      const int ci = i % F, x = (i / F) % X2, t = i / (F * X2);
+      float s = 0.f;
+      for (int kt = 0; kt < 2 && kt <= t; ++kt)
+        for (int kx = 0; kx < 2 && kx <= x; ++kx) {
+          const float* g = c2 + ((t - kt) * X2 + x - kx) * C2;
+          const float* w = w2s + ((kt * 2 + kx) * F + ci) * C2;
+          for (int co = 0; co < C2; ++co) s = fmaf(w[co], g[co], s);
+        }
+      gp1[i] = s;
+    }
+    __syncthreads();
+    // ---- pool-1 routing: c1 <- gradient of the conv-1 pre-activation
+    for (int i = tid; i < T2 * X2 * F; i += kThreads) {
+      const int f = i % F, x2 = (i / F) % X2, t2 = i / (F * X2);
+      float best = -INFINITY;
+      int arg = -1;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          const int t = 2 * t2 + a, x = 2 * x2 + b;
+          if (t >= T || x >= X) continue;
+          for (int d = 0; d < 2; ++d) {
+            const int at = ((t * X + x) * 2 + d) * F + f;
+            if (c1[at] > best) best = c1[at], arg = at;
+          }
+        }
+      const float g = best > 0.f ? gp1[i] : 0.f;
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b) {
+          const int t = 2 * t2 + a, x = 2 * x2 + b;
+          if (t >= T || x >= X) continue;
+          for (int d = 0; d < 2; ++d) {
+            const int at = ((t * X + x) * 2 + d) * F + f;
+            c1[at] = at == arg ? g : 0.f;
+          }
+        }
+    }
+    __syncthreads();
+    // ---- conv-1: weight / bias gradients, input gradient
+    for (int i = tid; i < 18 * F; i += kThreads) {
+      const int f = i % F, kd = (i / F) & 1, kx = (i / (2 * F)) % 3, kt = i / (6 * F);
+      float s = 0.f;
+      for (int t = 0; t < T; ++t) {
+        const int tt = t + kt - 1;
+        if (tt < 0 || tt >= T) continue;
+        for (int x = 0; x < X; ++x) {
+          const int xx = x + kx - 1;
+          if (xx < 0 || xx >= X) continue;
+          for (int d = 0; d + kd < 2; ++d)
+            s = fmaf(in_s[(tt * X + xx) * 2 + d + kd], c1[((t * X + x) * 2 + d) * F + f], s);
+        }
+      }
+      part[i] += s;
+    }
+    for (int f = tid; f < F; f += kThreads) {
+      float s = 0.f;
+      for (int j = 0; j < D; ++j) s += c1[j * F + f];
+      part[off_b1 + f] += s;
+    }
+    float* dst = p.g_in + static_cast<size_t>(n) * D;
+    for (int i = tid; i < D; i += kThreads) {
+      const int dd = i & 1, xx = (i >> 1) % X, tt = i / (2 * X);     // input position
+      float s = 0.f;
+      for (int kt = 0; kt < 3; ++kt) {
+        const int t = tt - kt + 1;
+        if (t < 0 || t >= T) continue;
+        for (int kx = 0; kx < 3; ++kx) {
+          const int x = xx - kx + 1;
+          if (x < 0 || x >= X) continue;
+          for (int kd = 0; kd <= dd; ++kd) {
+            const float* g = c1 + ((t * X + x) * 2 + dd - kd) * F;
+            const float* w = w1s + ((kt * 3 + kx) * 2 + kd) * F;
+            for (int f = 0; f < F; ++f) s = fmaf(w[f], g[f], s);
+          }
+        }
+      }
+      dst[i] += mk_s[i] * s;
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+using namespace l2hmc;
+
+extern "C" int l2hmc_conv3d_bwd_rows(int N) { return N < kMaxRows ? (N > 0 ? N : 1) : kMaxRows; }
+
+extern "C" int l2hmc_conv3d_bwd_cols(int F) { return 18 * F + F + 8 * F * 2 * F + 2 * F; }
+
+extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* stream) {
+  L2HMC_REQUIRE(a && a->w, "l2hmc_conv3d_backward: null arguments");
+  if (a->N == 0) return L2HMC_OK;
+  const int F = a->w->F, T = a->T, X = a->X;
+  L2HMC_REQUIRE(a->N > 0 && T > 0 && X > 0 && F > 0, "l2hmc_conv3d_backward: bad sizes N=%d T=%d X=%d F=%d", a->N, T, X, F);
+  L2HMC_REQUIRE(a->w->w1 && a->w->b1 && a->w->w2 && a->w->b2 && a->in && a->g_feat && a->g_in && a->partial,
+                "l2hmc_conv3d_backward: null pointer");
+  L2HMC_REQUIRE(!a->row_set || (!a->mask == !a->mask_alt), "l2hmc_conv3d_backward: mask and mask_alt go together");
+  const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, D = 2 * T * X;
+  const size_t floats = 2u * D + static_cast<size_t>(D) * F + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
+                        18u * F + 8u * F * F;
+  const size_t smem = floats * sizeof(float);
+  int dev = 0, max_smem = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (smem > static_cast<size_t>(max_smem)) {
+    set_error("l2hmc_conv3d_backward: %dx%d with F=%d needs %zu B of shared memory per chain (limit %d B)", T, X, F, smem,
+              max_smem);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(conv3d_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(conv3d_bwd_kernel): %s", cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+  }
+  ConvBwdParams p{a->w->w1, a->w->b1, a->w->w2, a->w->b2, F, a->in, a->mask, a->mask_invert, a->mask_alt,
+                  a->mask_invert_alt, a->row_set, a->N, T, X, a->g_feat, a->g_in, a->partial, l2hmc_conv3d_bwd_cols(F)};
+  conv3d_bwd_kernel<<<l2hmc_conv3d_bwd_rows(a->N), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_launch("conv3d_bwd_kernel");
+}

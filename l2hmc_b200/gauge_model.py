@@ -12,7 +12,7 @@ Mirrors, with the same names and argument meaning (reference l2hmc/gauge_model.p
   :925-945    learning-rate schedule + Adam (train_op)   :1155-1190  one iteration of the training loop (train_step)
   :519-556    saved state (save_state / restore_state)
 All arithmetic runs in csrc/loss.cu, csrc/stats.cu, csrc/train.cu and the path's own kernels; there is no CPU fallback.
-The backward pass covers network_arch='generic' and hmc=True; the conv3D front-end's backward is not built yet.
+The backward pass covers network_arch='generic', 'conv3D' (csrc/conv3d_bwd.cu) and hmc=True.
 """
 import collections
 import ctypes

@@ -139,10 +139,11 @@ class TrainEngine(object):
     """Forward with tape + backward sweep for one GaugeDynamics (generic nets or plain HMC)."""
 
     def __init__(self, dynamics, metric="cos_diff", loss_scale=1.):
-        if not dynamics.hmc and dynamics.network_arch != "generic":
-            raise NotImplementedError("the backward pass is built for network_arch='generic' and hmc=True; the conv3D "
-                                      "front-end's backward kernels are not written yet")
+        if not dynamics.hmc and dynamics.network_arch not in ("generic", "conv3D"):
+            raise NotImplementedError("the backward pass is built for network_arch in ('generic', 'conv3D') and hmc=True")
         self.dyn = dynamics
+        self.conv = (not dynamics.hmc) and dynamics.network_arch == "conv3D"
+        self._conv_partial = {}
         self.device = dynamics.device
         self.metric, self.loss_scale = metric, float(loss_scale)
         self.params = FlatParams(dynamics)
@@ -211,6 +212,46 @@ class TrainEngine(object):
         t1 = torch.tensor([tau_alt[0], tau_alt[1], 1.], dtype=torch.float32, device=self.device)
         tape.tau1[j] = torch.where(row_set[:, None] != 0, t1[None, :], t0[None, :])
 
+    def _conv_features(self, net, which, raw, feat, R, masks=None):
+        """Conv front-end of one input stream into the tape slot `feat` (csrc/conv3d.cu)."""
+        lib, dyn = _lib.get_lib(), self.dyn
+        if masks is None:
+            self._call(lib.l2hmc_conv3d_features, net._conv(which), _lib.dptr(raw), None, 0, R, dyn.T, dyn.X, _ptr(feat))
+        else:
+            m, inv, ma, inva, rs = masks
+            self._call(lib.l2hmc_conv3d_features_sets, net._conv(which), _lib.dptr(raw), _lib.dptr(m), int(inv),
+                       _lib.dptr(ma), int(inva), rs, R, dyn.T, dyn.X, _ptr(feat))
+
+    def _conv_backward(self, name, net, which, raw, g_feat, g_in, R, masks=None):
+        """Adjoint of _conv_features: g_in += mask * d loss / d input; weight gradients into the stream's partial rows."""
+        lib, dyn = _lib.get_lib(), self.dyn
+        key = (name, which)
+        if key not in self._conv_partial:
+            rows, cols = int(lib.l2hmc_conv3d_bwd_rows(R)), int(lib.l2hmc_conv3d_bwd_cols(int(net.num_filters)))
+            self._conv_partial[key] = torch.zeros(rows, cols, dtype=torch.float32, device=self.device)
+        a = _lib.Conv3dBwdArgs()
+        a.w = ctypes.pointer(net._conv(which))
+        a.in_, a.N, a.T, a.X = _lib.dptr(raw), R, dyn.T, dyn.X
+        if masks is not None:
+            m, inv, ma, inva, rs = masks
+            a.mask, a.mask_invert, a.mask_alt, a.mask_invert_alt, a.row_set = _lib.dptr(m), int(inv), _lib.dptr(ma), \
+                int(inva), rs
+        a.g_feat, a.g_in, a.partial = _lib.dptr(g_feat), _lib.dptr(g_in), _lib.dptr(self._conv_partial[key])
+        self._call(lib.l2hmc_conv3d_backward, ctypes.byref(a))
+
+    def _conv_weight_grads(self, name, net, tp):
+        """Sum the per-CTA rows of the conv partials (fixed order) into the flat gradient."""
+        P, F = self.params, int(net.num_filters)
+        ones = (_ptr(tp.tau1, 2), 0, 3)
+        for which in ("x", "v"):
+            part = self._conv_partial[(name, which)]
+            rows, cols = part.shape
+            off = 0
+            for key, n in ((f"conv_{which}1.kernel", 18 * F), (f"conv_{which}1.bias", F),
+                           (f"conv_{which}2.kernel", 16 * F * F), (f"conv_{which}2.bias", 2 * F)):
+                self.gemm(1, n, [ones + (_ptr(part, off), cols, 1, rows)], _ptr(P.view(P.grad, f"{name}.{key}")), n)
+                off += n
+
     # ------------------------------------------------------------------ forward with tape
     def forward(self, x, beta, draws_x, z, draws_z, weights):
         """Both chains' transitions + the loss.  draws_* = (v_f, v_b, u_dir, u_acc)."""
@@ -241,7 +282,7 @@ class TrainEngine(object):
             for kind, inv, inv_alt in (("m", 0, 0), ("p", 0, 1), ("p", 1, 0), ("m", 0, 0)):
                 if kind == "m":
                     rec = dict(kind="m", x=xs, v=vs, j=jv)
-                    if nets:
+                    if nets and not self.conv:
                         tp = tapes["VNet"]
                         tp.in0[jv].copy_(xs)
                         g = tp.in1[jv]
@@ -251,6 +292,10 @@ class TrainEngine(object):
                     rec["g"] = g
                     S = Tr = Q = None
                     if nets:
+                        tp = tapes["VNet"]
+                        if self.conv:        # momentum_fn([x, grad, t]): x through conv_v*, the force through conv_x*
+                            self._conv_features(dyn.momentum_fn, "v", xs, tp.in0[jv], R)
+                            self._conv_features(dyn.momentum_fn, "x", g, tp.in1[jv], R)
                         self._net_forward(dyn.momentum_fn, tp, jv, R, tau, tau_alt, row_set)
                         S, Tr, Q = _ptr(tp.S[jv]), _ptr(tp.T[jv]), _ptr(tp.Q[jv])
                         jv += 1
@@ -261,7 +306,11 @@ class TrainEngine(object):
                 else:
                     rec = dict(kind="p", x=xs, v=vs, j=jx, mask=row_f, inv=inv, mask_alt=row_b, inv_alt=inv_alt)
                     S = Tr = Q = None
-                    if nets:
+                    if nets and self.conv:       # position_fn([v, mask * x, t]): v through conv_v*, m*x through conv_x*
+                        tp = tapes["XNet"]
+                        self._conv_features(dyn.position_fn, "v", vs, tp.in0[jx], R)
+                        self._conv_features(dyn.position_fn, "x", xs, tp.in1[jx], R, (row_f, inv, row_b, inv_alt, rs))
+                    elif nets:
                         tp = tapes["XNet"]
                         tp.in0[jx].copy_(vs)
                         self._call(lib.l2hmc_mask_mul_sets, _lib.dptr(xs), _lib.dptr(row_f), inv, _lib.dptr(row_b),
@@ -312,9 +361,20 @@ class TrainEngine(object):
         self.gemm(R, H, [(_ptr(tp.dz2[j]), H, 1, _lib.dptr(w["h_layer.kernel"]), 1, H, H)], _ptr(tp.dz1[j]), H,
                   relu_gate=_ptr(tp.h1[j]), ldg=H)
 
+    def _feat_grads(self, net, tp, dz1, R):
+        """d loss / d conv features of both streams: dz1 . W_in0^T and dz1 . W_in1^T."""
+        H, K = tp.H, tp.K
+        if getattr(self, "_fg", None) is None or self._fg[0].shape != (R, K):
+            self._fg = (self._new(R, K), self._new(R, K))
+        for buf, layer in zip(self._fg, ("v_layer.kernel", "x_layer.kernel")):
+            self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights[layer]), 1, H, H)], _lib.dptr(buf), K)
+        return self._fg
+
     def backward(self, fw):
         """d loss / d (eps, weights) into self.params.grad; returns its dict of views."""
         dyn, lib = self.dyn, _lib.get_lib()
+        for part in self._conv_partial.values():
+            part.zero_()
         N, D, R, beta, eps = fw["N"], fw["D"], fw["R"], fw["beta"], fw["eps"]
         nets = not dyn.hmc
         rs = _lib.dptr(fw["row_set"], torch.uint8)
@@ -353,10 +413,15 @@ class TrainEngine(object):
                     H, K = tp.H, tp.K
                     dz1 = _ptr(tp.dz1[j])
                     # momentum_fn([x, grad, t]): first input x, second the force
-                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gx), D,
-                              accumulate=True)
-                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(dg), D,
-                              accumulate=True)
+                    if self.conv:
+                        f0, f1 = self._feat_grads(net, tp, dz1, R)
+                        self._conv_backward("VNet", net, "v", rec["x"], f0, gx, R)
+                        self._conv_backward("VNet", net, "x", rec["g"], f1, dg, R)
+                    else:
+                        self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gx),
+                                  D, accumulate=True)
+                        self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(dg),
+                                  D, accumulate=True)
                 self._call(lib.l2hmc_u1_force_hvp, _lib.dptr(rec["x"]), _lib.dptr(dg), beta, R, dyn.T, dyn.X,
                            _lib.dptr(gx))
             else:
@@ -369,11 +434,17 @@ class TrainEngine(object):
                     H, K = tp.H, tp.K
                     dz1 = _ptr(tp.dz1[j])
                     # position_fn([v, mask * x, t]): first input v, second the masked links
-                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gv), D,
-                              accumulate=True)
-                    self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(gx), D,
-                              accumulate=True, col_scale=_lib.dptr(rec["mask"]), invert=rec["inv"], row_set=rs,
-                              col_scale_alt=_lib.dptr(rec["mask_alt"]), invert_alt=rec["inv_alt"])
+                    if self.conv:
+                        f0, f1 = self._feat_grads(net, tp, dz1, R)
+                        self._conv_backward("XNet", net, "v", rec["v"], f0, gv, R)
+                        self._conv_backward("XNet", net, "x", rec["x"], f1, gx, R,
+                                            (rec["mask"], rec["inv"], rec["mask_alt"], rec["inv_alt"], rs))
+                    else:
+                        self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gv),
+                                  D, accumulate=True)
+                        self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["x_layer.kernel"]), 1, H, H)], _lib.dptr(gx),
+                                  D, accumulate=True, col_scale=_lib.dptr(rec["mask"]), invert=rec["inv"], row_set=rs,
+                                  col_scale_alt=_lib.dptr(rec["mask_alt"]), invert_alt=rec["inv_alt"])
         # ---- parameter gradients
         P = self.params
         P.grad.zero_()
@@ -382,6 +453,8 @@ class TrainEngine(object):
         if nets:
             for name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
                 self._weight_grads(name, fw["tapes"][name])
+                if self.conv:
+                    self._conv_weight_grads(name, net, fw["tapes"][name])
         return P.grads_dict()
 
     def _ksplit(self, M, N, K):

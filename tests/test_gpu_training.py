@@ -276,9 +276,6 @@ def test_gradients_against_reference_goldens(golden):
     g = golden("train_cases")
     checked = 0
     for tag in _tags(g, "loss"):
-        arch = tag.split(".")[1]
-        if arch == "conv3D":
-            continue                      # the conv front-end's backward kernels are not built yet
         model, (T, X, N, M, hmc, metric) = build_model(g, tag)
         loss, grads, x_out, px, x_dq = model._calc_loss_and_grads(
             g[tag + ".x"], float(g[tag + ".beta"]),
@@ -294,7 +291,7 @@ def test_gradients_against_reference_goldens(golden):
             # the loss divides by x_std ~ O(1e-3 .. 1): its gradient inherits the 5e-3 the loss value is held to
             close_scaled(gr, want, 1e-2, f"{tag} d loss / d {name}")
             checked += 1
-    assert checked >= 3 + 2 * 32
+    assert checked >= 3 + 2 * 33 + 49
 
 
 @pytest.mark.parametrize("T,X,N,M,metric", [(8, 8, 16, 5, "cos_diff"), (4, 6, 9, 3, "l2")])
@@ -430,3 +427,52 @@ def test_train_loop_and_saved_state(tmp_path):
     # inference after training uses the updated weights (packed tensor-core copies are rebuilt)
     xp, _, p, _ = model.dynamics.apply_transition(samples, 3.0)
     assert torch.isfinite(p).all()
+
+
+# --------------------------------------------------------------------------------------------- conv front-end adjoint
+@pytest.mark.parametrize("T,X,F,N", [(8, 8, 8, 21), (6, 10, 4, 9), (16, 16, 16, 300), (4, 4, 3, 400)])
+def test_conv3d_backward_against_autograd(T, X, F, N):
+    """l2hmc_conv3d_backward vs torch autograd through the oracle's Conv3D/MaxPool3D stack (conv_net.py:247-260),
+    with per-chain mask sets and more chains than partial rows (accumulation across CTA passes)."""
+    from l2hmc_b200 import _lib
+    rng = np.random.default_rng(T * 100 + X + F)
+    D = 2 * T * X
+    w = {"k1": rng.uniform(-0.4, 0.4, (3, 3, 2, 1, F)), "b1": rng.uniform(-0.1, 0.1, F),
+         "k2": rng.uniform(-0.3, 0.3, (2, 2, 2, F, 2 * F)), "b2": rng.uniform(-0.1, 0.1, 2 * F)}
+    leaves = {k: torch.tensor(v, dtype=torch.float64, requires_grad=True) for k, v in w.items()}
+    x = torch.tensor(rng.standard_normal((N, D)), dtype=torch.float64, requires_grad=True)
+    m0 = (rng.uniform(size=D) > 0.5).astype(np.float64)
+    m1 = (rng.uniform(size=D) > 0.5).astype(np.float64)
+    rows = rng.uniform(size=N) > 0.5
+    mrow = torch.tensor(np.where(rows[:, None], 1 - m1[None, :], m0[None, :]))
+    h = (mrow * x).reshape(N, T, X, 2, 1)
+    h = orc._maxpool3d_same(orc._conv3d_same_relu(h, leaves["k1"], leaves["b1"]))
+    h = orc._maxpool3d_same(orc._conv3d_same_relu(h, leaves["k2"], leaves["b2"]))
+    feat = h.reshape(N, -1)
+    K = feat.shape[1]
+    gf = torch.tensor(rng.standard_normal((N, K)), dtype=torch.float64)
+    gx_ref, g1, gb1, g2, gb2 = torch.autograd.grad((feat * gf).sum(), [x, leaves["k1"], leaves["b1"], leaves["k2"], leaves["b2"]])
+    lib = _lib.get_lib()
+    assert K == lib.l2hmc_conv3d_num_features(T, X, F)
+    dev = {k: cu(v) for k, v in w.items()}
+    cw = _lib.Conv3dWeights()
+    cw.w1, cw.b1, cw.w2, cw.b2, cw.F = _lib.dptr(dev["k1"]), _lib.dptr(dev["b1"]), _lib.dptr(dev["k2"]), _lib.dptr(dev["b2"]), F
+    prows, pcols = lib.l2hmc_conv3d_bwd_rows(N), lib.l2hmc_conv3d_bwd_cols(F)
+    assert pcols == 18 * F + F + 16 * F * F + 2 * F
+    part = torch.zeros(prows, pcols, device="cuda")
+    g_in0 = rng.standard_normal((N, D)).astype(np.float32)
+    tx, tg, tgin, tm0, tm1, trs = cu(x.detach().numpy()), cu(gf.numpy()), cu(g_in0), cu(m0), cu(m1), cu(rows.astype(np.uint8), torch.uint8)
+    a = _lib.Conv3dBwdArgs()
+    a.w, a.in_, a.N, a.T, a.X = ctypes.pointer(cw), _lib.dptr(tx), N, T, X
+    a.mask, a.mask_invert, a.mask_alt, a.mask_invert_alt = _lib.dptr(tm0), 0, _lib.dptr(tm1), 1
+    a.row_set = _lib.dptr(trs, torch.uint8)
+    a.g_feat, a.g_in, a.partial = _lib.dptr(tg), _lib.dptr(tgin), _lib.dptr(part)
+    _lib.check(lib.l2hmc_conv3d_backward(ctypes.byref(a), None))
+    torch.cuda.synchronize()
+    tot = part.double().sum(dim=0).cpu()
+    close_scaled(tgin, torch.tensor(g_in0, dtype=torch.float64) + gx_ref, 2e-5, "conv d/d input")
+    off = 0
+    for nm, ref in (("w1", g1), ("b1", gb1), ("w2", g2), ("b2", gb2)):
+        n = ref.numel()
+        close_scaled(tot[off:off + n], ref.reshape(-1), 5e-5, f"conv d/d {nm}")
+        off += n
