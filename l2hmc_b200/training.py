@@ -315,6 +315,7 @@ class TrainEngine(object):
                         tp.in0[jx].copy_(vs)
                         self._call(lib.l2hmc_mask_mul_sets, _lib.dptr(xs), _lib.dptr(row_f), inv, _lib.dptr(row_b),
                                    inv_alt, rs, R, D, _ptr(tp.in1[jx]))
+                    if nets:
                         self._net_forward(dyn.position_fn, tp, jx, R, tau, tau_alt, row_set)
                         S, Tr, Q = _ptr(tp.S[jx]), _ptr(tp.T[jx]), _ptr(tp.Q[jx])
                         jx += 1
