@@ -34,24 +34,28 @@ struct ConvBwdParams {
   int psize;
 };
 
+// FT > 0: the filter count is a compile-time constant (index arithmetic folds, tap / channel loops unroll);
+// FT = 0: any F.
+template <int FT>
 __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParams p) {
   extern __shared__ __align__(16) float sm[];
-  const int T = p.T, X = p.X, F = p.F, C2 = 2 * p.F;
+  const int T = p.T, X = p.X, F = FT > 0 ? FT : p.F, C2 = 2 * F;
+  const int FP = F + 1, CP = C2 + 1;   // padded row strides: lanes that walk rows hit distinct banks
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, T4 = (T2 + 1) / 2, X4 = (X2 + 1) / 2;
   const int D = 2 * T * X, K = T4 * X4 * C2;
   float* in_s = sm;                       // [T][X][2] (masked input)
   float* mk_s = in_s + D;                 // [T][X][2] the mask actually applied (1 if none)
-  float* c1 = mk_s + D;                   // [T][X][2][F]      conv-1 output, later its gradient
-  float* p1 = c1 + D * F;                 // [T2][X2][F]       pool-1 output
+  float* c1 = mk_s + D;                   // [T][X][2][F+1]    conv-1 output, later its gradient
+  float* p1 = c1 + D * FP;                // [T2][X2][F]       pool-1 output
   float* c2 = p1 + T2 * X2 * F;           // [T2][X2][2F]      conv-2 output, later its gradient
   float* gp1 = c2 + T2 * X2 * C2;         // [T2][X2][F]       gradient of the pool-1 output
   float* w1s = gp1 + T2 * X2 * F;         // [3][3][2][F]
-  float* w2s = w1s + 18 * F;              // [2][2][F][2F]     (kd = 0 taps)
+  float* w2s = w1s + 18 * F;              // [2][2][F][2F+1]   (kd = 0 taps)
   const int tid = threadIdx.x;
   for (int i = tid; i < 18 * F; i += kThreads) w1s[i] = p.w1[i];
   for (int i = tid; i < 4 * F * C2; i += kThreads) {
     const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F);       // kk = kt*2 + kx
-    w2s[i] = p.w2[((kk * 2 + 0) * F + ci) * C2 + co];
+    w2s[(kk * F + ci) * CP + co] = p.w2[((kk * 2 + 0) * F + ci) * C2 + co];
   }
   float* part = p.partial + static_cast<size_t>(blockIdx.x) * p.psize;
   const int off_b1 = 18 * F, off_w2 = 19 * F, off_b2 = 19 * F + 8 * F * C2;
@@ -69,19 +73,23 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     __syncthreads();
     // ---- forward, recomputed
     for (int i = tid; i < D * F; i += kThreads) {
-      const int f = i % F, d = (i / F) & 1, x = (i / (2 * F)) % X, t = i / (2 * F * X);
+      const int f = i % F, pos = i / F, d = pos & 1, site = pos >> 1, t = site / X, x = site - t * X;
       float acc = p.b1[f];
+#pragma unroll
       for (int kt = 0; kt < 3; ++kt) {
         const int tt = t + kt - 1;
         if (tt < 0 || tt >= T) continue;
+#pragma unroll
         for (int kx = 0; kx < 3; ++kx) {
           const int xx = x + kx - 1;
           if (xx < 0 || xx >= X) continue;
-          for (int kd = 0; kd + d < 2; ++kd)
-            acc = fmaf(in_s[(tt * X + xx) * 2 + d + kd], w1s[((kt * 3 + kx) * 2 + kd) * F + f], acc);
+          const float* src2 = in_s + (tt * X + xx) * 2;
+          const float* wk = w1s + ((kt * 3 + kx) * 2) * F + f;
+          acc = fmaf(src2[d], wk[0], acc);                 // kd = 0
+          if (d == 0) acc = fmaf(src2[1], wk[F], acc);     // kd = 1 (mu = 1 sees only padding there)
         }
       }
-      c1[i] = fmaxf(acc, 0.f);
+      c1[pos * FP + f] = fmaxf(acc, 0.f);
     }
     __syncthreads();
     for (int i = tid; i < T2 * X2 * F; i += kThreads) {
@@ -91,7 +99,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
         for (int b = 0; b < 2; ++b) {
           const int t = 2 * t2 + a, x = 2 * x2 + b;
           if (t >= T || x >= X) continue;
-          for (int d = 0; d < 2; ++d) best = fmaxf(best, c1[((t * X + x) * 2 + d) * F + f]);
+          for (int d = 0; d < 2; ++d) best = fmaxf(best, c1[((t * X + x) * 2 + d) * FP + f]);
         }
       p1[i] = best;
     }
@@ -104,8 +112,9 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           const int tt = t + kt, xx = x + kx;
           if (tt >= T2 || xx >= X2) continue;
           const float* a = p1 + (tt * X2 + xx) * F;
-          const float* w = w2s + ((kt * 2 + kx) * F) * C2 + co;
-          for (int ci = 0; ci < F; ++ci) acc = fmaf(a[ci], w[ci * C2], acc);
+          const float* w = w2s + ((kt * 2 + kx) * F) * CP + co;
+#pragma unroll 8
+          for (int ci = 0; ci < F; ++ci) acc = fmaf(a[ci], w[ci * CP], acc);
         }
       c2[i] = fmaxf(acc, 0.f);
     }
@@ -137,9 +146,13 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     for (int i = tid; i < 4 * F * C2; i += kThreads) {
       const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F), kt = kk >> 1, kx = kk & 1;
       float s = 0.f;
-      for (int t = 0; t + kt < T2; ++t)
-        for (int x = 0; x + kx < X2; ++x)
-          s = fmaf(p1[((t + kt) * X2 + x + kx) * F + ci], c2[(t * X2 + x) * C2 + co], s);
+      for (int t = 0; t + kt < T2; ++t) {
+        const float* a = p1 + ((t + kt) * X2 + kx) * F + ci;
+        const float* g = c2 + (t * X2) * C2 + co;
+        const int nx = X2 - kx;
+#pragma unroll 4
+        for (int x = 0; x < nx; ++x) s = fmaf(a[x * F], g[x * C2], s);
+      }
       part[off_w2 + ((kk * 2 + 0) * F + ci) * C2 + co] += s;
     }
     for (int co = tid; co < C2; co += kThreads) {
@@ -153,7 +166,8 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       for (int kt = 0; kt < 2 && kt <= t; ++kt)
         for (int kx = 0; kx < 2 && kx <= x; ++kx) {
           const float* g = c2 + ((t - kt) * X2 + x - kx) * C2;
-          const float* w = w2s + ((kt * 2 + kx) * F + ci) * C2;
+          const float* w = w2s + ((kt * 2 + kx) * F + ci) * CP;
+#pragma unroll 8
           for (int co = 0; co < C2; ++co) s = fmaf(w[co], g[co], s);
         }
       gp1[i] = s;
@@ -169,7 +183,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           const int t = 2 * t2 + a, x = 2 * x2 + b;
           if (t >= T || x >= X) continue;
           for (int d = 0; d < 2; ++d) {
-            const int at = ((t * X + x) * 2 + d) * F + f;
+            const int at = ((t * X + x) * 2 + d) * FP + f;
             if (c1[at] > best) best = c1[at], arg = at;
           }
         }
@@ -179,7 +193,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           const int t = 2 * t2 + a, x = 2 * x2 + b;
           if (t >= T || x >= X) continue;
           for (int d = 0; d < 2; ++d) {
-            const int at = ((t * X + x) * 2 + d) * F + f;
+            const int at = ((t * X + x) * 2 + d) * FP + f;
             c1[at] = at == arg ? g : 0.f;
           }
         }
@@ -189,21 +203,27 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     for (int i = tid; i < 18 * F; i += kThreads) {
       const int f = i % F, kd = (i / F) & 1, kx = (i / (2 * F)) % 3, kt = i / (6 * F);
       float s = 0.f;
-      for (int t = 0; t < T; ++t) {
-        const int tt = t + kt - 1;
-        if (tt < 0 || tt >= T) continue;
-        for (int x = 0; x < X; ++x) {
-          const int xx = x + kx - 1;
-          if (xx < 0 || xx >= X) continue;
-          for (int d = 0; d + kd < 2; ++d)
-            s = fmaf(in_s[(tt * X + xx) * 2 + d + kd], c1[((t * X + x) * 2 + d) * F + f], s);
+      const int t_lo = kt == 0 ? 1 : 0, t_hi = kt == 2 ? T - 1 : T;       // outputs whose tap lands inside the lattice
+      const int x_lo = kx == 0 ? 1 : 0, x_hi = kx == 2 ? X - 1 : X;
+      for (int t = t_lo; t < t_hi; ++t) {
+        const float* a = in_s + ((t + kt - 1) * X + kx - 1) * 2 + kd;
+        const float* g = c1 + (t * X) * 2 * FP + f;
+        if (kd == 0) {
+#pragma unroll 4
+          for (int x = x_lo; x < x_hi; ++x) {
+            s = fmaf(a[2 * x], g[(2 * x) * FP], s);
+            s = fmaf(a[2 * x + 1], g[(2 * x + 1) * FP], s);
+          }
+        } else {
+#pragma unroll 4
+          for (int x = x_lo; x < x_hi; ++x) s = fmaf(a[2 * x], g[(2 * x) * FP], s);
         }
       }
       part[i] += s;
     }
     for (int f = tid; f < F; f += kThreads) {
       float s = 0.f;
-      for (int j = 0; j < D; ++j) s += c1[j * F + f];
+      for (int j = 0; j < D; ++j) s += c1[j * FP + f];
       part[off_b1 + f] += s;
     }
     float* dst = p.g_in + static_cast<size_t>(n) * D;
@@ -217,8 +237,9 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           const int x = xx - kx + 1;
           if (x < 0 || x >= X) continue;
           for (int kd = 0; kd <= dd; ++kd) {
-            const float* g = c1 + ((t * X + x) * 2 + dd - kd) * F;
+            const float* g = c1 + ((t * X + x) * 2 + dd - kd) * FP;
             const float* w = w1s + ((kt * 3 + kx) * 2 + kd) * F;
+#pragma unroll 8
             for (int f = 0; f < F; ++f) s = fmaf(w[f], g[f], s);
           }
         }
@@ -247,8 +268,8 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
                 "l2hmc_conv3d_backward: null pointer");
   L2HMC_REQUIRE(!a->row_set || (!a->mask == !a->mask_alt), "l2hmc_conv3d_backward: mask and mask_alt go together");
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, D = 2 * T * X;
-  const size_t floats = 2u * D + static_cast<size_t>(D) * F + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
-                        18u * F + 8u * F * F;
+  const size_t floats = 2u * D + static_cast<size_t>(D) * (F + 1) + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
+                        18u * F + 4u * F * (2 * F + 1);
   const size_t smem = floats * sizeof(float);
   int dev = 0, max_smem = 0;
   cudaGetDevice(&dev);
@@ -258,9 +279,10 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
               max_smem);
     return L2HMC_ERR_UNSUPPORTED;
   }
+  void (*kernel)(const ConvBwdParams) = F == 8 ? conv3d_bwd_kernel<8> : F == 16 ? conv3d_bwd_kernel<16>
+                                        : F == 32 ? conv3d_bwd_kernel<32> : conv3d_bwd_kernel<0>;
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(conv3d_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(smem));
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(conv3d_bwd_kernel): %s", cudaGetErrorString(e));
       return L2HMC_ERR_CUDA;
@@ -268,6 +290,6 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
   }
   ConvBwdParams p{a->w->w1, a->w->b1, a->w->w2, a->w->b2, F, a->in, a->mask, a->mask_invert, a->mask_alt,
                   a->mask_invert_alt, a->row_set, a->N, T, X, a->g_feat, a->g_in, a->partial, l2hmc_conv3d_bwd_cols(F)};
-  conv3d_bwd_kernel<<<l2hmc_conv3d_bwd_rows(a->N), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  kernel<<<l2hmc_conv3d_bwd_rows(a->N), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_launch("conv3d_bwd_kernel");
 }

@@ -5,7 +5,7 @@ Oracles: (i) the gradients the UNMODIFIED reference produced with tf.gradients o
 (tests/golden/train_cases.npz, keys `<tag>.grad.*`); (ii) reverse-mode autodiff through the CPU oracle
 (oracle/train_oracle.py::loss_and_grads, itself pinned to (i)); (iii) torch-CPU autograd of the oracle's formulas for
 each adjoint kernel on its own.  Tolerances: gradients are sums of O(N*D*M) fp32 products whose order differs between
-the graph and the kernels, so they are compared at 2e-4 of each tensor's largest entry (stated per check)."""
+the graph and the kernels, so whole-pass gradients are compared at 5e-4 of each tensor's largest entry (measured: <= 2.2e-5, profiles/r1_train_grad_errors.txt) and single kernels at 1e-5 .. 1e-4 (stated per check)."""
 import ctypes
 import math
 import os
@@ -289,7 +289,7 @@ def test_gradients_against_reference_goldens(golden):
         for name, gr in grads.items():
             want = g[f"{tag}.grad.{name}"]
             # the loss divides by x_std ~ O(1e-3 .. 1): its gradient inherits the 5e-3 the loss value is held to
-            close_scaled(gr, want, 1e-2, f"{tag} d loss / d {name}")
+            close_scaled(gr, want, 5e-4, f"{tag} d loss / d {name}")
             checked += 1
     assert checked >= 3 + 2 * 33 + 49
 
@@ -330,7 +330,7 @@ def test_gradients_against_oracle_config2_shapes(T, X, N, M, metric):
     assert abs(float(loss) - float(ref_loss)) <= 2e-3 * max(abs(float(ref_loss)), 1.)
     assert set(grads) == set(ref_grads)
     for name, gr in grads.items():
-        close_scaled(gr, ref_grads[name], 5e-3, f"d loss / d {name}")
+        close_scaled(gr, ref_grads[name], 5e-4, f"d loss / d {name}")
     # run to run: bit-identical (no atomics, fixed split-K order)
     loss2, grads2, _, _, _ = model._calc_loss_and_grads(x, beta, draws_x=draws_x, z=z, draws_z=draws_z)
     flat1 = model.engine.params.grad.clone()
