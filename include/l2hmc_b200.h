@@ -554,6 +554,54 @@ int l2hmc_adam_step(float* param, const float* grad, float* m, float* v, long lo
                     float beta2, float epsilon, float grad_scale, const float* grad_sumsq, float clip_norm,
                     void* stream);
 
+/* ------------------------------------------------------------------ one host call = loss + gradients of one step
+ * GaugeModel._calc_loss_and_grads (gauge_model.py:805-832 over :728-803 and dynamics/gauge_dynamics.py:195-313):
+ * both chains' transitions recorded on a tape, the loss, and the explicit backward sweep -- the launches of the
+ * entry points above, in a fixed order, on a caller-provided workspace; nothing is allocated or synchronised.
+ * Rows: the x-chain (rows 0..N-1) and the auxiliary z-chain (rows N..2N-1) are stacked; v_f / v_b [2N,D] and
+ * u_dir [2N] are the draws of both (the reference's tf.random_normal / random_uniform, :754-758 over
+ * dynamics/gauge_dynamics.py:211-248), u_acc [N] the x-chain's accept draw.  xnet == NULL: plain HMC (only g_eps).
+ * Gradients are WRITTEN (not accumulated) through the l2hmc_net_grads / l2hmc_conv3d_grads pointer sets, which
+ * mirror the weight structs.  forward_only != 0 stops after the loss. */
+typedef struct {
+  float *w_in0, *b_in0, *w_in1, *b_in1, *w_t, *b_t, *w_h, *b_h, *w_s, *b_s, *w_tr, *b_tr, *w_q, *b_q, *coeff_s, *coeff_q;
+} l2hmc_net_grads;
+typedef struct {
+  float *w1, *b1, *w2, *b2;
+} l2hmc_conv3d_grads;
+
+typedef struct {
+  int N, T, X, M;
+  float eps, beta;
+  const float* masks; /* [M][2TX] device */
+  const float* ts;    /* [M][2] HOST (cos, sin) rows */
+  const l2hmc_net_weights *xnet, *vnet;                                         /* nullable together */
+  const l2hmc_conv3d_weights *xconv_in0, *xconv_in1, *vconv_in0, *vconv_in1;    /* nullable together */
+  const float *x, *z;     /* [N,2TX] */
+  const float *v_f, *v_b; /* [2N,2TX] */
+  const float* u_dir;     /* [2N] */
+  const float* u_acc;     /* [N] */
+  l2hmc_loss_params loss;
+  int forward_only;
+  float* loss_out;        /* [1] */
+  float* per_chain;       /* [N] */
+  float* x_out;           /* [N,2TX] */
+  float* px;              /* [N] */
+  float* pz;              /* [N] nullable */
+  float* x_prop;          /* [N,2TX] nullable */
+  int32_t* x_dq;          /* [N] nullable */
+  uint8_t* accepted;      /* [N] nullable */
+  float* g_eps;           /* [1] */
+  const l2hmc_net_grads *xnet_g, *vnet_g;
+  const l2hmc_conv3d_grads *xconv_in0_g, *xconv_in1_g, *vconv_in0_g, *vconv_in1_g;
+  int32_t* nonfinite_flag;
+  void* workspace;        /* >= l2hmc_u1_train_workspace_bytes(args), 256-byte aligned */
+  size_t workspace_bytes;
+} l2hmc_train_args;
+
+size_t l2hmc_u1_train_workspace_bytes(const l2hmc_train_args* a);
+int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

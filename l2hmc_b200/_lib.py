@@ -94,6 +94,17 @@ class Conv3dBwdArgs(Structure):
                 ("X", c_int), ("g_feat", c_void_p), ("g_in", c_void_p), ("partial", c_void_p)]
 
 
+class NetGrads(Structure):
+    """l2hmc_net_grads (include/l2hmc_b200.h)."""
+    _fields_ = [(n, c_void_p) for n in ("w_in0", "b_in0", "w_in1", "b_in1", "w_t", "b_t", "w_h", "b_h", "w_s", "b_s",
+                                        "w_tr", "b_tr", "w_q", "b_q", "coeff_s", "coeff_q")]
+
+
+class Conv3dGrads(Structure):
+    """l2hmc_conv3d_grads (include/l2hmc_b200.h)."""
+    _fields_ = [("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p)]
+
+
 class Gmm(Structure):
     """l2hmc_gmm (include/l2hmc_b200.h)."""
     _fields_ = [("k", c_int), ("m", c_int), ("mus", c_void_p), ("i_sigmas", c_void_p), ("log_consts", c_void_p)]
@@ -118,6 +129,24 @@ class LossParams(Structure):
     """l2hmc_loss_params (include/l2hmc_b200.h)."""
     _fields_ = [("metric", c_int), ("loss_scale", c_float), ("aux_weight", c_float), ("std_weight", c_float),
                 ("charge_weight", c_float)]
+
+
+class TrainArgs(Structure):
+    """l2hmc_train_args (include/l2hmc_b200.h)."""
+    _fields_ = [
+        ("N", c_int), ("T", c_int), ("X", c_int), ("M", c_int), ("eps", c_float), ("beta", c_float),
+        ("masks", c_void_p), ("ts", c_void_p), ("xnet", POINTER(NetWeights)), ("vnet", POINTER(NetWeights)),
+        ("xconv_in0", POINTER(Conv3dWeights)), ("xconv_in1", POINTER(Conv3dWeights)),
+        ("vconv_in0", POINTER(Conv3dWeights)), ("vconv_in1", POINTER(Conv3dWeights)),
+        ("x", c_void_p), ("z", c_void_p), ("v_f", c_void_p), ("v_b", c_void_p), ("u_dir", c_void_p), ("u_acc", c_void_p),
+        ("loss", LossParams), ("forward_only", c_int),
+        ("loss_out", c_void_p), ("per_chain", c_void_p), ("x_out", c_void_p), ("px", c_void_p), ("pz", c_void_p),
+        ("x_prop", c_void_p), ("x_dq", c_void_p), ("accepted", c_void_p), ("g_eps", c_void_p),
+        ("xnet_g", POINTER(NetGrads)), ("vnet_g", POINTER(NetGrads)),
+        ("xconv_in0_g", POINTER(Conv3dGrads)), ("xconv_in1_g", POINTER(Conv3dGrads)),
+        ("vconv_in0_g", POINTER(Conv3dGrads)), ("vconv_in1_g", POINTER(Conv3dGrads)),
+        ("nonfinite_flag", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+    ]
 
 
 class RunStats(Structure):
@@ -196,6 +225,8 @@ SIGNATURES = {
     "l2hmc_conv3d_bwd_rows": [c_int],
     "l2hmc_conv3d_bwd_cols": [c_int],
     "l2hmc_conv3d_backward": [POINTER(Conv3dBwdArgs), c_void_p],
+    "l2hmc_u1_train_workspace_bytes": [POINTER(TrainArgs)],
+    "l2hmc_u1_train_grads": [POINTER(TrainArgs), c_void_p],
     "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
                         c_float, c_void_p, c_float, c_void_p],
@@ -204,7 +235,7 @@ SIGNATURES = {
 }
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
-            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t}
+            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

@@ -97,6 +97,7 @@ class GaugeModel(object):
         self._z_step = 0
         self._engine = self._optimizer = None
         self.global_step = 0
+        self.native_train = True        # loss + gradients of a step in one C call (csrc/train_step.cu)
         self.using_hvd = False          # set by train(): lr * world size, gradients averaged (gauge_model.py:939-941)
 
     # ------------------------------------------------------------------ construction (:585-613)
@@ -225,8 +226,12 @@ class GaugeModel(object):
         draws_x, z, draws_z = self._draws(x, draws_x, z, draws_z)
         eng = self.engine
         with torch.cuda.device(self.device):
-            fw = eng.forward(x, beta, draws_x, z, draws_z, w)
-            grads = eng.backward(fw)
+            if self.native_train:          # one C call enqueues the whole step (csrc/train_step.cu)
+                fw = eng.native(x, beta, draws_x, z, draws_z, w)
+                grads = eng.params.grads_dict()
+            else:                          # the same launches driven from Python (kept for tests / debugging)
+                fw = eng.forward(x, beta, draws_x, z, draws_z, w)
+                grads = eng.backward(fw)
         self.last_per_chain_loss, self.last_forward = fw["per_chain"], fw
         return fw["loss"][0], grads, fw["x_out"], fw["px"], fw["x_dq"]
 

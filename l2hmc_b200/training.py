@@ -252,6 +252,82 @@ class TrainEngine(object):
                 self.gemm(1, n, [ones + (_ptr(part, off), cols, 1, rows)], _ptr(P.view(P.grad, f"{name}.{key}")), n)
                 off += n
 
+    # ------------------------------------------------------------------ native: one C call per step
+    def _grads_struct(self, name, net):
+        P = self.params
+        g = _lib.NetGrads()
+        p = lambda k: _ptr(P.view(P.grad, f"{name}.{k}"))
+        g.w_in0, g.b_in0 = p("v_layer.kernel"), p("v_layer.bias")           # first input -> v_layer
+        g.w_in1, g.b_in1 = p("x_layer.kernel"), p("x_layer.bias")
+        g.w_t, g.b_t, g.w_h, g.b_h = p("t_layer.kernel"), p("t_layer.bias"), p("h_layer.kernel"), p("h_layer.bias")
+        g.w_s, g.b_s = p("scale_layer.kernel"), p("scale_layer.bias")
+        g.w_tr, g.b_tr = p("translation_layer.kernel"), p("translation_layer.bias")
+        g.w_q, g.b_q = p("transformation_layer.kernel"), p("transformation_layer.bias")
+        g.coeff_s, g.coeff_q = p("coeff_scale"), p("coeff_transformation")
+        convs = {}
+        if self.conv:
+            for which in ("x", "v"):
+                c = _lib.Conv3dGrads()
+                c.w1, c.b1 = p(f"conv_{which}1.kernel"), p(f"conv_{which}1.bias")
+                c.w2, c.b2 = p(f"conv_{which}2.kernel"), p(f"conv_{which}2.bias")
+                convs[which] = c
+        return g, convs
+
+    def native(self, x, beta, draws_x, z, draws_z, weights, forward_only=False):
+        """Loss and gradients of one step enqueued by ONE C call (csrc/train_step.cu: l2hmc_u1_train_grads) -- the same
+        launches as forward() + backward(), issued from C++.  Returns the same dict keys the training loop reads."""
+        dyn, lib = self.dyn, _lib.get_lib()
+        N, D = x.shape
+        dev = self.device
+        new = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        a = _lib.TrainArgs()
+        a.N, a.T, a.X, a.M = N, dyn.T, dyn.X, int(dyn.num_steps)
+        a.eps, a.beta = dyn._eps(), dyn._beta(beta)
+        mask = dyn.mask if dyn.mask.is_contiguous() else dyn.mask.contiguous()
+        a.masks = _lib.dptr(mask)
+        ts = np.ascontiguousarray(dyn._ts_host, dtype=np.float32)
+        a.ts = ts.ctypes.data_as(ctypes.c_void_p)
+        keep = [mask, ts]
+        if not dyn.hmc:
+            if getattr(self, "_native_structs", None) is None:
+                xs, vs = self._net_struct(dyn.position_fn), self._net_struct(dyn.momentum_fn)
+                xg, xc = self._grads_struct("XNet", dyn.position_fn)
+                vg, vc = self._grads_struct("VNet", dyn.momentum_fn)
+                self._native_structs = (xs, vs, xg, vg, xc, vc)
+            xs, vs, xg, vg, xc, vc = self._native_structs
+            a.xnet, a.vnet = ctypes.pointer(xs), ctypes.pointer(vs)
+            a.xnet_g, a.vnet_g = ctypes.pointer(xg), ctypes.pointer(vg)
+            if self.conv:
+                a.xconv_in0, a.xconv_in1 = ctypes.pointer(dyn.position_fn._conv("v")), ctypes.pointer(dyn.position_fn._conv("x"))
+                a.vconv_in0, a.vconv_in1 = ctypes.pointer(dyn.momentum_fn._conv("v")), ctypes.pointer(dyn.momentum_fn._conv("x"))
+                a.xconv_in0_g, a.xconv_in1_g = ctypes.pointer(xc["v"]), ctypes.pointer(xc["x"])
+                a.vconv_in0_g, a.vconv_in1_g = ctypes.pointer(vc["v"]), ctypes.pointer(vc["x"])
+        v_f = torch.cat([draws_x[0], draws_z[0]], dim=0)
+        v_b = v_f if (draws_x[1] is draws_x[0] and draws_z[1] is draws_z[0]) else torch.cat([draws_x[1], draws_z[1]], dim=0)
+        u_dir = torch.cat([draws_x[2], draws_z[2]], dim=0)
+        u_acc = draws_x[3].contiguous()
+        a.x, a.z, a.v_f, a.v_b = _lib.dptr(x), _lib.dptr(z), _lib.dptr(v_f), _lib.dptr(v_b)
+        a.u_dir, a.u_acc = _lib.dptr(u_dir), _lib.dptr(u_acc)
+        a.loss.metric, a.loss.loss_scale = _lib.METRICS[self.metric], self.loss_scale
+        a.loss.aux_weight, a.loss.std_weight, a.loss.charge_weight = (float(weights[k]) for k in
+                                                                      ("aux_weight", "std_weight", "charge_weight"))
+        a.forward_only = int(bool(forward_only))
+        out = dict(N=N, D=D, loss=new(1), per_chain=new(N), x_out=new(N, D), px=new(N), pz=new(N), x_prop=new(N, D),
+                   x_dq=torch.empty(N, dtype=torch.int32, device=dev), accepted=torch.empty(N, dtype=torch.uint8, device=dev))
+        a.loss_out, a.per_chain, a.x_out, a.px, a.pz, a.x_prop = (_lib.dptr(out[k]) for k in
+                                                                  ("loss", "per_chain", "x_out", "px", "pz", "x_prop"))
+        a.x_dq, a.accepted = _lib.dptr(out["x_dq"], torch.int32), _lib.dptr(out["accepted"], torch.uint8)
+        P = self.params
+        a.g_eps = _ptr(P.view(P.grad, "eps"))
+        a.nonfinite_flag = _lib.dptr(dyn._flag, torch.int32)
+        need = int(lib.l2hmc_u1_train_workspace_bytes(ctypes.byref(a)))
+        if getattr(self, "_native_ws", None) is None or self._native_ws.numel() < need:
+            self._native_ws = torch.empty(need, dtype=torch.uint8, device=dev)
+        a.workspace, a.workspace_bytes = ctypes.c_void_p(self._native_ws.data_ptr()), need
+        _lib.check(lib.l2hmc_u1_train_grads(ctypes.byref(a), _lib.stream_ptr()))
+        del keep
+        return out
+
     # ------------------------------------------------------------------ forward with tape
     def forward(self, x, beta, draws_x, z, draws_z, weights):
         """Both chains' transitions + the loss.  draws_* = (v_f, v_b, u_dir, u_acc)."""

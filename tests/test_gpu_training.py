@@ -476,3 +476,34 @@ def test_conv3d_backward_against_autograd(T, X, F, N):
         n = ref.numel()
         close_scaled(tot[off:off + n], ref.reshape(-1), 5e-5, f"conv d/d {nm}")
         off += n
+
+
+def test_native_step_equals_python_walk(golden):
+    """l2hmc_u1_train_grads (one C call, csrc/train_step.cu) issues the same launches as the Python-driven walk of
+    training.py: loss, proposals and every gradient are bit-identical (plain HMC, generic and conv3D nets)."""
+    from test_gpu_train_rows import build_model
+    g = golden("train_cases")
+    seen = set()
+    for tag in _tags(g, "loss"):
+        arch = tag.split(".")[1]
+        if arch in seen:
+            continue
+        seen.add(arch)
+        model, _ = build_model(g, tag)
+        args = dict(draws_x=(g[tag + ".v_f"], g[tag + ".v_b"], g[tag + ".u_dir"], g[tag + ".u_acc"]), z=g[tag + ".z"],
+                    draws_z=(g[tag + ".vz_f"], g[tag + ".vz_b"], g[tag + ".uz_dir"], g[tag + ".uz_acc"]))
+        model.native_train = False
+        loss_a, _, xo_a, px_a, dq_a = model._calc_loss_and_grads(g[tag + ".x"], float(g[tag + ".beta"]), **args)
+        flat_a = model.engine.params.grad.clone()
+        model.engine.params.grad.fill_(float("nan"))
+        model.native_train = True
+        loss_b, _, xo_b, px_b, dq_b = model._calc_loss_and_grads(g[tag + ".x"], float(g[tag + ".beta"]), **args)
+        torch.cuda.synchronize()
+        flat_b = model.engine.params.grad
+        assert float(loss_a) == float(loss_b), tag
+        assert torch.equal(xo_a, xo_b) and torch.equal(px_a, px_b) and torch.equal(dq_a, dq_b), tag
+        # the arena's 16-byte padding between tensors is never written by either path
+        for name in model.engine.params.names:
+            va, vb = model.engine.params.view(flat_a, name), model.engine.params.view(flat_b, name)
+            assert torch.equal(va, vb), f"{tag} {name}"
+    assert seen == {"hmc", "generic", "conv3D"}
