@@ -441,8 +441,9 @@ int l2hmc_mode_switches(const int32_t* mode, int32_t* prev, uint32_t* switches, 
  *   relu_gate (nullable): the product is zeroed where gate[m*ldg + n] <= 0   (d relu: dZ = dH * [h > 0])
  *   col_scale (nullable [N]): multiplies column n by scale[n] (or 1 - scale[n]); rows with row_set[m] != 0 use
  *   col_scale_alt / col_scale_invert_alt  (the `mask * x` input of position_fn, dynamics/gauge_dynamics.py:515-517)
- * ksplit > 1 splits K over grid.z into `workspace` and sums the slices in order (one segment, no epilogue): the
- * deferred weight-gradient GEMMs, whose K is the whole tape. */
+ * ksplit > 1 splits K (of every segment) over grid.z into `workspace` (l2hmc_sgemm_workspace_bytes) and a second
+ * kernel sums the slices in fixed order and applies the epilogue: the deferred weight-gradient GEMMs, whose K is the
+ * whole tape, and -- ksplit = 0, chosen by the library -- the few-tile per-call GEMMs of a small batch. */
 typedef struct {
   const float* A;
   long long a_rs, a_cs;

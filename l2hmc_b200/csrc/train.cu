@@ -35,11 +35,23 @@ struct GemmParams {
   float* partial;   // [ksplit][M*N] when ksplit > 1
 };
 
+// 4-byte async copy global -> shared (LDGSTS), zero-filled when !valid: operand tiles are transposed on the fly
+// (any strides), so the copy granularity is one float.
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc, bool valid) {
+  const int sz = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int kStages = 5;   // K slabs in flight: the training GEMMs at config 2 are 32-CTA launches, latency-bound
+
 // A_KC / B_KC: the operand's K index is the contiguous one (only affects which threads read neighbouring words)
 template <bool A_KC, bool B_KC>
 __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p) {
-  __shared__ __align__(16) float As[GBK][GBM + 4];
-  __shared__ __align__(16) float Bs[GBK][GBN + 4];
+  __shared__ __align__(16) float As[kStages][GBK][GBM + 4];
+  __shared__ __align__(16) float Bs[kStages][GBK][GBN + 4];
   const l2hmc_gemm_args& g = p.a;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * GBM, n0 = blockIdx.x * GBN;
@@ -58,48 +70,72 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
     if (A_KC) ak[i] = e & 15, am[i] = e >> 4; else am[i] = e & 63, ak[i] = e >> 6;
     if (B_KC) bk[i] = e & 15, bn[i] = e >> 4; else bn[i] = e & 63, bk[i] = e >> 6;
   }
-  float a_reg[4], b_reg[4];
 
-  for (int s = 0; s < g.nseg; ++s) {
-    const l2hmc_gemm_seg& sg = g.seg[s];
-    int kb = 0, ke = sg.K;
+  // K range of segment s for this CTA (split-K slices segment 0 over grid.z)
+  auto seg_range = [&](int s, int& kb, int& ke) {
+    kb = 0, ke = g.seg[s].K;
     if (p.ksplit > 1) {
-      int chunk = (sg.K + p.ksplit - 1) / p.ksplit;
+      int chunk = (g.seg[s].K + p.ksplit - 1) / p.ksplit;
       chunk = (chunk + GBK - 1) / GBK * GBK;
-      kb = min(sg.K, z * chunk);
-      ke = min(sg.K, kb + chunk);
+      kb = min(g.seg[s].K, z * chunk);
+      ke = min(g.seg[s].K, kb + chunk);
     }
-    auto load = [&](int k0) {
+  };
+  int total = 0;
+  for (int s = 0; s < g.nseg; ++s) {
+    int kb, ke;
+    seg_range(s, kb, ke);
+    total += (ke - kb + GBK - 1) / GBK;
+  }
+  // issue cursor over the flattened (segment, slab) sequence
+  int iseg = 0, ik0 = 0, ike = 0;
+  seg_range(0, ik0, ike);
+  auto skip_empty = [&]() {
+    while (iseg < g.nseg && ik0 >= ike) {
+      ++iseg;
+      if (iseg < g.nseg) seg_range(iseg, ik0, ike);
+    }
+  };
+  skip_empty();
+  auto issue = [&](int stage) {
+    if (iseg < g.nseg) {
+      const l2hmc_gemm_seg& sg = g.seg[iseg];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const int m = m0 + am[i], k = k0 + ak[i];
-        a_reg[i] = (m < g.M && k < ke) ? sg.A[static_cast<long long>(m) * sg.a_rs + static_cast<long long>(k) * sg.a_cs]
-                                       : 0.f;
-        const int n = n0 + bn[i], k2 = k0 + bk[i];
-        b_reg[i] = (n < g.N && k2 < ke) ? sg.B[static_cast<long long>(k2) * sg.b_rs + static_cast<long long>(n) * sg.b_cs]
-                                        : 0.f;
+        const int m = m0 + am[i], k = ik0 + ak[i];
+        const bool va = m < g.M && k < ike;
+        cp_async4(&As[stage][ak[i]][am[i]],
+                  va ? sg.A + static_cast<long long>(m) * sg.a_rs + static_cast<long long>(k) * sg.a_cs : sg.A, va);
+        const int n = n0 + bn[i], k2 = ik0 + bk[i];
+        const bool vb = n < g.N && k2 < ike;
+        cp_async4(&Bs[stage][bk[i]][bn[i]],
+                  vb ? sg.B + static_cast<long long>(k2) * sg.b_rs + static_cast<long long>(n) * sg.b_cs : sg.B, vb);
       }
-    };
-    if (kb < ke) load(kb);
-    for (int k0 = kb; k0 < ke; k0 += GBK) {
+      ik0 += GBK;
+      skip_empty();
+    }
+    cp_async_commit();
+  };
 #pragma unroll
-      for (int i = 0; i < 4; ++i) As[ak[i]][am[i]] = a_reg[i], Bs[bk[i]][bn[i]] = b_reg[i];
-      __syncthreads();
-      if (k0 + GBK < ke) load(k0 + GBK);
+  for (int s = 0; s < kStages - 1; ++s) issue(s);
+  for (int it = 0; it < total; ++it) {
+    cp_async_wait<kStages - 2>();
+    __syncthreads();                       // slab `it` has landed; everyone is done with slab it - 1
+    issue((it + kStages - 1) % kStages);   // refill the stage slab it - 1 occupied
+    const int st = it % kStages;
 #pragma unroll
-      for (int k = 0; k < GBK; ++k) {
-        const float4 a4 = *reinterpret_cast<const float4*>(&As[k][4 * ty]);
-        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[k][4 * tx]);
-        const float a[4] = {a4.x, a4.y, a4.z, a4.w};
-        const float b[4] = {b4.x, b4.y, b4.z, b4.w};
+    for (int k = 0; k < GBK; ++k) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[st][k][4 * ty]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&Bs[st][k][4 * tx]);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w};
+      const float b[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+      for (int i = 0; i < 4; ++i)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
-      }
-      __syncthreads();
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
   }
+  cp_async_wait<0>();
 
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -128,17 +164,23 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
   }
 }
 
-// C[r][c] (+)= sum_z partial[z][r][c], z in fixed order
-__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int ksplit, int M, int N, float* C,
-                                     long long ldc, int accumulate) {
+// C[r][c] (=|+=) scale[c] * gate[r][c] * sum_z partial[z][r][c], z in fixed order (the epilogue of a split-K product)
+__global__ void splitk_reduce_kernel(const float* __restrict__ partial, int ksplit, const l2hmc_gemm_args g) {
   const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const size_t total = static_cast<size_t>(M) * N;
+  const size_t total = static_cast<size_t>(g.M) * g.N;
   if (idx >= total) return;
-  float s = 0.f;
-  for (int z = 0; z < ksplit; ++z) s = __fadd_rn(s, partial[static_cast<size_t>(z) * total + idx]);
-  const int r = static_cast<int>(idx / N), c = static_cast<int>(idx % N);
-  float* dst = C + static_cast<long long>(r) * ldc + c;
-  *dst = accumulate ? __fadd_rn(*dst, s) : s;
+  float val = 0.f;
+  for (int z = 0; z < ksplit; ++z) val = __fadd_rn(val, partial[static_cast<size_t>(z) * total + idx]);
+  const int r = static_cast<int>(idx / g.N), c = static_cast<int>(idx % g.N);
+  if (g.relu_gate != nullptr && !(g.relu_gate[static_cast<long long>(r) * g.ldg + c] > 0.f)) val = 0.f;
+  const bool alt = g.row_set != nullptr && g.row_set[r] != 0;
+  const float* cs = alt ? g.col_scale_alt : g.col_scale;
+  if (cs != nullptr) {
+    const float sc = cs[c];
+    val = __fmul_rn(val, (alt ? g.col_scale_invert_alt : g.col_scale_invert) ? __fsub_rn(1.f, sc) : sc);
+  }
+  float* dst = g.C + static_cast<long long>(r) * g.ldc + c;
+  *dst = g.accumulate ? __fadd_rn(*dst, val) : val;
 }
 
 // =============================================================================================== block helpers
@@ -584,8 +626,20 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ param, co
 using namespace l2hmc;
 
 // =============================================================================================== C ABI
+// ksplit = 0: enough K slices to put ~1.5 CTAs on every SM when the output has few tiles (the per-call GEMMs of a
+// config-2 training step are 32-tile launches), each slice keeping at least two K slabs
+static int auto_ksplit(const l2hmc_gemm_args* g) {
+  const int tiles = ((g->M + GBM - 1) / GBM) * ((g->N + GBN - 1) / GBN);
+  if (tiles >= 120) return 1;
+  int kmin = g->seg[0].K;
+  for (int s = 1; s < g->nseg; ++s) kmin = std::min(kmin, g->seg[s].K);
+  return std::max(1, std::min(8, std::min(240 / tiles, kmin / (2 * GBK))));
+}
+
 extern "C" size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {
-  if (!g || ksplit <= 1) return 0;
+  if (!g || g->nseg < 1 || g->nseg > 3) return 0;
+  if (ksplit == 0) ksplit = auto_ksplit(g);
+  if (ksplit <= 1) return 0;
   return sizeof(float) * static_cast<size_t>(ksplit) * g->M * g->N;
 }
 
@@ -597,13 +651,12 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   L2HMC_REQUIRE(g->C, "l2hmc_sgemm: null C");
   for (int s = 0; s < g->nseg; ++s)
     L2HMC_REQUIRE(g->seg[s].A && g->seg[s].B && g->seg[s].K >= 0, "l2hmc_sgemm: bad segment %d", s);
+  if (ksplit == 0) ksplit = auto_ksplit(g);
   if (ksplit < 1) ksplit = 1;
-  if (ksplit > 1) {
-    L2HMC_REQUIRE(g->nseg == 1 && !g->relu_gate && !g->col_scale && !g->row_set,
-                  "l2hmc_sgemm: split-K takes one segment and no epilogue");
+  if (ksplit > 1)
     L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_sgemm_workspace_bytes(g, ksplit),
-                  "l2hmc_sgemm: split-K workspace too small");
-  }
+                  "l2hmc_sgemm: split-K workspace too small (%zu < %zu bytes)", workspace_bytes,
+                  l2hmc_sgemm_workspace_bytes(g, ksplit));
   if (g->row_set) L2HMC_REQUIRE(!g->col_scale == !g->col_scale_alt, "l2hmc_sgemm: col_scale and col_scale_alt go together");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   GemmParams p{*g, ksplit, static_cast<float*>(workspace)};
@@ -616,8 +669,7 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   int rc = check_launch("sgemm_kernel");
   if (rc || ksplit == 1) return rc;
   const size_t total = static_cast<size_t>(g->M) * g->N;
-  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(p.partial, ksplit, g->M, g->N, g->C,
-                                                                                  g->ldc, g->accumulate);
+  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(p.partial, ksplit, *g);
   return check_launch("splitk_reduce_kernel");
 }
 

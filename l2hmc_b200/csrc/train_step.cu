@@ -122,6 +122,7 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
       const int K = static_cast<int>(Rt);
       auto need = [&](int Mm, int Nn) { gw = std::max(gw, sizeof(float) * ksplit_for(Mm, Nn, K) * Mm * static_cast<size_t>(Nn)); };
       need(w->H, w->D), need(1, w->D), need(w->H, w->H), need(1, w->H), need(w->K, w->H), need(2, w->H);
+      gw = std::max(gw, sizeof(float) * 8 * R * static_cast<size_t>(std::max(w->H, std::max(w->K, w->D))));   // per-call GEMMs, auto split <= 8
     }
     pl.gemm_ws_bytes = gw;
     pl.gemm_ws = c.take<char>(gw);
@@ -160,7 +161,7 @@ int gemm(const Ctx& c, int M, int N, std::initializer_list<l2hmc_gemm_seg> segs,
   return l2hmc_sgemm(&g, ksplit, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.stream);
 }
 
-int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long ldc, int accumulate = 0, int ksplit = 1) {
+int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long ldc, int accumulate = 0, int ksplit = 0) {
   return gemm(c, M, N, {s}, C, ldc, accumulate, nullptr, 0, nullptr, 0, nullptr, 0, false, ksplit);
 }
 
@@ -191,9 +192,9 @@ int net_backward(const Ctx& c, const l2hmc_net_weights* w, NetTape& t, int j) {
   L2HMC_TRY(gemm(c, c.pl.R, H,
                  {l2hmc_gemm_seg{dA, 3LL * D, 1, w->w_s, 1, D, D}, l2hmc_gemm_seg{dA + D, 3LL * D, 1, w->w_tr, 1, D, D},
                   l2hmc_gemm_seg{dA + 2 * D, 3LL * D, 1, w->w_q, 1, D, D}},
-                 t.dz2 + off * H, H, 0, t.h2 + off * H, H, nullptr, 0, nullptr, 0, false, 1));
+                 t.dz2 + off * H, H, 0, t.h2 + off * H, H, nullptr, 0, nullptr, 0, false, 0));
   return gemm(c, c.pl.R, H, {l2hmc_gemm_seg{t.dz2 + off * H, H, 1, w->w_h, 1, H, H}}, t.dz1 + off * H, H, 0,
-              t.h1 + off * H, H, nullptr, 0, nullptr, 0, false, 1);
+              t.h1 + off * H, H, nullptr, 0, nullptr, 0, false, 0);
 }
 
 int weight_grads(const Ctx& c, const NetTape& t, const l2hmc_net_grads* g) {
@@ -224,7 +225,7 @@ int conv_weight_grads(const Ctx& c, const NetTape& t, const float* part, const l
   const int n[4] = {18 * F, F, 16 * F * F, 2 * F};
   int off = 0;
   for (int i = 0; i < 4; ++i) {
-    L2HMC_TRY(plain_gemm(c, 1, n[i], l2hmc_gemm_seg{ones, 0, 3, part + off, cols, 1, rows}, dst[i], n[i]));
+    L2HMC_TRY(plain_gemm(c, 1, n[i], l2hmc_gemm_seg{ones, 0, 3, part + off, cols, 1, rows}, dst[i], n[i], 0, 1));
     off += n[i];
   }
   return L2HMC_OK;
@@ -425,7 +426,7 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
         } else {
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gv, D, 1));
           L2HMC_TRY(gemm(c, R, K, {l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}}, pl.gx, D, 1, nullptr, 0, row_f, rec.inv,
-                         row_b, rec.inv_alt, true, 1));
+                         row_b, rec.inv_alt, true, 0));
         }
       }
     }

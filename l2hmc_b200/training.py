@@ -42,7 +42,7 @@ class _Gemm(object):
         self.launches = 0
 
     def __call__(self, M, N, segs, C, ldc, accumulate=False, relu_gate=None, ldg=0, col_scale=None, invert=False,
-                 row_set=None, col_scale_alt=None, invert_alt=False, ksplit=1):
+                 row_set=None, col_scale_alt=None, invert_alt=False, ksplit=0):
         a = _lib.GemmArgs()
         a.M, a.N, a.nseg = int(M), int(N), len(segs)
         for i, (A, a_rs, a_cs, B, b_rs, b_cs, K) in enumerate(segs):
@@ -54,14 +54,14 @@ class _Gemm(object):
         a.row_set = row_set
         a.col_scale_alt, a.col_scale_invert_alt = col_scale_alt, int(bool(invert_alt))
         lib = _lib.get_lib()
-        ws, need = None, 0
-        if ksplit > 1:
-            need = int(lib.l2hmc_sgemm_workspace_bytes(ctypes.byref(a), int(ksplit)))
+        ws = None
+        need = int(lib.l2hmc_sgemm_workspace_bytes(ctypes.byref(a), int(ksplit)))     # ksplit = 0: the library chooses
+        if need:
             if self._ws is None or self._ws.numel() * 4 < need:
                 self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=self.device)
             ws = _ptr(self._ws)
         _lib.check(lib.l2hmc_sgemm(ctypes.byref(a), int(ksplit), ws, need, _lib.stream_ptr()))
-        self.launches += 1 if ksplit <= 1 else 2
+        self.launches += 2 if need else 1
 
 
 class _NetTape(object):
@@ -249,7 +249,8 @@ class TrainEngine(object):
             off = 0
             for key, n in ((f"conv_{which}1.kernel", 18 * F), (f"conv_{which}1.bias", F),
                            (f"conv_{which}2.kernel", 16 * F * F), (f"conv_{which}2.bias", 2 * F)):
-                self.gemm(1, n, [ones + (_ptr(part, off), cols, 1, rows)], _ptr(P.view(P.grad, f"{name}.{key}")), n)
+                self.gemm(1, n, [ones + (_ptr(part, off), cols, 1, rows)], _ptr(P.view(P.grad, f"{name}.{key}")), n,
+                          ksplit=1)
                 off += n
 
     # ------------------------------------------------------------------ native: one C call per step

@@ -50,7 +50,7 @@ def test_sgemm_forms(M, N, K, ta, tb):
     a_rs, a_cs = (1, M) if ta else (K, 1)
     b_rs, b_cs = (1, K) if tb else (N, 1)
     gemm = _Gemm(torch.device("cuda"))
-    for ksplit in (1, 4):
+    for ksplit in (1, 4, 0):
         C = torch.full((M, N), 7.0, device="cuda")
         gemm(M, N, [(_ptr(dA), a_rs, a_cs, _ptr(dB), b_rs, b_cs, K)], _ptr(C), N, ksplit=ksplit)
         close_scaled(C, ref, 1e-5, f"sgemm ksplit={ksplit}")
@@ -61,12 +61,14 @@ def test_sgemm_forms(M, N, K, ta, tb):
     rows = (rng.uniform(size=M) > 0.5).astype(np.uint8)
     scale = np.where(rows[:, None] != 0, 1 - m1[None, :], m0[None, :])
     want = C0 + ref * (gate > 0) * scale
-    C, tg, t0, t1, tr = cu(C0), cu(gate), cu(m0), cu(m1), cu(rows, torch.uint8)
-    gemm(M, N, [(_ptr(dA), a_rs, a_cs, _ptr(dB), b_rs, b_cs, K)], _ptr(C), N, accumulate=True, relu_gate=_ptr(tg),
-         ldg=N, col_scale=_ptr(t0), invert=False, row_set=_lib.dptr(tr, torch.uint8), col_scale_alt=_ptr(t1),
-         invert_alt=True)
-    torch.cuda.synchronize()
-    close_scaled(C, want, 1e-5, "sgemm epilogue")
+    tg, t0, t1, tr = cu(gate), cu(m0), cu(m1), cu(rows, torch.uint8)
+    for ksplit in (1, 3, 0):            # split-K applies the same epilogue in its second stage
+        C = cu(C0)
+        gemm(M, N, [(_ptr(dA), a_rs, a_cs, _ptr(dB), b_rs, b_cs, K)], _ptr(C), N, accumulate=True, relu_gate=_ptr(tg),
+             ldg=N, col_scale=_ptr(t0), invert=False, row_set=_lib.dptr(tr, torch.uint8), col_scale_alt=_ptr(t1),
+             invert_alt=True, ksplit=ksplit)
+        torch.cuda.synchronize()
+        close_scaled(C, want, 1e-5, f"sgemm epilogue ksplit={ksplit}")
 
 
 def test_sgemm_three_segments():
@@ -77,9 +79,11 @@ def test_sgemm_three_segments():
     Ws = [rng.standard_normal((H, D)).astype(np.float32) for _ in range(3)]
     ref = sum(dA[:, s * D:(s + 1) * D].astype(np.float64) @ Ws[s].T.astype(np.float64) for s in range(3))
     tA, tW = cu(dA), [cu(w) for w in Ws]
-    C = torch.empty(R, H, device="cuda")
-    _Gemm(torch.device("cuda"))(R, H, [(_ptr(tA, s * D), 3 * D, 1, _ptr(tW[s]), 1, D, D) for s in range(3)], _ptr(C), H)
-    close_scaled(C, ref, 1e-5, "3-segment NT gemm")
+    for ksplit in (1, 2, 0):
+        C = torch.empty(R, H, device="cuda")
+        _Gemm(torch.device("cuda"))(R, H, [(_ptr(tA, s * D), 3 * D, 1, _ptr(tW[s]), 1, D, D) for s in range(3)], _ptr(C), H,
+                                    ksplit=ksplit)
+        close_scaled(C, ref, 1e-5, f"3-segment NT gemm ksplit={ksplit}")
 
 
 # --------------------------------------------------------------------------------------------- update adjoints
