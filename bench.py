@@ -379,39 +379,67 @@ def run_l2hmc(r, steps):
         del dyn, net, x, v
         torch.cuda.empty_cache()
     out["config5_mog"] = run_mog(c, events_ms, steps)
-    out["config2_8x8_generic_training"] = run_training(c, events_ms, steps)
+    out["training"] = run_training(c, events_ms, steps)
     return out
 
 
 def run_training(c, events_ms, steps):
-    """BASELINE config 2: 8x8, generic S/T/Q MLPs (H = 4D = 512), batch 128, M = 5: one training step = loss over
-    the x- and z-chain, explicit backward pass (csrc/train.cu), [gradient all-reduce at N > 1], Adam."""
+    """Training step at BASELINE config 2 (8x8, generic S/T/Q MLPs H = 4D = 512, batch 128, M = 5)
+    and config 3 (16x16, conv3D F = 16, H = 1024, 2048 chains per GPU, M = 5): loss over the x- and z-chain with tape,
+    explicit backward pass (one C call, csrc/train_step.cu), [gradient all-reduce at N > 1], Adam, observables.
+    Rank 0 at N = 1 also times the CPU oracle (torch autograd through the oracle's transition) on the config-2 step."""
     import numpy as np
     from l2hmc_b200.gauge_model import GaugeModel
     torch, dev, world = c["torch"], c["dev"], c["world"]
-    np.random.seed(42)
-    model = GaugeModel(dict(time_size=8, space_size=8, num_samples=128, num_steps=5, eps=0.2, network_arch="generic",
-                            rand=True, train_steps=10000), device=dev)
-    model.dynamics.seed, model.dynamics.chain_offset = 13, c["dyn"].chain_offset // 512
-    model.using_hvd = world > 1
-    if world > 1:
-        from l2hmc_b200.sharding import broadcast_weights
-        broadcast_weights([model.engine.params.flat])
-    state = [model._x(model.lattice.samples).contiguous()]
+    out = {}
+    for tag, prm in (("config2_8x8_generic", dict(time_size=8, space_size=8, num_samples=128, network_arch="generic")),
+                     ("config3_16x16_conv3D", dict(time_size=16, space_size=16, num_samples=2048, network_arch="conv3D"))):
+        np.random.seed(42)
+        model = GaugeModel(dict(prm, num_steps=5, eps=0.2, rand=True, train_steps=10000), device=dev)
+        N, D, M = prm["num_samples"], 2 * prm["time_size"] ** 2, 5
+        model.dynamics.seed, model.dynamics.chain_offset = 13, (c["dyn"].chain_offset // 65536) * N
+        model.using_hvd = world > 1
+        eng = model.engine
+        if world > 1:
+            from l2hmc_b200.sharding import broadcast_weights
+            broadcast_weights([eng.params.flat])
+            eng.params.sync_to_dynamics()
+        state = [model._x(model.lattice.samples).contiguous()]
 
-    def step():
-        state[0] = model.train_step(state[0], 2.0)[1]
-    step()
-    eng = model.engine
-    l0 = eng.launches + eng.gemm.launches
-    step()
-    launches = eng.launches + eng.gemm.launches - l0 + 2          # + Adam, + observables
-    ms = events_ms(step, max(5, steps // 2), warm=1)
-    N, D, M = 128, 128, 5
-    return {"chains_per_gpu": N, "H": 512, "D": D, "lf_steps": M, "train_step_ms": ms, "launches_per_step": launches,
-            "params": int(eng.params.size), "link_updates_per_s": world * N * D * M / (ms * 1e-3),
-            "note": "both chains (x, z) forward with tape + backward + Adam; counts the x-chain's advance once; "
-                    "launch-latency bound at this size (Python-driven, ~%d launches per step)" % launches}
+        def step():
+            state[0] = model.train_step(state[0], 2.0)[1]
+        ms = events_ms(step, max(5, steps // 2), warm=2)
+        entry = {"chains_per_gpu": N, "H": int(model.dynamics.position_fn.num_hidden), "D": D, "lf_steps": M,
+                 "params": int(eng.params.size), "train_step_ms": ms,
+                 "link_updates_per_s": world * N * D * M / (ms * 1e-3),
+                 "note": "x- and z-chain forward with tape + backward + Adam + observables; the x-chain's advance is "
+                         "counted once; FFMA GEMMs (cp.async multi-stage, split-K), fp32"}
+        if tag.startswith("config2") and world == 1 and not c.get("no_cpu"):
+            import time
+            from oracle import train_oracle as tro
+            from oracle import u1_oracle as orc
+            torch.set_num_threads(os.cpu_count())
+            dyn = model.dynamics
+            od = orc.OracleDynamics(8, 8, M, dyn._eps(), hmc=False, network_arch="generic", mask=dyn.mask.cpu().numpy(),
+                                    xnet={k: v.cpu().numpy() for k, v in dyn.position_fn.weights.items()},
+                                    vnet={k: v.cpu().numpy() for k, v in dyn.momentum_fn.weights.items()})
+            rng = np.random.default_rng(3)
+            dr = lambda: (rng.standard_normal((N, D)).astype(np.float32), rng.standard_normal((N, D)).astype(np.float32),
+                          rng.uniform(size=N).astype(np.float32), rng.uniform(size=N).astype(np.float32))
+            args = (od, state[0].cpu().numpy(), 2.0, dr(), rng.standard_normal((N, D)).astype(np.float32), dr())
+            tro.loss_and_grads(*args, **model.loss_weights)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                tro.loss_and_grads(*args, **model.loss_weights)
+            cpu_ms = (time.perf_counter() - t0) / 3 * 1e3
+            entry["cpu_baseline"] = {"value": N * D * M / (cpu_ms * 1e-3), "unit": "link-updates/s", "ms_per_step": cpu_ms,
+                                     "cores": os.cpu_count(), "kind": "port",
+                                     "sample": "3 loss-and-gradient evaluations of the same config-2 batch (torch "
+                                               "autograd through the oracle's transition; no optimiser step)"}
+        out[tag] = entry
+        del model, eng
+        torch.cuda.empty_cache()
+    return out
 
 
 def run_mog(c, events_ms, steps):
@@ -463,6 +491,7 @@ def main():
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
     r = run_gpu(args, rank, local_rank, world)
     e2e = None if args.no_e2e else run_e2e(r)
+    r["ctx"]["no_cpu"] = bool(args.no_cpu_baseline) or rank != 0
     l2hmc = None if args.no_l2hmc else run_l2hmc(r, args.steps)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
