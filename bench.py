@@ -169,6 +169,8 @@ def run_gpu(args, rank, local_rank, world):
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from l2hmc_b200.sharding import bind_to_gpu_numa
+    numa_cpus = bind_to_gpu_numa(local_rank) if world > 1 else None     # pinned e2e buffers on the GPU's own node
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.get_lib()                                   # fail loudly if the CUDA library is missing
@@ -275,7 +277,7 @@ def run_gpu(args, rank, local_rank, world):
     mc_gbs = mc_bytes / (mc_kernel_ms * 1e-3) / 1e9
     return dict(value=value, step_ms=step_ms, clk=clk, obs=obs, peak=peak, peak_kind=peak_kind,
                 lf=dict(ms=lf_ms, gbs=lf_gbs, bytes=lf_bytes), mc=dict(ms=mc_kernel_ms, gbs=mc_gbs, bytes=mc_bytes),
-                ctx=dict(dyn=dyn, dev=dev, N=N, K=K, W=W, barrier=barrier, max_over_ranks=max_over_ranks, x=xa,
+                ctx=dict(numa_cpus=numa_cpus, dyn=dyn, dev=dev, N=N, K=K, W=W, barrier=barrier, max_over_ranks=max_over_ranks, x=xa,
                          GaugeSampler=GaugeSampler, torch=torch, world=world))
 
 
@@ -302,6 +304,7 @@ def run_e2e(r):
     return {"value": c["world"] * N * D * M / (step_ms * 1e-3), "unit": "link-updates/s",
             "h2d_bytes_per_step": sampler.h2d_bytes, "d2h_bytes_per_step": sampler.d2h_bytes,
             "ms_per_step": step_ms, "launches_per_step": sampler.launches_per_step,
+            "host_cpus_bound": None if not c.get("numa_cpus") else len(c["numa_cpus"]),
             "plaq": float(res.plaqs.mean()), "charge_diff": res.charge_diff}
 
 

@@ -104,3 +104,26 @@ def allreduce_mean_(flat_grad, group=None):
         dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
         flat_grad /= ws
     return flat_grad
+
+
+def bind_to_gpu_numa(device_index):
+    """Pin this process to the CPUs NVML reports as local to its GPU, BEFORE pinned host buffers are allocated: the
+    pages then land on the GPU's NUMA node (first touch) and the per-step host<->device copies of every rank stop
+    sharing one socket's memory controller.  Returns the CPU list, or None when NVML / affinity is unavailable."""
+    import os
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(device_index).uuid)
+        handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cpus = [w * 64 + b for w, bits in enumerate(mask) for b in range(64) if (int(bits) >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None
