@@ -469,6 +469,16 @@ typedef struct {
 
 size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit);
 int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t workspace_bytes, void* stream);
+/* The same product on the tcgen05 tensor cores (3xTF32 split: hi.lo + lo.hi + hi.hi, fp32 accumulation flushed every
+ * 128 K into round-to-nearest register sums, so the result is fp32-accurate): both operands are first converted from
+ * their strided fp32 form into the tiled TS32 layout inside `workspace` (l2hmc_tc_gemm_workspace_bytes), any of the
+ * NN / NT / TN forms without a transposed copy; same epilogues as l2hmc_sgemm, written row-major. */
+size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g);
+int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t workspace_bytes, void* stream);
+/* What the training step calls: l2hmc_tc_gemm when the product is a dense contraction (M >= 128, N >= 64, K >= 128 and
+ * M*N*K >= 2.5e8), l2hmc_sgemm(ksplit) otherwise. */
+size_t l2hmc_gemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit);
+int l2hmc_gemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t workspace_bytes, void* stream);
 
 /* The four sub-updates (formulas of l2hmc_update_momentum / l2hmc_update_position) with a per-chain parameter set:
  * chains with row_set[n] != 0 use dir_alt / mask_alt / invert_alt (mixed-direction batches).  S, T, Q nullable

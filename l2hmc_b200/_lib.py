@@ -213,6 +213,10 @@ SIGNATURES = {
                               c_void_p],
     "l2hmc_sgemm_workspace_bytes": [POINTER(GemmArgs), c_int],
     "l2hmc_sgemm": [POINTER(GemmArgs), c_int, c_void_p, c_size_t, c_void_p],
+    "l2hmc_tc_gemm_workspace_bytes": [POINTER(GemmArgs)],
+    "l2hmc_tc_gemm": [POINTER(GemmArgs), c_void_p, c_size_t, c_void_p],
+    "l2hmc_gemm_workspace_bytes": [POINTER(GemmArgs), c_int],
+    "l2hmc_gemm": [POINTER(GemmArgs), c_int, c_void_p, c_size_t, c_void_p],
     "l2hmc_train_update_fwd": [c_int] + [c_void_p] * 7 + [c_int, c_void_p, c_int, c_void_p, c_float, c_int, c_int,
                                                          c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
     "l2hmc_mask_mul_sets": [c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p],
@@ -235,7 +239,8 @@ SIGNATURES = {
 }
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
-            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t}
+            "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t,
+            "l2hmc_tc_gemm_workspace_bytes": c_size_t, "l2hmc_gemm_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

@@ -32,6 +32,7 @@
 //   smem ring of 2-3 stages (A 32 KB + B BN*256 B), full/empty mbarriers; two accumulator stages in
 //   TMEM (tmem_full / tmem_empty), one per in-flight 128-wide K chunk.
 #include <cstdlib>
+#include <string>
 
 #include "common.cuh"
 #include "nets.cuh"
@@ -45,7 +46,7 @@ constexpr int kTcThreads = (kEpiWarps + 2) * 32;
 constexpr int TC_BM = 128;
 constexpr uint32_t kATileBytes = TC_BM * 32 * 4 * 2;   // 128 rows x 32 k x (hi, lo)
 
-enum TcMode { kTcLayer = 0, kTcHeadsStq = 1, kTcHeadsMomentum = 2, kTcHeadsPosition = 3 };
+enum TcMode { kTcLayer = 0, kTcHeadsStq = 1, kTcHeadsMomentum = 2, kTcHeadsPosition = 3, kTcPlain = 4 };
 
 struct TcParams {
   const float* A;      // TS32, a_rg row groups
@@ -82,6 +83,15 @@ struct TcParams {
   float* uout;
   float* ld_part;
   int32_t* flag;
+  // plain epilogue (kTcPlain): C[r][n] (=|+=) scale[n] * gate[r][n] * product, row-major fp32
+  float* C;
+  long long ldc;
+  int accumulate;
+  const float* gate;
+  long long ldg;
+  const float* cscale;
+  const float* cscale_alt;
+  int cinv, cinv_alt;
   int debug_noload;    // diagnostics (L2HMC_TC_DEBUG_NOLOAD=1): operand tiles are fetched only while the ring first
                        // fills; later K blocks re-use stale shared memory -> wrong numbers, pure MMA / epilogue timing
 };
@@ -252,7 +262,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
     }
   } else {
     // ===== epilogue (8 warps: TMEM lane quadrant = warp % 4, column half = warp / 4) =====
-    constexpr int NG = (MODE == kTcLayer) ? BN / 64 : 3;     // 32-column groups owned by this thread
+    constexpr bool kWide = MODE == kTcLayer || MODE == kTcPlain;   // thread owns half the tile's columns of its row
+    constexpr int NG = kWide ? BN / 64 : 3;                  // 32-column groups owned by this thread
     const int quad = warp & 3, half = warp >> 2;
     uint32_t acc = 0, acc_phase = 0;
     const int row_in_tile = quad * 32 + lane;
@@ -270,7 +281,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * kAccCols;
 #pragma unroll
         for (int g = 0; g < NG; ++g) {
-          const int col = (MODE == kTcLayer) ? half * (BN / 2) + g * 32 : g * 64 + half * 32;
+          const int col = kWide ? half * (BN / 2) + g * 32 : g * 64 + half * 32;
           float v[32];
           tmem_ld32(taddr + col, v);
           tmem_ld_wait();
@@ -283,7 +294,40 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         if (acc == 0) acc_phase ^= 1;
       }
       const bool alt = p.row_set != nullptr && r < p.rows && p.row_set[r] != 0;
-      if (MODE == kTcLayer) {
+      if (MODE == kTcPlain) {
+        if (r < p.rows) {
+          const float* cs = alt ? p.cscale_alt : p.cscale;
+          const int cinv = alt ? p.cinv_alt : p.cinv;
+#pragma unroll
+          for (int g = 0; g < NG; ++g) {
+            const int n0 = n_blk * BN + half * (BN / 2) + g * 32;
+            float* dst = p.C + static_cast<long long>(r) * p.ldc + n0;
+            const float* gt = p.gate ? p.gate + static_cast<long long>(r) * p.ldg + n0 : nullptr;
+#pragma unroll
+            for (int j4 = 0; j4 < 32; j4 += 4) {
+              float o[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int n = n0 + j4 + j;
+                float val = sum[g][j4 + j];
+                if (n < p.cols) {
+                  if (gt != nullptr && !(gt[j4 + j] > 0.f)) val = 0.f;
+                  if (cs != nullptr) val = __fmul_rn(val, cinv ? __fsub_rn(1.f, cs[n]) : cs[n]);
+                  if (p.accumulate) val = __fadd_rn(dst[j4 + j], val);
+                }
+                o[j] = val;
+              }
+              if (n0 + j4 + 3 < p.cols && ((reinterpret_cast<uintptr_t>(dst + j4) & 15u) == 0)) {
+                *reinterpret_cast<float4*>(dst + j4) = make_float4(o[0], o[1], o[2], o[3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (n0 + j4 + j < p.cols) dst[j4 + j] = o[j];
+              }
+            }
+          }
+        }
+      } else if (MODE == kTcLayer) {
         const int rg = r >> 3, r8 = r & 7;
         const float* bias = alt ? p.bias_alt : p.bias;
 #pragma unroll
@@ -650,6 +694,133 @@ extern "C" int l2hmc_net_pack(const l2hmc_net_weights* w, void* packed, size_t p
   ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_tr, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 1);
   ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_q, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 2);
   return check_launch("ts32_pack_weight_kernel");
+}
+
+// ------------------------------------------------------------------ general tcgen05 GEMM (training backward)
+namespace l2hmc {
+namespace {
+
+// strided fp32 operand -> TS32: element (r, k) = src[r * rs + k * cs]; rows >= `rows` and k >= K are zero; K blocks
+// [kb0, kb0 + nkb) of a buffer with rg_total row groups.  Serves A (rows = output rows) and B (rows = output columns)
+// in NN / NT / TN forms without a transposed copy.
+__global__ void __launch_bounds__(256) ts32_from_strided_kernel(const float* __restrict__ src, long long rs, long long cs,
+                                                                int rows, int K, float* dst, int rg_total, int kb0,
+                                                                int nkb) {
+  const size_t total = static_cast<size_t>(nkb) * rg_total * 64;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int r8 = static_cast<int>(i & 7), kc = static_cast<int>((i >> 3) & 7);
+    const size_t blk = i >> 6;
+    const int rg = static_cast<int>(blk % rg_total), kb = static_cast<int>(blk / rg_total);
+    const int r = rg * 8 + r8, k = kb * 32 + kc * 4;
+    float a[4] = {0.f, 0.f, 0.f, 0.f};
+    if (r < rows) {
+      const float* s = src + static_cast<long long>(r) * rs + static_cast<long long>(k) * cs;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (k + j < K) a[j] = s[j * cs];
+    }
+    float h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) h[j] = tf32_hi(a[j]), l[j] = tf32_lo(a[j], h[j]);
+    float* d = dst + ((static_cast<size_t>(kb0 + kb) * rg_total + rg) * 2) * 256 + kc * 32 + r8 * 4;
+    *reinterpret_cast<float4*>(d) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(d + 256) = make_float4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+struct TcGemmDims {
+  int rows_p, n_p, kb;
+  size_t a_floats, b_floats;
+};
+TcGemmDims tc_gemm_dims(const l2hmc_gemm_args* g) {
+  TcGemmDims d{};
+  d.rows_p = (g->M + 127) / 128 * 128;
+  d.n_p = (g->N + 255) / 256 * 256;
+  for (int s = 0; s < g->nseg; ++s) d.kb += (g->seg[s].K + 31) / 32;
+  d.a_floats = static_cast<size_t>(d.kb) * d.rows_p * 64;
+  d.b_floats = static_cast<size_t>(d.kb) * d.n_p * 64;
+  return d;
+}
+
+}  // namespace
+}  // namespace l2hmc
+
+extern "C" size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g) {
+  if (!g || g->nseg < 1 || g->nseg > 3 || g->M <= 0 || g->N <= 0) return 0;
+  const TcGemmDims d = tc_gemm_dims(g);
+  return sizeof(float) * (d.a_floats + d.b_floats) + 256;
+}
+
+extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t workspace_bytes, void* stream) {
+  L2HMC_REQUIRE(g, "l2hmc_tc_gemm: null arguments");
+  L2HMC_REQUIRE(g->M >= 0 && g->N >= 0 && g->nseg >= 1 && g->nseg <= 3, "l2hmc_tc_gemm: bad sizes M=%d N=%d nseg=%d", g->M,
+                g->N, g->nseg);
+  if (g->M == 0 || g->N == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(g->C, "l2hmc_tc_gemm: null C");
+  for (int s = 0; s < g->nseg; ++s)
+    L2HMC_REQUIRE(g->seg[s].A && g->seg[s].B && g->seg[s].K >= 0, "l2hmc_tc_gemm: bad segment %d", s);
+  if (g->row_set) L2HMC_REQUIRE(!g->col_scale == !g->col_scale_alt, "l2hmc_tc_gemm: col_scale and col_scale_alt go together");
+  L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_tc_gemm_workspace_bytes(g) && aligned16(workspace),
+                "l2hmc_tc_gemm: workspace too small or misaligned (%zu < %zu bytes)", workspace_bytes,
+                l2hmc_tc_gemm_workspace_bytes(g));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const TcGemmDims d = tc_gemm_dims(g);
+  float* a_ts = static_cast<float*>(workspace);
+  float* b_ts = a_ts + d.a_floats;
+  int kb0 = 0;
+  for (int s = 0; s < g->nseg; ++s) {
+    const l2hmc_gemm_seg& sg = g->seg[s];
+    const int nkb = (sg.K + 31) / 32;
+    if (nkb == 0) continue;
+    ts32_from_strided_kernel<<<ew_grid(static_cast<size_t>(nkb) * (d.rows_p / 8) * 64), 256, 0, st>>>(
+        sg.A, sg.a_rs, sg.a_cs, g->M, sg.K, a_ts, d.rows_p / 8, kb0, nkb);
+    // B operand rows are the output columns: element (n, k) = B[k * b_rs + n * b_cs]
+    ts32_from_strided_kernel<<<ew_grid(static_cast<size_t>(nkb) * (d.n_p / 8) * 64), 256, 0, st>>>(
+        sg.B, sg.b_cs, sg.b_rs, g->N, sg.K, b_ts, d.n_p / 8, kb0, nkb);
+    kb0 += nkb;
+  }
+  int rc = check_launch("ts32_from_strided_kernel");
+  if (rc) return rc;
+  if (d.kb == 0) {
+    set_error("l2hmc_tc_gemm: empty K");
+    return L2HMC_ERR_INVALID;
+  }
+  TcParams p{};
+  p.A = a_ts, p.a_rg = d.rows_p / 8, p.B = b_ts, p.b_rg = d.n_p / 8, p.KB = d.kb;
+  p.m_tiles = d.rows_p / 128;
+  p.rows = g->M, p.cols = g->N;
+  p.C = g->C, p.ldc = g->ldc, p.accumulate = g->accumulate, p.gate = g->relu_gate, p.ldg = g->ldg;
+  p.cscale = g->col_scale, p.cinv = g->col_scale_invert, p.row_set = g->row_set;
+  p.cscale_alt = g->col_scale_alt, p.cinv_alt = g->col_scale_invert_alt;
+  // few tiles: halve the N tile so more SMs take part
+  const bool narrow = p.m_tiles * ((g->N + 255) / 256) < 120;
+  p.n_tiles = narrow ? (g->N + 127) / 128 : (g->N + 255) / 256;
+  return narrow ? launch_tc<128, kTcPlain>(p, st) : launch_tc<256, kTcPlain>(p, st);
+}
+
+// Dispatch of the training GEMMs (north star: tensor cores only where the product is a dense contraction, FFMA
+// otherwise): tcgen05 3xTF32 when every dimension fills MMA tiles and the product is large enough to amortise the two
+// operand conversions; l2hmc_sgemm (ksplit as given) for the small-batch, M = 1 / M = 2 and ragged cases.
+// L2HMC_TRAIN_GEMM=ffma forces the FFMA kernel (diagnostics).
+static bool gemm_wants_tc(const l2hmc_gemm_args* g) {
+  static const bool force_ffma = getenv("L2HMC_TRAIN_GEMM") && std::string(getenv("L2HMC_TRAIN_GEMM")) == "ffma";
+  if (force_ffma || g->M < 128 || g->N < 64) return false;
+  long long k = 0;
+  for (int s = 0; s < g->nseg; ++s) k += g->seg[s].K;
+  if (k < 128) return false;
+  return static_cast<double>(g->M) * g->N * static_cast<double>(k) >= 2.5e8;
+}
+
+extern "C" size_t l2hmc_gemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {
+  if (!g || g->nseg < 1 || g->nseg > 3 || g->M <= 0 || g->N <= 0) return 0;
+  return gemm_wants_tc(g) ? l2hmc_tc_gemm_workspace_bytes(g) : l2hmc_sgemm_workspace_bytes(g, ksplit);
+}
+
+extern "C" int l2hmc_gemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t workspace_bytes, void* stream) {
+  L2HMC_REQUIRE(g && g->nseg >= 1 && g->nseg <= 3, "l2hmc_gemm: bad arguments");
+  if (g->M > 0 && g->N > 0 && gemm_wants_tc(g)) return l2hmc_tc_gemm(g, workspace, workspace_bytes, stream);
+  return l2hmc_sgemm(g, ksplit, workspace, workspace_bytes, stream);
 }
 
 // Diagnostic: C = relu(A . W) through the tensor-core layer kernel and the TS32 converters

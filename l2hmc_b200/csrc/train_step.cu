@@ -120,9 +120,16 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
     size_t gw = 0;
     for (const l2hmc_net_weights* w : {a->xnet, a->vnet}) {
       const int K = static_cast<int>(Rt);
-      auto need = [&](int Mm, int Nn) { gw = std::max(gw, sizeof(float) * ksplit_for(Mm, Nn, K) * Mm * static_cast<size_t>(Nn)); };
-      need(w->H, w->D), need(1, w->D), need(w->H, w->H), need(1, w->H), need(w->K, w->H), need(2, w->H);
-      gw = std::max(gw, sizeof(float) * 8 * R * static_cast<size_t>(std::max(w->H, std::max(w->K, w->D))));   // per-call GEMMs, auto split <= 8
+      auto need = [&](int Mm, int Nn, int nseg, int Kk, int ksplit) {     // what l2hmc_gemm will ask for this shape
+        l2hmc_gemm_args g{};
+        g.M = Mm, g.N = Nn, g.nseg = nseg;
+        for (int s = 0; s < nseg; ++s) g.seg[s].K = Kk;
+        gw = std::max(gw, l2hmc_gemm_workspace_bytes(&g, ksplit));
+      };
+      auto deferred = [&](int Mm, int Nn) { need(Mm, Nn, 1, K, ksplit_for(Mm, Nn, K)); };
+      deferred(w->H, w->D), deferred(1, w->D), deferred(w->H, w->H), deferred(1, w->H), deferred(w->K, w->H);
+      deferred(2, w->H);
+      need(pl.R, w->H, 3, w->D, 0), need(pl.R, w->H, 1, w->H, 0), need(pl.R, w->K, 1, w->H, 0);   // per-call GEMMs
     }
     pl.gemm_ws_bytes = gw;
     pl.gemm_ws = c.take<char>(gw);
@@ -158,7 +165,7 @@ int gemm(const Ctx& c, int M, int N, std::initializer_list<l2hmc_gemm_seg> segs,
   g.C = C, g.ldc = ldc, g.accumulate = accumulate, g.relu_gate = gate, g.ldg = ldg;
   g.col_scale = cs, g.col_scale_invert = inv;
   g.row_set = sets ? c.pl.row_set : nullptr, g.col_scale_alt = cs_alt, g.col_scale_invert_alt = inv_alt;
-  return l2hmc_sgemm(&g, ksplit, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.stream);
+  return l2hmc_gemm(&g, ksplit, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.stream);
 }
 
 int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long ldc, int accumulate = 0, int ksplit = 0) {

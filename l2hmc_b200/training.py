@@ -34,7 +34,7 @@ def _ptr(t, offset=0):
 
 
 class _Gemm(object):
-    """Thin caller of l2hmc_sgemm with a cached split-K workspace."""
+    """Thin caller of l2hmc_gemm (tcgen05 for dense contractions, FFMA otherwise) with a cached workspace."""
 
     def __init__(self, device):
         self.device = device
@@ -55,12 +55,12 @@ class _Gemm(object):
         a.col_scale_alt, a.col_scale_invert_alt = col_scale_alt, int(bool(invert_alt))
         lib = _lib.get_lib()
         ws = None
-        need = int(lib.l2hmc_sgemm_workspace_bytes(ctypes.byref(a), int(ksplit)))     # ksplit = 0: the library chooses
+        need = int(lib.l2hmc_gemm_workspace_bytes(ctypes.byref(a), int(ksplit)))      # ksplit = 0: the library chooses
         if need:
             if self._ws is None or self._ws.numel() * 4 < need:
                 self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=self.device)
             ws = _ptr(self._ws)
-        _lib.check(lib.l2hmc_sgemm(ctypes.byref(a), int(ksplit), ws, need, _lib.stream_ptr()))
+        _lib.check(lib.l2hmc_gemm(ctypes.byref(a), int(ksplit), ws, need, _lib.stream_ptr()))
         self.launches += 2 if need else 1
 
 

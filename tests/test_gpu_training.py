@@ -511,3 +511,63 @@ def test_native_step_equals_python_walk(golden):
             va, vb = model.engine.params.view(flat_a, name), model.engine.params.view(flat_b, name)
             assert torch.equal(va, vb), f"{tag} {name}"
     assert seen == {"hmc", "generic", "conv3D"}
+
+
+# --------------------------------------------------------------------------------------------- tcgen05 training GEMM
+def _tc_gemm(M, N, segs, C, ldc, **kw):
+    """l2hmc_tc_gemm through ctypes (same argument struct as l2hmc_sgemm)."""
+    from l2hmc_b200 import _lib
+    a = _lib.GemmArgs()
+    a.M, a.N, a.nseg = M, N, len(segs)
+    for i, (A, a_rs, a_cs, B, b_rs, b_cs, K) in enumerate(segs):
+        s = a.seg[i]
+        s.A, s.a_rs, s.a_cs, s.B, s.b_rs, s.b_cs, s.K = A, a_rs, a_cs, B, b_rs, b_cs, K
+    a.C, a.ldc, a.accumulate = C, ldc, int(kw.get("accumulate", False))
+    a.relu_gate, a.ldg = kw.get("relu_gate"), kw.get("ldg", 0)
+    a.col_scale, a.col_scale_invert = kw.get("col_scale"), int(kw.get("invert", False))
+    a.row_set, a.col_scale_alt, a.col_scale_invert_alt = kw.get("row_set"), kw.get("col_scale_alt"), int(kw.get("invert_alt", False))
+    lib = _lib.get_lib()
+    need = int(lib.l2hmc_tc_gemm_workspace_bytes(ctypes.byref(a)))
+    ws = torch.empty(need // 4 + 64, device="cuda")
+    _lib.check(lib.l2hmc_tc_gemm(ctypes.byref(a), ctypes.c_void_p(ws.data_ptr()), need, None))
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("M,N,K,ta,tb", [(256, 512, 384, False, True), (130, 70, 100, False, False), (512, 1024, 4096, True, False),
+                                         (1024, 512, 333, True, True), (4096, 1024, 512, False, True), (128, 64, 128, False, True)])
+def test_tc_gemm_forms(M, N, K, ta, tb):
+    """The tcgen05 3xTF32 product in NN / NT / TN forms against a float64 product: fp32-level accuracy (2e-6 of scale)."""
+    from l2hmc_b200 import _lib
+    from l2hmc_b200.training import _ptr
+    rng = np.random.default_rng(M + 3 * N + K)
+    A = rng.standard_normal((K, M) if ta else (M, K)).astype(np.float32)
+    B = rng.standard_normal((N, K) if tb else (K, N)).astype(np.float32)
+    ref = (A.T if ta else A).astype(np.float64) @ (B.T if tb else B).astype(np.float64)
+    dA, dB = cu(A), cu(B)
+    a_rs, a_cs = (1, M) if ta else (K, 1)
+    b_rs, b_cs = (1, K) if tb else (N, 1)
+    C = torch.full((M, N), 7.0, device="cuda")
+    _tc_gemm(M, N, [(_ptr(dA), a_rs, a_cs, _ptr(dB), b_rs, b_cs, K)], _ptr(C), N)
+    close_scaled(C, ref, 2e-6, "tc gemm")
+    C0 = rng.standard_normal((M, N)).astype(np.float32)
+    gate = rng.standard_normal((M, N)).astype(np.float32)
+    m0, m1 = (rng.uniform(size=N) > 0.5).astype(np.float32), (rng.uniform(size=N) > 0.5).astype(np.float32)
+    rows = (rng.uniform(size=M) > 0.5).astype(np.uint8)
+    want = C0 + ref * (gate > 0) * np.where(rows[:, None] != 0, 1 - m1[None, :], m0[None, :])
+    C, tg, t0, t1, tr = cu(C0), cu(gate), cu(m0), cu(m1), cu(rows, torch.uint8)
+    _tc_gemm(M, N, [(_ptr(dA), a_rs, a_cs, _ptr(dB), b_rs, b_cs, K)], _ptr(C), N, accumulate=True, relu_gate=_ptr(tg), ldg=N,
+             col_scale=_ptr(t0), invert=False, row_set=_lib.dptr(tr, torch.uint8), col_scale_alt=_ptr(t1), invert_alt=True)
+    close_scaled(C, want, 2e-6, "tc gemm epilogue")
+
+
+def test_tc_gemm_three_segments():
+    from l2hmc_b200.training import _ptr
+    rng = np.random.default_rng(8)
+    R, D, H = 300, 80, 200
+    dA = rng.standard_normal((R, 3 * D)).astype(np.float32)
+    Ws = [rng.standard_normal((H, D)).astype(np.float32) for _ in range(3)]
+    ref = sum(dA[:, s * D:(s + 1) * D].astype(np.float64) @ Ws[s].T.astype(np.float64) for s in range(3))
+    tA, tW = cu(dA), [cu(w) for w in Ws]
+    C = torch.empty(R, H, device="cuda")
+    _tc_gemm(R, H, [(_ptr(tA, s * D), 3 * D, 1, _ptr(tW[s]), 1, D, D) for s in range(3)], _ptr(C), H)
+    close_scaled(C, ref, 2e-6, "tc 3-segment gemm")
