@@ -243,9 +243,8 @@ typedef struct {
   int dir_alt;                 /* +1 / -1 */
   const float* mask_alt;       /* POSITION: mask row [D] */
   int mask_invert_alt;
-  /* Training tape (FFMA path only, L2HMC_ERR_UNSUPPORTED with L2HMC_NET_PATH_TCGEN05): when given, the hidden
-     activations h1 / h2 [N,H] (after the ReLU) are written here instead of the workspace and survive the call,
-     for the backward pass of l2hmc_sgemm / l2hmc_update_bwd.  Nullable, together. */
+  /* Training tape: when given, the hidden activations h1 / h2 [N,H] (after the ReLU, row-major fp32) are written
+     here and survive the call, for the backward pass (l2hmc_gemm / l2hmc_update_bwd).  Nullable, together. */
   float *h1_out, *h2_out;
 } l2hmc_net_call;
 

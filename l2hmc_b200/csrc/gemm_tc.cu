@@ -650,6 +650,13 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
     logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, 2 * d.d_tiles, N, c->logdet);
     rc = check_launch("logdet_reduce_tc_kernel");
   }
+  if (rc == L2HMC_OK && c->h1_out != nullptr) {
+    // training tape: the hidden activations back in row-major fp32 (hi + lo is the fp32 value up to 2^-22; its
+    // sign, i.e. the ReLU mask the backward pass reads, is exact)
+    ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(N) * H), 256, 0, st>>>(h1, rg, N, H, c->h1_out);
+    ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(N) * H), 256, 0, st>>>(h2, rg, N, H, c->h2_out);
+    rc = check_launch("ts32_to_rowmajor_kernel");
+  }
   return rc;
 }
 

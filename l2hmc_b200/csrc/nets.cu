@@ -393,10 +393,6 @@ int net_validate(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
       return L2HMC_ERR_INVALID;
   }
   L2HMC_REQUIRE((c->h1_out == nullptr) == (c->h2_out == nullptr), "l2hmc_net_run: h1_out and h2_out go together");
-  if (c->h1_out != nullptr && c->path == L2HMC_NET_PATH_TCGEN05) {
-    set_error("l2hmc_net_run: the training tape (h1_out / h2_out) is written by the FFMA path only");
-    return L2HMC_ERR_UNSUPPORTED;
-  }
   if (c->row_set != nullptr) {
     L2HMC_REQUIRE((c->in1_mask == nullptr) == (c->in1_mask_alt == nullptr),
                   "l2hmc_net_run: in1_mask and in1_mask_alt must be given together");
@@ -424,7 +420,6 @@ extern "C" int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* c
   if (rc != L2HMC_OK || c->N == 0) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (c->path == L2HMC_NET_PATH_FFMA) return net_run_simt(w, c, st);
-  if (c->h1_out != nullptr) return net_run_simt(w, c, st);
   const bool tc = c->path == L2HMC_NET_PATH_TCGEN05 ? tc_supported(w, c) : tc_eligible(w, c);
   if (c->path == L2HMC_NET_PATH_TCGEN05 && !tc) {
     set_error("l2hmc_net_run: shape K=%d H=%d D=%d N=%d (packed=%p) has no tcgen05 path", w->K, w->H, w->D, c->N,

@@ -70,6 +70,9 @@ struct Plan {
   NetTape xt, vt;
   void* net_ws;
   size_t net_ws_bytes;
+  void *xpack, *vpack;   // TS32 copies of the dense weights (tcgen05 forward), re-packed every step
+  size_t xpack_bytes, vpack_bytes;
+  bool tc_forward;
   float *fg0, *fg1;
   float* part[4];        // conv partial rows: XNet.x, XNet.v, VNet.x, VNet.v
   int prow, pcol;
@@ -117,6 +120,15 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
     pl.net_ws_bytes = std::max(l2hmc_net_workspace_bytes(a->xnet->K, a->xnet->H, a->xnet->D, pl.R),
                                l2hmc_net_workspace_bytes(a->vnet->K, a->vnet->H, a->vnet->D, pl.R));
     pl.net_ws = c.take<char>(pl.net_ws_bytes);
+    // forward layers on tcgen05 when the stacked batch fills MMA tiles (same rule as l2hmc_net_run's AUTO path, from
+    // 1024 rows: below that the FFMA layers are as fast and the step is launch-bound anyway)
+    auto fits = [](const l2hmc_net_weights* w) { return w->K >= 64 && w->H >= 128 && w->D >= 64 && w->D % 16 == 0; };
+    pl.tc_forward = pl.R >= 1024 && fits(a->xnet) && fits(a->vnet);
+    if (pl.tc_forward) {
+      pl.xpack_bytes = l2hmc_net_pack_bytes(a->xnet->K, a->xnet->H, a->xnet->D);
+      pl.vpack_bytes = l2hmc_net_pack_bytes(a->vnet->K, a->vnet->H, a->vnet->D);
+      pl.xpack = c.take<char>(pl.xpack_bytes), pl.vpack = c.take<char>(pl.vpack_bytes);
+    }
     size_t gw = 0;
     for (const l2hmc_net_weights* w : {a->xnet, a->vnet}) {
       const int K = static_cast<int>(Rt);
@@ -172,11 +184,12 @@ int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long
   return gemm(c, M, N, {s}, C, ldc, accumulate, nullptr, 0, nullptr, 0, nullptr, 0, false, ksplit);
 }
 
-int net_forward(const Ctx& c, const l2hmc_net_weights* w, NetTape& t, int j, const float* tau, const float* tau_alt) {
+int net_forward(const Ctx& c, const l2hmc_net_weights* w, const void* packed, NetTape& t, int j, const float* tau,
+                const float* tau_alt) {
   const Plan& pl = c.pl;
   const size_t R = pl.R, off = static_cast<size_t>(j) * R;
   l2hmc_net_weights ww = *w;
-  ww.packed = nullptr;
+  ww.packed = packed;
   l2hmc_net_call n{};
   n.mode = L2HMC_NET_STQ;
   n.in0 = t.in0 + off * t.K, n.in1 = t.in1 + off * t.K;
@@ -184,7 +197,8 @@ int net_forward(const Ctx& c, const l2hmc_net_weights* w, NetTape& t, int j, con
   n.row_set = pl.row_set, n.dir = n.dir_alt = 1, n.N = pl.R;
   n.S = t.S + off * t.D, n.T = t.T + off * t.D, n.Q = t.Q + off * t.D;
   n.h1_out = t.h1 + off * t.H, n.h2_out = t.h2 + off * t.H;
-  n.workspace = pl.net_ws, n.workspace_bytes = pl.net_ws_bytes, n.path = L2HMC_NET_PATH_FFMA;
+  n.workspace = pl.net_ws, n.workspace_bytes = pl.net_ws_bytes;
+  n.path = packed ? L2HMC_NET_PATH_TCGEN05 : L2HMC_NET_PATH_FFMA;
   L2HMC_TRY(l2hmc_net_run(&ww, &n, c.stream));
   tau_rows_kernel<<<(pl.R + 255) / 256, 256, 0, c.st>>>(pl.row_set, tau[0], tau[1], tau_alt[0], tau_alt[1], pl.R,
                                                          t.tau1 + off * 3);
@@ -304,6 +318,10 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
   pick_rows_kernel<<<R, 128, 0, st>>>(a->v_f, a->v_b, pl.row_set, D, Vs(0));
   L2HMC_TRY(check_launch("pick_rows_kernel"));
   cudaMemsetAsync(pl.sld, 0, R * sizeof(float), st);
+  if (nets && pl.tc_forward) {      // the weights moved since the last step: refresh their TS32 copies
+    L2HMC_TRY(l2hmc_net_pack(a->xnet, pl.xpack, pl.xpack_bytes, stream));
+    L2HMC_TRY(l2hmc_net_pack(a->vnet, pl.vpack, pl.vpack_bytes, stream));
+  }
   struct Rec { int kind, j, xi, vi, inv, inv_alt, step, ib; float* g; };
   std::vector<Rec> recs;
   recs.reserve(4 * M);
@@ -330,7 +348,7 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           } else {
             L2HMC_TRY(copy(t.in0 + off * t.K, Xs(xi), RD));
           }
-          L2HMC_TRY(net_forward(c, a->vnet, t, jv, tau, tau_alt));
+          L2HMC_TRY(net_forward(c, a->vnet, pl.tc_forward ? pl.vpack : nullptr, t, jv, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
         L2HMC_TRY(l2hmc_train_update_fwd(0, nullptr, Vs(vi), g, S, Tr, Q, nullptr, 0, nullptr, 0, pl.row_set, eps, 1, -1, R,
@@ -351,7 +369,7 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
             L2HMC_TRY(l2hmc_mask_mul_sets(Xs(xi), row_f, invs[q], row_b, invs_alt[q], pl.row_set, R, D, t.in1 + off * t.K,
                                           stream));
           }
-          L2HMC_TRY(net_forward(c, a->xnet, t, jx, tau, tau_alt));
+          L2HMC_TRY(net_forward(c, a->xnet, pl.tc_forward ? pl.xpack : nullptr, t, jx, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
         L2HMC_TRY(l2hmc_train_update_fwd(1, Xs(xi), Vs(vi), nullptr, S, Tr, Q, row_f, invs[q], row_b, invs_alt[q], pl.row_set,

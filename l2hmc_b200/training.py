@@ -149,6 +149,7 @@ class TrainEngine(object):
         self.params = FlatParams(dynamics)
         self.gemm = _Gemm(self.device)
         self._tapes, self._structs = {}, {}
+        self._tc_forward = False
         self._scratch = torch.empty(1024, dtype=torch.float32, device=self.device)
         self.launches = 0
 
@@ -190,6 +191,28 @@ class TrainEngine(object):
             self._structs[key] = s
         return self._structs[key]
 
+    def _pack_for_forward(self, R):
+        """Forward layers on tcgen05 when the stacked batch has >= 1024 rows and the shapes tile (the rule of
+        csrc/train_step.cu): refresh the TS32 copies of the dense weights, which moved since the last step."""
+        dyn, lib = self.dyn, _lib.get_lib()
+        nets = (dyn.position_fn, dyn.momentum_fn)
+        fits = lambda n: n.num_features >= 64 and n.num_hidden >= 128 and n.x_dim >= 64 and n.x_dim % 16 == 0
+        if R < 1024 or not all(fits(n) for n in nets):
+            return False
+        if not hasattr(self, "_packed_structs"):
+            self._packed_structs, self._packed_bufs = {}, {}
+        for net in nets:
+            base = self._net_struct(net)
+            nbytes = int(lib.l2hmc_net_pack_bytes(base.K, base.H, base.D))
+            if id(net) not in self._packed_bufs:
+                self._packed_bufs[id(net)] = torch.empty((nbytes + 3) // 4, dtype=torch.float32, device=self.device)
+                s = _lib.NetWeights()
+                ctypes.memmove(ctypes.byref(s), ctypes.byref(base), ctypes.sizeof(s))
+                s.packed = _lib.dptr(self._packed_bufs[id(net)])
+                self._packed_structs[id(net)] = s
+            _lib.check(lib.l2hmc_net_pack(base, _lib.dptr(self._packed_bufs[id(net)]), nbytes, _lib.stream_ptr()))
+        return True
+
     def _net_forward(self, net, tape, j, R, tau, tau_alt, row_set):
         lib = _lib.get_lib()
         c = _lib.NetCall()
@@ -204,8 +227,12 @@ class TrainEngine(object):
         c.h1_out, c.h2_out = _ptr(tape.h1[j]), _ptr(tape.h2[j])
         ws, need = net._workspace(R)
         c.workspace, c.workspace_bytes = _lib.dptr(ws), need
+        struct = self._net_struct(net)
         c.path = _lib.NET_PATH_FFMA
-        _lib.check(lib.l2hmc_net_run(self._net_struct(net), c, _lib.stream_ptr()))
+        if self._tc_forward:              # tcgen05 layers; h1 / h2 come back row-major for the tape
+            struct = self._packed_structs[id(net)]
+            c.path = _lib.NET_PATH_TCGEN05
+        _lib.check(lib.l2hmc_net_run(struct, c, _lib.stream_ptr()))
         self.launches += 3
         # (cos, sin, 1) rows of this call: the t_layer input of each chain
         t0 = torch.tensor([tau[0], tau[1], 1.], dtype=torch.float32, device=self.device)
@@ -347,6 +374,7 @@ class TrainEngine(object):
         self._call(lib.l2hmc_mh_select, _lib.dptr(v_f), _lib.dptr(v_f), _lib.dptr(v_b), None, None, _lib.dptr(ones),
                    _lib.dptr(ones), _lib.dptr(u_dir), None, R, D, 0, _lib.dptr(v0), None, None, None, None)
         tapes = {n: self._tape(n, R) for n in ("XNet", "VNet")} if nets else {}
+        self._tc_forward = nets and self._pack_for_forward(R)
         sld = torch.zeros(R, dtype=torch.float32, device=self.device)
         flag = dyn._flag
         calls, jx, jv = [], 0, 0

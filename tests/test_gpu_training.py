@@ -571,3 +571,40 @@ def test_tc_gemm_three_segments():
     C = torch.empty(R, H, device="cuda")
     _tc_gemm(R, H, [(_ptr(tA, s * D), 3 * D, 1, _ptr(tW[s]), 1, D, D) for s in range(3)], _ptr(C), H)
     close_scaled(C, ref, 2e-6, "tc 3-segment gemm")
+
+
+def test_training_step_with_tcgen05_layers():
+    """From 1024 stacked rows the forward layers and the dense backward products run on tcgen05 (3xTF32): native and
+    Python-driven walks stay bit-identical, and the gradients match autodiff through the CPU oracle."""
+    import l2hmc_b200 as pkg
+    from l2hmc_b200.gauge_model import GaugeModel
+    T, X, N, M, eps, beta = 8, 8, 512, 2, 0.15, 2.5
+    D = 2 * T * X
+    rng = np.random.default_rng(77)
+    weights = {net: orc.init_net_weights("generic", T, X, f, rng) for net, f in (("XNet", 2.), ("VNet", 1.))}
+    mask = orc.construct_masks(D, M)
+    x = rng.uniform(0, 2 * np.pi, (N, D)).astype(np.float32)
+    z = rng.standard_normal((N, D)).astype(np.float32)
+    dr = lambda: (rng.standard_normal((N, D)).astype(np.float32), rng.standard_normal((N, D)).astype(np.float32),
+                  rng.uniform(size=N).astype(np.float32), rng.uniform(size=N).astype(np.float32))
+    draws_x, draws_z = dr(), dr()
+    lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
+    dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch="generic", num_steps=M, eps=eps, weights=weights)
+    dyn.set_masks(mask)
+    model = GaugeModel(dict(time_size=T, space_size=X, num_samples=N), lattice=lat, dynamics=dyn)
+    model.native_train = False
+    loss_a, _, _, px_a, _ = model._calc_loss_and_grads(x, beta, draws_x=draws_x, z=z, draws_z=draws_z)
+    assert model.engine._tc_forward
+    flat_a = model.engine.params.grad.clone()
+    model.native_train = True
+    loss_b, grads, _, px_b, _ = model._calc_loss_and_grads(x, beta, draws_x=draws_x, z=z, draws_z=draws_z)
+    torch.cuda.synchronize()
+    assert float(loss_a) == float(loss_b) and torch.equal(px_a, px_b)
+    for name in model.engine.params.names:
+        assert torch.equal(model.engine.params.view(flat_a, name), model.engine.params.view(model.engine.params.grad, name)), name
+    od = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch="generic", mask=mask, xnet=weights["XNet"],
+                            vnet=weights["VNet"])
+    ref_loss, ref = tro.loss_and_grads(od, x, beta, draws_x, z, draws_z, aux_weight=1., std_weight=1., charge_weight=1.)
+    assert abs(float(loss_b) - float(ref_loss)) <= 2e-3 * max(1., abs(float(ref_loss)))
+    for name, gr in grads.items():
+        close_scaled(gr, ref[name], 5e-4, f"tcgen05 step d loss / d {name}")
