@@ -40,7 +40,9 @@ template <int FT>
 __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParams p) {
   extern __shared__ __align__(16) float sm[];
   const int T = p.T, X = p.X, F = FT > 0 ? FT : p.F, C2 = 2 * F;
-  const int FP = F + 1, CP = C2 + 1;   // padded row strides: lanes that walk rows hit distinct banks
+  constexpr bool kFast = FT > 0 && FT % 8 == 0;   // register-tiled phases with 128-bit shared loads
+  // padded row strides: lanes that walk rows hit distinct banks (+4 keeps float4 alignment on the fast path)
+  const int FP = kFast ? F + 4 : F + 1, CP = kFast ? C2 + 4 : C2 + 1;
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, T4 = (T2 + 1) / 2, X4 = (X2 + 1) / 2;
   const int D = 2 * T * X, K = T4 * X4 * C2;
   float* in_s = sm;                       // [T][X][2] (masked input)
@@ -72,6 +74,38 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     }
     __syncthreads();
     // ---- forward, recomputed
+    if (kFast) {       // thread = (site, 4 filters): both mu outputs, weights as float4
+      for (int i = tid; i < T * X * (F / 4); i += kThreads) {
+        const int f4 = (i % (F / 4)) * 4, site = i / (F / 4), t = site / X, x = site - t * X;
+        float o0[4], o1[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o0[j] = o1[j] = p.b1[f4 + j];
+#pragma unroll
+        for (int kt = 0; kt < 3; ++kt) {
+          const int tt = t + kt - 1;
+          if (tt < 0 || tt >= T) continue;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int xx = x + kx - 1;
+            if (xx < 0 || xx >= X) continue;
+            const float in0 = in_s[(tt * X + xx) * 2], in1 = in_s[(tt * X + xx) * 2 + 1];
+            const float4 w0 = *reinterpret_cast<const float4*>(w1s + ((kt * 3 + kx) * 2) * F + f4);
+            const float4 w1 = *reinterpret_cast<const float4*>(w1s + ((kt * 3 + kx) * 2 + 1) * F + f4);
+            const float a0[4] = {w0.x, w0.y, w0.z, w0.w}, a1[4] = {w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              o0[j] = fmaf(in0, a0[j], o0[j]);       // mu = 0: taps kd = 0 (mu 0) and kd = 1 (mu 1)
+              o0[j] = fmaf(in1, a1[j], o0[j]);
+              o1[j] = fmaf(in1, a0[j], o1[j]);       // mu = 1: kd = 0 only (kd = 1 is padding)
+            }
+          }
+        }
+        *reinterpret_cast<float4*>(c1 + (site * 2) * FP + f4) =
+            make_float4(fmaxf(o0[0], 0.f), fmaxf(o0[1], 0.f), fmaxf(o0[2], 0.f), fmaxf(o0[3], 0.f));
+        *reinterpret_cast<float4*>(c1 + (site * 2 + 1) * FP + f4) =
+            make_float4(fmaxf(o1[0], 0.f), fmaxf(o1[1], 0.f), fmaxf(o1[2], 0.f), fmaxf(o1[3], 0.f));
+      }
+    } else
     for (int i = tid; i < D * F; i += kThreads) {
       const int f = i % F, pos = i / F, d = pos & 1, site = pos >> 1, t = site / X, x = site - t * X;
       float acc = p.b1[f];
@@ -104,6 +138,34 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       p1[i] = best;
     }
     __syncthreads();
+    if (kFast) {       // thread = (position, 4 output channels)
+      for (int i = tid; i < T2 * X2 * (C2 / 4); i += kThreads) {
+        const int co4 = (i % (C2 / 4)) * 4, pos = i / (C2 / 4), x = pos % X2, t = pos / X2;
+        float acc[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[j] = p.b2[co4 + j];
+        for (int kt = 0; kt < 2; ++kt)
+          for (int kx = 0; kx < 2; ++kx) {
+            const int tt = t + kt, xx = x + kx;
+            if (tt >= T2 || xx >= X2) continue;
+            const float* a = p1 + (tt * X2 + xx) * F;
+            const float* w = w2s + ((kt * 2 + kx) * F) * CP + co4;
+#pragma unroll
+            for (int c4 = 0; c4 < F; c4 += 4) {
+              const float4 av = *reinterpret_cast<const float4*>(a + c4);
+              const float aa[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 wv = *reinterpret_cast<const float4*>(w + (c4 + q) * CP);
+                acc[0] = fmaf(aa[q], wv.x, acc[0]), acc[1] = fmaf(aa[q], wv.y, acc[1]);
+                acc[2] = fmaf(aa[q], wv.z, acc[2]), acc[3] = fmaf(aa[q], wv.w, acc[3]);
+              }
+            }
+          }
+        *reinterpret_cast<float4*>(c2 + pos * C2 + co4) =
+            make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+      }
+    } else
     for (int i = tid; i < T2 * X2 * C2; i += kThreads) {
       const int co = i % C2, x = (i / C2) % X2, t = i / (C2 * X2);
       float acc = p.b2[co];
@@ -143,6 +205,30 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     }
     __syncthreads();
     // ---- conv-2: weight / bias gradients (kd = 0 taps), input gradient
+    if (kFast) {       // thread = (tap, output channel, 8 input channels): one gradient load feeds 8 FMAs
+      for (int i = tid; i < 4 * C2 * (F / 8); i += kThreads) {
+        const int co = i % C2, ci0 = ((i / C2) % (F / 8)) * 8, kk = i / (C2 * (F / 8)), kt = kk >> 1, kx = kk & 1;
+        float s8[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s8[j] = 0.f;
+        for (int t = 0; t + kt < T2; ++t) {
+          const float* a = p1 + ((t + kt) * X2 + kx) * F + ci0;
+          const float* g = c2 + (t * X2) * C2 + co;
+          const int nx = X2 - kx;
+#pragma unroll 2
+          for (int x = 0; x < nx; ++x) {
+            const float gv = g[x * C2];
+            const float4 a0 = *reinterpret_cast<const float4*>(a + x * F);
+            const float4 a1 = *reinterpret_cast<const float4*>(a + x * F + 4);
+            s8[0] = fmaf(a0.x, gv, s8[0]), s8[1] = fmaf(a0.y, gv, s8[1]), s8[2] = fmaf(a0.z, gv, s8[2]);
+            s8[3] = fmaf(a0.w, gv, s8[3]), s8[4] = fmaf(a1.x, gv, s8[4]), s8[5] = fmaf(a1.y, gv, s8[5]);
+            s8[6] = fmaf(a1.z, gv, s8[6]), s8[7] = fmaf(a1.w, gv, s8[7]);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) part[off_w2 + ((kk * 2 + 0) * F + ci0 + j) * C2 + co] += s8[j];
+      }
+    } else
     for (int i = tid; i < 4 * F * C2; i += kThreads) {
       const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F), kt = kk >> 1, kx = kk & 1;
       float s = 0.f;
@@ -167,8 +253,17 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
         for (int kx = 0; kx < 2 && kx <= x; ++kx) {
           const float* g = c2 + ((t - kt) * X2 + x - kx) * C2;
           const float* w = w2s + ((kt * 2 + kx) * F + ci) * CP;
+          if (kFast) {
+#pragma unroll
+            for (int c4 = 0; c4 < C2; c4 += 4) {
+              const float4 wv = *reinterpret_cast<const float4*>(w + c4);
+              const float4 gv = *reinterpret_cast<const float4*>(g + c4);
+              s = fmaf(wv.x, gv.x, s), s = fmaf(wv.y, gv.y, s), s = fmaf(wv.z, gv.z, s), s = fmaf(wv.w, gv.w, s);
+            }
+          } else {
 #pragma unroll 8
-          for (int co = 0; co < C2; ++co) s = fmaf(w[co], g[co], s);
+            for (int co = 0; co < C2; ++co) s = fmaf(w[co], g[co], s);
+          }
         }
       gp1[i] = s;
     }
@@ -200,6 +295,48 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     }
     __syncthreads();
     // ---- conv-1: weight / bias gradients, input gradient
+    if (kFast) {
+      // thread = (row slab, tap, 4 filters): both kd entries from one pass over the slab's outputs; the slabs'
+      // partial sums meet in the (now free) conv-2 buffers and are added in slab order
+      int S = 1;
+      while (S * 2 <= 8 && T % (S * 2) == 0 && (S * 2) * 18 * F <= T2 * X2 * (C2 + F)) S *= 2;
+      float* scratch = c2;
+      const int rows_per = T / S;
+      for (int i = tid; i < S * 9 * (F / 4); i += kThreads) {
+        const int f4 = (i % (F / 4)) * 4, tap = (i / (F / 4)) % 9, slab = i / ((F / 4) * 9), kt = tap / 3, kx = tap - 3 * kt;
+        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+        const int t_lo = max(kt == 0 ? 1 : 0, slab * rows_per), t_hi = min(kt == 2 ? T - 1 : T, (slab + 1) * rows_per);
+        const int x_lo = kx == 0 ? 1 : 0, x_hi = kx == 2 ? X - 1 : X;
+        for (int t = t_lo; t < t_hi; ++t) {
+          const float* a = in_s + ((t + kt - 1) * X + kx - 1) * 2;
+          const float* g = c1 + (t * X) * 2 * FP + f4;
+#pragma unroll 2
+          for (int x = x_lo; x < x_hi; ++x) {
+            const float in0 = a[2 * x], in1 = a[2 * x + 1];
+            const float4 g0 = *reinterpret_cast<const float4*>(g + (2 * x) * FP);
+            const float4 g1 = *reinterpret_cast<const float4*>(g + (2 * x + 1) * FP);
+            const float b0[4] = {g0.x, g0.y, g0.z, g0.w}, b1[4] = {g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              s0[j] = fmaf(in0, b0[j], s0[j]);       // kd = 0: output mu = 0 reads input mu = 0, mu = 1 reads mu = 1
+              s0[j] = fmaf(in1, b1[j], s0[j]);
+              s1[j] = fmaf(in1, b0[j], s1[j]);       // kd = 1: output mu = 0 reads input mu = 1
+            }
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          scratch[slab * 18 * F + (tap * 2) * F + f4 + j] = s0[j];
+          scratch[slab * 18 * F + (tap * 2 + 1) * F + f4 + j] = s1[j];
+        }
+      }
+      __syncthreads();
+      for (int i = tid; i < 18 * F; i += kThreads) {
+        float s = 0.f;
+        for (int q = 0; q < S; ++q) s += scratch[q * 18 * F + i];
+        part[i] += s;
+      }
+    } else
     for (int i = tid; i < 18 * F; i += kThreads) {
       const int f = i % F, kd = (i / F) & 1, kx = (i / (2 * F)) % 3, kt = i / (6 * F);
       float s = 0.f;
@@ -239,8 +376,17 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           for (int kd = 0; kd <= dd; ++kd) {
             const float* g = c1 + ((t * X + x) * 2 + dd - kd) * FP;
             const float* w = w1s + ((kt * 3 + kx) * 2 + kd) * F;
+            if (kFast) {
+#pragma unroll
+              for (int f4 = 0; f4 < F; f4 += 4) {
+                const float4 wv = *reinterpret_cast<const float4*>(w + f4);
+                const float4 gv = *reinterpret_cast<const float4*>(g + f4);
+                s = fmaf(wv.x, gv.x, s), s = fmaf(wv.y, gv.y, s), s = fmaf(wv.z, gv.z, s), s = fmaf(wv.w, gv.w, s);
+              }
+            } else {
 #pragma unroll 8
-            for (int f = 0; f < F; ++f) s = fmaf(w[f], g[f], s);
+              for (int f = 0; f < F; ++f) s = fmaf(w[f], g[f], s);
+            }
           }
         }
       }
@@ -268,8 +414,10 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
                 "l2hmc_conv3d_backward: null pointer");
   L2HMC_REQUIRE(!a->row_set || (!a->mask == !a->mask_alt), "l2hmc_conv3d_backward: mask and mask_alt go together");
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, D = 2 * T * X;
-  const size_t floats = 2u * D + static_cast<size_t>(D) * (F + 1) + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
-                        18u * F + 4u * F * (2 * F + 1);
+  const bool fast = (F == 8 || F == 16 || F == 32) && D % 4 == 0;   // float4 rows need 16-byte aligned buffers
+  const size_t fp = fast ? F + 4 : F + 1, cp = fast ? 2 * F + 4 : 2 * F + 1;
+  const size_t floats = 2u * D + static_cast<size_t>(D) * fp + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
+                        18u * F + 4u * F * cp;
   const size_t smem = floats * sizeof(float);
   int dev = 0, max_smem = 0;
   cudaGetDevice(&dev);
@@ -279,8 +427,8 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
               max_smem);
     return L2HMC_ERR_UNSUPPORTED;
   }
-  void (*kernel)(const ConvBwdParams) = F == 8 ? conv3d_bwd_kernel<8> : F == 16 ? conv3d_bwd_kernel<16>
-                                        : F == 32 ? conv3d_bwd_kernel<32> : conv3d_bwd_kernel<0>;
+  void (*kernel)(const ConvBwdParams) = !fast ? conv3d_bwd_kernel<0> : F == 8 ? conv3d_bwd_kernel<8>
+                                        : F == 16 ? conv3d_bwd_kernel<16> : conv3d_bwd_kernel<32>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) {
