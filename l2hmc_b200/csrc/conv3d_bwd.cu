@@ -16,7 +16,7 @@ namespace l2hmc {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxRows = 296;
+constexpr int kMaxRows = 444;   // 3 resident CTAs per SM (72 KB of shared memory each at 16x16, F = 16)
 
 struct ConvBwdParams {
   const float *w1, *b1, *w2, *b2;
