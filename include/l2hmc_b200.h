@@ -554,6 +554,12 @@ int l2hmc_conv3d_bwd_rows(int N);
 int l2hmc_conv3d_bwd_cols(int F);
 int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* stream);
 
+/* out[c] = sum_r B[r*ld + c] (bias / coeff_* gradients: batch sums of an activation gradient), two stages with a fixed
+ * order; workspace: l2hmc_col_sum_workspace_bytes(rows, cols). */
+size_t l2hmc_col_sum_workspace_bytes(int rows, int cols);
+int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, float* out, void* workspace, size_t workspace_bytes,
+                  void* stream);
+
 /* out[0] = sum v[i] (square = 0) or sum v[i]^2 (square = 1), fixed two-stage tree; scratch: 1024 floats. */
 int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch, void* stream);
 

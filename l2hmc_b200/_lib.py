@@ -231,6 +231,8 @@ SIGNATURES = {
     "l2hmc_conv3d_backward": [POINTER(Conv3dBwdArgs), c_void_p],
     "l2hmc_u1_train_workspace_bytes": [POINTER(TrainArgs)],
     "l2hmc_u1_train_grads": [POINTER(TrainArgs), c_void_p],
+    "l2hmc_col_sum_workspace_bytes": [c_int, c_int],
+    "l2hmc_col_sum": [c_void_p, c_longlong, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p],
     "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
                         c_float, c_void_p, c_float, c_void_p],
@@ -240,7 +242,7 @@ SIGNATURES = {
 
 RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
             "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t,
-            "l2hmc_tc_gemm_workspace_bytes": c_size_t, "l2hmc_gemm_workspace_bytes": c_size_t}
+            "l2hmc_tc_gemm_workspace_bytes": c_size_t, "l2hmc_gemm_workspace_bytes": c_size_t, "l2hmc_col_sum_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
 

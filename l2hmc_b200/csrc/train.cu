@@ -599,6 +599,34 @@ __global__ void __launch_bounds__(256) reduce_stage2_kernel(const float* __restr
   if (threadIdx.x == 0) out[0] = tot;
 }
 
+// Column sums of a row-major matrix (bias and coeff_* gradients: the batch sum of an activation gradient):
+// stage 1: partial[slab][c] over a slab of rows, threads along the contiguous columns; stage 2: slabs in fixed order.
+__global__ void __launch_bounds__(128) colsum_stage1_kernel(const float* __restrict__ B, long long ld, int rows, int cols,
+                                                            int slabs, float* partial) {
+  const int c = blockIdx.x * 128 + threadIdx.x;
+  if (c >= cols) return;
+  const int per = (rows + slabs - 1) / slabs;
+  const int r0 = blockIdx.y * per, r1 = min(rows, r0 + per);
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int r = r0;
+  for (; r + 3 < r1; r += 4) {
+    s0 += B[static_cast<long long>(r) * ld + c];
+    s1 += B[static_cast<long long>(r + 1) * ld + c];
+    s2 += B[static_cast<long long>(r + 2) * ld + c];
+    s3 += B[static_cast<long long>(r + 3) * ld + c];
+  }
+  for (; r < r1; ++r) s0 += B[static_cast<long long>(r) * ld + c];
+  partial[static_cast<size_t>(blockIdx.y) * cols + c] = (s0 + s1) + (s2 + s3);
+}
+__global__ void __launch_bounds__(128) colsum_stage2_kernel(const float* __restrict__ partial, int slabs, int cols,
+                                                            float* out) {
+  const int c = blockIdx.x * 128 + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int q = 0; q < slabs; ++q) s += partial[static_cast<size_t>(q) * cols + c];
+  out[c] = s;
+}
+
 // tf.train.AdamOptimizer (lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) folded on the host):
 //   m = b1 m + (1 - b1) g;  v = b2 v + (1 - b2) g^2;  theta -= lr_t m / (sqrt(v) + eps)
 // with g scaled by clip / max(||g||, clip) when a global-norm clip is given (tf.clip_by_global_norm).
@@ -767,6 +795,26 @@ extern "C" int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, c
                   prm->charge_weight, g_xprop, g_px, g_pz};
   loss_bwd_kernel<<<grid, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p, warps);
   return check_launch("loss_bwd_kernel");
+}
+
+static int colsum_slabs(int rows) { return std::max(1, std::min(64, rows / 64)); }
+
+extern "C" size_t l2hmc_col_sum_workspace_bytes(int rows, int cols) {
+  if (rows <= 0 || cols <= 0) return 0;
+  return sizeof(float) * static_cast<size_t>(colsum_slabs(rows)) * cols;
+}
+
+extern "C" int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, float* out, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  L2HMC_REQUIRE(B && out && rows > 0 && cols > 0 && ld >= cols, "l2hmc_col_sum: bad arguments");
+  L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_col_sum_workspace_bytes(rows, cols),
+                "l2hmc_col_sum: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int slabs = colsum_slabs(rows);
+  float* partial = static_cast<float*>(workspace);
+  colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
+  colsum_stage2_kernel<<<(cols + 127) / 128, 128, 0, st>>>(partial, slabs, cols, out);
+  return check_launch("colsum_kernel");
 }
 
 extern "C" int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch /* [1024] */,

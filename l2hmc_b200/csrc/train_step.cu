@@ -142,6 +142,7 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
       deferred(w->H, w->D), deferred(1, w->D), deferred(w->H, w->H), deferred(1, w->H), deferred(w->K, w->H);
       deferred(2, w->H);
       need(pl.R, w->H, 3, w->D, 0), need(pl.R, w->H, 1, w->H, 0), need(pl.R, w->K, 1, w->H, 0);   // per-call GEMMs
+      gw = std::max(gw, l2hmc_col_sum_workspace_bytes(K, 3 * std::max(w->H, w->D)));
     }
     pl.gemm_ws_bytes = gw;
     pl.gemm_ws = c.take<char>(gw);
@@ -184,6 +185,10 @@ int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long
   return gemm(c, M, N, {s}, C, ldc, accumulate, nullptr, 0, nullptr, 0, nullptr, 0, false, ksplit);
 }
 
+int col_sum(const Ctx& c, const float* B, long long ld, int rows, int cols, float* out) {
+  return l2hmc_col_sum(B, ld, rows, cols, out, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.stream);
+}
+
 int net_forward(const Ctx& c, const l2hmc_net_weights* w, const void* packed, NetTape& t, int j, const float* tau,
                 const float* tau_alt) {
   const Plan& pl = c.pl;
@@ -220,33 +225,33 @@ int net_backward(const Ctx& c, const l2hmc_net_weights* w, NetTape& t, int j) {
 
 int weight_grads(const Ctx& c, const NetTape& t, const l2hmc_net_grads* g) {
   const int Rt = 2 * c.pl.M * c.pl.R, H = t.H, D = t.D, K = t.K;
-  const float* ones = t.tau1 + 2;
   auto ks = [&](int M, int N) { return ksplit_for(M, N, Rt); };
   float* wk[3] = {g->w_s, g->w_tr, g->w_q};
   float* bk[3] = {g->b_s, g->b_tr, g->b_q};
   for (int s = 0; s < 3; ++s) {
     L2HMC_TRY(plain_gemm(c, H, D, l2hmc_gemm_seg{t.h2, 1, H, t.dA + s * D, 3LL * D, 1, Rt}, wk[s], D, 0, ks(H, D)));
-    L2HMC_TRY(plain_gemm(c, 1, D, l2hmc_gemm_seg{ones, 0, 3, t.dA + s * D, 3LL * D, 1, Rt}, bk[s], D, 0, ks(1, D)));
+    L2HMC_TRY(col_sum(c, t.dA + s * D, 3LL * D, Rt, D, bk[s]));
   }
   L2HMC_TRY(plain_gemm(c, H, H, l2hmc_gemm_seg{t.h1, 1, H, t.dz2, H, 1, Rt}, g->w_h, H, 0, ks(H, H)));
-  L2HMC_TRY(plain_gemm(c, 1, H, l2hmc_gemm_seg{ones, 0, 3, t.dz2, H, 1, Rt}, g->b_h, H, 0, ks(1, H)));
+  L2HMC_TRY(col_sum(c, t.dz2, H, Rt, H, g->b_h));
   L2HMC_TRY(plain_gemm(c, K, H, l2hmc_gemm_seg{t.in0, 1, K, t.dz1, H, 1, Rt}, g->w_in0, H, 0, ks(K, H)));
   L2HMC_TRY(plain_gemm(c, K, H, l2hmc_gemm_seg{t.in1, 1, K, t.dz1, H, 1, Rt}, g->w_in1, H, 0, ks(K, H)));
   L2HMC_TRY(plain_gemm(c, 2, H, l2hmc_gemm_seg{t.tau1, 1, 3, t.dz1, H, 1, Rt}, g->w_t, H, 0, ks(2, H)));
-  for (float* b : {g->b_in0, g->b_in1, g->b_t})
-    L2HMC_TRY(plain_gemm(c, 1, H, l2hmc_gemm_seg{ones, 0, 3, t.dz1, H, 1, Rt}, b, H, 0, ks(1, H)));
-  L2HMC_TRY(plain_gemm(c, 1, D, l2hmc_gemm_seg{ones, 0, 3, t.ps, D, 1, Rt}, g->coeff_s, D, 0, ks(1, D)));
-  return plain_gemm(c, 1, D, l2hmc_gemm_seg{ones, 0, 3, t.pq, D, 1, Rt}, g->coeff_q, D, 0, ks(1, D));
+  L2HMC_TRY(col_sum(c, t.dz1, H, Rt, H, g->b_in0));        // the three first-layer biases add into the same sum
+  for (float* b : {g->b_in1, g->b_t})
+    if (cudaMemcpyAsync(b, g->b_in0, H * sizeof(float), cudaMemcpyDeviceToDevice, c.st) != cudaSuccess) return L2HMC_ERR_CUDA;
+  L2HMC_TRY(col_sum(c, t.ps, D, Rt, D, g->coeff_s));
+  return col_sum(c, t.pq, D, Rt, D, g->coeff_q);
 }
 
 int conv_weight_grads(const Ctx& c, const NetTape& t, const float* part, const l2hmc_conv3d_grads* g, int F) {
-  const float* ones = t.tau1 + 2;
+  (void)t;
   const int rows = c.pl.prow, cols = c.pl.pcol;
   float* dst[4] = {g->w1, g->b1, g->w2, g->b2};
   const int n[4] = {18 * F, F, 16 * F * F, 2 * F};
   int off = 0;
   for (int i = 0; i < 4; ++i) {
-    L2HMC_TRY(plain_gemm(c, 1, n[i], l2hmc_gemm_seg{ones, 0, 3, part + off, cols, 1, rows}, dst[i], n[i], 0, 1));
+    L2HMC_TRY(col_sum(c, part + off, cols, rows, n[i], dst[i]));
     off += n[i];
   }
   return L2HMC_OK;

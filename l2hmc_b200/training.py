@@ -64,6 +64,16 @@ class _Gemm(object):
         self.launches += 2 if need else 1
 
 
+    def col_sum(self, B, ld, rows, cols, out):
+        """out[c] = sum_r B[r*ld + c] (l2hmc_col_sum: fixed two-stage order)."""
+        lib = _lib.get_lib()
+        need = int(lib.l2hmc_col_sum_workspace_bytes(int(rows), int(cols)))
+        if self._ws is None or self._ws.numel() * 4 < need:
+            self._ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=self.device)
+        _lib.check(lib.l2hmc_col_sum(B, int(ld), int(rows), int(cols), out, _ptr(self._ws), need, _lib.stream_ptr()))
+        self.launches += 2
+
+
 class _NetTape(object):
     """Activations and activation gradients of one network's 2M calls (rows = calls * R)."""
 
@@ -269,15 +279,13 @@ class TrainEngine(object):
     def _conv_weight_grads(self, name, net, tp):
         """Sum the per-CTA rows of the conv partials (fixed order) into the flat gradient."""
         P, F = self.params, int(net.num_filters)
-        ones = (_ptr(tp.tau1, 2), 0, 3)
         for which in ("x", "v"):
             part = self._conv_partial[(name, which)]
             rows, cols = part.shape
             off = 0
             for key, n in ((f"conv_{which}1.kernel", 18 * F), (f"conv_{which}1.bias", F),
                            (f"conv_{which}2.kernel", 16 * F * F), (f"conv_{which}2.bias", 2 * F)):
-                self.gemm(1, n, [ones + (_ptr(part, off), cols, 1, rows)], _ptr(P.view(P.grad, f"{name}.{key}")), n,
-                          ksplit=1)
+                self.gemm.col_sum(_ptr(part, off), cols, rows, n, _ptr(P.view(P.grad, f"{name}.{key}")))
                 off += n
 
     # ------------------------------------------------------------------ native: one C call per step
@@ -568,27 +576,28 @@ class TrainEngine(object):
         return int(max(1, min(64, -(-296 // tiles), K // 64)))
 
     def _weight_grads(self, name, tp):
-        """One transposed GEMM over the whole tape per weight tensor (K = calls * R rows)."""
+        """One transposed GEMM over the whole tape per weight tensor (K = calls * R rows); biases and coeff_* are
+        column sums of the activation gradients."""
         P, H, D, Kin = self.params, tp.H, tp.D, tp.K
         Rt = tp.calls * tp.R
         g = lambda key: _ptr(P.view(P.grad, f"{name}.{key}"))
-        ones = (_ptr(tp.tau1, 2), 0, 3)                             # A(0, r) = 1
-        dA, dz2, dz1 = _ptr(tp.dA), _ptr(tp.dz2), _ptr(tp.dz1)
+        dz2, dz1 = _ptr(tp.dz2), _ptr(tp.dz1)
         for s, layer in enumerate(("scale_layer", "translation_layer", "transformation_layer")):
             B = (_ptr(tp.dA, s * D), 3 * D, 1)
             self.gemm(H, D, [(_ptr(tp.h2), 1, H) + B + (Rt,)], g(layer + ".kernel"), D, ksplit=self._ksplit(H, D, Rt))
-            self.gemm(1, D, [ones + B + (Rt,)], g(layer + ".bias"), D, ksplit=self._ksplit(1, D, Rt))
+            self.gemm.col_sum(_ptr(tp.dA, s * D), 3 * D, Rt, D, g(layer + ".bias"))
         self.gemm(H, H, [(_ptr(tp.h1), 1, H, dz2, H, 1, Rt)], g("h_layer.kernel"), H, ksplit=self._ksplit(H, H, Rt))
-        self.gemm(1, H, [ones + (dz2, H, 1, Rt)], g("h_layer.bias"), H, ksplit=self._ksplit(1, H, Rt))
+        self.gemm.col_sum(dz2, H, Rt, H, g("h_layer.bias"))
         self.gemm(Kin, H, [(_ptr(tp.in0), 1, Kin, dz1, H, 1, Rt)], g("v_layer.kernel"), H,
                   ksplit=self._ksplit(Kin, H, Rt))
         self.gemm(Kin, H, [(_ptr(tp.in1), 1, Kin, dz1, H, 1, Rt)], g("x_layer.kernel"), H,
                   ksplit=self._ksplit(Kin, H, Rt))
         self.gemm(2, H, [(_ptr(tp.tau1), 1, 3, dz1, H, 1, Rt)], g("t_layer.kernel"), H, ksplit=self._ksplit(2, H, Rt))
-        for layer in ("v_layer", "x_layer", "t_layer"):
-            self.gemm(1, H, [ones + (dz1, H, 1, Rt)], g(layer + ".bias"), H, ksplit=self._ksplit(1, H, Rt))
-        self.gemm(1, D, [ones + (_ptr(tp.ps), D, 1, Rt)], g("coeff_scale"), D, ksplit=self._ksplit(1, D, Rt))
-        self.gemm(1, D, [ones + (_ptr(tp.pq), D, 1, Rt)], g("coeff_transformation"), D, ksplit=self._ksplit(1, D, Rt))
+        self.gemm.col_sum(dz1, H, Rt, H, g("v_layer.bias"))          # the three first-layer biases share one sum
+        for layer in ("x_layer", "t_layer"):
+            P.view(P.grad, f"{name}.{layer}.bias").copy_(P.view(P.grad, f"{name}.v_layer.bias"))
+        self.gemm.col_sum(_ptr(tp.ps), D, Rt, D, g("coeff_scale"))
+        self.gemm.col_sum(_ptr(tp.pq), D, Rt, D, g("coeff_transformation"))
 
 
 def exponential_decay(lr_init, global_step, decay_steps, decay_rate, staircase=True):
