@@ -416,7 +416,8 @@ def run_training(c, events_ms, steps):
                  "params": int(eng.params.size), "train_step_ms": ms,
                  "link_updates_per_s": world * N * D * M / (ms * 1e-3),
                  "note": "x- and z-chain forward with tape + backward + Adam + observables; the x-chain's advance is "
-                         "counted once; FFMA GEMMs (cp.async multi-stage, split-K), fp32"}
+                         "counted once; fp32: tcgen05 3xTF32 layers / backward products from 1024 stacked rows, FFMA "
+                         "(cp.async multi-stage, split-K) below"}
         if tag.startswith("config2") and world == 1 and not c.get("no_cpu"):
             import time
             from oracle import train_oracle as tro
