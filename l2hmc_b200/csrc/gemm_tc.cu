@@ -92,6 +92,10 @@ struct TcParams {
   const float* cscale;
   const float* cscale_alt;
   int cinv, cinv_alt;
+  // split-K (kTcPlain only): work item = (tile, z); z covers K blocks [z * kb_per, min(KB, (z + 1) * kb_per)) and writes
+  // its raw sums to partial[z][rows][cols]; the epilogue runs in the reduce stage (fixed z order).  ksplit <= 1: off.
+  int ksplit, kb_per;
+  float* partial;
   int debug_noload;    // diagnostics (L2HMC_TC_DEBUG_NOLOAD=1): operand tiles are fetched only while the ring first
                        // fills; later K blocks re-use stale shared memory -> wrong numbers, pure MMA / epilogue timing
 };
@@ -197,8 +201,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const int num_tiles = p.m_tiles * p.n_tiles;
-  const int num_chunks = (p.KB + kChunkKB - 1) / kChunkKB;
+  const int mn_tiles = p.m_tiles * p.n_tiles;
+  const bool split = MODE == kTcPlain && p.ksplit > 1;
+  const int num_tiles = split ? mn_tiles * p.ksplit : mn_tiles;
 
   if (warp == kProducerWarp) {
     // ===== producer =====
@@ -206,8 +211,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
       int stage = 0, issued = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
-        for (int kb = 0; kb < p.KB; ++kb) {
+        const int mn = tile % mn_tiles, z = tile / mn_tiles;
+        const int m_blk = mn % p.m_tiles, n_blk = mn / p.m_tiles;
+        const int kb_lo = split ? z * p.kb_per : 0, kb_hi = split ? min(p.KB, kb_lo + p.kb_per) : p.KB;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (p.debug_noload && issued++ >= NSTAGE) {
             mbar_arrive(&full[stage]);
@@ -231,8 +238,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
       int stage = 0;
       uint32_t phase = 0, acc = 0, acc_phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        for (int kb = 0; kb < p.KB; ++kb) {
-          const int in_chunk = kb % kChunkKB;
+        const int kb_lo = split ? (tile / mn_tiles) * p.kb_per : 0;
+        const int kb_hi = split ? min(p.KB, kb_lo + p.kb_per) : p.KB;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
+          const int in_chunk = (kb - kb_lo) % kChunkKB;
           if (in_chunk == 0) {                   // fresh accumulator stage for this K chunk
             mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
             tc_fence_after();
@@ -252,7 +261,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
           }
           umma_commit(&empty[stage]);            // smem slot free once these MMAs have read it
           if (++stage == NSTAGE) stage = 0, phase ^= 1;
-          if (in_chunk == kChunkKB - 1 || kb == p.KB - 1) {
+          if (in_chunk == kChunkKB - 1 || kb == kb_hi - 1) {
             umma_commit(&tmem_full[acc]);        // chunk complete
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
@@ -268,7 +277,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
     uint32_t acc = 0, acc_phase = 0;
     const int row_in_tile = quad * 32 + lane;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m_blk = tile % p.m_tiles, n_blk = tile / p.m_tiles;
+      const int mn = tile % mn_tiles, z = tile / mn_tiles;
+      const int m_blk = mn % p.m_tiles, n_blk = mn / p.m_tiles;
+      const int kb_lo = split ? z * p.kb_per : 0, kb_hi = split ? min(p.KB, kb_lo + p.kb_per) : p.KB;
+      const int num_chunks = (kb_hi - kb_lo + kChunkKB - 1) / kChunkKB;
       const int r = m_blk * TC_BM + row_in_tile;
       float sum[NG][32];
 #pragma unroll
@@ -296,13 +308,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
       const bool alt = p.row_set != nullptr && r < p.rows && p.row_set[r] != 0;
       if (MODE == kTcPlain) {
         if (r < p.rows) {
-          const float* cs = alt ? p.cscale_alt : p.cscale;
+          // split-K: raw sums of this K range; gate / scale / accumulate happen in the reduce stage
+          const float* cs = split ? nullptr : alt ? p.cscale_alt : p.cscale;
           const int cinv = alt ? p.cinv_alt : p.cinv;
+          const int accumulate = split ? 0 : p.accumulate;
+          float* crow = split ? p.partial + (static_cast<size_t>(z) * p.rows + r) * p.cols
+                              : p.C + static_cast<long long>(r) * p.ldc;
 #pragma unroll
           for (int g = 0; g < NG; ++g) {
             const int n0 = n_blk * BN + half * (BN / 2) + g * 32;
-            float* dst = p.C + static_cast<long long>(r) * p.ldc + n0;
-            const float* gt = p.gate ? p.gate + static_cast<long long>(r) * p.ldg + n0 : nullptr;
+            float* dst = crow + n0;
+            const float* gt = (p.gate && !split) ? p.gate + static_cast<long long>(r) * p.ldg + n0 : nullptr;
 #pragma unroll
             for (int j4 = 0; j4 < 32; j4 += 4) {
               float o[4];
@@ -313,7 +329,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
                 if (n < p.cols) {
                   if (gt != nullptr && !(gt[j4 + j] > 0.f)) val = 0.f;
                   if (cs != nullptr) val = __fmul_rn(val, cinv ? __fsub_rn(1.f, cs[n]) : cs[n]);
-                  if (p.accumulate) val = __fadd_rn(dst[j4 + j], val);
+                  if (accumulate) val = __fadd_rn(dst[j4 + j], val);
                 }
                 o[j] = val;
               }
@@ -548,7 +564,7 @@ int launch_tc(const TcParams& p, cudaStream_t st) {
     opted[slot] = dev < kMaxDevices;
   }
   const int sms = sm_count[slot];
-  const int tiles = p.m_tiles * p.n_tiles;
+  const int tiles = p.m_tiles * p.n_tiles * (MODE == kTcPlain && p.ksplit > 1 ? p.ksplit : 1);
   if (tiles == 0) return L2HMC_OK;
   kern<<<std::min(tiles, sms), kTcThreads, smem, st>>>(p);
   return check_launch("gemm_tc_kernel");
@@ -739,7 +755,13 @@ __global__ void __launch_bounds__(256) ts32_from_strided_kernel(const float* __r
 struct TcGemmDims {
   int rows_p, n_p, kb;
   size_t a_floats, b_floats;
+  bool narrow;          // 128-wide N tiles (few tiles: more SMs take part)
+  int n_tiles;
+  int ksplit, kb_per;   // split-K: ksplit K ranges of kb_per K blocks each (the last one shorter), 1 = off
+  size_t partial_floats;
 };
+constexpr int kTcSplitTargetCtas = 148;   // B200 SM count; a fixed constant so that results do not depend on the device
+constexpr int kTcSplitMinKB = 32;         // at least K = 1024 per range
 TcGemmDims tc_gemm_dims(const l2hmc_gemm_args* g) {
   TcGemmDims d{};
   d.rows_p = (g->M + 127) / 128 * 128;
@@ -747,6 +769,19 @@ TcGemmDims tc_gemm_dims(const l2hmc_gemm_args* g) {
   for (int s = 0; s < g->nseg; ++s) d.kb += (g->seg[s].K + 31) / 32;
   d.a_floats = static_cast<size_t>(d.kb) * d.rows_p * 64;
   d.b_floats = static_cast<size_t>(d.kb) * d.n_p * 64;
+  const int m_tiles = d.rows_p / 128;
+  d.narrow = m_tiles * ((g->N + 255) / 256) < 120;
+  d.n_tiles = d.narrow ? (g->N + 127) / 128 : (g->N + 255) / 256;
+  // long-K products with few output tiles (the weight gradients over the whole tape): split K over the idle SMs
+  const int tiles = m_tiles * d.n_tiles;
+  int ks = tiles > 0 ? std::min(kTcSplitTargetCtas / tiles, d.kb / kTcSplitMinKB) : 1;
+  d.ksplit = 1, d.kb_per = d.kb;
+  if (ks >= 2) {
+    const int per = ((d.kb + ks - 1) / ks + kChunkKB - 1) / kChunkKB * kChunkKB;
+    ks = (d.kb + per - 1) / per;          // no empty range
+    if (ks >= 2) d.ksplit = ks, d.kb_per = per;
+  }
+  d.partial_floats = d.ksplit > 1 ? static_cast<size_t>(d.ksplit) * g->M * g->N : 0;
   return d;
 }
 
@@ -756,7 +791,7 @@ TcGemmDims tc_gemm_dims(const l2hmc_gemm_args* g) {
 extern "C" size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g) {
   if (!g || g->nseg < 1 || g->nseg > 3 || g->M <= 0 || g->N <= 0) return 0;
   const TcGemmDims d = tc_gemm_dims(g);
-  return sizeof(float) * (d.a_floats + d.b_floats) + 256;
+  return sizeof(float) * (d.a_floats + d.b_floats + d.partial_floats) + 256;
 }
 
 extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t workspace_bytes, void* stream) {
@@ -800,10 +835,11 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
   p.C = g->C, p.ldc = g->ldc, p.accumulate = g->accumulate, p.gate = g->relu_gate, p.ldg = g->ldg;
   p.cscale = g->col_scale, p.cinv = g->col_scale_invert, p.row_set = g->row_set;
   p.cscale_alt = g->col_scale_alt, p.cinv_alt = g->col_scale_invert_alt;
-  // few tiles: halve the N tile so more SMs take part
-  const bool narrow = p.m_tiles * ((g->N + 255) / 256) < 120;
-  p.n_tiles = narrow ? (g->N + 127) / 128 : (g->N + 255) / 256;
-  return narrow ? launch_tc<128, kTcPlain>(p, st) : launch_tc<256, kTcPlain>(p, st);
+  p.n_tiles = d.n_tiles;
+  p.ksplit = d.ksplit, p.kb_per = d.kb_per, p.partial = b_ts + d.b_floats;
+  rc = d.narrow ? launch_tc<128, kTcPlain>(p, st) : launch_tc<256, kTcPlain>(p, st);
+  if (rc || d.ksplit <= 1) return rc;
+  return launch_splitk_reduce(p.partial, d.ksplit, g, st);
 }
 
 // Dispatch of the training GEMMs (north star: tensor cores only where the product is a dense contraction, FFMA

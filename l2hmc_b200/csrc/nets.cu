@@ -24,7 +24,8 @@
 namespace l2hmc {
 namespace {
 
-constexpr int BM = 64, BK = 16, kThreads = 256;
+constexpr int BM = 64, BK = 32, kThreads = 256;
+constexpr int AV = BK / 16;   // float4 A loads per thread and K slab
 
 enum Mode { kBiasRelu = 0, kHeadsStq = 1, kHeadsMomentum = 2, kHeadsPosition = 3 };
 
@@ -89,35 +90,39 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) acc[i][j] = 0.f;
 
-  // A: one float4 along K per thread
+  // A: AV float4 along K per thread (k offsets ak + 16 q)
   const int ar = tid >> 2, ak = (tid & 3) * 4;
   const bool a_alt = p.row_set != nullptr && m0 + ar < p.rows && p.row_set[m0 + ar] != 0;
-  float a_reg[4];
+  float a_reg[AV][4];
   float b_reg[BV][4];
 
   auto load_tile = [&](const Seg& s, int k0) {
     const int gr = m0 + ar;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) a_reg[i] = 0.f;
-    if (gr < p.rows) {
-      const float* src = s.A + static_cast<size_t>(gr) * s.lda + k0 + ak;
-      if (k0 + ak + 3 < s.K && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
-        const float4 t = *reinterpret_cast<const float4*>(src);
-        a_reg[0] = t.x, a_reg[1] = t.y, a_reg[2] = t.z, a_reg[3] = t.w;
-      } else {
+    for (int q = 0; q < AV; ++q) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (k0 + ak + i < s.K) a_reg[i] = src[i];
-      }
-      const float* mask = a_alt ? s.mask_alt : s.mask;
-      if (mask != nullptr) {
-        const int invert = a_alt ? s.invert_alt : s.invert;
+      for (int i = 0; i < 4; ++i) a_reg[q][i] = 0.f;
+      if (gr < p.rows) {
+        const int kq = k0 + ak + 16 * q;
+        const float* src = s.A + static_cast<size_t>(gr) * s.lda + kq;
+        if (kq + 3 < s.K && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
+          const float4 t = *reinterpret_cast<const float4*>(src);
+          a_reg[q][0] = t.x, a_reg[q][1] = t.y, a_reg[q][2] = t.z, a_reg[q][3] = t.w;
+        } else {
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
-          if (k0 + ak + i < s.K) {
-            const float m = mask[k0 + ak + i];
-            a_reg[i] = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a_reg[i]);
-          }
+          for (int i = 0; i < 4; ++i)
+            if (kq + i < s.K) a_reg[q][i] = src[i];
+        }
+        const float* mask = a_alt ? s.mask_alt : s.mask;
+        if (mask != nullptr) {
+          const int invert = a_alt ? s.invert_alt : s.invert;
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (kq + i < s.K) {
+              const float m = mask[kq + i];
+              a_reg[q][i] = __fmul_rn(invert ? __fsub_rn(1.f, m) : m, a_reg[q][i]);
+            }
+        }
       }
     }
 #pragma unroll
@@ -145,7 +150,9 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
   };
   auto store_tile = [&]() {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) As[ak + i][ar] = a_reg[i];
+    for (int q = 0; q < AV; ++q)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) As[ak + 16 * q + i][ar] = a_reg[q][i];
 #pragma unroll
     for (int q = 0; q < BV; ++q) {
       const int idx = tid + q * kThreads;

@@ -696,8 +696,12 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   else sgemm_kernel<false, false><<<grid, kGemmThreads, 0, st>>>(p);
   int rc = check_launch("sgemm_kernel");
   if (rc || ksplit == 1) return rc;
+  return l2hmc::launch_splitk_reduce(p.partial, ksplit, g, st);
+}
+
+int l2hmc::launch_splitk_reduce(const float* partial, int ksplit, const l2hmc_gemm_args* g, cudaStream_t stream) {
   const size_t total = static_cast<size_t>(g->M) * g->N;
-  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(p.partial, ksplit, *g);
+  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(partial, ksplit, *g);
   return check_launch("splitk_reduce_kernel");
 }
 

@@ -534,7 +534,10 @@ def _tc_gemm(M, N, segs, C, ldc, **kw):
 
 
 @pytest.mark.parametrize("M,N,K,ta,tb", [(256, 512, 384, False, True), (130, 70, 100, False, False), (512, 1024, 4096, True, False),
-                                         (1024, 512, 333, True, True), (4096, 1024, 512, False, True), (128, 64, 128, False, True)])
+                                         (1024, 512, 333, True, True), (4096, 1024, 512, False, True), (128, 64, 128, False, True),
+                                         # long K, few tiles: split-K over the idle SMs (ragged last range; the deferred
+                                         # weight-gradient shape of config 3)
+                                         (256, 192, 8200, True, False), (1024, 512, 40960, True, False)])
 def test_tc_gemm_forms(M, N, K, ta, tb):
     """The tcgen05 3xTF32 product in NN / NT / TN forms against a float64 product: fp32-level accuracy (2e-6 of scale)."""
     from l2hmc_b200 import _lib
