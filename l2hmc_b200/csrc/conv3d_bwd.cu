@@ -249,6 +249,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
     for (int i = tid; i < T2 * X2 * F; i += kThreads) {
       const int ci = i % F, x = (i / F) % X2, t = i / (F * X2);
       float s = 0.f;
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};       // fast path: four independent chains, joined in fixed order below
       for (int kt = 0; kt < 2 && kt <= t; ++kt)
         for (int kx = 0; kx < 2 && kx <= x; ++kx) {
           const float* g = c2 + ((t - kt) * X2 + x - kx) * C2;
@@ -258,13 +259,15 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
             for (int c4 = 0; c4 < C2; c4 += 4) {
               const float4 wv = *reinterpret_cast<const float4*>(w + c4);
               const float4 gv = *reinterpret_cast<const float4*>(g + c4);
-              s = fmaf(wv.x, gv.x, s), s = fmaf(wv.y, gv.y, s), s = fmaf(wv.z, gv.z, s), s = fmaf(wv.w, gv.w, s);
+              s4[0] = fmaf(wv.x, gv.x, s4[0]), s4[1] = fmaf(wv.y, gv.y, s4[1]);
+              s4[2] = fmaf(wv.z, gv.z, s4[2]), s4[3] = fmaf(wv.w, gv.w, s4[3]);
             }
           } else {
 #pragma unroll 8
             for (int co = 0; co < C2; ++co) s = fmaf(w[co], g[co], s);
           }
         }
+      if (kFast) s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       gp1[i] = s;
     }
     __syncthreads();
@@ -364,6 +367,40 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       part[off_b1 + f] += s;
     }
     float* dst = p.g_in + static_cast<size_t>(n) * D;
+    if (kFast) {
+      // thread = input site (t, x), both mu: mu = 0 gets tap kd = 0 of output mu = 0; mu = 1 gets kd = 0 of output
+      // mu = 1 and kd = 1 of output mu = 0 -- the two output rows and the two weight rows are loaded once per tap
+      for (int site = tid; site < T * X; site += kThreads) {
+        const int xx = site % X, tt = site / X;
+        float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int kt = 0; kt < 3; ++kt) {
+          const int t = tt - kt + 1;
+          if (t < 0 || t >= T) continue;
+          for (int kx = 0; kx < 3; ++kx) {
+            const int x = xx - kx + 1;
+            if (x < 0 || x >= X) continue;
+            const float* g = c1 + ((t * X + x) * 2) * FP;
+            const float* w = w1s + ((kt * 3 + kx) * 2) * F;
+#pragma unroll
+            for (int f4 = 0; f4 < F; f4 += 4) {
+              const float4 w0 = *reinterpret_cast<const float4*>(w + f4);
+              const float4 w1 = *reinterpret_cast<const float4*>(w + F + f4);
+              const float4 g0 = *reinterpret_cast<const float4*>(g + f4);
+              const float4 g1 = *reinterpret_cast<const float4*>(g + FP + f4);
+              s0[0] = fmaf(w0.x, g0.x, s0[0]), s0[1] = fmaf(w0.y, g0.y, s0[1]);
+              s0[2] = fmaf(w0.z, g0.z, s0[2]), s0[3] = fmaf(w0.w, g0.w, s0[3]);
+              s1[0] = fmaf(w0.x, g1.x, s1[0]), s1[1] = fmaf(w0.y, g1.y, s1[1]);
+              s1[2] = fmaf(w0.z, g1.z, s1[2]), s1[3] = fmaf(w0.w, g1.w, s1[3]);
+              s1[0] = fmaf(w1.x, g0.x, s1[0]), s1[1] = fmaf(w1.y, g0.y, s1[1]);
+              s1[2] = fmaf(w1.z, g0.z, s1[2]), s1[3] = fmaf(w1.w, g0.w, s1[3]);
+            }
+          }
+        }
+        const int i0 = 2 * site;
+        dst[i0] += mk_s[i0] * ((s0[0] + s0[1]) + (s0[2] + s0[3]));
+        dst[i0 + 1] += mk_s[i0 + 1] * ((s1[0] + s1[1]) + (s1[2] + s1[3]));
+      }
+    } else
     for (int i = tid; i < D; i += kThreads) {
       const int dd = i & 1, xx = (i >> 1) % X, tt = i / (2 * X);     // input position
       float s = 0.f;

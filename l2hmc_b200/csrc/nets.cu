@@ -314,6 +314,13 @@ int launch_dense(const DenseParams& p, cudaStream_t st) {
   return check_launch("dense_kernel");
 }
 
+// Layers: 64-column tiles; when those leave most SMs idle (config 2: 256 stacked rows x 512 columns = 32 tiles),
+// 32-column tiles.  Every output element sums the same products in the same K order either way (bit-identical).
+int launch_layer(const DenseParams& p, cudaStream_t st) {
+  const int wide_tiles = ((p.cols + 63) / 64) * ((p.rows + BM - 1) / BM);
+  return wide_tiles < 74 ? launch_dense<1, 2, kBiasRelu>(p, st) : launch_dense<1, 4, kBiasRelu>(p, st);
+}
+
 }  // namespace
 
 int heads_col_tiles(int D) { return (D + 31) / 32; }
@@ -336,7 +343,7 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
   p.wt = w->w_t, p.tau0 = c->tau_cos, p.tau1 = c->tau_sin;
   p.row_set = c->row_set, p.tau0_alt = c->tau_cos_alt, p.tau1_alt = c->tau_sin_alt;
   p.out[0] = h1;
-  int rc = launch_dense<1, 4, kBiasRelu>(p, st);
+  int rc = launch_layer(p, st);
   if (rc) return rc;
 
   p = DenseParams{};
@@ -345,7 +352,7 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
   p.rows = N, p.cols = H;
   p.bias[0] = w->b_h;
   p.out[0] = h2;
-  rc = launch_dense<1, 4, kBiasRelu>(p, st);
+  rc = launch_layer(p, st);
   if (rc) return rc;
 
   p = DenseParams{};
