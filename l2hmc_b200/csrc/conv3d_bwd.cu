@@ -35,11 +35,12 @@ struct ConvBwdParams {
 };
 
 // FT > 0: the filter count is a compile-time constant (index arithmetic folds, tap / channel loops unroll);
-// FT = 0: any F.
-template <int FT>
+// FT = 0: any F.  XT > 0: the lattice extent X too (the reference builds its networks with F = space_size,
+// gauge_dynamics.py:121-143, so X == F is the usual case): the (t, x, channel) decodes of every phase become shifts.
+template <int FT, int XT>
 __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParams p) {
   extern __shared__ __align__(16) float sm[];
-  const int T = p.T, X = p.X, F = FT > 0 ? FT : p.F, C2 = 2 * F;
+  const int T = p.T, X = XT > 0 ? XT : p.X, F = FT > 0 ? FT : p.F, C2 = 2 * F;
   constexpr bool kFast = FT > 0 && FT % 8 == 0;   // register-tiled phases with 128-bit shared loads
   // padded row strides: lanes that walk rows hit distinct banks (+4 keeps float4 alignment on the fast path)
   const int FP = kFast ? F + 4 : F + 1, CP = kFast ? C2 + 4 : C2 + 1;
@@ -333,11 +334,28 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
           scratch[slab * 18 * F + (tap * 2 + 1) * F + f4 + j] = s1[j];
         }
       }
+      // bias gradient: thread = (slab of outputs, filter), taken from the top of the CTA (the threads the last pass
+      // above leaves idle); the slab sums meet in the (now free) pool-1 buffer
+      const int bs = min(kThreads / F, min(8, T2 * X2)), b_per = (D + bs - 1) / bs;
+      {
+        const int j = kThreads - 1 - tid;
+        if (j < bs * F) {
+          const int f = j % F, slab = j / F;
+          float sb = 0.f;
+          for (int r = slab * b_per; r < min(D, (slab + 1) * b_per); ++r) sb += c1[r * FP + f];
+          p1[j] = sb;
+        }
+      }
       __syncthreads();
       for (int i = tid; i < 18 * F; i += kThreads) {
         float s = 0.f;
         for (int q = 0; q < S; ++q) s += scratch[q * 18 * F + i];
         part[i] += s;
+      }
+      for (int f = tid; f < F; f += kThreads) {
+        float s = 0.f;
+        for (int q = 0; q < bs; ++q) s += p1[q * F + f];
+        part[off_b1 + f] += s;
       }
     } else
     for (int i = tid; i < 18 * F; i += kThreads) {
@@ -361,11 +379,12 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       }
       part[i] += s;
     }
-    for (int f = tid; f < F; f += kThreads) {
-      float s = 0.f;
-      for (int j = 0; j < D; ++j) s += c1[j * FP + f];
-      part[off_b1 + f] += s;
-    }
+    if (!kFast)
+      for (int f = tid; f < F; f += kThreads) {
+        float s = 0.f;
+        for (int j = 0; j < D; ++j) s += c1[j * FP + f];
+        part[off_b1 + f] += s;
+      }
     float* dst = p.g_in + static_cast<size_t>(n) * D;
     if (kFast) {
       // thread = input site (t, x), both mu: mu = 0 gets tap kd = 0 of output mu = 0; mu = 1 gets kd = 0 of output
@@ -464,8 +483,11 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
               max_smem);
     return L2HMC_ERR_UNSUPPORTED;
   }
-  void (*kernel)(const ConvBwdParams) = !fast ? conv3d_bwd_kernel<0> : F == 8 ? conv3d_bwd_kernel<8>
-                                        : F == 16 ? conv3d_bwd_kernel<16> : conv3d_bwd_kernel<32>;
+  void (*kernel)(const ConvBwdParams) =
+      !fast     ? conv3d_bwd_kernel<0, 0>
+      : F == 8  ? (X == 8 ? conv3d_bwd_kernel<8, 8> : conv3d_bwd_kernel<8, 0>)
+      : F == 16 ? (X == 16 ? conv3d_bwd_kernel<16, 16> : conv3d_bwd_kernel<16, 0>)
+                : (X == 32 ? conv3d_bwd_kernel<32, 32> : conv3d_bwd_kernel<32, 0>);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (e != cudaSuccess) {
