@@ -38,7 +38,7 @@ struct ConvBwdParams {
 // FT = 0: any F.  XT > 0: the lattice extent X too (the reference builds its networks with F = space_size,
 // gauge_dynamics.py:121-143, so X == F is the usual case): the (t, x, channel) decodes of every phase become shifts.
 template <int FT, int XT>
-__global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParams p) {
+__global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdParams p) {
   extern __shared__ __align__(16) float sm[];
   const int T = p.T, X = XT > 0 ? XT : p.X, F = FT > 0 ? FT : p.F, C2 = 2 * F;
   constexpr bool kFast = FT > 0 && FT % 8 == 0;   // register-tiled phases with 128-bit shared loads
@@ -139,7 +139,42 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       p1[i] = best;
     }
     __syncthreads();
-    if (kFast) {       // thread = (position, 4 output channels)
+    if (kFast && (X2 & 1) == 0) {       // thread = (two adjacent positions, 4 output channels): one weight load, 8 FMAs
+      const int XH = X2 / 2;
+      for (int i = tid; i < T2 * XH * (C2 / 4); i += kThreads) {
+        const int co4 = (i % (C2 / 4)) * 4, pp = i / (C2 / 4), x = (pp % XH) * 2, t = pp / XH;
+        float acc[4], bcc[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[j] = bcc[j] = p.b2[co4 + j];
+        for (int kt = 0; kt < 2; ++kt)
+          for (int kx = 0; kx < 2; ++kx) {
+            const int tt = t + kt, xx = x + kx;          // xx <= X2 - 1; the second position's tap may fall outside
+            if (tt >= T2) continue;
+            const bool okb = xx + 1 < X2;
+            const float* a = p1 + (tt * X2 + xx) * F;
+            const float* w = w2s + ((kt * 2 + kx) * F) * CP + co4;
+#pragma unroll
+            for (int c4 = 0; c4 < F; c4 += 4) {
+              const float4 av = *reinterpret_cast<const float4*>(a + c4);
+              const float4 bv = okb ? *reinterpret_cast<const float4*>(a + F + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+              const float aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 wv = *reinterpret_cast<const float4*>(w + (c4 + q) * CP);
+                acc[0] = fmaf(aa[q], wv.x, acc[0]), acc[1] = fmaf(aa[q], wv.y, acc[1]);
+                acc[2] = fmaf(aa[q], wv.z, acc[2]), acc[3] = fmaf(aa[q], wv.w, acc[3]);
+                bcc[0] = fmaf(bb[q], wv.x, bcc[0]), bcc[1] = fmaf(bb[q], wv.y, bcc[1]);
+                bcc[2] = fmaf(bb[q], wv.z, bcc[2]), bcc[3] = fmaf(bb[q], wv.w, bcc[3]);
+              }
+            }
+          }
+        float* o = c2 + (t * X2 + x) * C2 + co4;
+        *reinterpret_cast<float4*>(o) =
+            make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+        *reinterpret_cast<float4*>(o + C2) =
+            make_float4(fmaxf(bcc[0], 0.f), fmaxf(bcc[1], 0.f), fmaxf(bcc[2], 0.f), fmaxf(bcc[3], 0.f));
+      }
+    } else if (kFast) {       // thread = (position, 4 output channels)
       for (int i = tid; i < T2 * X2 * (C2 / 4); i += kThreads) {
         const int co4 = (i % (C2 / 4)) * 4, pos = i / (C2 / 4), x = pos % X2, t = pos / X2;
         float acc[4];
@@ -247,6 +282,33 @@ __global__ void __launch_bounds__(kThreads) conv3d_bwd_kernel(const ConvBwdParam
       for (int j = 0; j < T2 * X2; ++j) s += c2[j * C2 + co];
       part[off_b2 + co] += s;
     }
+    if (kFast && (X2 & 1) == 0) {
+      // thread = (two adjacent positions, input channel): the weight row of a tap is loaded once for both
+      const int XH = X2 / 2;
+      for (int i = tid; i < T2 * XH * F; i += kThreads) {
+        const int ci = i % F, x1 = ((i / F) % XH) * 2 + 1, t = i / (F * XH);      // positions x1 - 1 and x1
+        float sa[4] = {0.f, 0.f, 0.f, 0.f}, sb[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int kt = 0; kt < 2 && kt <= t; ++kt)
+          for (int kx = 0; kx < 2; ++kx) {
+            const bool oka = x1 - 1 - kx >= 0;
+            const float* gb = c2 + ((t - kt) * X2 + x1 - kx) * C2;          // gradient row read by position x1
+            const float* w = w2s + ((kt * 2 + kx) * F + ci) * CP;
+#pragma unroll
+            for (int c4 = 0; c4 < C2; c4 += 4) {
+              const float4 wv = *reinterpret_cast<const float4*>(w + c4);
+              const float4 gv = *reinterpret_cast<const float4*>(gb + c4);
+              const float4 ga = oka ? *reinterpret_cast<const float4*>(gb - C2 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+              sb[0] = fmaf(wv.x, gv.x, sb[0]), sb[1] = fmaf(wv.y, gv.y, sb[1]);
+              sb[2] = fmaf(wv.z, gv.z, sb[2]), sb[3] = fmaf(wv.w, gv.w, sb[3]);
+              sa[0] = fmaf(wv.x, ga.x, sa[0]), sa[1] = fmaf(wv.y, ga.y, sa[1]);
+              sa[2] = fmaf(wv.z, ga.z, sa[2]), sa[3] = fmaf(wv.w, ga.w, sa[3]);
+            }
+          }
+        float* o = gp1 + (t * X2 + x1 - 1) * F + ci;
+        o[0] = (sa[0] + sa[1]) + (sa[2] + sa[3]);
+        o[F] = (sb[0] + sb[1]) + (sb[2] + sb[3]);
+      }
+    } else
     for (int i = tid; i < T2 * X2 * F; i += kThreads) {
       const int ci = i % F, x = (i / F) % X2, t = i / (F * X2);
       float s = 0.f;
