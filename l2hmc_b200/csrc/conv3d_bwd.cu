@@ -75,7 +75,48 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
     }
     __syncthreads();
     // ---- forward, recomputed
-    if (kFast) {       // thread = (site, 4 filters): both mu outputs, weights as float4
+    if (kFast && (X & 1) == 0) {       // thread = (two adjacent sites, 4 filters): a tap's weights feed 24 FMAs
+      const int XH = X / 2;
+      for (int i = tid; i < T * XH * (F / 4); i += kThreads) {
+        const int f4 = (i % (F / 4)) * 4, pp = i / (F / 4), t = pp / XH, x = (pp - t * XH) * 2;
+        float o0[4], o1[4], q0[4], q1[4];       // (site x: mu 0, mu 1), (site x + 1: mu 0, mu 1)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o0[j] = o1[j] = q0[j] = q1[j] = p.b1[f4 + j];
+#pragma unroll
+        for (int kt = 0; kt < 3; ++kt) {
+          const int tt = t + kt - 1;
+          if (tt < 0 || tt >= T) continue;
+#pragma unroll
+          for (int kx = 0; kx < 3; ++kx) {
+            const int xa = x + kx - 1, xb = xa + 1;       // xa >= -1, xb <= X
+            const float* row = in_s + (tt * X) * 2;
+            const bool oka = xa >= 0, okb = xb < X;
+            const float a0 = oka ? row[2 * xa] : 0.f, a1 = oka ? row[2 * xa + 1] : 0.f;
+            const float b0 = okb ? row[2 * xb] : 0.f, b1 = okb ? row[2 * xb + 1] : 0.f;
+            const float4 w0 = *reinterpret_cast<const float4*>(w1s + ((kt * 3 + kx) * 2) * F + f4);
+            const float4 w1 = *reinterpret_cast<const float4*>(w1s + ((kt * 3 + kx) * 2 + 1) * F + f4);
+            const float u0[4] = {w0.x, w0.y, w0.z, w0.w}, u1[4] = {w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              o0[j] = fmaf(a0, u0[j], o0[j]);       // mu = 0: taps kd = 0 (mu 0) and kd = 1 (mu 1)
+              o0[j] = fmaf(a1, u1[j], o0[j]);
+              o1[j] = fmaf(a1, u0[j], o1[j]);       // mu = 1: kd = 0 only (kd = 1 is padding)
+              q0[j] = fmaf(b0, u0[j], q0[j]);
+              q0[j] = fmaf(b1, u1[j], q0[j]);
+              q1[j] = fmaf(b1, u0[j], q1[j]);
+            }
+          }
+        }
+        float* o = c1 + ((t * X + x) * 2) * FP + f4;
+        *reinterpret_cast<float4*>(o) = make_float4(fmaxf(o0[0], 0.f), fmaxf(o0[1], 0.f), fmaxf(o0[2], 0.f), fmaxf(o0[3], 0.f));
+        *reinterpret_cast<float4*>(o + FP) =
+            make_float4(fmaxf(o1[0], 0.f), fmaxf(o1[1], 0.f), fmaxf(o1[2], 0.f), fmaxf(o1[3], 0.f));
+        *reinterpret_cast<float4*>(o + 2 * FP) =
+            make_float4(fmaxf(q0[0], 0.f), fmaxf(q0[1], 0.f), fmaxf(q0[2], 0.f), fmaxf(q0[3], 0.f));
+        *reinterpret_cast<float4*>(o + 3 * FP) =
+            make_float4(fmaxf(q1[0], 0.f), fmaxf(q1[1], 0.f), fmaxf(q1[2], 0.f), fmaxf(q1[3], 0.f));
+      }
+    } else if (kFast) {       // thread = (site, 4 filters): both mu outputs, weights as float4
       for (int i = tid; i < T * X * (F / 4); i += kThreads) {
         const int f4 = (i % (F / 4)) * 4, site = i / (F / 4), t = site / X, x = site - t * X;
         float o0[4], o1[4];
