@@ -607,16 +607,17 @@ __global__ void __launch_bounds__(128) colsum_stage1_kernel(const float* __restr
   if (c >= cols) return;
   const int per = (rows + slabs - 1) / slabs;
   const int r0 = blockIdx.y * per, r1 = min(rows, r0 + per);
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   int r = r0;
-  for (; r + 3 < r1; r += 4) {
-    s0 += B[static_cast<long long>(r) * ld + c];
-    s1 += B[static_cast<long long>(r + 1) * ld + c];
-    s2 += B[static_cast<long long>(r + 2) * ld + c];
-    s3 += B[static_cast<long long>(r + 3) * ld + c];
+  for (; r + 7 < r1; r += 8) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = B[static_cast<long long>(r + j) * ld + c];      // 8 independent loads in flight
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += v[j];
   }
-  for (; r < r1; ++r) s0 += B[static_cast<long long>(r) * ld + c];
-  partial[static_cast<size_t>(blockIdx.y) * cols + c] = (s0 + s1) + (s2 + s3);
+  for (; r < r1; ++r) s[0] += B[static_cast<long long>(r) * ld + c];
+  partial[static_cast<size_t>(blockIdx.y) * cols + c] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
 }
 __global__ void __launch_bounds__(128) colsum_stage2_kernel(const float* __restrict__ partial, int slabs, int cols,
                                                             float* out) {
@@ -801,7 +802,8 @@ extern "C" int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, c
   return check_launch("loss_bwd_kernel");
 }
 
-static int colsum_slabs(int rows) { return std::max(1, std::min(64, rows / 64)); }
+// enough slabs that the loads in flight cover HBM latency (40 960 tape rows: 512 slabs x 8 column tiles of CTAs)
+static int colsum_slabs(int rows) { return std::max(1, std::min(512, rows / 32)); }
 
 extern "C" size_t l2hmc_col_sum_workspace_bytes(int rows, int cols) {
   if (rows <= 0 || cols <= 0) return 0;

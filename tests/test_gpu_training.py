@@ -611,3 +611,22 @@ def test_training_step_with_tcgen05_layers():
     assert abs(float(loss_b) - float(ref_loss)) <= 2e-3 * max(1., abs(float(ref_loss)))
     for name, gr in grads.items():
         close_scaled(gr, ref[name], 5e-4, f"tcgen05 step d loss / d {name}")
+
+
+@pytest.mark.parametrize("rows,cols,ld", [(1, 5, 5), (31, 130, 130), (2560, 384, 1536), (40960, 1024, 1024), (1000, 77, 90)])
+def test_col_sum(rows, cols, ld):
+    """l2hmc_col_sum (bias / coeff gradients: batch sums of an activation gradient) against a float64 sum, on a column
+    window of a wider matrix; two evaluations are bit-identical (fixed two-stage order)."""
+    from l2hmc_b200.training import _Gemm, _ptr
+    rng = np.random.default_rng(rows + cols)
+    B = rng.standard_normal((rows, ld)).astype(np.float32)
+    ref = B[:, :cols].astype(np.float64).sum(axis=0)
+    tB = cu(B)
+    g = _Gemm(torch.device("cuda"))
+    out, out2 = torch.full((cols,), 3.0, device="cuda"), torch.empty(cols, device="cuda")
+    g.col_sum(_ptr(tB), ld, rows, cols, _ptr(out))
+    g.col_sum(_ptr(tB), ld, rows, cols, _ptr(out2))
+    torch.cuda.synchronize()
+    assert torch.equal(out, out2)
+    err = np.abs(out.cpu().numpy().astype(np.float64) - ref).max()
+    assert err <= 2e-6 * np.abs(B[:, :cols]).astype(np.float64).sum(axis=0).max(), err
