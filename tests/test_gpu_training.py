@@ -434,7 +434,10 @@ def test_train_loop_and_saved_state(tmp_path):
 
 
 # --------------------------------------------------------------------------------------------- conv front-end adjoint
-@pytest.mark.parametrize("T,X,F,N", [(8, 8, 8, 21), (6, 10, 4, 9), (16, 16, 16, 300), (4, 4, 3, 400)])
+# register-tiled kernels: F in {8, 16, 32}; X == F folds the index arithmetic; even X / even pooled X take the
+# paired-position phases, odd ones the single-position phases; other F: the generic kernel
+@pytest.mark.parametrize("T,X,F,N", [(8, 8, 8, 21), (6, 10, 4, 9), (16, 16, 16, 300), (4, 4, 3, 400), (8, 12, 8, 50),
+                                     (6, 10, 16, 40), (8, 7, 8, 30), (8, 8, 32, 20)])
 def test_conv3d_backward_against_autograd(T, X, F, N):
     """l2hmc_conv3d_backward vs torch autograd through the oracle's Conv3D/MaxPool3D stack (conv_net.py:247-260),
     with per-chain mask sets and more chains than partial rows (accumulation across CTA passes)."""
