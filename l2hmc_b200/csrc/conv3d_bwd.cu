@@ -49,9 +49,12 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
   float* in_s = sm;                       // [T][X][2] (masked input)
   float* mk_s = in_s + D;                 // [T][X][2] the mask actually applied (1 if none)
   float* c1 = mk_s + D;                   // [T][X][2][F+1]    conv-1 output, later its gradient
-  float* p1 = c1 + D * FP;                // [T2][X2][F]       pool-1 output
-  float* c2 = p1 + T2 * X2 * F;           // [T2][X2][2F]      conv-2 output, later its gradient
-  float* gp1 = c2 + T2 * X2 * C2;         // [T2][X2][F]       gradient of the pool-1 output
+  // pool-1 / conv-2 rows: +4 on the fast path too -- lanes that read 2 or 4 different positions with 128-bit loads
+  // (rows 2F or 4F floats apart: the same banks) otherwise serialise
+  const int PS = kFast ? F + 4 : F, CS = kFast ? C2 + 4 : C2;
+  float* p1 = c1 + D * FP;                // [T2][X2][PS]      pool-1 output
+  float* c2 = p1 + T2 * X2 * PS;          // [T2][X2][CS]      conv-2 output, later its gradient
+  float* gp1 = c2 + T2 * X2 * CS;         // [T2][X2][F]       gradient of the pool-1 output
   float* w1s = gp1 + T2 * X2 * F;         // [3][3][2][F]
   float* w2s = w1s + 18 * F;              // [2][2][F][2F+1]   (kd = 0 taps)
   const int tid = threadIdx.x;
@@ -177,7 +180,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
           if (t >= T || x >= X) continue;
           for (int d = 0; d < 2; ++d) best = fmaxf(best, c1[((t * X + x) * 2 + d) * FP + f]);
         }
-      p1[i] = best;
+      p1[(t2 * X2 + x2) * PS + f] = best;
     }
     __syncthreads();
     if (kFast && (X2 & 1) == 0) {       // thread = (two adjacent positions, 4 output channels): one weight load, 8 FMAs
@@ -192,12 +195,12 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
             const int tt = t + kt, xx = x + kx;          // xx <= X2 - 1; the second position's tap may fall outside
             if (tt >= T2) continue;
             const bool okb = xx + 1 < X2;
-            const float* a = p1 + (tt * X2 + xx) * F;
+            const float* a = p1 + (tt * X2 + xx) * PS;
             const float* w = w2s + ((kt * 2 + kx) * F) * CP + co4;
 #pragma unroll
             for (int c4 = 0; c4 < F; c4 += 4) {
               const float4 av = *reinterpret_cast<const float4*>(a + c4);
-              const float4 bv = okb ? *reinterpret_cast<const float4*>(a + F + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+              const float4 bv = okb ? *reinterpret_cast<const float4*>(a + PS + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
               const float aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
               for (int q = 0; q < 4; ++q) {
@@ -209,10 +212,10 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
               }
             }
           }
-        float* o = c2 + (t * X2 + x) * C2 + co4;
+        float* o = c2 + (t * X2 + x) * CS + co4;
         *reinterpret_cast<float4*>(o) =
             make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-        *reinterpret_cast<float4*>(o + C2) =
+        *reinterpret_cast<float4*>(o + CS) =
             make_float4(fmaxf(bcc[0], 0.f), fmaxf(bcc[1], 0.f), fmaxf(bcc[2], 0.f), fmaxf(bcc[3], 0.f));
       }
     } else if (kFast) {       // thread = (position, 4 output channels)
@@ -225,7 +228,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
           for (int kx = 0; kx < 2; ++kx) {
             const int tt = t + kt, xx = x + kx;
             if (tt >= T2 || xx >= X2) continue;
-            const float* a = p1 + (tt * X2 + xx) * F;
+            const float* a = p1 + (tt * X2 + xx) * PS;
             const float* w = w2s + ((kt * 2 + kx) * F) * CP + co4;
 #pragma unroll
             for (int c4 = 0; c4 < F; c4 += 4) {
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
               }
             }
           }
-        *reinterpret_cast<float4*>(c2 + pos * C2 + co4) =
+        *reinterpret_cast<float4*>(c2 + pos * CS + co4) =
             make_float4(fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
       }
     } else
@@ -250,7 +253,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
         for (int kx = 0; kx < 2; ++kx) {
           const int tt = t + kt, xx = x + kx;
           if (tt >= T2 || xx >= X2) continue;
-          const float* a = p1 + (tt * X2 + xx) * F;
+          const float* a = p1 + (tt * X2 + xx) * PS;
           const float* w = w2s + ((kt * 2 + kx) * F) * CP + co;
 #pragma unroll 8
           for (int ci = 0; ci < F; ++ci) acc = fmaf(a[ci], w[ci * CP], acc);
@@ -268,7 +271,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
         for (int b = 0; b < 2; ++b) {
           const int t = 2 * t4 + a, x = 2 * x4 + b;
           if (t >= T2 || x >= X2) continue;
-          const int at = (t * X2 + x) * C2 + co;
+          const int at = (t * X2 + x) * CS + co;
           if (c2[at] > best) best = c2[at], arg = at;
         }
       const float g = best > 0.f ? gf[i] : 0.f;
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
         for (int b = 0; b < 2; ++b) {
           const int t = 2 * t4 + a, x = 2 * x4 + b;
           if (t >= T2 || x >= X2) continue;
-          const int at = (t * X2 + x) * C2 + co;
+          const int at = (t * X2 + x) * CS + co;
           c2[at] = at == arg ? g : 0.f;
         }
     }
@@ -289,14 +292,14 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
 #pragma unroll
         for (int j = 0; j < 8; ++j) s8[j] = 0.f;
         for (int t = 0; t + kt < T2; ++t) {
-          const float* a = p1 + ((t + kt) * X2 + kx) * F + ci0;
-          const float* g = c2 + (t * X2) * C2 + co;
+          const float* a = p1 + ((t + kt) * X2 + kx) * PS + ci0;
+          const float* g = c2 + (t * X2) * CS + co;
           const int nx = X2 - kx;
 #pragma unroll 2
           for (int x = 0; x < nx; ++x) {
-            const float gv = g[x * C2];
-            const float4 a0 = *reinterpret_cast<const float4*>(a + x * F);
-            const float4 a1 = *reinterpret_cast<const float4*>(a + x * F + 4);
+            const float gv = g[x * CS];
+            const float4 a0 = *reinterpret_cast<const float4*>(a + x * PS);
+            const float4 a1 = *reinterpret_cast<const float4*>(a + x * PS + 4);
             s8[0] = fmaf(a0.x, gv, s8[0]), s8[1] = fmaf(a0.y, gv, s8[1]), s8[2] = fmaf(a0.z, gv, s8[2]);
             s8[3] = fmaf(a0.w, gv, s8[3]), s8[4] = fmaf(a1.x, gv, s8[4]), s8[5] = fmaf(a1.y, gv, s8[5]);
             s8[6] = fmaf(a1.z, gv, s8[6]), s8[7] = fmaf(a1.w, gv, s8[7]);
@@ -310,17 +313,17 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
       const int co = i % C2, ci = (i / C2) % F, kk = i / (C2 * F), kt = kk >> 1, kx = kk & 1;
       float s = 0.f;
       for (int t = 0; t + kt < T2; ++t) {
-        const float* a = p1 + ((t + kt) * X2 + kx) * F + ci;
-        const float* g = c2 + (t * X2) * C2 + co;
+        const float* a = p1 + ((t + kt) * X2 + kx) * PS + ci;
+        const float* g = c2 + (t * X2) * CS + co;
         const int nx = X2 - kx;
 #pragma unroll 4
-        for (int x = 0; x < nx; ++x) s = fmaf(a[x * F], g[x * C2], s);
+        for (int x = 0; x < nx; ++x) s = fmaf(a[x * PS], g[x * CS], s);
       }
       part[off_w2 + ((kk * 2 + 0) * F + ci) * C2 + co] += s;
     }
     for (int co = tid; co < C2; co += kThreads) {
       float s = 0.f;
-      for (int j = 0; j < T2 * X2; ++j) s += c2[j * C2 + co];
+      for (int j = 0; j < T2 * X2; ++j) s += c2[j * CS + co];
       part[off_b2 + co] += s;
     }
     if (kFast && (X2 & 1) == 0) {
@@ -332,13 +335,13 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
         for (int kt = 0; kt < 2 && kt <= t; ++kt)
           for (int kx = 0; kx < 2; ++kx) {
             const bool oka = x1 - 1 - kx >= 0;
-            const float* gb = c2 + ((t - kt) * X2 + x1 - kx) * C2;          // gradient row read by position x1
+            const float* gb = c2 + ((t - kt) * X2 + x1 - kx) * CS;          // gradient row read by position x1
             const float* w = w2s + ((kt * 2 + kx) * F + ci) * CP;
 #pragma unroll
             for (int c4 = 0; c4 < C2; c4 += 4) {
               const float4 wv = *reinterpret_cast<const float4*>(w + c4);
               const float4 gv = *reinterpret_cast<const float4*>(gb + c4);
-              const float4 ga = oka ? *reinterpret_cast<const float4*>(gb - C2 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+              const float4 ga = oka ? *reinterpret_cast<const float4*>(gb - CS + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
               sb[0] = fmaf(wv.x, gv.x, sb[0]), sb[1] = fmaf(wv.y, gv.y, sb[1]);
               sb[2] = fmaf(wv.z, gv.z, sb[2]), sb[3] = fmaf(wv.w, gv.w, sb[3]);
               sa[0] = fmaf(wv.x, ga.x, sa[0]), sa[1] = fmaf(wv.y, ga.y, sa[1]);
@@ -356,7 +359,7 @@ __global__ void __launch_bounds__(kThreads, 3) conv3d_bwd_kernel(const ConvBwdPa
       float s4[4] = {0.f, 0.f, 0.f, 0.f};       // fast path: four independent chains, joined in fixed order below
       for (int kt = 0; kt < 2 && kt <= t; ++kt)
         for (int kx = 0; kx < 2 && kx <= x; ++kx) {
-          const float* g = c2 + ((t - kt) * X2 + x - kx) * C2;
+          const float* g = c2 + ((t - kt) * X2 + x - kx) * CS;
           const float* w = w2s + ((kt * 2 + kx) * F + ci) * CP;
           if (kFast) {
 #pragma unroll
@@ -575,8 +578,9 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, D = 2 * T * X;
   const bool fast = (F == 8 || F == 16 || F == 32) && D % 4 == 0;   // float4 rows need 16-byte aligned buffers
   const size_t fp = fast ? F + 4 : F + 1, cp = fast ? 2 * F + 4 : 2 * F + 1;
-  const size_t floats = 2u * D + static_cast<size_t>(D) * fp + 2u * T2 * X2 * F + static_cast<size_t>(T2) * X2 * 2 * F +
-                        18u * F + 4u * F * cp;
+  const size_t ps = fast ? F + 4 : F, cs = fast ? 2 * F + 4 : 2 * F;       // pool-1 / conv-2 row strides
+  const size_t floats = 2u * D + static_cast<size_t>(D) * fp + static_cast<size_t>(T2) * X2 * (ps + F + cs) + 18u * F +
+                        4u * F * cp;
   const size_t smem = floats * sizeof(float);
   int dev = 0, max_smem = 0;
   cudaGetDevice(&dev);
