@@ -61,6 +61,7 @@ struct TcParams {
   const uint8_t* row_set;  // nullable [rows]
   float* out_ts;       // next layer's A operand (TS32), out_rg row groups, out_kb K blocks
   int out_rg, out_kb;
+  float* out_rm;       // nullable: the same activations row-major fp32 [rows, cols] (training tape)
   // heads epilogue
   const float* b_s;
   const float* b_tr;
@@ -354,17 +355,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
             float* dst = p.out_ts + ((static_cast<size_t>(kb) * p.out_rg + rg) * 2) * 256 + r8 * 4;
 #pragma unroll
             for (int kc = 0; kc < 8; ++kc) {
-              float h[4], l[4];
+              float h[4], l[4], o[4];
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int n = n0 + kc * 4 + j;
                 const float b = n < p.cols ? __ldg(bias + n) : 0.f;
-                const float o = fmaxf(__fadd_rn(sum[g][kc * 4 + j], b), 0.f);
-                h[j] = tf32_hi(o);
-                l[j] = tf32_lo(o, h[j]);
+                o[j] = fmaxf(__fadd_rn(sum[g][kc * 4 + j], b), 0.f);
+                h[j] = tf32_hi(o[j]);
+                l[j] = tf32_lo(o[j], h[j]);
               }
               *reinterpret_cast<float4*>(dst + kc * 32) = make_float4(h[0], h[1], h[2], h[3]);
               *reinterpret_cast<float4*>(dst + 256 + kc * 32) = make_float4(l[0], l[1], l[2], l[3]);
+              if (p.out_rm != nullptr && r < p.rows) {
+                float* rm = p.out_rm + static_cast<size_t>(r) * p.cols + n0 + kc * 4;
+                if (n0 + kc * 4 + 3 < p.cols && (reinterpret_cast<uintptr_t>(rm) & 15u) == 0) {
+                  *reinterpret_cast<float4*>(rm) = make_float4(o[0], o[1], o[2], o[3]);
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 4; ++j)
+                    if (n0 + kc * 4 + j < p.cols) rm[j] = o[j];
+                }
+              }
             }
           }
         }
@@ -638,11 +649,12 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   p.m_tiles = m_tiles, p.n_tiles = narrow ? (H + 127) / 128 : (H + 255) / 256;
   p.debug_noload = debug_noload;
   p.rows = N, p.cols = H, p.bias = bias_eff, p.bias_alt = bias_eff + d.h_rows, p.row_set = c->row_set;
-  p.out_ts = h1, p.out_rg = rg, p.out_kb = d.kbH;
+  p.out_ts = h1, p.out_rg = rg, p.out_kb = d.kbH, p.out_rm = c->h1_out;
   rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
   if (rc) return rc;
 
   p.A = h1, p.B = W2, p.KB = d.kbH, p.bias = w->b_h, p.bias_alt = nullptr, p.row_set = nullptr, p.out_ts = h2;
+  p.out_rm = c->h2_out;
   rc = narrow ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
   if (rc) return rc;
 
@@ -666,13 +678,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
     logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, 2 * d.d_tiles, N, c->logdet);
     rc = check_launch("logdet_reduce_tc_kernel");
   }
-  if (rc == L2HMC_OK && c->h1_out != nullptr) {
-    // training tape: the hidden activations back in row-major fp32 (hi + lo is the fp32 value up to 2^-22; its
-    // sign, i.e. the ReLU mask the backward pass reads, is exact)
-    ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(N) * H), 256, 0, st>>>(h1, rg, N, H, c->h1_out);
-    ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(N) * H), 256, 0, st>>>(h2, rg, N, H, c->h2_out);
-    rc = check_launch("ts32_to_rowmajor_kernel");
-  }
+  // training tape (h1_out / h2_out): the layer epilogues above also wrote the hidden activations row-major fp32
   return rc;
 }
 

@@ -655,6 +655,46 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ param, co
 using namespace l2hmc;
 
 // =============================================================================================== C ABI
+// Skinny products (M <= 4 output rows over a long K: the t_layer kernel's gradient, [2, tape rows] x [tape rows, H]):
+// a weighted column sum -- threads along the contiguous columns of B, K in slabs, M accumulators per thread; the
+// slab partials [slab][M][N] go through the split-K reduce stage like any other split product.
+constexpr int kSkinnyMaxM = 4, kSkinnyMinK = 2048;
+template <int MM>
+__global__ void __launch_bounds__(128) skinny_gemm_kernel(const l2hmc_gemm_args g, int slabs, float* partial) {
+  const int n = blockIdx.x * 128 + threadIdx.x;
+  if (n >= g.N) return;
+  const l2hmc_gemm_seg sg = g.seg[0];
+  const int per = (sg.K + slabs - 1) / slabs;
+  const int k0 = blockIdx.y * per, k1 = min(sg.K, k0 + per);
+  float acc[MM];
+#pragma unroll
+  for (int m = 0; m < MM; ++m) acc[m] = 0.f;
+  int k = k0;
+  for (; k + 7 < k1; k += 8) {
+    float b[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b[j] = sg.B[static_cast<long long>(k + j) * sg.b_rs + n];      // 8 loads in flight
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int m = 0; m < MM; ++m)
+        if (m < g.M) acc[m] = fmaf(__ldg(sg.A + m * sg.a_rs + static_cast<long long>(k + j) * sg.a_cs), b[j], acc[m]);
+  }
+  for (; k < k1; ++k) {
+    const float b = sg.B[static_cast<long long>(k) * sg.b_rs + n];
+#pragma unroll
+    for (int m = 0; m < MM; ++m)
+      if (m < g.M) acc[m] = fmaf(__ldg(sg.A + m * sg.a_rs + static_cast<long long>(k) * sg.a_cs), b, acc[m]);
+  }
+#pragma unroll
+  for (int m = 0; m < MM; ++m)
+    if (m < g.M) partial[(static_cast<size_t>(blockIdx.y) * g.M + m) * g.N + n] = acc[m];
+}
+static int skinny_slabs(const l2hmc_gemm_args* g) {      // 0: not a skinny product
+  if (g->M > kSkinnyMaxM || g->nseg != 1 || g->seg[0].b_cs != 1 || g->seg[0].K < kSkinnyMinK) return 0;
+  return std::min(128, g->seg[0].K / 32);
+}
+
 // ksplit = 0: enough K slices to put ~1.5 CTAs on every SM when the output has few tiles (the per-call GEMMs of a
 // config-2 training step are 32-tile launches), each slice keeping at least two K slabs
 static int auto_ksplit(const l2hmc_gemm_args* g) {
@@ -667,6 +707,7 @@ static int auto_ksplit(const l2hmc_gemm_args* g) {
 
 extern "C" size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {
   if (!g || g->nseg < 1 || g->nseg > 3) return 0;
+  if (skinny_slabs(g)) ksplit = skinny_slabs(g);
   if (ksplit == 0) ksplit = auto_ksplit(g);
   if (ksplit <= 1) return 0;
   return sizeof(float) * static_cast<size_t>(ksplit) * g->M * g->N;
@@ -680,6 +721,8 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   L2HMC_REQUIRE(g->C, "l2hmc_sgemm: null C");
   for (int s = 0; s < g->nseg; ++s)
     L2HMC_REQUIRE(g->seg[s].A && g->seg[s].B && g->seg[s].K >= 0, "l2hmc_sgemm: bad segment %d", s);
+  const int skinny = skinny_slabs(g);
+  if (skinny) ksplit = skinny;
   if (ksplit == 0) ksplit = auto_ksplit(g);
   if (ksplit < 1) ksplit = 1;
   if (ksplit > 1)
@@ -688,6 +731,12 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
                   l2hmc_sgemm_workspace_bytes(g, ksplit));
   if (g->row_set) L2HMC_REQUIRE(!g->col_scale == !g->col_scale_alt, "l2hmc_sgemm: col_scale and col_scale_alt go together");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (skinny) {
+    skinny_gemm_kernel<kSkinnyMaxM><<<dim3((g->N + 127) / 128, skinny), 128, 0, st>>>(*g, skinny,
+                                                                                     static_cast<float*>(workspace));
+    int rc = check_launch("skinny_gemm_kernel");
+    return rc ? rc : l2hmc::launch_splitk_reduce(static_cast<float*>(workspace), skinny, g, st);
+  }
   GemmParams p{*g, ksplit, static_cast<float*>(workspace)};
   dim3 grid((g->N + GBN - 1) / GBN, (g->M + GBM - 1) / GBM, ksplit);
   const bool akc = g->seg[0].a_cs == 1, bkc = g->seg[0].b_rs == 1 && g->seg[0].b_cs != 1;
@@ -802,8 +851,9 @@ extern "C" int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, c
   return check_launch("loss_bwd_kernel");
 }
 
-// enough slabs that the loads in flight cover HBM latency (40 960 tape rows: 512 slabs x 8 column tiles of CTAs)
-static int colsum_slabs(int rows) { return std::max(1, std::min(512, rows / 32)); }
+// enough slabs that the loads in flight cover HBM latency (40 960 tape rows: 128 slabs x 8 column tiles of CTAs,
+// 8 loads per thread), few enough that the serial second stage stays short
+static int colsum_slabs(int rows) { return std::max(1, std::min(128, rows / 32)); }
 
 extern "C" size_t l2hmc_col_sum_workspace_bytes(int rows, int cols) {
   if (rows <= 0 || cols <= 0) return 0;

@@ -38,7 +38,10 @@ def close_scaled(got, want, tol=2e-4, what=""):
 
 # --------------------------------------------------------------------------------------------- SGEMM
 @pytest.mark.parametrize("M,N,K,ta,tb", [(70, 130, 50, False, False), (64, 64, 16, False, True), (33, 257, 100, True, False),
-                                         (1, 200, 777, True, False), (3, 64, 1000, True, True), (256, 512, 384, False, True)])
+                                         (1, 200, 777, True, False), (3, 64, 1000, True, True), (256, 512, 384, False, True),
+                                         # M <= 4 over a long K with row-major B: the weighted-column-sum kernel
+                                         (2, 1000, 5003, True, False), (4, 130, 2560, False, False),
+                                         (1, 64, 40960, True, False)])
 def test_sgemm_forms(M, N, K, ta, tb):
     from l2hmc_b200 import _lib
     from l2hmc_b200.training import _Gemm, _ptr
