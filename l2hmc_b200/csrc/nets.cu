@@ -187,9 +187,11 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
         if (CW == 4) {
           const float4 t = *reinterpret_cast<const float4*>(&Bs[k][g * GS + 4 * tx]);
           b[g * CW + 0] = t.x, b[g * CW + 1] = t.y, b[g * CW + 2] = t.z, b[g * CW + 3] = t.w;
-        } else {
+        } else if (CW == 2) {
           const float2 t = *reinterpret_cast<const float2*>(&Bs[k][g * GS + 2 * tx]);
           b[g * CW + 0] = t.x, b[g * CW + 1] = t.y;
+        } else {
+          b[g * CW] = Bs[k][g * GS + tx];
         }
       }
 #pragma unroll
@@ -323,7 +325,10 @@ int launch_layer(const DenseParams& p, cudaStream_t st) {
 
 }  // namespace
 
-int heads_col_tiles(int D) { return (D + 31) / 32; }
+// Heads: a CTA owns 32 outputs of all three heads; when that leaves most SMs idle (config 2: 256 stacked rows x 128
+// outputs = 16 CTAs), 16 outputs.  The per-row log-det partials are one per column tile either way.
+static bool heads_narrow(int D, int N) { return ((D + 31) / 32) * ((N + BM - 1) / BM) < 74; }
+int heads_col_tiles(int D, int N) { return heads_narrow(D, N) ? (D + 15) / 16 : (D + 31) / 32; }
 
 // Layers 1, 2 and the heads on the FFMA path (also called by gemm_tc.cu for shapes it rejects).
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
@@ -366,12 +371,18 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
   p.eps = c->eps, p.dir = c->dir, p.uout = c->out, p.flag = c->nonfinite_flag;
   p.row_set = c->row_set, p.umask_alt = c->mask_alt, p.uinvert_alt = c->mask_invert_alt, p.dir_alt = c->dir_alt;
   p.ld_part = c->logdet ? ld_part : nullptr;
-  if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 2, kHeadsStq>(p, st);
-  else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 2, kHeadsMomentum>(p, st);
-  else rc = launch_dense<3, 2, kHeadsPosition>(p, st);
+  if (heads_narrow(D, N)) {
+    if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 1, kHeadsStq>(p, st);
+    else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 1, kHeadsMomentum>(p, st);
+    else rc = launch_dense<3, 1, kHeadsPosition>(p, st);
+  } else {
+    if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 2, kHeadsStq>(p, st);
+    else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 2, kHeadsMomentum>(p, st);
+    else rc = launch_dense<3, 2, kHeadsPosition>(p, st);
+  }
   if (rc) return rc;
   if (c->mode != L2HMC_NET_STQ && c->logdet) {
-    logdet_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, heads_col_tiles(D), N, c->logdet);
+    logdet_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, heads_col_tiles(D, N), N, c->logdet);
     rc = check_launch("logdet_reduce_kernel");
   }
   return rc;
@@ -425,7 +436,7 @@ extern "C" size_t l2hmc_net_workspace_bytes(int K, int H, int D, int N) {
   if (K <= 0 || H <= 0 || D <= 0 || N <= 0) return 16;
   // h1, h2 [N,H] (fp32 row-major on the FFMA path; tiled hi/lo pairs on the tcgen05 path need
   // 2x and 128-row padding) + log-det partials [D/32][N]
-  const size_t simt = 2 * static_cast<size_t>(N) * H + static_cast<size_t>(heads_col_tiles(D)) * N;
+  const size_t simt = 2 * static_cast<size_t>(N) * H + static_cast<size_t>((D + 15) / 16) * N;   // log-det partials at the finer column tiling (monotonic in N)
   return sizeof(float) * std::max(simt, tc_workspace_floats(K, H, D, N)) + 256;
 }
 

@@ -21,6 +21,6 @@ bool tc_eligible(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
-int heads_col_tiles(int D);
+int heads_col_tiles(int D, int N);
 
 }  // namespace l2hmc
