@@ -732,9 +732,23 @@ namespace {
 // strided fp32 operand -> TS32: element (r, k) = src[r * rs + k * cs]; rows >= `rows` and k >= K are zero; K blocks
 // [kb0, kb0 + nkb) of a buffer with rg_total row groups.  Serves A (rows = output rows) and B (rows = output columns)
 // in NN / NT / TN forms without a transposed copy.
-__global__ void __launch_bounds__(256) ts32_from_strided_kernel(const float* __restrict__ src, long long rs, long long cs,
-                                                                int rows, int K, float* dst, int rg_total, int kb0,
-                                                                int nkb) {
+// One launch converts every operand segment of a product (blockIdx.y = job): up to 3 segments x (A, B).
+struct Ts32Job {
+  const float* src;
+  long long rs, cs;
+  int rows, K;
+  float* dst;
+  int rg_total, kb0, nkb;
+};
+struct Ts32Jobs {
+  Ts32Job j[6];
+};
+__global__ void __launch_bounds__(256) ts32_from_strided_kernel(const Ts32Jobs jobs) {
+  const Ts32Job& jb = jobs.j[blockIdx.y];
+  const float* __restrict__ src = jb.src;
+  const long long rs = jb.rs, cs = jb.cs;
+  const int rows = jb.rows, K = jb.K, rg_total = jb.rg_total, kb0 = jb.kb0, nkb = jb.nkb;
+  float* dst = jb.dst;
   const size_t total = static_cast<size_t>(nkb) * rg_total * 64;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
@@ -816,19 +830,24 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
   const TcGemmDims d = tc_gemm_dims(g);
   float* a_ts = static_cast<float*>(workspace);
   float* b_ts = a_ts + d.a_floats;
-  int kb0 = 0;
+  int kb0 = 0, njobs = 0, gx = 1;
+  Ts32Jobs jobs{};
   for (int s = 0; s < g->nseg; ++s) {
     const l2hmc_gemm_seg& sg = g->seg[s];
     const int nkb = (sg.K + 31) / 32;
     if (nkb == 0) continue;
-    ts32_from_strided_kernel<<<ew_grid(static_cast<size_t>(nkb) * (d.rows_p / 8) * 64), 256, 0, st>>>(
-        sg.A, sg.a_rs, sg.a_cs, g->M, sg.K, a_ts, d.rows_p / 8, kb0, nkb);
+    jobs.j[njobs++] = Ts32Job{sg.A, sg.a_rs, sg.a_cs, g->M, sg.K, a_ts, d.rows_p / 8, kb0, nkb};
+    gx = std::max(gx, ew_grid(static_cast<size_t>(nkb) * (d.rows_p / 8) * 64));
     // B operand rows are the output columns: element (n, k) = B[k * b_rs + n * b_cs]
-    ts32_from_strided_kernel<<<ew_grid(static_cast<size_t>(nkb) * (d.n_p / 8) * 64), 256, 0, st>>>(
-        sg.B, sg.b_cs, sg.b_rs, g->N, sg.K, b_ts, d.n_p / 8, kb0, nkb);
+    jobs.j[njobs++] = Ts32Job{sg.B, sg.b_cs, sg.b_rs, g->N, sg.K, b_ts, d.n_p / 8, kb0, nkb};
+    gx = std::max(gx, ew_grid(static_cast<size_t>(nkb) * (d.n_p / 8) * 64));
     kb0 += nkb;
   }
-  int rc = check_launch("ts32_from_strided_kernel");
+  int rc = L2HMC_OK;
+  if (njobs > 0) {
+    ts32_from_strided_kernel<<<dim3(gx, njobs), 256, 0, st>>>(jobs);
+    rc = check_launch("ts32_from_strided_kernel");
+  }
   if (rc) return rc;
   if (d.kb == 0) {
     set_error("l2hmc_tc_gemm: empty K");
