@@ -18,6 +18,8 @@
 // the tape; every WEIGHT gradient is one deferred TN GEMM over the whole tape (K = calls x rows instead of `calls`
 // small GEMMs), split along K with a fixed-order second stage, so results are deterministic (no atomics anywhere).
 // Training shapes (configs 2-3) are small: these kernels are FFMA; the tcgen05 path serves inference.
+#include <cooperative_groups.h>
+
 #include <algorithm>
 
 #include "common.cuh"
@@ -32,7 +34,10 @@ constexpr int GBM = 64, GBN = 64, GBK = 16, kGemmThreads = 256;
 struct GemmParams {
   l2hmc_gemm_args a;
   int ksplit;
-  float* partial;   // [ksplit][M*N] when ksplit > 1
+  float* partial;   // [ksplit][M*N] when ksplit > 1 and the K ranges are not a cluster
+  int cluster;      // 1: the ksplit (<= 8) CTAs of a tile form a thread-block cluster along z; rank 0 adds the other
+                    // ranks' accumulators out of their shared memory in rank order (the same order as
+                    // splitk_reduce_kernel) and runs the epilogue -- no partial round trip, no second launch
 };
 
 // 4-byte async copy global -> shared (LDGSTS), zero-filled when !valid: operand tiles are transposed on the fly
@@ -137,6 +142,32 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
   }
   cp_async_wait<0>();
 
+  if (p.cluster) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    float* red = &As[0][0][0];             // 64 x 64 accumulators; the operand ring is drained
+    __syncthreads();
+    if (z != 0) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<float4*>(red + (4 * ty + i) * GBN + 4 * tx) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    }
+    cl.sync();
+    if (z == 0) {
+      for (int q = 1; q < p.ksplit; ++q) {
+        const float* remote = cl.map_shared_rank(red, q);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 v = *reinterpret_cast<const float4*>(remote + (4 * ty + i) * GBN + 4 * tx);
+          acc[i][0] = __fadd_rn(acc[i][0], v.x), acc[i][1] = __fadd_rn(acc[i][1], v.y);
+          acc[i][2] = __fadd_rn(acc[i][2], v.z), acc[i][3] = __fadd_rn(acc[i][3], v.w);
+        }
+      }
+    }
+    cl.sync();                             // the other ranks' shared memory stays alive until rank 0 has read it
+    if (z != 0) return;
+  }
+
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int r = m0 + 4 * ty + i;
@@ -147,7 +178,7 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
       const int c = n0 + 4 * tx + j;
       if (c >= g.N) continue;
       float val = acc[i][j];
-      if (p.ksplit > 1) {
+      if (p.ksplit > 1 && !p.cluster) {
         p.partial[(static_cast<size_t>(z) * g.M + r) * g.N + c] = val;
         continue;
       }
@@ -737,15 +768,23 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
     int rc = check_launch("skinny_gemm_kernel");
     return rc ? rc : l2hmc::launch_splitk_reduce(static_cast<float*>(workspace), skinny, g, st);
   }
-  GemmParams p{*g, ksplit, static_cast<float*>(workspace)};
+  const int cluster = ksplit >= 2 && ksplit <= 8;      // portable cluster size
+  GemmParams p{*g, ksplit, static_cast<float*>(workspace), cluster};
   dim3 grid((g->N + GBN - 1) / GBN, (g->M + GBM - 1) / GBM, ksplit);
   const bool akc = g->seg[0].a_cs == 1, bkc = g->seg[0].b_rs == 1 && g->seg[0].b_cs != 1;
-  if (akc && bkc) sgemm_kernel<true, true><<<grid, kGemmThreads, 0, st>>>(p);
-  else if (akc) sgemm_kernel<true, false><<<grid, kGemmThreads, 0, st>>>(p);
-  else if (bkc) sgemm_kernel<false, true><<<grid, kGemmThreads, 0, st>>>(p);
-  else sgemm_kernel<false, false><<<grid, kGemmThreads, 0, st>>>(p);
+  void (*kern)(const GemmParams) = akc && bkc ? sgemm_kernel<true, true>
+                                   : akc      ? sgemm_kernel<true, false>
+                                   : bkc      ? sgemm_kernel<false, true>
+                                              : sgemm_kernel<false, false>;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = dim3(kGemmThreads), cfg.dynamicSmemBytes = 0, cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 1, attr.val.clusterDim.y = 1, attr.val.clusterDim.z = cluster ? ksplit : 1;
+  cfg.attrs = &attr, cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, kern, p) != cudaSuccess) return check_launch("sgemm_kernel");
   int rc = check_launch("sgemm_kernel");
-  if (rc || ksplit == 1) return rc;
+  if (rc || ksplit == 1 || cluster) return rc;
   return l2hmc::launch_splitk_reduce(p.partial, ksplit, g, st);
 }
 
