@@ -650,13 +650,23 @@ __global__ void __launch_bounds__(128) colsum_stage1_kernel(const float* __restr
   for (; r < r1; ++r) s[0] += B[static_cast<long long>(r) * ld + c];
   partial[static_cast<size_t>(blockIdx.y) * cols + c] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
 }
-__global__ void __launch_bounds__(128) colsum_stage2_kernel(const float* __restrict__ partial, int slabs, int cols,
+// stage 2: a CTA owns 32 columns; warp g adds slabs g, g + 8, ... and the 8 warp sums meet in warp order
+__global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restrict__ partial, int slabs, int cols,
                                                             float* out) {
-  const int c = blockIdx.x * 128 + threadIdx.x;
-  if (c >= cols) return;
+  __shared__ float sm[8][32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
   float s = 0.f;
-  for (int q = 0; q < slabs; ++q) s += partial[static_cast<size_t>(q) * cols + c];
-  out[c] = s;
+  if (c < cols)
+    for (int q = g; q < slabs; q += 8) s += partial[static_cast<size_t>(q) * cols + c];
+  sm[g][lane] = s;
+  __syncthreads();
+  if (g == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += sm[j][lane];
+    out[c] = t;
+  }
 }
 
 // tf.train.AdamOptimizer (lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) folded on the host):
@@ -890,9 +900,9 @@ extern "C" int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, c
   return check_launch("loss_bwd_kernel");
 }
 
-// enough slabs that the loads in flight cover HBM latency (40 960 tape rows: 128 slabs x 8 column tiles of CTAs,
-// 8 loads per thread), few enough that the serial second stage stays short
-static int colsum_slabs(int rows) { return std::max(1, std::min(128, rows / 32)); }
+// enough slabs that the loads in flight cover HBM latency (40 960 tape rows: 512 slabs x 8 column tiles of CTAs,
+// 8 loads per thread); the second stage splits the slabs over 8 warps
+static int colsum_slabs(int rows) { return std::max(1, std::min(512, rows / 32)); }
 
 extern "C" size_t l2hmc_col_sum_workspace_bytes(int rows, int cols) {
   if (rows <= 0 || cols <= 0) return 0;
@@ -908,7 +918,7 @@ extern "C" int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, f
   const int slabs = colsum_slabs(rows);
   float* partial = static_cast<float*>(workspace);
   colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
-  colsum_stage2_kernel<<<(cols + 127) / 128, 128, 0, st>>>(partial, slabs, cols, out);
+  colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
   return check_launch("colsum_kernel");
 }
 
