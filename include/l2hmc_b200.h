@@ -440,9 +440,12 @@ int l2hmc_mode_switches(const int32_t* mode, int32_t* prev, uint32_t* switches, 
  *   relu_gate (nullable): the product is zeroed where gate[m*ldg + n] <= 0   (d relu: dZ = dH * [h > 0])
  *   col_scale (nullable [N]): multiplies column n by scale[n] (or 1 - scale[n]); rows with row_set[m] != 0 use
  *   col_scale_alt / col_scale_invert_alt  (the `mask * x` input of position_fn, dynamics/gauge_dynamics.py:515-517)
- * ksplit > 1 splits K (of every segment) over grid.z into `workspace` (l2hmc_sgemm_workspace_bytes) and a second
- * kernel sums the slices in fixed order and applies the epilogue: the deferred weight-gradient GEMMs, whose K is the
- * whole tape, and -- ksplit = 0, chosen by the library -- the few-tile per-call GEMMs of a small batch. */
+ * ksplit > 1 splits K (of every segment) over grid.z; the slices are summed in slice order and the epilogue applied
+ * once: up to 8 slices inside a thread-block cluster (rank 0 reads the other ranks' accumulators over distributed shared
+ * memory), more through `workspace` (l2hmc_sgemm_workspace_bytes) and a second kernel -- the same sums either way.
+ * Used by the deferred weight-gradient GEMMs, whose K is the whole tape, and -- ksplit = 0, chosen by the library --
+ * the few-tile per-call GEMMs of a small batch.  M <= 4 over K >= 2048 with row-major B (the t_layer kernel's
+ * gradient) runs as a weighted column sum with the library's own slab count. */
 typedef struct {
   const float* A;
   long long a_rs, a_cs;
@@ -471,7 +474,8 @@ int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace, size_t wo
 /* The same product on the tcgen05 tensor cores (3xTF32 split: hi.lo + lo.hi + hi.hi, fp32 accumulation flushed every
  * 128 K into round-to-nearest register sums, so the result is fp32-accurate): both operands are first converted from
  * their strided fp32 form into the tiled TS32 layout inside `workspace` (l2hmc_tc_gemm_workspace_bytes), any of the
- * NN / NT / TN forms without a transposed copy; same epilogues as l2hmc_sgemm, written row-major. */
+ * NN / NT / TN forms without a transposed copy; same epilogues as l2hmc_sgemm, written row-major.  Long-K products
+ * with few output tiles are split over K (fixed ranges, fixed summation order) so that all SMs take part. */
 size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g);
 int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t workspace_bytes, void* stream);
 /* What the training step calls: l2hmc_tc_gemm when the product is a dense contraction (M >= 128, N >= 64, K >= 128 and
