@@ -62,7 +62,7 @@ def main():
         out["forward_tape_ms"] = events_ms(fwd, args.iters)
         l0 = eng.launches + eng.gemm.launches
         bwd()
-        out["backward_launches"] = eng.launches + eng.gemm.launches - l0
+        out["backward_launches_estimate"] = eng.launches + eng.gemm.launches - l0   # host-side tally (a GEMM with workspace counts 2); the ncu launch list is exact
         out["backward_ms"] = events_ms(bwd, args.iters)
         out["train_step_ms"] = events_ms(step, args.iters)
         t0 = time.perf_counter()
