@@ -564,6 +564,19 @@ size_t l2hmc_col_sum_workspace_bytes(int rows, int cols);
 int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, float* out, void* workspace, size_t workspace_bytes,
                   void* stream);
 
+/* l2hmc_col_sum WITHOUT a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating library
+ * call, here or on first use): the first-stage partials live in a file-scope `static __device__` array inside the
+ * library (4 MiB; every GPU that loads the library holds it until the process exits).  No counterpart in the
+ * reference: added for callers that cannot allocate (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  Same kernels, same summation order and therefore
+ * the same bits as l2hmc_col_sum.  Limit: colsum row slabs x cols = min(512, max(1, rows / 32)) * cols <=
+ * L2HMC_COL_SUM_STATIC_MAX_FLOATS, else L2HMC_ERR_INVALID with the sizes in l2hmc_last_error().  The device address
+ * of the array is looked up once per device (cudaGetSymbolAddress, with that device current) on the first call
+ * there -- make that first call outside stream capture.  All calls share the one array: calls that overlap on the
+ * GPU (different streams, no ordering between them) race; calls on one stream, or ordered by events, do not. */
+#define L2HMC_COL_SUM_STATIC_MAX_FLOATS (1 << 20)
+int l2hmc_col_sum_static(const float* B, long long ld, int rows, int cols, float* out, void* stream);
+
 /* out[0] = sum v[i] (square = 0) or sum v[i]^2 (square = 1), fixed two-stage tree; scratch: 1024 floats. */
 int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch, void* stream);
 

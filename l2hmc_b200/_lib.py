@@ -233,6 +233,7 @@ SIGNATURES = {
     "l2hmc_u1_train_grads": [POINTER(TrainArgs), c_void_p],
     "l2hmc_col_sum_workspace_bytes": [c_int, c_int],
     "l2hmc_col_sum": [c_void_p, c_longlong, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p],
+    "l2hmc_col_sum_static": [c_void_p, c_longlong, c_int, c_int, c_void_p, c_void_p],
     "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
                         c_float, c_void_p, c_float, c_void_p],

@@ -21,6 +21,7 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <atomic>
 
 #include "common.cuh"
 #include "update_math.cuh"
@@ -920,6 +921,58 @@ extern "C" int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, f
   colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
   colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
   return check_launch("colsum_kernel");
+}
+
+// ----------------------------------------------------------------------------------------------- no-allocation variant
+// l2hmc_col_sum for callers that cannot provide (or allocate) a workspace: the first-stage partials live in a
+// file-scope device array that every GPU loading the library holds until exit.  The array's NAME is only a host-side
+// handle: its device address is looked up once per device with cudaGetSymbolAddress and cached; the kernels get that
+// pointer.  Nothing has to start at zero (stage 1 writes every partial[slab][c] stage 2 reads), but all calls share
+// the array, so two calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) float g_colsum_static_scratch[L2HMC_COL_SUM_STATIC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::atomic<float*> g_colsum_static_ptr[kMaxDevices];   // zero-initialised: nullptr = not looked up on that device yet
+
+int colsum_static_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    set_error("l2hmc_col_sum_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return L2HMC_ERR_CUDA;
+  }
+  float* p = g_colsum_static_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {   // once per device, with that device current (racing threads look up the same address)
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_colsum_static_scratch);
+    if (e != cudaSuccess || sym == nullptr) {
+      set_error("l2hmc_col_sum_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      return L2HMC_ERR_CUDA;
+    }
+    p = static_cast<float*>(sym);
+    g_colsum_static_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return L2HMC_OK;
+}
+}  // namespace
+
+extern "C" int l2hmc_col_sum_static(const float* B, long long ld, int rows, int cols, float* out, void* stream) {
+  L2HMC_REQUIRE(B && out && rows > 0 && cols > 0 && ld >= cols, "l2hmc_col_sum_static: bad arguments");
+  const int slabs = colsum_slabs(rows);
+  const size_t need = static_cast<size_t>(slabs) * cols;
+  L2HMC_REQUIRE(need <= static_cast<size_t>(L2HMC_COL_SUM_STATIC_MAX_FLOATS),
+                "l2hmc_col_sum_static: rows=%d x cols=%d needs %zu scratch floats (%d row slabs x cols), the built-in "
+                "scratch holds L2HMC_COL_SUM_STATIC_MAX_FLOATS = %d; use l2hmc_col_sum with a caller workspace",
+                rows, cols, need, slabs, L2HMC_COL_SUM_STATIC_MAX_FLOATS);
+  float* partial = nullptr;
+  int rc = colsum_static_scratch(&partial);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
+  colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
+  return check_launch("colsum_kernel (static scratch)");
 }
 
 extern "C" int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch /* [1024] */,
