@@ -6,6 +6,7 @@ snapshot.  `python -m l2hmc_b200.build [--force] [--verbose]`.
 """
 import glob
 import os
+import re
 import shutil
 import subprocess
 import sys
@@ -36,6 +37,28 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def _includes(path, seen=None):
+    """Transitive closure of the quoted #include files of `path` (for per-object staleness)."""
+    seen = set() if seen is None else seen
+    try:
+        text = open(path).read()
+    except OSError:
+        return seen
+    for inc in re.findall(r'^\s*#\s*include\s+"([^"]+)"', text, flags=re.M):
+        full = os.path.normpath(os.path.join(os.path.dirname(path), inc))
+        if full not in seen and os.path.exists(full):
+            seen.add(full)
+            _includes(full, seen)
+    return seen
+
+
+def _obj_stale(src, obj):
+    if not os.path.exists(obj):
+        return True
+    t = os.path.getmtime(obj)
+    return any(os.path.getmtime(d) > t for d in [src, os.path.abspath(__file__)] + sorted(_includes(src)))
+
+
 def build(force=False, verbose=False):
     """Compile every CUDA source into one shared library.  Returns the library path."""
     if not force and not _stale():
@@ -48,6 +71,8 @@ def build(force=False, verbose=False):
     for src in sources():  # one nvcc per translation unit, in parallel
         obj = src[:-3] + ".o"
         objs.append(obj)
+        if not force and not verbose and not _obj_stale(src, obj):
+            continue
         cmd = [nvcc] + [f for f in NVCC_FLAGS if f != "-shared"] + (["-Xptxas", "-v"] if verbose else []) + \
               ["-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
