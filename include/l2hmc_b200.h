@@ -587,6 +587,12 @@ int l2hmc_adam_step(float* param, const float* grad, float* m, float* v, long lo
                     float beta2, float epsilon, float grad_scale, const float* grad_sumsq, float clip_norm,
                     void* stream);
 
+/* tf.clip_by_global_norm (gauge_model.py:826-827) on the flat gradient arena, in place: grad *= clip_norm /
+ * max(sqrt(grad_sumsq[0]), clip_norm), grad_sumsq from l2hmc_reduce_sum(square = 1).  The reference clips inside
+ * _calc_loss_and_grads, i.e. per rank BEFORE Horovod averages (gauge_model.py:941-943); same bits as handing the clip
+ * to l2hmc_adam_step. */
+int l2hmc_clip_by_global_norm(float* grad, long long n, const float* grad_sumsq, float clip_norm, void* stream);
+
 /* ------------------------------------------------------------------ one host call = loss + gradients of one step
  * GaugeModel._calc_loss_and_grads (gauge_model.py:805-832 over :728-803 and dynamics/gauge_dynamics.py:195-313):
  * both chains' transitions recorded on a tape, the loss, and the explicit backward sweep -- the launches of the

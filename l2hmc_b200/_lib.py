@@ -235,6 +235,7 @@ SIGNATURES = {
     "l2hmc_col_sum": [c_void_p, c_longlong, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p],
     "l2hmc_col_sum_static": [c_void_p, c_longlong, c_int, c_int, c_void_p, c_void_p],
     "l2hmc_reduce_sum": [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p],
+    "l2hmc_clip_by_global_norm": [c_void_p, c_longlong, c_void_p, c_float, c_void_p],
     "l2hmc_adam_step": [c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_float, c_float, c_float, c_float,
                         c_float, c_void_p, c_float, c_void_p],
     "l2hmc_conv3d_features_sets": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,

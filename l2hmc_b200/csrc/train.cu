@@ -691,6 +691,15 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ param, co
   }
 }
 
+// tf.clip_by_global_norm (gauge_model.py:826-827): every gradient scaled by clip / max(||g||, clip), in place -- the
+// same product adam_kernel forms when it is handed the clip, so clipping first and stepping with no clip gives the
+// same bits.
+__global__ void __launch_bounds__(256) clip_kernel(float* __restrict__ grad, long long n, const float* sumsq, float clip) {
+  const float scale = 1.f * (clip / fmaxf(sqrtf(sumsq[0]) * 1.f, clip));
+  for (long long i = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * 256)
+    grad[i] = grad[i] * scale;
+}
+
 }  // namespace
 }  // namespace l2hmc
 
@@ -986,6 +995,17 @@ extern "C" int l2hmc_reduce_sum(const float* v, long long n, int square, float* 
   if (rc) return rc;
   reduce_stage2_kernel<<<1, 256, 0, st>>>(scratch, nb, out);
   return check_launch("reduce_stage2_kernel");
+}
+
+extern "C" int l2hmc_clip_by_global_norm(float* grad, long long n, const float* grad_sumsq, float clip_norm, void* stream) {
+  if (n == 0) return L2HMC_OK;
+  L2HMC_REQUIRE(grad && grad_sumsq && n > 0 && clip_norm > 0.f, "l2hmc_clip_by_global_norm: bad arguments");
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int nb = static_cast<int>(std::max<long long>(1, std::min<long long>(sms * 8LL, (n + 255) / 256)));
+  clip_kernel<<<nb, 256, 0, static_cast<cudaStream_t>(stream)>>>(grad, n, grad_sumsq, clip_norm);
+  return check_launch("clip_kernel");
 }
 
 extern "C" int l2hmc_adam_step(float* param, const float* grad, float* m, float* v, long long n, float lr_t, float beta1,

@@ -153,16 +153,10 @@ class GaugeModel(object):
         w = dict(self.loss_weights)
         w.update(weights)
         dyn = self.dynamics
-        inj = lambda d: {} if d is None else dict(momentum_f=d[0], momentum_b=d[1], direction_uniform=d[2],
-                                                  accept_uniform=d[3])
+        # the same draws, from the same counters, as the training path (_calc_loss_and_grads)
+        draws_x, z, draws_z = self._draws(x, draws_x, z, draws_z)
+        inj = lambda d: dict(momentum_f=d[0], momentum_b=d[1], direction_uniform=d[2], accept_uniform=d[3])
         x_prop, _, px, x_out = dyn(x, beta, **inj(draws_x))
-        if z is None:
-            z = torch.empty_like(x)
-            with torch.cuda.device(x.device):                  # z ~ N(0,1): its own Philox substream
-                _lib.check(_lib.get_lib().l2hmc_philox_draws(int(dyn.seed) ^ 0x5A5A5A5A, self._z_step, int(dyn.chain_offset), N, D,
-                                                             _lib.dptr(z), None, None, _lib.stream_ptr()))
-            self._z_step += 1
-        z = self._x(z)
         _, _, pz, _ = dyn(z, beta, **inj(draws_z))
         prm = _lib.LossParams()
         prm.metric, prm.loss_scale = _lib.METRICS[self.metric_fn], float(self.loss_scale)
@@ -203,14 +197,16 @@ class GaugeModel(object):
                 _lib.check(lib.l2hmc_philox_draws(int(seed), int(dyn._mc_step), int(dyn.chain_offset), N, D,
                                                   _lib.dptr(v), _lib.dptr(ud), _lib.dptr(ua), _lib.stream_ptr()))
             return v, ud, ua
+        drew = False
         if draws_x is None:
             v, ud, ua = philox(dyn.seed)
-            draws_x = (v, v, ud, ua)
+            draws_x, drew = (v, v, ud, ua), True
         if z is None:
-            z = philox(int(dyn.seed) ^ 0x5A5A5A5A)[0]
+            z, drew = philox(int(dyn.seed) ^ 0x5A5A5A5A)[0], True
         if draws_z is None:
             v, ud, ua = philox(int(dyn.seed) ^ 0x3C3C3C3C)
-            draws_z = (v, v, ud, ua)
+            draws_z, drew = (v, v, ud, ua), True
+        if drew:                       # one counter tick per call whenever any of the three sets came from Philox
             dyn._mc_step += 1
         dv = lambda a: to_device(a, self.device).reshape(N, -1).contiguous()
         d1 = lambda a: to_device(a, self.device).reshape(-1).contiguous()
@@ -219,7 +215,8 @@ class GaugeModel(object):
 
     def _calc_loss_and_grads(self, x, beta, draws_x=None, z=None, draws_z=None, **weights):
         """(loss, grads, x_out, px, x_dq) -- gauge_model.py:805-832.  `grads` is a dict of views into the flat
-        gradient arena keyed 'eps', 'XNet.<layer>.kernel', ... in the order of dynamics.variables."""
+        gradient arena keyed 'eps', 'XNet.<layer>.kernel', ... in the order of dynamics.variables; with clip_grads
+        they are already clipped by their global norm (:826-827), as the reference returns them."""
         x = self._x(x).contiguous()
         w = dict(self.loss_weights)
         w.update(weights)
@@ -232,6 +229,8 @@ class GaugeModel(object):
             else:                          # the same launches driven from Python (kept for tests / debugging)
                 fw = eng.forward(x, beta, draws_x, z, draws_z, w)
                 grads = eng.backward(fw)
+            if self.clip_grads and not fw.get("forward_only"):   # tf.clip_by_global_norm, per rank (:826-827)
+                self._optimizer.clip_by_global_norm(self.clip_value)
         self.last_per_chain_loss, self.last_forward = fw["per_chain"], fw
         return fw["loss"][0], grads, fw["x_out"], fw["px"], fw["x_dq"]
 
@@ -252,13 +251,12 @@ class GaugeModel(object):
         beta = self.beta if beta is None else beta
         loss, grads, x_out, px, x_dq = self._calc_loss_and_grads(samples, beta, **inject)
         eng, opt = self.engine, self._optimizer
-        scale = 1.
-        if self.using_hvd:
+        if self.using_hvd:             # hvd.DistributedOptimizer (:941-943): average of the per-rank (clipped) gradients
             from .sharding import allreduce_mean_
-            allreduce_mean_(eng.params.grad)                      # hvd.DistributedOptimizer: averaged gradients
+            allreduce_mean_(eng.params.grad)
         lr = self.learning_rate()
         with torch.cuda.device(self.device):
-            opt.step(lr, grad_scale=scale, clip_norm=self.clip_value if self.clip_grads else 0.)
+            opt.step(lr)               # the clip (if any) was applied by _calc_loss_and_grads, before the average
         self.global_step += 1
         x_new = self._wrap(x_out)
         actions, plaqs, _, charges = self.lattice.observables(x_new)
@@ -287,9 +285,19 @@ class GaugeModel(object):
         if self.using_hvd:
             import torch.distributed as dist
             from .sharding import broadcast_weights
-            broadcast_weights([eng.params.flat])
+            rank, ws = dist.get_rank(), dist.get_world_size()
+            # each rank owns num_samples chains of the global batch: key its Philox draws by the GLOBAL chain index
+            # (otherwise every rank would draw the same momenta / uniforms and the average would change nothing)
+            if self.dynamics.chain_offset == 0:
+                self.dynamics.chain_offset = rank * self.num_samples
+            elif rank > 0 and self.dynamics.chain_offset < self.num_samples:
+                raise ValueError(f"rank {rank}: chain_offset {self.dynamics.chain_offset} overlaps rank 0's chains")
+            # the masks come from each process's NumPy global RNG: rank 0's are THE model's (they are state, :651-661)
+            mask = self.dynamics.mask.clone()
+            broadcast_weights([eng.params.flat, mask])
+            self.dynamics.set_masks(mask.cpu().numpy())
             eng.params.sync_to_dynamics()
-            train_steps = train_steps // dist.get_world_size()
+            train_steps = train_steps // ws
         history = []
         for step in range(self.global_step, train_steps):
             self.beta = self.update_beta(step) if self.annealing else (self.beta_init if beta_init is None else beta_init)
@@ -306,17 +314,18 @@ class GaugeModel(object):
         """Weights, eps, Adam moments, masks, step, beta and the current samples in one torch.save file (the
         reference pickles the same items next to a TF checkpoint; its on-disk format is not kept)."""
         eng, opt = self.engine, self._optimizer
-        state = {"names": eng.params.names, "shapes": eng.params.shapes, "offsets": eng.params.offsets,
+        state = {"names": list(eng.params.names), "shapes": [list(sh) for sh in eng.params.shapes],
+                 "offsets": [int(o) for o in eng.params.offsets],
                  "flat": eng.params.flat.cpu(), "adam_m": opt.m.cpu(), "adam_v": opt.v.cpu(), "adam_t": opt.t,
                  "global_step": self.global_step, "beta": float(self.beta), "lr": self.learning_rate(),
                  "mask": self.dynamics.mask.cpu(), "mc_step": self.dynamics._mc_step, "z_step": self._z_step,
                  "samples": None if samples is None else to_device(samples, self.device).cpu(),
-                 "params": dict(self.params)}
+                 "params": {k: v for k, v in self.params.items() if isinstance(v, (int, float, str, bool, type(None)))}}
         torch.save(state, path)
 
     def restore_state(self, path):
         """Inverse of save_state; returns the saved samples (or None)."""
-        state = torch.load(path, map_location="cpu", weights_only=False)
+        state = torch.load(path, map_location="cpu", weights_only=True)   # plain tensors / lists / scalars only
         eng, opt = self.engine, self._optimizer
         if list(state["names"]) != list(eng.params.names) or list(state["offsets"]) != list(eng.params.offsets):
             raise ValueError("restore_state: the saved variables do not match this model")

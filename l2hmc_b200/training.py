@@ -621,6 +621,15 @@ class Adam(object):
         self._sumsq = torch.zeros(1, dtype=torch.float32, device=params.flat.device)
         self._scratch = torch.empty(1024, dtype=torch.float32, device=params.flat.device)
 
+    def clip_by_global_norm(self, clip_norm):
+        """tf.clip_by_global_norm on the gradient arena, in place (gauge_model.py:826-827: inside
+        _calc_loss_and_grads, so under Horovod every rank clips its own gradient BEFORE the average)."""
+        P, lib = self.params, _lib.get_lib()
+        _lib.check(lib.l2hmc_reduce_sum(_lib.dptr(P.grad), P.size, 1, _lib.dptr(self._sumsq),
+                                        _lib.dptr(self._scratch), _lib.stream_ptr()))
+        _lib.check(lib.l2hmc_clip_by_global_norm(_lib.dptr(P.grad), P.size, _lib.dptr(self._sumsq), float(clip_norm),
+                                                 _lib.stream_ptr()))
+
     def step(self, lr, grad_scale=1., clip_norm=0.):
         P, lib = self.params, _lib.get_lib()
         self.t += 1

@@ -221,8 +221,75 @@ def gen_l2hmc_cases():
     print("l2hmc_cases.npz", len(out), "arrays")
 
 
+def load_net(net, w):
+    """Install given weights (Keras layouts, oracle key names) into a built reference net."""
+    for nm in net_layers(net):
+        lyr = getattr(net, nm)
+        assert tuple(lyr.kernel.shape) == w[nm + ".kernel"].shape, (nm, tuple(lyr.kernel.shape), w[nm + ".kernel"].shape)
+        lyr.kernel.copy_(torch.as_tensor(w[nm + ".kernel"]))
+        lyr.bias.copy_(torch.as_tensor(w[nm + ".bias"]))
+    net.coeff_scale.copy_(torch.as_tensor(w["coeff_scale"]).reshape(net.coeff_scale.shape))
+    net.coeff_transformation.copy_(torch.as_tensor(w["coeff_transformation"]).reshape(net.coeff_transformation.shape))
+
+
+def gen_l2hmc_config3_case():
+    """BASELINE config 3's shape through the unmodified reference: 16x16, conv3D nets (F = 16, H = 1024), M = 5,
+    eps = 0.25 (globals.py:27-30), N = 4.  The 2 x 3.7 M weights are NOT stored: they are a pure function of
+    default_rng(WEIGHT_SEED) (tests/parity_util.trained_like_weights); the file keeps their sha256."""
+    sys.path.insert(0, os.path.dirname(HERE))
+    from parity_util import trained_like_weights, weights_digest
+    out = {}
+    arch, T, X, N, M, eps, beta, wseed = "conv3D", 16, 16, 4, 5, 0.25, 3.0, 316
+    rng = np.random.default_rng(31)
+    lat = make_lattice(T, X, N)
+    dyn = make_dynamics(lat, hmc=False, num_steps=M, eps=eps, network_arch=arch)
+    D = 2 * T * X
+    tag = f"{arch}.{T}x{X}"
+    out[tag + ".meta"] = np.array([T, X, N, M], dtype=np.int64)
+    out[tag + ".eps"], out[tag + ".beta"] = np.float32(eps), np.float32(beta)
+    out[tag + ".mask"] = npf(dyn.mask)
+    x, v_f, v_b, u_dir, u_acc = common_inputs(rng, N, D, out, tag)
+    # links near a thermalised configuration (fluctuations around the cold start) and heads of O(0.1): the accept
+    # probabilities then spread over (1e-4, 1) instead of underflowing as they do from a hot start at this eps
+    x = np.mod(rng.normal(0, 0.5, size=(N, D)), 2 * np.pi).astype(np.float32)
+    out[tag + ".x"] = x
+    tvec = dyn._format_time(tf.constant(0.0, dtype=tf.float32), tile=N)
+    dyn.position_fn([torch.as_tensor(v_f), torch.as_tensor(x), tvec])     # builds the lazily-created layers
+    dyn.momentum_fn([torch.as_tensor(x), torch.as_tensor(v_f), tvec])
+    ws = trained_like_weights(arch, T, X, np.random.default_rng(wseed), gain=1.0)
+    load_net(dyn.position_fn, ws["XNet"])
+    load_net(dyn.momentum_fn, ws["VNet"])
+    out[tag + ".weight_seed"] = np.int64(wseed)
+    out[tag + ".weight_sha256"] = np.frombuffer(bytes.fromhex(weights_digest(ws)), dtype=np.uint8)
+    b = tf.constant(beta, dtype=tf.float32)
+    step = tf.constant(1.0, dtype=tf.float32)
+    tv = dyn._format_time(step, tile=N)
+    for name, net in (("XNet", dyn.position_fn), ("VNet", dyn.momentum_fn)):
+        S, Tr, Q = net([torch.as_tensor(v_f), torch.as_tensor(x), tv])
+        out[f"{tag}.{name}.call.tvec"] = npf(tv)
+        out[f"{tag}.{name}.call.S"], out[f"{tag}.{name}.call.T"], out[f"{tag}.{name}.call.Q"] = npf(S), npf(Tr), npf(Q)
+    m, mi = dyn._get_mask_while(step)
+    for nm, fn in (("vf", dyn._update_momentum_forward), ("vb", dyn._update_momentum_backward)):
+        vv, ld = fn(leaf(x), torch.as_tensor(v_f), b, tv)
+        out[f"{tag}.sub.{nm}.v"], out[f"{tag}.sub.{nm}.logdet"] = npf(vv), npf(ld)
+    for nm, fn in (("xf", dyn._update_position_forward), ("xb", dyn._update_position_backward)):
+        xx, ld = fn(leaf(x), torch.as_tensor(v_f), tv, m, mi)
+        out[f"{tag}.sub.{nm}.x"], out[f"{tag}.sub.{nm}.logdet"] = npf(xx), npf(ld)
+    xx, vv, ld = dyn._forward_lf(leaf(x), torch.as_tensor(v_f), b, step)
+    out[tag + ".lf_f.x"], out[tag + ".lf_f.v"], out[tag + ".lf_f.logdet"] = npf(xx), npf(vv), npf(ld)
+    xx, vv, ld = dyn._backward_lf(leaf(x), torch.as_tensor(v_f), b, step)
+    out[tag + ".lf_b.x"], out[tag + ".lf_b.v"], out[tag + ".lf_b.logdet"] = npf(xx), npf(vv), npf(ld)
+    run_transition(dyn, x, beta, v_f, v_b, u_dir, u_acc, out, tag)
+    # observables of the state the step ends in (lattice.py:285-313)
+    act, plaq, q = lat.calc_plaq_observables(torch.as_tensor(out[tag + ".x_out"]))
+    out[tag + ".obs_action"], out[tag + ".obs_avg_plaq"], out[tag + ".obs_charge"] = npf(act), npf(plaq), npf(q)
+    np.savez_compressed(os.path.join(HERE, "l2hmc_config3_case.npz"), **out)
+    print("l2hmc_config3_case.npz", len(out), "arrays")
+
+
 if __name__ == "__main__":
     assert os.path.isdir(REF), "the reference tree is only present in the build container"
     gen_lattice_cases()
     gen_hmc_cases()
     gen_l2hmc_cases()
+    gen_l2hmc_config3_case()

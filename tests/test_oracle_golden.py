@@ -47,10 +47,22 @@ def test_masks_match_reference_rng(golden):
         assert (m.sum(axis=1) == T * X).all()
 
 
+def regenerated_nets(g, tag, arch):
+    """Goldens whose weights are a function of a seed (tests/parity_util.trained_like_weights) keep the seed and the
+    sha256 of the weights instead of the tensors."""
+    from parity_util import trained_like_weights, weights_digest
+    T, X = (int(v) for v in g[tag + ".meta"][:2])
+    ws = trained_like_weights(arch, T, X, np.random.default_rng(int(g[tag + ".weight_seed"])), gain=1.0)
+    assert weights_digest(ws) == bytes(g[tag + ".weight_sha256"]).hex(), "regenerated weights differ from the golden's"
+    return ws
+
+
 def _dyn_from(g, tag, hmc, arch="generic"):
     T, X, N, M = (int(v) for v in g[tag + ".meta"])
     nets = {}
-    if not hmc:
+    if not hmc and tag + ".weight_seed" in g:
+        nets = regenerated_nets(g, tag, arch)
+    elif not hmc:
         for net in ("XNet", "VNet"):
             pre = f"{tag}.{net}."
             nets[net] = {k[len(pre):]: v for k, v in g.items() if k.startswith(pre) and ".call." not in k}
@@ -79,9 +91,10 @@ def test_hmc_transition(golden, tag):
     close(xo, g[tag + ".x_out"], atol=2e-5)
 
 
-@pytest.mark.parametrize("tag,arch", [("generic.4x4", "generic"), ("conv3D.4x4", "conv3D"), ("conv3D.8x8", "conv3D")])
+@pytest.mark.parametrize("tag,arch", [("generic.4x4", "generic"), ("conv3D.4x4", "conv3D"), ("conv3D.8x8", "conv3D"),
+                                      ("conv3D.16x16", "conv3D")])
 def test_l2hmc_pieces_and_transition(golden, tag, arch):
-    g = golden("l2hmc_cases")
+    g = golden("l2hmc_config3_case" if tag == "conv3D.16x16" else "l2hmc_cases")   # BASELINE config 3's shape
     dyn, (T, X, N, M) = _dyn_from(g, tag, hmc=False, arch=arch)
     beta = torch.tensor(float(g[tag + ".beta"]))
     x, v = t32(g[tag + ".x"]), t32(g[tag + ".v_f"])
