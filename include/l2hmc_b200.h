@@ -20,7 +20,8 @@
  *   - `nonfinite_flag` (nullable, device int32) is OR-ed with 1 when an exp() produced a
  *     non-finite value -- the device-side mirror of tf.check_numerics
  *     (dynamics/gauge_dynamics.py:26-28); the host wrapper raises on it;
- *   - re-entrant, no global state apart from the thread-local error string.
+ *   - re-entrant, no global state apart from the thread-local error string, the launch counter and the scratch
+ *     array of l2hmc_col_sum_static.
  */
 #ifndef L2HMC_B200_H_
 #define L2HMC_B200_H_
@@ -37,10 +38,14 @@ extern "C" {
 #define L2HMC_ERR_UNSUPPORTED 2 /* shape has no kernel instantiation */
 #define L2HMC_ERR_CUDA 3        /* launch failed; see l2hmc_last_error() */
 
-#define L2HMC_ABI_VERSION 1
+#define L2HMC_ABI_VERSION 2
 
 int l2hmc_abi_version(void);
 const char* l2hmc_last_error(void);
+/* Number of kernels this library has launched in the process so far (every launch site adds to one relaxed atomic
+ * counter): difference it around a region to count the region's launches.  No counterpart in the reference; it is what
+ * bench.py reports as `gpu_launches`. */
+unsigned long long l2hmc_launch_count(void);
 
 /* Device limits the host side sizes its launches with. */
 int l2hmc_device_info(int* sm_count, int* max_smem_per_block);
@@ -169,6 +174,8 @@ typedef struct {
   float* obs_action;
   float* obs_plaq;
   int32_t* obs_charge;
+  const uint64_t* mc_step_dev; /* nullable device counter ADDED to mc_step inside the kernel: a captured CUDA graph of
+                                  the step replays with fresh draws when l2hmc_counter_add advances it in the graph */
 } l2hmc_hmc_mc_args;
 
 int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* args, void* stream);
@@ -177,6 +184,14 @@ int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* args, void* stream);
  * generic path's free-running mode).  normals [N,D], u_dir/u_acc [N], each nullable. */
 int l2hmc_philox_draws(uint64_t seed, uint64_t mc_step, uint64_t chain0, int N, int D,
                        float* normals, float* u_dir, float* u_acc, void* stream);
+/* Same with the MC step = mc_step + *mc_step_dev read on the device (mc_step_dev nullable), and the one-thread kernel
+ * that advances such a counter in stream order: together they let a whole MC step -- every launch of
+ * l2hmc_u1_l2hmc_mc_step / l2hmc_u1_hmc_mc_step is capturable, nothing allocates or synchronises -- be captured ONCE as
+ * a CUDA graph and replayed per step (the small-batch configs are launch-latency-bound: host loop gauge_model.py:1158-1177,
+ * 1379-1388). */
+int l2hmc_philox_draws_dev(uint64_t seed, uint64_t mc_step, const uint64_t* mc_step_dev, uint64_t chain0, int N, int D,
+                           float* normals, float* u_dir, float* u_acc, void* stream);
+int l2hmc_counter_add(uint64_t* counter, uint64_t inc, void* stream);
 
 /* ------------------------------------------------------------------ K3: S/T/Q networks
  * Dense trunk + heads of GenericNet.call (network/generic_net.py:129-146) and of ConvNet3D.call
@@ -320,6 +335,7 @@ typedef struct {
   int32_t* nonfinite_flag;
   void* workspace;        /* >= l2hmc_u1_l2hmc_mc_workspace_bytes(args), 256-byte aligned */
   size_t workspace_bytes;
+  const uint64_t* mc_step_dev; /* nullable device counter added to mc_step on the device (see l2hmc_hmc_mc_args) */
 } l2hmc_l2hmc_mc_args;
 
 size_t l2hmc_u1_l2hmc_mc_workspace_bytes(const l2hmc_l2hmc_mc_args* a);
@@ -636,6 +652,11 @@ typedef struct {
   int32_t* nonfinite_flag;
   void* workspace;        /* >= l2hmc_u1_train_workspace_bytes(args), 256-byte aligned */
   size_t workspace_bytes;
+  void* first_bucket_event; /* nullable cudaEvent_t, recorded on `stream` as soon as g_eps and position_fn's gradients
+                               (xnet_g, xconv_*_g) are complete, BEFORE momentum_fn's weight-gradient products are
+                               enqueued: a data-parallel caller starts averaging that bucket on a side stream under the
+                               rest of the backward pass (hvd.DistributedOptimizer overlaps the same way,
+                               gauge_model.py:941-943) */
 } l2hmc_train_args;
 
 size_t l2hmc_u1_train_workspace_bytes(const l2hmc_train_args* a);

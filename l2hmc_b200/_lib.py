@@ -25,7 +25,7 @@ class HmcMcArgs(Structure):
         ("N", c_int), ("T", c_int), ("X", c_int),
         ("x_post", c_void_p), ("v_post", c_void_p), ("accept_prob", c_void_p), ("x_out", c_void_p),
         ("accepted", c_void_p), ("h_old", c_void_p), ("h_new", c_void_p), ("nonfinite_flag", c_void_p),
-        ("obs_action", c_void_p), ("obs_plaq", c_void_p), ("obs_charge", c_void_p),
+        ("obs_action", c_void_p), ("obs_plaq", c_void_p), ("obs_charge", c_void_p), ("mc_step_dev", c_void_p),
     ]
 
 
@@ -122,6 +122,7 @@ class L2hmcMcArgs(Structure):
         ("x_post", c_void_p), ("v_post", c_void_p), ("accept_prob", c_void_p), ("x_out", c_void_p),
         ("accepted", c_void_p), ("obs_action", c_void_p), ("obs_plaq", c_void_p), ("obs_charge", c_void_p),
         ("nonfinite_flag", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("mc_step_dev", c_void_p),
     ]
 
 
@@ -146,6 +147,7 @@ class TrainArgs(Structure):
         ("xconv_in0_g", POINTER(Conv3dGrads)), ("xconv_in1_g", POINTER(Conv3dGrads)),
         ("vconv_in0_g", POINTER(Conv3dGrads)), ("vconv_in1_g", POINTER(Conv3dGrads)),
         ("nonfinite_flag", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
+        ("first_bucket_event", c_void_p),
     ]
 
 
@@ -176,6 +178,7 @@ NET_PATH_AUTO, NET_PATH_FFMA, NET_PATH_TCGEN05 = 0, 1, 2
 SIGNATURES = {
     "l2hmc_abi_version": [],
     "l2hmc_last_error": [],
+    "l2hmc_launch_count": [],
     "l2hmc_device_info": [POINTER(c_int), POINTER(c_int)],
     "l2hmc_u1_action_force": [c_void_p, c_float, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_u1_observables": [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
@@ -192,6 +195,8 @@ SIGNATURES = {
                           c_void_p],
     "l2hmc_u1_hmc_mc_step": [POINTER(HmcMcArgs), c_void_p],
     "l2hmc_philox_draws": [c_uint64, c_uint64, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_philox_draws_dev": [c_uint64, c_uint64, c_void_p, c_uint64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p],
+    "l2hmc_counter_add": [c_void_p, c_uint64, c_void_p],
     "l2hmc_net_workspace_bytes": [c_int, c_int, c_int, c_int],
     "l2hmc_net_run": [POINTER(NetWeights), POINTER(NetCall), c_void_p],
     "l2hmc_net_pack_bytes": [c_int, c_int, c_int],
@@ -242,11 +247,12 @@ SIGNATURES = {
                                    c_int, c_int, c_int, c_void_p, c_void_p],
 }
 
-RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
+RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_launch_count": ctypes.c_ulonglong, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
             "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t,
             "l2hmc_tc_gemm_workspace_bytes": c_size_t, "l2hmc_gemm_workspace_bytes": c_size_t, "l2hmc_col_sum_workspace_bytes": c_size_t}
 
 L2HMC_OK, L2HMC_ERR_INVALID, L2HMC_ERR_UNSUPPORTED, L2HMC_ERR_CUDA = 0, 1, 2, 3
+ABI_VERSION = 2          # L2HMC_ABI_VERSION of include/l2hmc_b200.h
 
 
 class L2hmcError(RuntimeError):
@@ -273,7 +279,7 @@ def get_lib():
     global _lib
     if _lib is None:
         _lib = load_library()
-        if _lib.l2hmc_abi_version() != 1:
+        if _lib.l2hmc_abi_version() != ABI_VERSION:
             raise ImportError("libl2hmc_b200.so ABI version mismatch; rebuild")
     return _lib
 
@@ -300,6 +306,11 @@ def dptr(t, dtype=torch.float32):
         raise TypeError(f"expected a contiguous CUDA {dtype} tensor, got "
                         f"{type(t).__name__} {getattr(t, 'dtype', None)} {getattr(t, 'device', None)}")
     return c_void_p(t.data_ptr())
+
+
+def launch_count():
+    """Kernels launched by the library in this process so far (l2hmc_launch_count)."""
+    return int(get_lib().l2hmc_launch_count())
 
 
 def device_info():

@@ -1,6 +1,8 @@
 // C-ABI glue shared by all entry points: error text, version, device limits.
 #include <stdarg.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace l2hmc {
@@ -14,7 +16,12 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-int check_launch(const char* what) {
+// Every kernel launch of the library is followed by one check_launch (with the number of launches it covers): the
+// process-wide tally is what bench.py reports as `gpu_launches` (counted where the launches happen, not estimated).
+static std::atomic<unsigned long long> g_launches{0};
+
+int check_launch(const char* what, int launches) {
+  g_launches.fetch_add(static_cast<unsigned long long>(launches), std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
@@ -28,6 +35,8 @@ int check_launch(const char* what) {
 extern "C" int l2hmc_abi_version(void) { return L2HMC_ABI_VERSION; }
 
 extern "C" const char* l2hmc_last_error(void) { return l2hmc::g_error; }
+
+extern "C" unsigned long long l2hmc_launch_count(void) { return l2hmc::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int l2hmc_device_info(int* sm_count, int* max_smem_per_block) {
   int dev = 0;

@@ -13,7 +13,7 @@ constexpr float kPi = 3.14159265358979323846f;
 constexpr float kTwoPi = 6.28318530717958647692f;
 
 void set_error(const char* fmt, ...);
-int check_launch(const char* what);
+int check_launch(const char* what, int launches = 1);   // also adds `launches` to l2hmc_launch_count()
 // C (=|+=) epilogue(sum_z partial[z][M][N]), z in fixed order: the second stage of every split-K product (train.cu)
 int launch_splitk_reduce(const float* partial, int ksplit, const l2hmc_gemm_args* g, cudaStream_t stream);
 

@@ -15,7 +15,12 @@
 // conv-2 positions of a pooling window together from a 3x3 patch of P1 held in registers.
 // relu(max(.)) == max(relu(.)), and max(a_i + b) == max(a_i) + b in floating point (monotone),
 // so bias and relu are applied once per pooled output.
+#include <algorithm>
+#include <cstdlib>
+#include <string>
+
 #include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace l2hmc {
 namespace {
@@ -345,6 +350,307 @@ __global__ void __launch_bounds__(TH, 512 / TH) conv3d_tiled_kernel(const ConvPa
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Tensor-core variant (F in {8, 16, 32}, T and X multiples of 4): phase 1 as above on the FMA pipe; the second
+// convolution -- over a batch a [positions] x [4 taps x F] x [2F] contraction, more than half of the front-end's
+// multiply-adds -- as an IMPLICIT GEMM on tcgen05 with the 3xTF32 split of gemm_tc.cu (hi.lo + lo.hi + hi.hi, fp32
+// accumulation in TMEM; K = 4F <= 128 per output, far below the 128-deep flush the long products need).
+//
+//   A operand = the pooled conv-1 plane P1 itself, never an im2col copy.  Phase 1 writes P1 (split into TF32 hi / lo)
+//   into shared memory as  A[part][f / 4][row][f % 4],  row = chain * R1 + t1 * (X1 + 1) + x1  over a (T1+1) x (X1+1)
+//   grid whose last row / column stay zero (TF's 'same' padding of the 2-wide kernel).  That is the UMMA K-major
+//   SWIZZLE_NONE layout with rows 16 B apart (SBO = 128 B, LBO = ROWS * 16 B), so the operand of tap (a, b) is the
+//   SAME buffer with the start address advanced by a * (X1 + 1) + b rows: four taps = four accumulating MMAs per
+//   K step, no data movement.  Rows of the padding column / of the tail produce values nobody reads.
+//   B operand = w2[tap][kd = 0] as [part][tap][f / 4][c][f % 4], split once per CTA.
+//   D: M tile = 128 consecutive rows (chains back to back), N = 2F columns of TMEM per tile.
+//   Epilogue: tcgen05.ld (a thread owns one row), rows staged through shared memory (XOR-swizzled float4 groups), then
+//   the 2x2 max-pool + bias + ReLU of the generic kernel and the feature store.
+// One elected thread issues the MMAs and commits them to an mbarrier the CTA waits on; with two CTAs per SM one CTA's
+// MMAs / epilogue run under the other's phase 1.
+template <int F, int PF, int TH>
+__global__ void __launch_bounds__(TH, 512 / TH) conv3d_tc_kernel(const ConvParams p, const int CH, const int MT,
+                                                                  const int ROWS) {
+  extern __shared__ __align__(128) float sm[];
+  constexpr int C = 2 * F, CG = C / 4, FH = F / 2, G = TH / FH, KC = F / 4;
+  constexpr uint32_t kIdesc = umma_idesc_tf32(128, C);
+  const int T = p.T, X = p.X;
+  const int T1 = T / 2, X1 = X / 2, T2 = T1 / 2, X2 = X1 / 2;
+  const int D = 2 * T * X, XB = X + 2, IN = (T + 2) * XB * 4;          // bordered plane: [t][x][mu][dup]
+  const int X1B = X1 + 1, R1 = (T1 + 1) * X1B;                        // rows of one chain's padded P1 grid
+  const int APART = KC * ROWS * 4, BPART = 4 * F * C;                 // floats per hi / lo part
+  float* s_bw = sm;                        // [2][4][KC][C][4]
+  float* s_b2 = s_bw + 2 * BPART;          // [C]
+  float* s_a = s_b2 + C;                   // [2][KC][ROWS][4]   (16-byte rows: 128-byte aligned start)
+  float* s_z = s_a + 2 * APART;            // [MT * 128][C], float4 groups XOR-swizzled by row
+  float* s_in = s_z + MT * 128 * C;        // [CH][IN]
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_in + CH * IN);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  {                                                                    // w2[kt][kx][kd = 0][f][c], hi / lo split
+    constexpr int NW4 = F * C, PER = (NW4 + TH - 1) / TH;              // float4 groups; all loads of a thread in flight at once
+    float4 wq[PER];
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int i = 4 * (tid + q * TH), tap = i / (F * C), rest = i % (F * C);
+      wq[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < 4 * F * C) wq[q] = __ldg(reinterpret_cast<const float4*>(p.w2 + static_cast<size_t>(tap) * 2 * F * C + rest));
+    }
+#pragma unroll
+    for (int q = 0; q < PER; ++q) {
+      const int i = 4 * (tid + q * TH), tap = i / (F * C), rest = i % (F * C), f = rest / C, c = rest % C;
+      if (i >= 4 * F * C) continue;
+      const float wv[4] = {wq[q].x, wq[q].y, wq[q].z, wq[q].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float hi = tf32_hi(wv[e]);
+        const int dst = ((tap * KC + f / 4) * C + c + e) * 4 + (f & 3);
+        s_bw[dst] = hi;
+        s_bw[BPART + dst] = tf32_lo(wv[e], hi);
+      }
+    }
+  }
+  for (int i = tid; i < C; i += TH) s_b2[i] = p.b2[i];
+  for (int i = tid; i < CH * IN; i += TH) s_in[i] = 0.f;    // borders stay zero for the whole kernel
+  for (int i = tid; i < 2 * APART; i += TH) s_a[i] = 0.f;   // the padding row / column of every chain's grid stays zero
+  uint32_t tmem_cols = 32;
+  while (tmem_cols < static_cast<uint32_t>(MT * C)) tmem_cols <<= 1;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  uint32_t bar_phase = 0;
+
+  const int fp = tid % FH, grp = tid / FH;                             // filters 2 fp, 2 fp + 1
+  f32x2 w[3][3][2];
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+#pragma unroll
+    for (int b = 0; b < 3; ++b)
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+        w[a][b][m] = pack2(p.w1[((a * 3 + b) * 2 + m) * F + 2 * fp], p.w1[((a * 3 + b) * 2 + m) * F + 2 * fp + 1]);
+  const float bias1a = p.b1[2 * fp], bias1b = p.b1[2 * fp + 1];
+  const int quads = D / 4;                 // float4 per chain
+
+  float4 pre[PF];
+  auto fetch = [&](int n0, int cnt) {      // links of chains n0 .. n0 + cnt - 1 -> registers
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i4 = tid + q * TH;
+      const int ch = i4 / quads;
+      pre[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ch < cnt)
+        pre[q] = __ldcs(reinterpret_cast<const float4*>(p.in + static_cast<size_t>(n0 + ch) * D) + (i4 - ch * quads));
+    }
+  };
+  auto stage = [&](int n0, int cnt) {      // registers -> bordered plane, mask applied, values duplicated
+#pragma unroll
+    for (int q = 0; q < PF; ++q) {
+      const int i4 = tid + q * TH;
+      const int ch = i4 / quads;
+      if (ch >= cnt) continue;
+      const int j = (i4 - ch * quads) * 4;
+      float4 a = pre[q];
+      const bool alt = p.row_set != nullptr && p.row_set[n0 + ch] != 0;
+      const float* mask = alt ? p.mask_alt : p.mask;
+      if (mask) {
+        float4 m = *reinterpret_cast<const float4*>(mask + j);
+        if (alt ? p.invert_alt : p.invert)
+          m = make_float4(__fsub_rn(1.f, m.x), __fsub_rn(1.f, m.y), __fsub_rn(1.f, m.z), __fsub_rn(1.f, m.w));
+        a = make_float4(__fmul_rn(m.x, a.x), __fmul_rn(m.y, a.y), __fmul_rn(m.z, a.z), __fmul_rn(m.w, a.w));
+      }
+      const int site = j >> 1, t = site / X, x = site - t * X;       // two sites (x, x + 1) of one row
+      float* dst = s_in + ch * IN + ((t + 1) * XB + x + 1) * 4;
+      *reinterpret_cast<float4*>(dst) = make_float4(a.x, a.x, a.y, a.y);
+      *reinterpret_cast<float4*>(dst + 4) = make_float4(a.z, a.z, a.w, a.w);
+    }
+  };
+
+  // This CTA's chains: a contiguous block of N / grid (+1) chains, cut into passes of nearly equal size (<= CH chains).
+  // A launch is only a few passes per CTA, so an even split decides the time (2048 chains on 296 CTAs: 7 chains = passes
+  // of 3 + 2 + 2 instead of a grid-strided 3 + 3 + 3).
+  const int nb = static_cast<int>(gridDim.x), bi = static_cast<int>(blockIdx.x);
+  const int c_cnt = p.N / nb + (bi < p.N % nb ? 1 : 0), c_lo = bi * (p.N / nb) + min(bi, p.N % nb);
+  const int npass = (c_cnt + CH - 1) / CH;
+  auto pass_lo = [&](int j) { return c_lo + j * (c_cnt / npass) + min(j, c_cnt % npass); };
+  if (npass > 0) {
+    fetch(c_lo, pass_lo(1) - c_lo);
+    __syncthreads();                       // the zero fills are complete
+    stage(c_lo, pass_lo(1) - c_lo);
+    if (npass > 1) fetch(pass_lo(1), pass_lo(2) - pass_lo(1));
+  }
+  for (int j = 0; j < npass; ++j) {
+    const int n0 = pass_lo(j), nch = pass_lo(j + 1) - n0;
+    __syncthreads();                       // the plane staged during the previous pass is visible; s_z is free
+
+    // ---- phase 1: one pooled output (t1, x1) of filters (2 fp, 2 fp + 1) per item -> P1 as the TF32-split A operand
+    for (int item = grp; item < nch * T1 * X1; item += G) {
+      const int x1 = item % X1, rest = item / X1, t1 = rest % T1, ch = rest / T1;
+      const float* in_c = s_in + ch * IN + (2 * t1 * XB + 2 * x1) * 4;   // bordered coords of (2 t1 - 1, 2 x1 - 1)
+      f32x2 s0[2][2], s1[2][2];            // conv outputs at mu = 0 / mu = 1 of the four window positions
+#pragma unroll
+      for (int i = 0; i < 4; ++i) (&s0[0][0])[i] = 0ull, (&s1[0][0])[i] = 0ull;
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {        // patch row r feeds window row dt through tap row a = r - dt
+        ulonglong2 row[4];                 // .x = (mu0, mu0), .y = (mu1, mu1)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) row[b] = *reinterpret_cast<const ulonglong2*>(&in_c[(r * XB + b) * 4]);
+#pragma unroll
+        for (int dt = 0; dt < 2; ++dt) {
+          const int a = r - dt;
+          if (a < 0 || a > 2) continue;
+#pragma unroll
+          for (int dx = 0; dx < 2; ++dx)
+#pragma unroll
+            for (int b = 0; b < 3; ++b) {
+              s0[dt][dx] = fma2(row[dx + b].x, w[a][b][0], s0[dt][dx]);
+              s0[dt][dx] = fma2(row[dx + b].y, w[a][b][1], s0[dt][dx]);
+              s1[dt][dx] = fma2(row[dx + b].y, w[a][b][0], s1[dt][dx]);
+            }
+        }
+      }
+      float ba = -INFINITY, bb = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        ba = fmaxf(ba, fmaxf(lo2((&s0[0][0])[i]), lo2((&s1[0][0])[i])));
+        bb = fmaxf(bb, fmaxf(hi2((&s0[0][0])[i]), hi2((&s1[0][0])[i])));
+      }
+      ba = fmaxf(__fadd_rn(ba, bias1a), 0.f);
+      bb = fmaxf(__fadd_rn(bb, bias1b), 0.f);
+      const float ha = tf32_hi(ba), hb = tf32_hi(bb);
+      float* dst = s_a + (((2 * fp) >> 2) * ROWS + ch * R1 + t1 * X1B + x1) * 4 + ((2 * fp) & 3);
+      *reinterpret_cast<float2*>(dst) = make_float2(ha, hb);
+      *reinterpret_cast<float2*>(dst + APART) = make_float2(tf32_lo(ba, ha), tf32_lo(bb, hb));
+    }
+    fence_proxy_async_smem();              // P1 (generic-proxy stores) -> visible to the tensor core's reads
+    __syncthreads();
+
+    // ---- conv 2: per M tile and tap, F / 8 K steps x (hi.lo + lo.hi + hi.hi)
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t a_base = smem_u32(s_a), b_base = smem_u32(s_bw);
+      const uint32_t a_lbo = static_cast<uint32_t>(ROWS) * 16u, b_lbo = static_cast<uint32_t>(C) * 16u;
+      for (int mt = 0; mt < MT; ++mt) {
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(mt * C);
+        uint32_t acc = 0;
+#pragma unroll
+        for (int tap = 0; tap < 4; ++tap) {
+          const int shift = (tap >> 1) * X1B + (tap & 1);
+#pragma unroll
+          for (int ks = 0; ks < F / 8; ++ks) {
+            const uint32_t a_off = (static_cast<uint32_t>(2 * ks * ROWS + mt * 128 + shift)) * 16u;
+            const uint32_t b_off = (static_cast<uint32_t>((tap * KC + 2 * ks) * C)) * 16u;
+            const uint64_t a_hi = umma_desc_kmajor(a_base + a_off, a_lbo, 128u);
+            const uint64_t a_lo = umma_desc_kmajor(a_base + static_cast<uint32_t>(APART) * 4u + a_off, a_lbo, 128u);
+            const uint64_t b_hi = umma_desc_kmajor(b_base + b_off, b_lbo, 128u);
+            const uint64_t b_lo = umma_desc_kmajor(b_base + static_cast<uint32_t>(BPART) * 4u + b_off, b_lbo, 128u);
+            umma_tf32(d_tmem, a_hi, b_lo, kIdesc, acc);
+            umma_tf32(d_tmem, a_lo, b_hi, kIdesc, 1);
+            umma_tf32(d_tmem, a_hi, b_hi, kIdesc, 1);
+            acc = 1;
+          }
+        }
+      }
+      umma_commit(bar);
+    }
+    // under the tensor core's latency: the next pass's links into the plane (phase 1 is done with it), the pass after
+    // that into registers
+    if (j + 1 < npass) {
+      stage(pass_lo(j + 1), pass_lo(j + 2) - pass_lo(j + 1));
+      if (j + 2 < npass) fetch(pass_lo(j + 2), pass_lo(j + 3) - pass_lo(j + 2));
+    }
+    if (tid == 0) mbar_wait_sleep(bar, bar_phase);   // one waiter: 255 polling threads would take the other CTA's issue slots
+    bar_phase ^= 1;
+    __syncthreads();
+    tc_fence_after();
+
+    // ---- epilogue: TMEM -> shared (thread = row), then pool (2,2,[1]) + bias + relu -> flattened features
+    for (int mt = warp >> 2; mt < MT; mt += TH / 128) {
+      const int row = mt * 128 + (warp & 3) * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + static_cast<uint32_t>(mt * C);
+      float* zrow = s_z + row * C;
+#pragma unroll
+      for (int c0 = 0; c0 < C; c0 += 32) {
+        float v[32];
+        if (C >= 32) tmem_ld32(taddr + c0, v);
+        else tmem_ld16(taddr + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < (C >= 32 ? 8 : 4); ++g) {
+          const int grp4 = (c0 / 4 + g) ^ (row & (CG - 1));
+          *reinterpret_cast<float4*>(zrow + grp4 * 4) = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    const int cg = tid % CG;
+    for (int item = tid / CG; item < nch * T2 * X2; item += TH / CG) {
+      const int x2 = item % X2, rest = item / X2, t2 = rest % T2, ch = rest / T2;
+      const int r00 = ch * R1 + 2 * t2 * X1B + 2 * x2;
+      float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int row = r00 + (k >> 1) * X1B + (k & 1);
+        const float4 z = *reinterpret_cast<const float4*>(s_z + row * C + ((cg ^ (row & (CG - 1))) * 4));
+        best = make_float4(fmaxf(best.x, z.x), fmaxf(best.y, z.y), fmaxf(best.z, z.z), fmaxf(best.w, z.w));
+      }
+      const float4 b = *reinterpret_cast<const float4*>(s_b2 + 4 * cg);
+      float* dst = p.feat + static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
+      __stcs(reinterpret_cast<float4*>(dst), make_float4(fmaxf(__fadd_rn(best.x, b.x), 0.f), fmaxf(__fadd_rn(best.y, b.y), 0.f),
+                                                          fmaxf(__fadd_rn(best.z, b.z), 0.f), fmaxf(__fadd_rn(best.w, b.w), 0.f)));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// -1: the shape does not fit (shared memory); the FFMA kernels below take it
+template <int F>
+int launch_tc(const ConvParams& p, int sms, int max_smem, cudaStream_t stream) {
+  constexpr int TH = 256, C = 2 * F;
+  const auto misaligned = [](const void* a) { return (reinterpret_cast<uintptr_t>(a) & 15u) != 0; };
+  if (p.T % 4 != 0 || p.X % 4 != 0 || misaligned(p.in) || misaligned(p.feat) || misaligned(p.mask) ||
+      misaligned(p.mask_alt) || misaligned(p.w2))
+    return -1;
+  const int T1 = p.T / 2, X1 = p.X / 2, R1 = (T1 + 1) * (X1 + 1), D = 2 * p.T * p.X;
+  // chains per pass: at most two M tiles of rows and 4 float4 of links per thread
+  const int CH = std::max(1, std::min(256 / R1, 4 * TH * 4 / D));
+  const int MT = (CH * R1 + 127) / 128;
+  int ROWS = MT * 128 + X1 + 2;                                        // the last tile's taps read up to X1 + 2 rows further
+  while ((ROWS * 4) % 32 != 8) ++ROWS;                                 // K chunks land 8 banks apart
+  const size_t floats = 2u * 4 * F * C + C + 2u * (F / 4) * ROWS * 4 + static_cast<size_t>(MT) * 128 * C +
+                        static_cast<size_t>(CH) * (p.T + 2) * (p.X + 2) * 4;
+  const size_t smem = sizeof(float) * floats + 16;
+  if (smem > static_cast<size_t>(max_smem) || MT * C > 512) return -1;
+  const int pf = (CH * D / 4 + TH - 1) / TH;
+  const int per_sm = std::max(1, std::min(static_cast<int>((200 * 1024) / (smem + 1024)), 512 / TH));
+  const int grid = std::max(1, std::min(p.N, sms * per_sm));           // every CTA gets N / grid (+1) chains
+  auto go = [&](auto kern) -> int {
+    if (smem > 48 * 1024) {
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+      if (e != cudaSuccess) {
+        set_error("cudaFuncSetAttribute(conv3d_tc_kernel): %s", cudaGetErrorString(e));
+        return L2HMC_ERR_CUDA;
+      }
+    }
+    kern<<<grid, TH, smem, stream>>>(p, CH, MT, ROWS);
+    return check_launch("conv3d_tc_kernel");
+  };
+  if (pf <= 1) return go(conv3d_tc_kernel<F, 1, TH>);
+  if (pf <= 2) return go(conv3d_tc_kernel<F, 2, TH>);
+  if (pf <= 4) return go(conv3d_tc_kernel<F, 4, TH>);
+  return -1;
+}
+
 template <int F, int PF, int CH, int TH>
 int launch_tiled_pf(const ConvParams& p, int sms, size_t smem, cudaStream_t stream) {
   if (smem > 48 * 1024) {
@@ -420,6 +726,14 @@ extern "C" int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const f
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, mask_alt, mask_invert_alt, row_set, N, T, X, F, feat};
   int rc = -1;
+  // conv 2 on the tensor cores unless the shape does not fit or L2HMC_CONV_PATH=ffma asks for the FMA-pipe kernels
+  static const bool ffma_only = [] { const char* e = std::getenv("L2HMC_CONV_PATH"); return e && std::string(e) == "ffma"; }();
+  if (!ffma_only) {
+    if (F == 8) rc = launch_tc<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+    else if (F == 16) rc = launch_tc<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+    else if (F == 32) rc = launch_tc<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+    if (rc >= 0) return rc;
+  }
   if (F == 8) rc = launch_tiled<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
   else if (F == 16) rc = launch_tiled<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
   else if (F == 32) rc = launch_tiled<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));

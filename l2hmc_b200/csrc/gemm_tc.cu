@@ -36,6 +36,7 @@
 
 #include "common.cuh"
 #include "nets.cuh"
+#include "tc_ptx.cuh"
 #include "update_math.cuh"
 
 namespace l2hmc {
@@ -101,70 +102,12 @@ struct TcParams {
                        // fills; later K blocks re-use stale shared memory -> wrong numbers, pure MMA / epilogue timing
 };
 
-// ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
-               : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
-}
-__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
+// tcgen05 / TMEM PTX wrappers: tc_ptx.cuh
 // K-major, no swizzle: start address, LBO = 128 B (next 16-byte K chunk), SBO = 2048 B (next 8-row group)
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
   return static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu) | (static_cast<uint64_t>(128u >> 4) << 16) |
          (static_cast<uint64_t>(2048u >> 4) << 32) | (1ULL << 46);
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
-  uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
-      "[%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// round-to-nearest TF32 (10-bit mantissa, low 13 bits zero): |a - tf32_rn(a)| <= 2^-11 |a|
-__device__ __forceinline__ float tf32_rn(float a) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(a));
-  return __uint_as_float(r);
-}
-__device__ __forceinline__ float tf32_hi(float a) { return tf32_rn(a); }
-// lo = a - hi is exact in fp32; rounding it to TF32 here (instead of the MMA truncating it) halves its error
-__device__ __forceinline__ float tf32_lo(float a, float hi) { return tf32_rn(__fsub_rn(a, hi)); }
 
 // ------------------------------------------------------------------ the GEMM kernel
 // Tensor-core accumulation truncates (round-toward-zero) every time an MMA adds into the TMEM
@@ -637,7 +580,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   if (c->row_set)
     bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos_alt, c->tau_sin_alt,
                                                       H, bias_eff + d.h_rows);
-  int rc = check_launch("ts32_from_rowmajor_kernel");
+  int rc = check_launch("ts32_from_rowmajor_kernel", c->row_set ? 4 : 3);
   if (rc) return rc;
 
   static const int debug_noload = getenv("L2HMC_TC_DEBUG_NOLOAD") ? atoi(getenv("L2HMC_TC_DEBUG_NOLOAD")) : 0;
@@ -722,7 +665,7 @@ extern "C" int l2hmc_net_pack(const l2hmc_net_weights* w, void* packed, size_t p
   ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_s, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 0);
   ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_tr, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 1);
   ts32_pack_weight_kernel<<<ew_grid(t3), 256, 0, st>>>(w->w_q, H, D, W3, d.d_tiles * 192 / 8, 0, 1, 2);
-  return check_launch("ts32_pack_weight_kernel");
+  return check_launch("ts32_pack_weight_kernel", 6);
 }
 
 // ------------------------------------------------------------------ general tcgen05 GEMM (training backward)
@@ -920,5 +863,5 @@ extern "C" int l2hmc_tc_selftest(const float* A, const float* W, int M, int Nc, 
   int rc = bn == 128 ? launch_tc<128, kTcLayer>(p, st) : launch_tc<256, kTcLayer>(p, st);
   if (rc) return rc;
   ts32_to_rowmajor_kernel<<<ew_grid(static_cast<size_t>(M) * Nc), 256, 0, st>>>(c_ts, rows_p / 8, M, Nc, C);
-  return check_launch("l2hmc_tc_selftest");
+  return check_launch("l2hmc_tc_selftest", 3);
 }

@@ -50,6 +50,7 @@ struct HmcParams {
   float beta, eps, one;
   int num_steps, default_dir, wrap, N, num_tiles;
   unsigned long long seed, mc_step, chain0;
+  const unsigned long long* mc_step_dev;   // nullable: added to mc_step on the device (replayed CUDA graphs)
   float* x_post;
   float* v_post;
   float* accept_prob;
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
   const int warp = tid >> 5, lane = tid & 31;
   const bool rng = MC && (p.v_f == nullptr);
   const bool per_chain_v = MC && !rng && p.v_b != nullptr;
+  const unsigned long long mc_step = p.mc_step + ((MC && p.mc_step_dev != nullptr) ? *p.mc_step_dev : 0ull);
 
   if (tid == 0) {
     mbar_init(&full[0], 1);
@@ -222,7 +224,7 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       if (rng) {
         float ud = 0.f, ua = 0.f;
         if ((lane & (GW - 1)) == 0)   // one Philox call per chain and warp, then broadcast
-          philox_uniform2(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, ud, ua);
+          philox_uniform2(p.seed, p.chain0 + static_cast<unsigned long long>(chain), mc_step, ud, ua);
         ud = __shfl_sync(0xffffffffu, ud, lane & ~(GW - 1));
         ua = __shfl_sync(0xffffffffu, ua, lane & ~(GW - 1));
         sgn = (p.u_dir ? (valid ? p.u_dir[chain] : 1.f) : ud) > 0.5f ? 1.f : -1.f;
@@ -254,8 +256,8 @@ __global__ void __launch_bounds__(kThreads, MC ? 3 : 4) hmc_kernel(const HmcPara
       X0b = pack2(a1.x, a1.z), X1b = pack2(a1.y, a1.w);
       if (rng) {
         float z[8];
-        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k, z);
-        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), p.mc_step, 2u * k + 1u, z + 4);
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), mc_step, 2u * k, z);
+        philox_normal4(p.seed, p.chain0 + static_cast<unsigned long long>(chain), mc_step, 2u * k + 1u, z + 4);
         V0a = pack2(z[0], z[2]), V1a = pack2(z[1], z[3]);
         V0b = pack2(z[4], z[6]), V1b = pack2(z[5], z[7]);
       } else {
@@ -479,6 +481,7 @@ extern "C" int l2hmc_u1_hmc_mc_step(const l2hmc_hmc_mc_args* a, void* stream) {
   p.x = a->x, p.v_f = a->v_f, p.v_b = a->v_b, p.u_dir = a->u_dir, p.u_acc = a->u_acc;
   p.beta = a->beta, p.eps = a->eps, p.num_steps = a->num_steps, p.default_dir = a->default_dir;
   p.wrap = a->wrap_2pi, p.N = a->N, p.seed = a->seed, p.mc_step = a->mc_step, p.chain0 = a->chain0;
+  p.mc_step_dev = reinterpret_cast<const unsigned long long*>(a->mc_step_dev);
   p.x_post = a->x_post, p.v_post = a->v_post, p.accept_prob = a->accept_prob, p.x_out = a->x_out;
   p.accepted = a->accepted, p.h_old = a->h_old, p.h_new = a->h_new, p.flag = a->nonfinite_flag;
   p.obs_action = a->obs_action, p.obs_plaq = a->obs_plaq, p.obs_charge = a->obs_charge;

@@ -106,7 +106,8 @@ extern "C" int l2hmc_u1_l2hmc_mc_step(const l2hmc_l2hmc_mc_args* a, void* stream
   const float* u_dir = a->u_dir;
   const float* u_acc = a->u_acc;
   if (!inject) {
-    L2HMC_TRY(l2hmc_philox_draws(a->seed, a->mc_step, a->chain0, N, D, a->v_post, u_dir_ws, u_acc_ws, st));
+    L2HMC_TRY(l2hmc_philox_draws_dev(a->seed, a->mc_step, a->mc_step_dev, a->chain0, N, D, a->v_post, u_dir_ws, u_acc_ws,
+                                     st));
     u_dir = u_dir_ws, u_acc = u_acc_ws;
   } else if (a->v_b == nullptr || a->v_b == a->v_f) {
     if (cudaMemcpyAsync(a->v_post, a->v_f, sizeof(float) * static_cast<size_t>(N) * D, cudaMemcpyDeviceToDevice, st) !=

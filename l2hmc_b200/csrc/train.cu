@@ -802,7 +802,7 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   attr.id = cudaLaunchAttributeClusterDimension;
   attr.val.clusterDim.x = 1, attr.val.clusterDim.y = 1, attr.val.clusterDim.z = cluster ? ksplit : 1;
   cfg.attrs = &attr, cfg.numAttrs = 1;
-  if (cudaLaunchKernelEx(&cfg, kern, p) != cudaSuccess) return check_launch("sgemm_kernel");
+  if (cudaLaunchKernelEx(&cfg, kern, p) != cudaSuccess) return check_launch("sgemm_kernel", 0);
   int rc = check_launch("sgemm_kernel");
   if (rc || ksplit == 1 || cluster) return rc;
   return l2hmc::launch_splitk_reduce(p.partial, ksplit, g, st);
@@ -929,7 +929,7 @@ extern "C" int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, f
   float* partial = static_cast<float*>(workspace);
   colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
   colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
-  return check_launch("colsum_kernel");
+  return check_launch("colsum_kernel", 2);
 }
 
 // ----------------------------------------------------------------------------------------------- no-allocation variant
@@ -981,7 +981,7 @@ extern "C" int l2hmc_col_sum_static(const float* B, long long ld, int rows, int 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
   colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
-  return check_launch("colsum_kernel (static scratch)");
+  return check_launch("colsum_kernel (static scratch)", 2);
 }
 
 extern "C" int l2hmc_reduce_sum(const float* v, long long n, int square, float* out, float* scratch /* [1024] */,

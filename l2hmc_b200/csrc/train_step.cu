@@ -321,7 +321,7 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
   L2HMC_TRY(copy(Xs(0) + ND, a->z, ND));
   train_row_set_kernel<<<(R + 255) / 256, 256, 0, st>>>(a->u_dir, R, pl.row_set);
   pick_rows_kernel<<<R, 128, 0, st>>>(a->v_f, a->v_b, pl.row_set, D, Vs(0));
-  L2HMC_TRY(check_launch("pick_rows_kernel"));
+  L2HMC_TRY(check_launch("pick_rows_kernel", 2));
   cudaMemsetAsync(pl.sld, 0, R * sizeof(float), st);
   if (nets && pl.tc_forward) {      // the weights moved since the last step: refresh their TS32 copies
     L2HMC_TRY(l2hmc_net_pack(a->xnet, pl.xpack, pl.xpack_bytes, stream));
@@ -468,6 +468,11 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
     if (conv) {
       L2HMC_TRY(conv_weight_grads(c, pl.xt, pl.part[0], a->xconv_in1_g, a->xconv_in0->F));
       L2HMC_TRY(conv_weight_grads(c, pl.xt, pl.part[1], a->xconv_in0_g, a->xconv_in0->F));
+    }
+    if (a->first_bucket_event != nullptr &&
+        cudaEventRecord(static_cast<cudaEvent_t>(a->first_bucket_event), st) != cudaSuccess) {
+      set_error("l2hmc_u1_train_grads: cudaEventRecord(first_bucket_event): %s", cudaGetErrorString(cudaGetLastError()));
+      return L2HMC_ERR_CUDA;
     }
     L2HMC_TRY(weight_grads(c, pl.vt, a->vnet_g));
     if (conv) {

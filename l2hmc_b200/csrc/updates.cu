@@ -233,8 +233,10 @@ __global__ void __launch_bounds__(kWarps * 32) mh_select_kernel(
 }
 
 __global__ void __launch_bounds__(256) philox_draws_kernel(unsigned long long seed, unsigned long long mc_step,
+                                                            const unsigned long long* mc_step_dev,
                                                             unsigned long long chain0, int N, int D, float* normals,
                                                             float* u_dir, float* u_acc) {
+  if (mc_step_dev != nullptr) mc_step += *mc_step_dev;     // replayed CUDA graphs: the step counter lives on the device
   const int quads = (D + 3) / 4;
   const size_t total = static_cast<size_t>(N) * quads;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -372,15 +374,29 @@ extern "C" int l2hmc_mh_select(const float* x, const float* x_f, const float* x_
   return check_launch("mh_select_kernel");
 }
 
+// one thread: *ctr += inc (the Philox step counter of a captured MC step, advanced inside the graph)
+__global__ void counter_add_kernel(unsigned long long* ctr, unsigned long long inc) { *ctr += inc; }
+
+extern "C" int l2hmc_counter_add(uint64_t* counter, uint64_t inc, void* stream) {
+  L2HMC_REQUIRE(counter, "l2hmc_counter_add: null counter");
+  counter_add_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(counter), inc);
+  return check_launch("counter_add_kernel");
+}
+
 extern "C" int l2hmc_philox_draws(uint64_t seed, uint64_t mc_step, uint64_t chain0, int N, int D, float* normals,
                                   float* u_dir, float* u_acc, void* stream) {
+  return l2hmc_philox_draws_dev(seed, mc_step, nullptr, chain0, N, D, normals, u_dir, u_acc, stream);
+}
+
+extern "C" int l2hmc_philox_draws_dev(uint64_t seed, uint64_t mc_step, const uint64_t* mc_step_dev, uint64_t chain0, int N,
+                                      int D, float* normals, float* u_dir, float* u_acc, void* stream) {
   if (N == 0) return L2HMC_OK;  // empty batch: nothing to enqueue (pointers may be null)
   L2HMC_REQUIRE(N >= 0 && D > 0, "l2hmc_philox_draws: bad sizes");
   L2HMC_REQUIRE(normals || u_dir || u_acc, "l2hmc_philox_draws: nothing requested");
   if (N == 0) return L2HMC_OK;
   const size_t total = static_cast<size_t>(N) * ((D + 3) / 4);
   const int grid = static_cast<int>(std::min<size_t>((total + 255) / 256, 148 * 16));
-  philox_draws_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(seed, mc_step, chain0, N, D, normals,
-                                                                           u_dir, u_acc);
+  philox_draws_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      seed, mc_step, reinterpret_cast<const unsigned long long*>(mc_step_dev), chain0, N, D, normals, u_dir, u_acc);
   return check_launch("philox_draws_kernel");
 }

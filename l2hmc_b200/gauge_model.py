@@ -99,6 +99,7 @@ class GaugeModel(object):
         self.global_step = 0
         self.native_train = True        # loss + gradients of a step in one C call (csrc/train_step.cu)
         self.using_hvd = False          # set by train(): lr * world size, gradients averaged (gauge_model.py:939-941)
+        self.overlap_allreduce = True   # average the first gradient bucket under the tail of the backward pass
 
     # ------------------------------------------------------------------ construction (:585-613)
     def _create_lattice(self):
@@ -213,7 +214,7 @@ class GaugeModel(object):
         fix = lambda d: (dv(d[0]), dv(d[1] if d[1] is not None else d[0]), d1(d[2]), d1(d[3]))
         return fix(draws_x), dv(z), fix(draws_z)
 
-    def _calc_loss_and_grads(self, x, beta, draws_x=None, z=None, draws_z=None, **weights):
+    def _calc_loss_and_grads(self, x, beta, draws_x=None, z=None, draws_z=None, _first_bucket_event=None, **weights):
         """(loss, grads, x_out, px, x_dq) -- gauge_model.py:805-832.  `grads` is a dict of views into the flat
         gradient arena keyed 'eps', 'XNet.<layer>.kernel', ... in the order of dynamics.variables; with clip_grads
         they are already clipped by their global norm (:826-827), as the reference returns them."""
@@ -224,7 +225,7 @@ class GaugeModel(object):
         eng = self.engine
         with torch.cuda.device(self.device):
             if self.native_train:          # one C call enqueues the whole step (csrc/train_step.cu)
-                fw = eng.native(x, beta, draws_x, z, draws_z, w)
+                fw = eng.native(x, beta, draws_x, z, draws_z, w, first_bucket_event=_first_bucket_event)
                 grads = eng.params.grads_dict()
             else:                          # the same launches driven from Python (kept for tests / debugging)
                 fw = eng.forward(x, beta, draws_x, z, draws_z, w)
@@ -249,11 +250,34 @@ class GaugeModel(object):
         new samples.  Returns (loss, samples_out, px, eps, actions, plaqs, charges, lr, charge_diff) with
         samples_out = mod(x_out, 2 pi) as the loop feeds it back (:1180)."""
         beta = self.beta if beta is None else beta
-        loss, grads, x_out, px, x_dq = self._calc_loss_and_grads(samples, beta, **inject)
         eng, opt = self.engine, self._optimizer
-        if self.using_hvd:             # hvd.DistributedOptimizer (:941-943): average of the per-rank (clipped) gradients
+        # hvd.DistributedOptimizer (:941-943): average of the per-rank (clipped) gradients.  Two buckets of the flat
+        # arena, eps | XNet and VNet: the first is averaged on a side stream while momentum_fn's weight-gradient products
+        # still run (the C call records an event in between).  A global-norm clip needs the whole gradient first.
+        overlap = (self.using_hvd and self.native_train and not self.clip_grads and not self.dynamics.hmc
+                   and self.overlap_allreduce)
+        ev = None
+        if overlap:
+            if getattr(self, "_bucket_event", None) is None:
+                self._bucket_event = torch.cuda.Event()
+                self._bucket_event.record()                           # creates the handle the C call records into
+                self._comm_stream = torch.cuda.Stream(device=self.device)
+                names = eng.params.names
+                self._bucket_split = int(eng.params.offsets[next(i for i, n in enumerate(names) if n.startswith("VNet."))])
+            ev = self._bucket_event
+        loss, grads, x_out, px, x_dq = self._calc_loss_and_grads(samples, beta, _first_bucket_event=ev, **inject)
+        if self.using_hvd:
             from .sharding import allreduce_mean_
-            allreduce_mean_(eng.params.grad)
+            if overlap:
+                main = torch.cuda.current_stream(self.device)
+                split = self._bucket_split
+                self._comm_stream.wait_event(ev)
+                with torch.cuda.stream(self._comm_stream):
+                    allreduce_mean_(eng.params.grad[:split])
+                allreduce_mean_(eng.params.grad[split:])
+                main.wait_stream(self._comm_stream)
+            else:
+                allreduce_mean_(eng.params.grad)
         lr = self.learning_rate()
         with torch.cuda.device(self.device):
             opt.step(lr)               # the clip (if any) was applied by _calc_loss_and_grads, before the average
@@ -277,7 +301,8 @@ class GaugeModel(object):
 
     def train(self, train_steps, samples_init=None, beta_init=None, distributed=False, log=None):
         """The training loop (:1112-1230) without files / TensorBoard: beta annealing (:1158), train_step, feed the
-        wrapped samples back.  distributed=True: one process per GPU, weights broadcast from rank 0 at the start
+        wrapped samples back.  `log`: a callable (step, train_step's tuple, beta), a run_logger.RunLogger, or a file path
+        (rank-0 JSONL rows STEP LOSS t/STEP %ACC EPS BETA ACTION PLAQ (EXACT) dQ LR, :1104-1110).  distributed=True: one process per GPU, weights broadcast from rank 0 at the start
         (BroadcastGlobalVariablesHook), lr * world size, gradients averaged, steps // world size (:2085-2096)."""
         self.using_hvd = bool(distributed)
         samples = self._x(self.lattice.samples if samples_init is None else samples_init).contiguous()
@@ -298,6 +323,9 @@ class GaugeModel(object):
             self.dynamics.set_masks(mask.cpu().numpy())
             eng.params.sync_to_dynamics()
             train_steps = train_steps // ws
+        if isinstance(log, str):       # a path: rank-0 JSONL rows with the reference's columns (:1104-1110, 1190-1221)
+            from .run_logger import RunLogger
+            log = RunLogger(log, print_steps=getattr(self, "print_steps", 1), train_steps=train_steps)
         history = []
         for step in range(self.global_step, train_steps):
             self.beta = self.update_beta(step) if self.annealing else (self.beta_init if beta_init is None else beta_init)

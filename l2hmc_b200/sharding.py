@@ -109,21 +109,39 @@ def allreduce_mean_(flat_grad, group=None):
 def bind_to_gpu_numa(device_index):
     """Pin this process to the CPUs NVML reports as local to its GPU, BEFORE pinned host buffers are allocated: the
     pages then land on the GPU's NUMA node (first touch) and the per-step host<->device copies of every rank stop
-    sharing one socket's memory controller.  Returns the CPU list, or None when NVML / affinity is unavailable."""
+    sharing one socket's memory controller.
+
+    Returns a dict that says what happened: {"bound": bool, "cpus": number of CPUs now allowed, "why": text}.  "bound"
+    is False -- with the reason -- when NVML / the affinity call is unavailable, when NVML's CPU set does not intersect
+    the CPUs this process may use, or when the GPU's set is the whole machine (a single NUMA node: nothing to gain)."""
     import os
     try:
+        allowed_now = sorted(os.sched_getaffinity(0))
+    except (AttributeError, OSError) as e:
+        return {"bound": False, "cpus": None, "why": f"sched_getaffinity unavailable: {e}"}
+    try:
         import pynvml
+    except ImportError as e:
+        return {"bound": False, "cpus": len(allowed_now), "why": f"pynvml not importable: {e}"}
+    try:
         import torch
         pynvml.nvmlInit()
         uuid = str(torch.cuda.get_device_properties(device_index).uuid)
         handle = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
         words = (os.cpu_count() + 63) // 64
         mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
-        cpus = [w * 64 + b for w, bits in enumerate(mask) for b in range(64) if (int(bits) >> b) & 1]
-        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
-        if not allowed:
-            return None
-        os.sched_setaffinity(0, allowed)
-        return allowed
-    except Exception:
-        return None
+    except Exception as e:                       # NVML errors are their own exception hierarchy
+        return {"bound": False, "cpus": len(allowed_now), "why": f"NVML affinity query failed: {type(e).__name__}: {e}"}
+    cpus = [w * 64 + b for w, bits in enumerate(mask) for b in range(64) if (int(bits) >> b) & 1]
+    target = sorted(set(cpus) & set(allowed_now))
+    if not target:
+        return {"bound": False, "cpus": len(allowed_now),
+                "why": f"NVML's {len(cpus)} GPU-local CPUs do not intersect the {len(allowed_now)} CPUs this process may use"}
+    if target == allowed_now:
+        return {"bound": False, "cpus": len(allowed_now),
+                "why": f"the GPU's local CPU set is all {len(allowed_now)} allowed CPUs (one NUMA node): nothing to bind"}
+    try:
+        os.sched_setaffinity(0, target)
+    except OSError as e:
+        return {"bound": False, "cpus": len(allowed_now), "why": f"sched_setaffinity failed: {e}"}
+    return {"bound": True, "cpus": len(target), "why": f"bound to the {len(target)} CPUs NVML reports local to GPU {device_index}"}

@@ -309,7 +309,7 @@ class TrainEngine(object):
                 convs[which] = c
         return g, convs
 
-    def native(self, x, beta, draws_x, z, draws_z, weights, forward_only=False):
+    def native(self, x, beta, draws_x, z, draws_z, weights, forward_only=False, first_bucket_event=None):
         """Loss and gradients of one step enqueued by ONE C call (csrc/train_step.cu: l2hmc_u1_train_grads) -- the same
         launches as forward() + backward(), issued from C++.  Returns the same dict keys the training loop reads."""
         dyn, lib = self.dyn, _lib.get_lib()
@@ -360,6 +360,8 @@ class TrainEngine(object):
         if getattr(self, "_native_ws", None) is None or self._native_ws.numel() < need:
             self._native_ws = torch.empty(need, dtype=torch.uint8, device=dev)
         a.workspace, a.workspace_bytes = ctypes.c_void_p(self._native_ws.data_ptr()), need
+        if first_bucket_event is not None:     # a torch.cuda.Event that has been recorded once (its handle exists)
+            a.first_bucket_event = ctypes.c_void_p(int(first_bucket_event.cuda_event))
         _lib.check(lib.l2hmc_u1_train_grads(ctypes.byref(a), _lib.stream_ptr()))
         del keep
         return out

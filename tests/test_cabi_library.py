@@ -26,7 +26,7 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
         assert hasattr(lib, name), f"{name} declared in the header but not exported"
         assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
     assert set(_lib.SIGNATURES) == set(syms)
-    assert lib.l2hmc_abi_version() == 1
+    assert lib.l2hmc_abi_version() == _lib.ABI_VERSION
 
 
 def test_argument_validation_needs_no_device():

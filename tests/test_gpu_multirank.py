@@ -109,7 +109,23 @@ def _worker(rank, port, tmp):
     g_local_norm = float(g_avg.norm())
     sharding.allreduce_mean_(g_avg)
     full_samples = sharding.gather_chains(samples, WORLD * n)
+    # ------------------------------------------------------------------ overlapped first-bucket all-reduce == one all-reduce
+    flats = {}
+    for overlap in (True, False):
+        np.random.seed(2000)
+        m = GaugeModel(dict(params, clip_grads=False))
+        m.overlap_allreduce = overlap
+        m.train(3 * WORLD, samples_init=x_loc, distributed=True)
+        flats[overlap] = m.engine.params.flat.clone()
+        if overlap:
+            used_overlap = getattr(m, "_bucket_event", None) is not None
+    both_o = [torch.empty_like(flats[True]) for _ in range(WORLD)]
+    dist.all_gather(both_o, flats[True])
     if rank == 0:
+        report["overlap.used"] = bool(used_overlap)
+        report["overlap.equals_single_allreduce"] = bool(torch.equal(flats[True], flats[False]))
+        report["overlap.ranks_equal"] = bool(torch.equal(both_o[0], both_o[1]))
+        report["overlap.moved"] = float((flats[True] - flat).abs().max())
         report["train.offsets"] = [int(o) for o in all_offs]
         report["train.steps_per_rank"] = report_local["n_steps"]
         report["train.weights_equal"] = bool(torch.equal(both[0], both[1]))
@@ -150,6 +166,8 @@ def test_two_nccl_ranks_equal_one_rank(tmp_path):
     assert r["train.own_masks_differed"] and r["train.masks_equal"]
     assert r["train.weights_equal"]
     assert r["train.losses_differ"]                           # the ranks drew different momenta
+    # the first gradient bucket averaged on a side stream under momentum_fn's weight-gradient products: same weights
+    assert r["overlap.used"] and r["overlap.equals_single_allreduce"] and r["overlap.ranks_equal"]
     # clip_value = 1e6 >> |g|: the per-rank clip (gauge_model.py:826-827) runs but is the identity, so the average of the
     # ranks' gradients must equal the 1-rank gradient of the concatenated batch
     assert r["grad.local_norm"] < 1e5

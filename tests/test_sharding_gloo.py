@@ -97,3 +97,28 @@ def test_shard_ranges_partition_the_batch():
     with pytest.raises(ValueError):
         sharding.shard_range(10, 3, 2)
     assert sharding.world() == (0, 1)
+
+
+def test_run_logger_rows_have_the_reference_columns(tmp_path):
+    """Rank-0 JSONL log (gauge_model.py:1104-1110, 1190-1221; rank gate utils/file_io.py:27-46): one parsed line."""
+    import json
+    from l2hmc_b200.lattice import u1_plaq_exact
+    from l2hmc_b200.run_logger import COLUMNS, RunLogger
+    path = str(tmp_path / "run_info.jsonl")
+    N = 6
+    out = (torch.tensor(-12.5), None, torch.full((N,), 0.75), torch.tensor(0.21), torch.full((N,), 40.0),
+           torch.full((N,), 0.6), torch.zeros(N), 9.6e-4, torch.tensor(0.5))
+    log = RunLogger(path, print_steps=2, train_steps=10)
+    assert log(0, out, 2.0) is not None and log(1, out, 2.0) is None and log(2, out, 2.5) is not None
+    rows = [json.loads(line) for line in open(path)]
+    assert [r["STEP"] for r in rows] == [0, 2]
+    assert tuple(rows[0].keys()) == COLUMNS
+    r = rows[1]
+    assert r["LOSS"] == -12.5 and r["% ACC"] == 0.75 and abs(r["EPS"] - 0.21) < 1e-7 and r["BETA"] == 2.5
+    assert r["ACTION"] == 40.0 and abs(r["PLAQ"] - 0.6) < 1e-7 and r["dQ"] == 0.5 and r["LR"] == 9.6e-4
+    assert abs(r["(EXACT)"] - u1_plaq_exact(2.5)) < 1e-12 and r["t/STEP"] >= 0
+    text = log.text(r)
+    assert text.split()[0] == "2/10" and len(log.header.splitlines()) == 3 and "(EXACT)" in log.header
+    # any other rank writes nothing
+    quiet = RunLogger(str(tmp_path / "other.jsonl"), rank=1)
+    assert quiet(0, out, 2.0) is None and not (tmp_path / "other.jsonl").exists()
