@@ -254,6 +254,7 @@ class GaugeModel(object):
         # hvd.DistributedOptimizer (:941-943): average of the per-rank (clipped) gradients.  Two buckets of the flat
         # arena, eps | XNet and VNet: the first is averaged on a side stream while momentum_fn's weight-gradient products
         # still run (the C call records an event in between).  A global-norm clip needs the whole gradient first.
+        scale = 1.
         overlap = (self.using_hvd and self.native_train and not self.clip_grads and not self.dynamics.hmc
                    and self.overlap_allreduce)
         ev = None
@@ -273,14 +274,16 @@ class GaugeModel(object):
                 split = self._bucket_split
                 self._comm_stream.wait_event(ev)
                 with torch.cuda.stream(self._comm_stream):
-                    allreduce_mean_(eng.params.grad[:split])
-                allreduce_mean_(eng.params.grad[split:])
+                    allreduce_mean_(eng.params.grad[:split], divide=False)
+                allreduce_mean_(eng.params.grad[split:], divide=False)
                 main.wait_stream(self._comm_stream)
             else:
-                allreduce_mean_(eng.params.grad)
+                allreduce_mean_(eng.params.grad, divide=False)
+            import torch.distributed as dist
+            scale = 1.0 / dist.get_world_size()        # the SUM becomes the average inside the Adam kernel
         lr = self.learning_rate()
         with torch.cuda.device(self.device):
-            opt.step(lr)               # the clip (if any) was applied by _calc_loss_and_grads, before the average
+            opt.step(lr, grad_scale=scale)   # the clip (if any) was applied by _calc_loss_and_grads, before the average
         self.global_step += 1
         x_new = self._wrap(x_out)
         actions, plaqs, _, charges = self.lattice.observables(x_new)

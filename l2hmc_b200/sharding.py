@@ -96,13 +96,15 @@ def broadcast_weights(tensors, src=0, group=None):
             dist.broadcast(t, src=src, group=group)
 
 
-def allreduce_mean_(flat_grad, group=None):
+def allreduce_mean_(flat_grad, group=None, divide=True):
     """In-place average of one flat gradient bucket over ranks (hvd.DistributedOptimizer,
-    gauge_model.py:941-943): one collective per step, launched by the caller on its comm stream."""
+    gauge_model.py:941-943), on the current stream.  divide=False leaves the SUM: the caller folds 1 / world size into
+    the optimiser step (l2hmc_adam_step's grad_scale) instead of spending a kernel on it."""
     ws = world()[1]
     if ws > 1:
         dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, group=group)
-        flat_grad /= ws
+        if divide:
+            flat_grad /= ws
     return flat_grad
 
 

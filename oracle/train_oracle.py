@@ -140,9 +140,18 @@ def exponential_decay(lr_init, global_step, decay_steps, decay_rate, staircase=T
 
 
 def adam_update(param, grad, m, v, t, lr, beta1=0.9, beta2=0.999, epsilon=1e-8):
-    """tf.train.AdamOptimizer.apply_gradients (gauge_model.py:940-945; TensorFlow 1.x's published update):
-    lr_t = lr sqrt(1 - b2^t) / (1 - b1^t);  m <- b1 m + (1 - b1) g;  v <- b2 v + (1 - b2) g^2;
-    param <- param - lr_t m / (sqrt(v) + epsilon).  float64 NumPy.  Returns (m, v, param)."""
+    """tf.train.AdamOptimizer.apply_gradients (gauge_model.py:940-945).  TensorFlow is a third-party dependency that is
+    absent from /root/reference (unpinned: no requirements file; API use implies >= 1.12, < 2.0), so this restates the
+    update published in the class docstring of tensorflow/python/training/adam.py (TF 1.x), which nothing here can pin:
+        t <- t + 1
+        lr_t <- learning_rate * sqrt(1 - beta2^t) / (1 - beta1^t)
+        m_t <- beta1 * m_{t-1} + (1 - beta1) * g
+        v_t <- beta2 * v_{t-1} + (1 - beta2) * g * g
+        variable <- variable - lr_t * m_t / (sqrt(v_t) + epsilon)
+    i.e. the bias corrections m_hat, v_hat of Kingma & Ba's Algorithm 1 are FOLDED into lr_t and epsilon sits OUTSIDE
+    the square root, un-corrected ("epsilon hat" of the paper's section 2) -- not Algorithm 1's epsilon.  Defaults
+    beta1 = 0.9, beta2 = 0.999, epsilon = 1e-8 (the reference passes only the learning rate).  float64 NumPy.
+    Returns (m, v, param)."""
     lr_t = lr * np.sqrt(1. - beta2 ** t) / (1. - beta1 ** t)
     m = beta1 * m + (1. - beta1) * grad
     v = beta2 * v + (1. - beta2) * grad * grad
