@@ -303,6 +303,25 @@ int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const float* in, c
                                const float* mask_alt, int mask_invert_alt, const uint8_t* row_set, int N, int T,
                                int X, float* feat, void* stream);
 
+/* Routing tape of the conv front-end for the training pass: what the adjoint needs of the forward pass, 5.5 KB per chain
+ * and call at 16x16 instead of recomputing both convolutions (tf.gradients keeps the activations themselves).
+ *   p1   [N][T1*X1*F]   pooled conv-1 output (after bias + ReLU), T1 = ceil(T/2), X1 = ceil(X/2)
+ *   arg1 [N][T1*X1*F]   uint8: which of the window's (dt, dx, mu) candidates was the maximum, dt*4 + dx*2 + mu (the
+ *                       first one in that order), or 255 when the pooled value is 0 (ReLU-dead: no gradient)
+ *   arg2 [N][features]  uint8: dt*2 + dx of the second pool's maximum, or 255 when dead
+ * All three caller-owned device memory, written by l2hmc_conv3d_features_tape, read by l2hmc_conv3d_backward. */
+typedef struct {
+  float* p1;
+  uint8_t* arg1;
+  uint8_t* arg2;
+} l2hmc_conv3d_tape;
+
+int l2hmc_conv3d_tape_elems(int T, int X, int F); /* T1*X1*F: elements of p1 / arg1 per chain */
+/* l2hmc_conv3d_features_sets that also records the tape (tape non-null). */
+int l2hmc_conv3d_features_tape(const l2hmc_conv3d_weights* w, const float* in, const float* mask, int mask_invert,
+                               const float* mask_alt, int mask_invert_alt, const uint8_t* row_set, int N, int T, int X,
+                               float* feat, const l2hmc_conv3d_tape* tape, void* stream);
+
 /* ------------------------------------------------------------------ one host call = one L2HMC MC step
  * GaugeDynamics.apply_transition WITH the S/T/Q networks (dynamics/gauge_dynamics.py:195-313, 412-483): momentum and
  * direction draws, M augmented leapfrog steps (each chain in the direction it drew, both kinds in the same
@@ -556,7 +575,8 @@ int l2hmc_u1_loss_bwd(const l2hmc_loss_params* prm, const float* x, const float*
  * (+= mask (*) d loss / d masked input); `partial` [l2hmc_conv3d_bwd_rows(N)][l2hmc_conv3d_bwd_cols(F)] is
  * ACCUMULATED into: each row holds (d w1 [3,3,2,1,F] | d b1 [F] | d w2 [2,2,2,F,2F] | d b2 [2F]) of the chains
  * n = row mod rows; the caller zeroes it before the first call of a step and sums its rows (fixed order) at the end.
- * L2HMC_ERR_UNSUPPORTED when a chain's activations do not fit shared memory (32x32 with F = 32). */
+ * L2HMC_ERR_UNSUPPORTED when a chain's activations do not fit shared memory (32x32 with F = 32 WITHOUT a tape; with
+ * the tape that shape fits). */
 typedef struct {
   const l2hmc_conv3d_weights* w;
   const float* in;          /* [N,2TX] the stream's input (before masking) */
@@ -569,6 +589,10 @@ typedef struct {
   const float* g_feat;
   float* g_in;
   float* partial;
+  const l2hmc_conv3d_tape* tape; /* nullable: the forward pass's routing tape (l2hmc_conv3d_features_tape).  With it
+                                    nothing is recomputed and every product runs over the NON-ZEROS of the pooled
+                                    gradients (one per pooling window); without it both convolutions are recomputed
+                                    on-chip.  Same gradients up to summation order. */
 } l2hmc_conv3d_bwd_args;
 int l2hmc_conv3d_bwd_rows(int N);
 int l2hmc_conv3d_bwd_cols(int F);

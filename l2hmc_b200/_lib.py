@@ -87,11 +87,17 @@ class Conv3dWeights(Structure):
     _fields_ = [("w1", c_void_p), ("b1", c_void_p), ("w2", c_void_p), ("b2", c_void_p), ("F", c_int)]
 
 
+class Conv3dTape(Structure):
+    """l2hmc_conv3d_tape (include/l2hmc_b200.h)."""
+    _fields_ = [("p1", c_void_p), ("arg1", c_void_p), ("arg2", c_void_p)]
+
+
 class Conv3dBwdArgs(Structure):
     """l2hmc_conv3d_bwd_args (include/l2hmc_b200.h)."""
     _fields_ = [("w", POINTER(Conv3dWeights)), ("in_", c_void_p), ("mask", c_void_p), ("mask_invert", c_int),
                 ("mask_alt", c_void_p), ("mask_invert_alt", c_int), ("row_set", c_void_p), ("N", c_int), ("T", c_int),
-                ("X", c_int), ("g_feat", c_void_p), ("g_in", c_void_p), ("partial", c_void_p)]
+                ("X", c_int), ("g_feat", c_void_p), ("g_in", c_void_p), ("partial", c_void_p),
+                ("tape", POINTER(Conv3dTape))]
 
 
 class NetGrads(Structure):
@@ -216,6 +222,9 @@ SIGNATURES = {
     "l2hmc_conv3d_num_features": [c_int, c_int, c_int],
     "l2hmc_conv3d_features": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                               c_void_p],
+    "l2hmc_conv3d_tape_elems": [c_int, c_int, c_int],
+    "l2hmc_conv3d_features_tape": [POINTER(Conv3dWeights), c_void_p, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                                   c_int, c_int, c_int, c_void_p, POINTER(Conv3dTape), c_void_p],
     "l2hmc_sgemm_workspace_bytes": [POINTER(GemmArgs), c_int],
     "l2hmc_sgemm": [POINTER(GemmArgs), c_int, c_void_p, c_size_t, c_void_p],
     "l2hmc_tc_gemm_workspace_bytes": [POINTER(GemmArgs)],

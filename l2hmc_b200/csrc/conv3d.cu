@@ -40,6 +40,10 @@ struct ConvParams {
   const uint8_t* row_set;    // nullable [N]
   int N, T, X, F;
   float* feat;       // [N][T2*X2*2F]
+  // routing tape for the training pass (l2hmc_conv3d_tape), all three nullable together
+  float* t_p1;       // [N][T1*X1*F]
+  uint8_t* t_a1;     // [N][T1*X1*F]
+  uint8_t* t_a2;     // [N][T2*X2*2F]
 };
 
 __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
@@ -51,7 +55,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
   float* s_b1 = s_w1 + 18 * F;            // [F]
   float* s_w2 = s_b1 + F;                 // [4][F][C]   (kd = 0 taps only)
   float* s_b2 = s_w2 + 4 * F * C;         // [C]
-  float* s_in = s_b2 + C;                 // [T][X][2]
+  float* s_in = sm + ((18 * F + F + 4 * F * C + C + 3) & ~3);   // [T][X][2]  (float2 loads: aligned also for odd F)
   float* s_p1 = s_in + ((D + 3) & ~3);    // [T1][X1][F]
   const int tid = threadIdx.x;
 
@@ -103,6 +107,7 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
           w[a][b][1] = s_w1[((a * 3 + b) * 2 + 1) * F + f];
         }
       float best = -INFINITY;
+      int arg = 0;                                                 // first maximum in (dt, dx, mu) order
 #pragma unroll
       for (int dt = 0; dt < 2; ++dt)
 #pragma unroll
@@ -118,9 +123,15 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
               s0 = fmaf(in[dt + a][dx + b][1], w[a][b][1], s0);
               s1 = fmaf(in[dt + a][dx + b][1], w[a][b][0], s1);
             }
-          best = fmaxf(best, fmaxf(s0, s1));
+          if (s0 > best) best = s0, arg = dt * 4 + dx * 2;
+          if (s1 > best) best = s1, arg = dt * 4 + dx * 2 + 1;
         }
-      s_p1[o] = fmaxf(__fadd_rn(best, s_b1[f]), 0.f);
+      const float pooled = fmaxf(__fadd_rn(best, s_b1[f]), 0.f);
+      s_p1[o] = pooled;
+      if (p.t_p1 != nullptr) {
+        p.t_p1[static_cast<size_t>(n) * T1 * X1 * F + o] = pooled;
+        p.t_a1[static_cast<size_t>(n) * T1 * X1 * F + o] = pooled > 0.f ? static_cast<uint8_t>(arg) : 255;
+      }
     }
     __syncthreads();
 
@@ -155,12 +166,15 @@ __global__ void __launch_bounds__(kThreads) conv3d_kernel(const ConvParams p) {
           }
       }
       float best = -INFINITY;
+      int arg = 0;
 #pragma unroll
       for (int dt = 0; dt < 2; ++dt)
 #pragma unroll
         for (int dx = 0; dx < 2; ++dx)
-          if (tb + dt < T1 && xb + dx < X1) best = fmaxf(best, acc[dt][dx]);
-      dst[o] = fmaxf(__fadd_rn(best, s_b2[c]), 0.f);
+          if (tb + dt < T1 && xb + dx < X1 && acc[dt][dx] > best) best = acc[dt][dx], arg = dt * 2 + dx;
+      const float pooled = fmaxf(__fadd_rn(best, s_b2[c]), 0.f);
+      dst[o] = pooled;
+      if (p.t_a2 != nullptr) p.t_a2[static_cast<size_t>(n) * T2 * X2 * C + o] = pooled > 0.f ? static_cast<uint8_t>(arg) : 255;
     }
   }
 }
@@ -517,13 +531,23 @@ __global__ void __launch_bounds__(TH, 512 / TH) conv3d_tc_kernel(const ConvParam
         }
       }
       float ba = -INFINITY, bb = -INFINITY;
+      int aa = 0, ab = 0;                  // first maximum in (dt, dx, mu) order (training tape)
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        ba = fmaxf(ba, fmaxf(lo2((&s0[0][0])[i]), lo2((&s1[0][0])[i])));
-        bb = fmaxf(bb, fmaxf(hi2((&s0[0][0])[i]), hi2((&s1[0][0])[i])));
+        const float a0 = lo2((&s0[0][0])[i]), a1 = lo2((&s1[0][0])[i]);
+        const float b0 = hi2((&s0[0][0])[i]), b1 = hi2((&s1[0][0])[i]);
+        if (a0 > ba) ba = a0, aa = 2 * i;
+        if (a1 > ba) ba = a1, aa = 2 * i + 1;
+        if (b0 > bb) bb = b0, ab = 2 * i;
+        if (b1 > bb) bb = b1, ab = 2 * i + 1;
       }
       ba = fmaxf(__fadd_rn(ba, bias1a), 0.f);
       bb = fmaxf(__fadd_rn(bb, bias1b), 0.f);
+      if (p.t_p1 != nullptr) {
+        const size_t at = (static_cast<size_t>(n0 + ch) * T1 * X1 + t1 * X1 + x1) * F + 2 * fp;
+        *reinterpret_cast<float2*>(p.t_p1 + at) = make_float2(ba, bb);
+        *reinterpret_cast<uchar2*>(p.t_a1 + at) = make_uchar2(ba > 0.f ? aa : 255, bb > 0.f ? ab : 255);
+      }
       const float ha = tf32_hi(ba), hb = tf32_hi(bb);
       float* dst = s_a + (((2 * fp) >> 2) * ROWS + ch * R1 + t1 * X1B + x1) * 4 + ((2 * fp) & 3);
       *reinterpret_cast<float2*>(dst) = make_float2(ha, hb);
@@ -595,17 +619,25 @@ __global__ void __launch_bounds__(TH, 512 / TH) conv3d_tc_kernel(const ConvParam
     for (int item = tid / CG; item < nch * T2 * X2; item += TH / CG) {
       const int x2 = item % X2, rest = item / X2, t2 = rest % T2, ch = rest / T2;
       const int r00 = ch * R1 + 2 * t2 * X1B + 2 * x2;
-      float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+      float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      int arg[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const int row = r00 + (k >> 1) * X1B + (k & 1);
-        const float4 z = *reinterpret_cast<const float4*>(s_z + row * C + ((cg ^ (row & (CG - 1))) * 4));
-        best = make_float4(fmaxf(best.x, z.x), fmaxf(best.y, z.y), fmaxf(best.z, z.z), fmaxf(best.w, z.w));
+        const float4 z4 = *reinterpret_cast<const float4*>(s_z + row * C + ((cg ^ (row & (CG - 1))) * 4));
+        const float z[4] = {z4.x, z4.y, z4.z, z4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (z[e] > best[e]) best[e] = z[e], arg[e] = k;
       }
       const float4 b = *reinterpret_cast<const float4*>(s_b2 + 4 * cg);
-      float* dst = p.feat + static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
-      __stcs(reinterpret_cast<float4*>(dst), make_float4(fmaxf(__fadd_rn(best.x, b.x), 0.f), fmaxf(__fadd_rn(best.y, b.y), 0.f),
-                                                          fmaxf(__fadd_rn(best.z, b.z), 0.f), fmaxf(__fadd_rn(best.w, b.w), 0.f)));
+      const float o[4] = {fmaxf(__fadd_rn(best[0], b.x), 0.f), fmaxf(__fadd_rn(best[1], b.y), 0.f),
+                          fmaxf(__fadd_rn(best[2], b.z), 0.f), fmaxf(__fadd_rn(best[3], b.w), 0.f)};
+      const size_t at = static_cast<size_t>(n0 + ch) * T2 * X2 * C + (t2 * X2 + x2) * C + 4 * cg;
+      __stcs(reinterpret_cast<float4*>(p.feat + at), make_float4(o[0], o[1], o[2], o[3]));
+      if (p.t_a2 != nullptr)
+        *reinterpret_cast<uchar4*>(p.t_a2 + at) = make_uchar4(o[0] > 0.f ? arg[0] : 255, o[1] > 0.f ? arg[1] : 255,
+                                                              o[2] > 0.f ? arg[2] : 255, o[3] > 0.f ? arg[3] : 255);
     }
   }
   tc_fence_before();
@@ -713,18 +745,30 @@ extern "C" int l2hmc_conv3d_features(const l2hmc_conv3d_weights* w, const float*
 extern "C" int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const float* in, const float* mask,
                                           int mask_invert, const float* mask_alt, int mask_invert_alt,
                                           const uint8_t* row_set, int N, int T, int X, float* feat, void* stream) {
+  return l2hmc_conv3d_features_tape(w, in, mask, mask_invert, mask_alt, mask_invert_alt, row_set, N, T, X, feat, nullptr,
+                                    stream);
+}
+
+extern "C" int l2hmc_conv3d_tape_elems(int T, int X, int F) { return ((T + 1) / 2) * ((X + 1) / 2) * F; }
+
+extern "C" int l2hmc_conv3d_features_tape(const l2hmc_conv3d_weights* w, const float* in, const float* mask,
+                                          int mask_invert, const float* mask_alt, int mask_invert_alt,
+                                          const uint8_t* row_set, int N, int T, int X, float* feat,
+                                          const l2hmc_conv3d_tape* tape, void* stream) {
   L2HMC_REQUIRE(w, "l2hmc_conv3d_features: null weights");
+  L2HMC_REQUIRE(!tape || (tape->p1 && tape->arg1 && tape->arg2), "l2hmc_conv3d_features_tape: null tape array");
   if (N == 0) return L2HMC_OK;
   L2HMC_REQUIRE(w->w1 && w->b1 && w->w2 && w->b2 && in && feat, "l2hmc_conv3d_features: null pointer");
   L2HMC_REQUIRE(N >= 0 && T > 0 && X > 0 && w->F > 0, "l2hmc_conv3d_features: bad sizes N=%d T=%d X=%d F=%d", N, T, X,
                 w->F);
   const int F = w->F, C = 2 * F, D = 2 * T * X, T1 = (T + 1) / 2, X1 = (X + 1) / 2;
-  const size_t smem = sizeof(float) * (18 * F + F + 4 * F * C + C + ((D + 3) & ~3) + T1 * X1 * F);
+  const size_t smem = sizeof(float) * (((18 * F + F + 4 * F * C + C + 3) & ~3) + ((D + 3) & ~3) + T1 * X1 * F);
   int dev = 0, max_smem = 0, sms = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, mask_alt, mask_invert_alt, row_set, N, T, X, F, feat};
+  ConvParams p{w->w1, w->b1, w->w2, w->b2, in, mask, mask_invert, mask_alt, mask_invert_alt, row_set, N, T, X, F, feat,
+               tape ? tape->p1 : nullptr, tape ? tape->arg1 : nullptr, tape ? tape->arg2 : nullptr};
   int rc = -1;
   // conv 2 on the tensor cores unless the shape does not fit or L2HMC_CONV_PATH=ffma asks for the FMA-pipe kernels
   static const bool ffma_only = [] { const char* e = std::getenv("L2HMC_CONV_PATH"); return e && std::string(e) == "ffma"; }();
@@ -734,9 +778,11 @@ extern "C" int l2hmc_conv3d_features_sets(const l2hmc_conv3d_weights* w, const f
     else if (F == 32) rc = launch_tc<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
     if (rc >= 0) return rc;
   }
-  if (F == 8) rc = launch_tiled<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
-  else if (F == 16) rc = launch_tiled<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
-  else if (F == 32) rc = launch_tiled<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+  if (tape == nullptr) {                  // (the all-FFMA2 tiled kernel does not record the training tape)
+    if (F == 8) rc = launch_tiled<8>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+    else if (F == 16) rc = launch_tiled<16>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+    else if (F == 32) rc = launch_tiled<32>(p, sms, max_smem, static_cast<cudaStream_t>(stream));
+  }
   if (rc >= 0) return rc;                 // -1: not covered by the tiled kernel, use the generic one
   if (smem > static_cast<size_t>(max_smem)) {
     set_error("l2hmc_conv3d_features: %dx%d lattice with F=%d needs %zu B of shared memory (limit %d)", T, X, F, smem,

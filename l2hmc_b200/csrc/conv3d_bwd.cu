@@ -11,6 +11,7 @@
 // deterministic, no atomics.  TF 'same' semantics as in conv3d.cu (zero padding, odd cell at the end, clipped
 // pooling windows; the kd = 1 taps of conv-2 only ever see padding, so their gradient is exactly zero).
 #include "common.cuh"
+#include "conv3d_bwd.cuh"
 
 namespace l2hmc {
 namespace {
@@ -575,6 +576,14 @@ extern "C" int l2hmc_conv3d_backward(const l2hmc_conv3d_bwd_args* a, void* strea
   L2HMC_REQUIRE(a->w->w1 && a->w->b1 && a->w->w2 && a->w->b2 && a->in && a->g_feat && a->g_in && a->partial,
                 "l2hmc_conv3d_backward: null pointer");
   L2HMC_REQUIRE(!a->row_set || (!a->mask == !a->mask_alt), "l2hmc_conv3d_backward: mask and mask_alt go together");
+  if (a->tape != nullptr) {      // the forward pass's routing tape: nothing recomputed, products over the non-zeros only
+    L2HMC_REQUIRE(a->tape->p1 && a->tape->arg1 && a->tape->arg2, "l2hmc_conv3d_backward: null tape array");
+    const int rc = conv3d_backward_tape(a, l2hmc_conv3d_bwd_rows(a->N), l2hmc_conv3d_bwd_cols(F),
+                                        static_cast<cudaStream_t>(stream));
+    if (rc >= 0) return rc;
+    set_error("l2hmc_conv3d_backward: %dx%d with F=%d does not fit shared memory even with the tape", T, X, F);
+    return L2HMC_ERR_UNSUPPORTED;
+  }
   const int T2 = (T + 1) / 2, X2 = (X + 1) / 2, D = 2 * T * X;
   const bool fast = (F == 8 || F == 16 || F == 32) && D % 4 == 0;   // float4 rows need 16-byte aligned buffers
   const size_t fp = fast ? F + 4 : F + 1, cp = fast ? 2 * F + 4 : 2 * F + 1;

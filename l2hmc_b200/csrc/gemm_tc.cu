@@ -402,11 +402,11 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
 // ------------------------------------------------------------------ format kernels
 // row-major fp32 [rows, K] (leading dimension ld, optional 0/1 mask row) -> TS32 K blocks
 // [kb0, kb0 + ceil(K/32)) of a buffer with `rg_total` row groups; rows >= `rows` and k >= K are zero.
-__global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __restrict__ src, int ld, int rows, int K,
-                                                                 const float* __restrict__ mask, int invert,
-                                                                 const float* __restrict__ mask_alt, int invert_alt,
-                                                                 const uint8_t* __restrict__ row_set,
-                                                                 float* dst, int rg_total, int kb0, int nkb) {
+__device__ __forceinline__ void ts32_from_rowmajor(const float* __restrict__ src, int ld, int rows, int K,
+                                                   const float* __restrict__ mask, int invert,
+                                                   const float* __restrict__ mask_alt, int invert_alt,
+                                                   const uint8_t* __restrict__ row_set, float* dst, int rg_total, int kb0,
+                                                   int nkb) {
   // one thread per (kb, rg, kc, r8): consecutive threads write consecutive 16 B
   const size_t total = static_cast<size_t>(nkb) * rg_total * 64;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -443,6 +443,49 @@ __global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __
     *reinterpret_cast<float4*>(d + 256) = make_float4(l[0], l[1], l[2], l[3]);
   }
 }
+__global__ void __launch_bounds__(256) ts32_from_rowmajor_kernel(const float* __restrict__ src, int ld, int rows, int K,
+                                                                 const float* __restrict__ mask, int invert,
+                                                                 const float* __restrict__ mask_alt, int invert_alt,
+                                                                 const uint8_t* __restrict__ row_set,
+                                                                 float* dst, int rg_total, int kb0, int nkb) {
+  ts32_from_rowmajor(src, ld, rows, K, mask, invert, mask_alt, invert_alt, row_set, dst, rg_total, kb0, nkb);
+}
+
+// Everything a network call needs before its first GEMM, in ONE launch (it was four: at config 3 each was ~4 us of
+// launch latency in a 136 us call): blockIdx.y = 0 / 1: the two inputs -> TS32 (mask folded into the second),
+// blockIdx.y = 2: the effective first-layer bias of both time-embedding sets.
+struct NetPrologueParams {
+  const float *in0, *in1;
+  int K, N;
+  const float* mask;
+  int invert;
+  const float* mask_alt;
+  int invert_alt;
+  const uint8_t* row_set;
+  float* acat;
+  int rg, kbK;
+  const float *b0, *b1, *b2, *wt;
+  float tau0, tau1, tau0_alt, tau1_alt;
+  int H, h_rows;
+  float* bias_eff;
+};
+__global__ void __launch_bounds__(256) net_prologue_kernel(const NetPrologueParams q) {
+  if (blockIdx.y == 0) {
+    ts32_from_rowmajor(q.in0, q.K, q.N, q.K, nullptr, 0, nullptr, 0, nullptr, q.acat, q.rg, 0, q.kbK);
+  } else if (blockIdx.y == 1) {
+    ts32_from_rowmajor(q.in1, q.K, q.N, q.K, q.mask, q.invert, q.mask_alt, q.invert_alt, q.row_set, q.acat, q.rg, q.kbK,
+                       q.kbK);
+  } else {
+    // bias_eff[n] = b0[n] + b1[n] + (tau0*wt[0][n] + tau1*wt[1][n] + b2[n]), the op order of bias_eff_kernel
+    const int sets = q.row_set != nullptr ? 2 : 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < sets * q.H; i += gridDim.x * blockDim.x) {
+      const int set = i / q.H, n = i - set * q.H;
+      const float t0 = set ? q.tau0_alt : q.tau0, t1 = set ? q.tau1_alt : q.tau1;
+      const float tt = __fadd_rn(__fadd_rn(__fmul_rn(t0, q.wt[n]), __fmul_rn(t1, q.wt[q.H + n])), q.b2[n]);
+      q.bias_eff[set * q.h_rows + n] = __fadd_rn(__fadd_rn(q.b0[n], q.b1[n]), tt);
+    }
+  }
+}
 
 // Keras kernel W [K, cols] (row-major) -> TS32 of W^T: packed row `prow(n)` = output feature n, K blocks
 // [kb0, kb0 + ceil(K/32)).  heads != 0: n = output d of head `head`, packed row = (d/64)*192 + head*64 + d%64.
@@ -475,15 +518,6 @@ __global__ void __launch_bounds__(256) ts32_to_rowmajor_kernel(const float* __re
                      (r % 8) * 4 + k % 4;
     dst[i] = __fadd_rn(s[0], s[256]);
   }
-}
-
-// bias_eff[n] = b0[n] + b1[n] + (tau0*wt[0][n] + tau1*wt[1][n] + b2[n])   (first layer)
-__global__ void bias_eff_kernel(const float* b0, const float* b1, const float* b2, const float* wt, float tau0,
-                                float tau1, int H, float* out) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= H) return;
-  const float tt = __fadd_rn(__fadd_rn(__fmul_rn(tau0, wt[n]), __fmul_rn(tau1, wt[H + n])), b2[n]);
-  out[n] = __fadd_rn(__fadd_rn(b0[n], b1[n]), tt);
 }
 
 __global__ void logdet_reduce_tc_kernel(const float* __restrict__ part, int tiles, int N, float* logdet) {
@@ -570,17 +604,11 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   const int rg = d.rows_p / 8;
 
   // network inputs -> TS32 (mask folded into the second input)
-  ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
-      c->in0, K, N, K, nullptr, 0, nullptr, 0, nullptr, acat, rg, 0, d.kbK);
-  ts32_from_rowmajor_kernel<<<ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 256, 0, st>>>(
-      c->in1, K, N, K, c->in1_mask, c->in1_mask_invert, c->in1_mask_alt, c->in1_mask_invert_alt, c->row_set, acat, rg,
-      d.kbK, d.kbK);
-  bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos, c->tau_sin, H,
-                                                    bias_eff);
-  if (c->row_set)
-    bias_eff_kernel<<<(H + 255) / 256, 256, 0, st>>>(w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos_alt, c->tau_sin_alt,
-                                                      H, bias_eff + d.h_rows);
-  int rc = check_launch("ts32_from_rowmajor_kernel", c->row_set ? 4 : 3);
+  NetPrologueParams q{c->in0, c->in1, K, N, c->in1_mask, c->in1_mask_invert, c->in1_mask_alt, c->in1_mask_invert_alt,
+                      c->row_set, acat, rg, d.kbK, w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos, c->tau_sin,
+                      c->tau_cos_alt, c->tau_sin_alt, H, d.h_rows, bias_eff};
+  net_prologue_kernel<<<dim3(ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 3), 256, 0, st>>>(q);
+  int rc = check_launch("net_prologue_kernel");
   if (rc) return rc;
 
   static const int debug_noload = getenv("L2HMC_TC_DEBUG_NOLOAD") ? atoi(getenv("L2HMC_TC_DEBUG_NOLOAD")) : 0;

@@ -76,6 +76,11 @@ struct Plan {
   float *fg0, *fg1;
   float* part[4];        // conv partial rows: XNet.x, XNet.v, VNet.x, VNet.v
   int prow, pcol;
+  // conv routing tapes (l2hmc_conv3d_tape): per network and input stream, one slot per call
+  float* cp1[2][2];      // [net: 0 = XNet, 1 = VNet][stream: 0 = in0, 1 = in1][2M calls][R][tape_elems]
+  uint8_t* ca1[2][2];
+  uint8_t* ca2[2][2];    // [..][R][K]
+  size_t tape_elems;
   void* gemm_ws;
   size_t gemm_ws_bytes;
   size_t total;
@@ -150,6 +155,14 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
       pl.fg0 = c.take<float>(R * a->xnet->K), pl.fg1 = c.take<float>(R * a->xnet->K);
       pl.prow = l2hmc_conv3d_bwd_rows(pl.R), pl.pcol = l2hmc_conv3d_bwd_cols(a->xconv_in0->F);
       for (int i = 0; i < 4; ++i) pl.part[i] = c.take<float>(static_cast<size_t>(pl.prow) * pl.pcol);
+      pl.tape_elems = static_cast<size_t>(l2hmc_conv3d_tape_elems(a->T, a->X, a->xconv_in0->F));
+      const size_t calls = 2 * M;
+      for (int net = 0; net < 2; ++net)
+        for (int sidx = 0; sidx < 2; ++sidx) {
+          pl.cp1[net][sidx] = c.take<float>(calls * R * pl.tape_elems);
+          pl.ca1[net][sidx] = c.take<uint8_t>(calls * R * pl.tape_elems);
+          pl.ca2[net][sidx] = c.take<uint8_t>(calls * R * static_cast<size_t>(a->xnet->K));
+        }
     }
   }
   pl.total = c.used + 256;
@@ -257,9 +270,24 @@ int conv_weight_grads(const Ctx& c, const NetTape& t, const float* part, const l
   return L2HMC_OK;
 }
 
-int conv_bwd(const Ctx& c, const l2hmc_conv3d_weights* w, const float* raw, const float* g_feat, float* g_in, float* part,
+// tape slot of (net, input stream, call j)
+l2hmc_conv3d_tape conv_tape(const Ctx& c, int net, int sidx, int j) {
+  const Plan& pl = c.pl;
+  const size_t off = static_cast<size_t>(j) * pl.R;
+  return l2hmc_conv3d_tape{pl.cp1[net][sidx] + off * pl.tape_elems, pl.ca1[net][sidx] + off * pl.tape_elems,
+                           pl.ca2[net][sidx] + off * static_cast<size_t>(c.a->xnet->K)};
+}
+
+int conv_fwd(const Ctx& c, const l2hmc_conv3d_weights* w, const float* raw, float* feat, const l2hmc_conv3d_tape& tape,
              const float* mask, int inv, const float* mask_alt, int inv_alt) {
+  return l2hmc_conv3d_features_tape(w, raw, mask, inv, mask_alt, inv_alt, mask ? c.pl.row_set : nullptr, c.pl.R, c.a->T,
+                                    c.a->X, feat, &tape, c.stream);
+}
+
+int conv_bwd(const Ctx& c, const l2hmc_conv3d_weights* w, const float* raw, const float* g_feat, float* g_in, float* part,
+             const float* mask, int inv, const float* mask_alt, int inv_alt, const l2hmc_conv3d_tape& tape) {
   l2hmc_conv3d_bwd_args b{};
+  b.tape = &tape;
   b.w = w, b.in = raw, b.N = c.pl.R, b.T = c.a->T, b.X = c.a->X;
   b.mask = mask, b.mask_invert = inv, b.mask_alt = mask_alt, b.mask_invert_alt = inv_alt;
   b.row_set = mask ? c.pl.row_set : nullptr;
@@ -348,8 +376,8 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           NetTape& t = pl.vt;
           const size_t off = static_cast<size_t>(jv) * R;
           if (conv) {   // momentum_fn([x, grad, t]): x through conv_v*, the force through conv_x*
-            L2HMC_TRY(l2hmc_conv3d_features(a->vconv_in0, Xs(xi), nullptr, 0, R, T, X, t.in0 + off * t.K, stream));
-            L2HMC_TRY(l2hmc_conv3d_features(a->vconv_in1, g, nullptr, 0, R, T, X, t.in1 + off * t.K, stream));
+            L2HMC_TRY(conv_fwd(c, a->vconv_in0, Xs(xi), t.in0 + off * t.K, conv_tape(c, 1, 0, jv), nullptr, 0, nullptr, 0));
+            L2HMC_TRY(conv_fwd(c, a->vconv_in1, g, t.in1 + off * t.K, conv_tape(c, 1, 1, jv), nullptr, 0, nullptr, 0));
           } else {
             L2HMC_TRY(copy(t.in0 + off * t.K, Xs(xi), RD));
           }
@@ -366,9 +394,9 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           NetTape& t = pl.xt;
           const size_t off = static_cast<size_t>(jx) * R;
           if (conv) {   // position_fn([v, mask * x, t]): v through conv_v*, m*x through conv_x*
-            L2HMC_TRY(l2hmc_conv3d_features(a->xconv_in0, Vs(vi), nullptr, 0, R, T, X, t.in0 + off * t.K, stream));
-            L2HMC_TRY(l2hmc_conv3d_features_sets(a->xconv_in1, Xs(xi), row_f, invs[q], row_b, invs_alt[q], pl.row_set, R, T,
-                                                 X, t.in1 + off * t.K, stream));
+            L2HMC_TRY(conv_fwd(c, a->xconv_in0, Vs(vi), t.in0 + off * t.K, conv_tape(c, 0, 0, jx), nullptr, 0, nullptr, 0));
+            L2HMC_TRY(conv_fwd(c, a->xconv_in1, Xs(xi), t.in1 + off * t.K, conv_tape(c, 0, 1, jx), row_f, invs[q], row_b,
+                               invs_alt[q]));
           } else {
             L2HMC_TRY(copy(t.in0 + off * t.K, Vs(vi), RD));
             L2HMC_TRY(l2hmc_mask_mul_sets(Xs(xi), row_f, invs[q], row_b, invs_alt[q], pl.row_set, R, D, t.in1 + off * t.K,
@@ -432,8 +460,10 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
         if (conv) {
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K));
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K));
-          L2HMC_TRY(conv_bwd(c, a->vconv_in0, Xs(rec.xi), pl.fg0, pl.gx, pl.part[3], nullptr, 0, nullptr, 0));
-          L2HMC_TRY(conv_bwd(c, a->vconv_in1, rec.g, pl.fg1, pl.dg, pl.part[2], nullptr, 0, nullptr, 0));
+          L2HMC_TRY(conv_bwd(c, a->vconv_in0, Xs(rec.xi), pl.fg0, pl.gx, pl.part[3], nullptr, 0, nullptr, 0,
+                             conv_tape(c, 1, 0, rec.j)));
+          L2HMC_TRY(conv_bwd(c, a->vconv_in1, rec.g, pl.fg1, pl.dg, pl.part[2], nullptr, 0, nullptr, 0,
+                             conv_tape(c, 1, 1, rec.j)));
         } else {
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gx, D, 1));
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.dg, D, 1));
@@ -451,8 +481,10 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
         if (conv) {
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K));
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K));
-          L2HMC_TRY(conv_bwd(c, a->xconv_in0, Vs(rec.vi), pl.fg0, pl.gv, pl.part[1], nullptr, 0, nullptr, 0));
-          L2HMC_TRY(conv_bwd(c, a->xconv_in1, Xs(rec.xi), pl.fg1, pl.gx, pl.part[0], row_f, rec.inv, row_b, rec.inv_alt));
+          L2HMC_TRY(conv_bwd(c, a->xconv_in0, Vs(rec.vi), pl.fg0, pl.gv, pl.part[1], nullptr, 0, nullptr, 0,
+                             conv_tape(c, 0, 0, rec.j)));
+          L2HMC_TRY(conv_bwd(c, a->xconv_in1, Xs(rec.xi), pl.fg1, pl.gx, pl.part[0], row_f, rec.inv, row_b, rec.inv_alt,
+                             conv_tape(c, 0, 1, rec.j)));
         } else {
           L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gv, D, 1));
           L2HMC_TRY(gemm(c, R, K, {l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}}, pl.gx, D, 1, nullptr, 0, row_f, rec.inv,

@@ -154,6 +154,7 @@ class TrainEngine(object):
         self.dyn = dynamics
         self.conv = (not dynamics.hmc) and dynamics.network_arch == "conv3D"
         self._conv_partial = {}
+        self._conv_tapes = {}
         self.device = dynamics.device
         self.metric, self.loss_scale = metric, float(loss_scale)
         self.params = FlatParams(dynamics)
@@ -249,19 +250,29 @@ class TrainEngine(object):
         t1 = torch.tensor([tau_alt[0], tau_alt[1], 1.], dtype=torch.float32, device=self.device)
         tape.tau1[j] = torch.where(row_set[:, None] != 0, t1[None, :], t0[None, :])
 
-    def _conv_features(self, net, which, raw, feat, R, masks=None):
-        """Conv front-end of one input stream into the tape slot `feat` (csrc/conv3d.cu)."""
-        lib, dyn = _lib.get_lib(), self.dyn
-        if masks is None:
-            self._call(lib.l2hmc_conv3d_features, net._conv(which), _lib.dptr(raw), None, 0, R, dyn.T, dyn.X, _ptr(feat))
-        else:
-            m, inv, ma, inva, rs = masks
-            self._call(lib.l2hmc_conv3d_features_sets, net._conv(which), _lib.dptr(raw), _lib.dptr(m), int(inv),
-                       _lib.dptr(ma), int(inva), rs, R, dyn.T, dyn.X, _ptr(feat))
+    def _conv_tape(self, key, net, R):
+        """The routing tape (l2hmc_conv3d_tape) of one conv call: pooled conv-1 plane + the two pools' argmax codes."""
+        if key not in self._conv_tapes:
+            n = int(_lib.get_lib().l2hmc_conv3d_tape_elems(self.dyn.T, self.dyn.X, int(net.num_filters)))
+            u8 = dict(dtype=torch.uint8, device=self.device)
+            self._conv_tapes[key] = (self._new(R, n), torch.empty(R, n, **u8), torch.empty(R, int(net.num_features), **u8))
+        p1, a1, a2 = self._conv_tapes[key]
+        t = _lib.Conv3dTape()
+        t.p1, t.arg1, t.arg2 = _lib.dptr(p1), _lib.dptr(a1, torch.uint8), _lib.dptr(a2, torch.uint8)
+        return t
 
-    def _conv_backward(self, name, net, which, raw, g_feat, g_in, R, masks=None):
+    def _conv_features(self, name, j, net, which, raw, feat, R, masks=None):
+        """Conv front-end of one input stream into the tape slot `feat`, recording its routing tape (csrc/conv3d.cu)."""
+        lib, dyn = _lib.get_lib(), self.dyn
+        tape = self._conv_tape((name, which, j), net, R)
+        m, inv, ma, inva, rs = masks if masks is not None else (None, 0, None, 0, None)
+        self._call(lib.l2hmc_conv3d_features_tape, net._conv(which), _lib.dptr(raw), _lib.dptr(m), int(inv),
+                   _lib.dptr(ma), int(inva), rs, R, dyn.T, dyn.X, _ptr(feat), ctypes.byref(tape))
+
+    def _conv_backward(self, name, j, net, which, raw, g_feat, g_in, R, masks=None):
         """Adjoint of _conv_features: g_in += mask * d loss / d input; weight gradients into the stream's partial rows."""
         lib, dyn = _lib.get_lib(), self.dyn
+        tape = self._conv_tape((name, which, j), net, R)
         key = (name, which)
         if key not in self._conv_partial:
             rows, cols = int(lib.l2hmc_conv3d_bwd_rows(R)), int(lib.l2hmc_conv3d_bwd_cols(int(net.num_filters)))
@@ -274,6 +285,7 @@ class TrainEngine(object):
             a.mask, a.mask_invert, a.mask_alt, a.mask_invert_alt, a.row_set = _lib.dptr(m), int(inv), _lib.dptr(ma), \
                 int(inva), rs
         a.g_feat, a.g_in, a.partial = _lib.dptr(g_feat), _lib.dptr(g_in), _lib.dptr(self._conv_partial[key])
+        a.tape = ctypes.pointer(tape)
         self._call(lib.l2hmc_conv3d_backward, ctypes.byref(a))
 
     def _conv_weight_grads(self, name, net, tp):
@@ -409,8 +421,8 @@ class TrainEngine(object):
                     if nets:
                         tp = tapes["VNet"]
                         if self.conv:        # momentum_fn([x, grad, t]): x through conv_v*, the force through conv_x*
-                            self._conv_features(dyn.momentum_fn, "v", xs, tp.in0[jv], R)
-                            self._conv_features(dyn.momentum_fn, "x", g, tp.in1[jv], R)
+                            self._conv_features("VNet", jv, dyn.momentum_fn, "v", xs, tp.in0[jv], R)
+                            self._conv_features("VNet", jv, dyn.momentum_fn, "x", g, tp.in1[jv], R)
                         self._net_forward(dyn.momentum_fn, tp, jv, R, tau, tau_alt, row_set)
                         S, Tr, Q = _ptr(tp.S[jv]), _ptr(tp.T[jv]), _ptr(tp.Q[jv])
                         jv += 1
@@ -423,8 +435,8 @@ class TrainEngine(object):
                     S = Tr = Q = None
                     if nets and self.conv:       # position_fn([v, mask * x, t]): v through conv_v*, m*x through conv_x*
                         tp = tapes["XNet"]
-                        self._conv_features(dyn.position_fn, "v", vs, tp.in0[jx], R)
-                        self._conv_features(dyn.position_fn, "x", xs, tp.in1[jx], R, (row_f, inv, row_b, inv_alt, rs))
+                        self._conv_features("XNet", jx, dyn.position_fn, "v", vs, tp.in0[jx], R)
+                        self._conv_features("XNet", jx, dyn.position_fn, "x", xs, tp.in1[jx], R, (row_f, inv, row_b, inv_alt, rs))
                     elif nets:
                         tp = tapes["XNet"]
                         tp.in0[jx].copy_(vs)
@@ -531,8 +543,8 @@ class TrainEngine(object):
                     # momentum_fn([x, grad, t]): first input x, second the force
                     if self.conv:
                         f0, f1 = self._feat_grads(net, tp, dz1, R)
-                        self._conv_backward("VNet", net, "v", rec["x"], f0, gx, R)
-                        self._conv_backward("VNet", net, "x", rec["g"], f1, dg, R)
+                        self._conv_backward("VNet", j, net, "v", rec["x"], f0, gx, R)
+                        self._conv_backward("VNet", j, net, "x", rec["g"], f1, dg, R)
                     else:
                         self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gx),
                                   D, accumulate=True)
@@ -552,8 +564,8 @@ class TrainEngine(object):
                     # position_fn([v, mask * x, t]): first input v, second the masked links
                     if self.conv:
                         f0, f1 = self._feat_grads(net, tp, dz1, R)
-                        self._conv_backward("XNet", net, "v", rec["v"], f0, gv, R)
-                        self._conv_backward("XNet", net, "x", rec["x"], f1, gx, R,
+                        self._conv_backward("XNet", j, net, "v", rec["v"], f0, gv, R)
+                        self._conv_backward("XNet", j, net, "x", rec["x"], f1, gx, R,
                                             (rec["mask"], rec["inv"], rec["mask_alt"], rec["inv_alt"], rs))
                     else:
                         self.gemm(R, K, [(dz1, H, 1, _lib.dptr(net.weights["v_layer.kernel"]), 1, H, H)], _lib.dptr(gv),

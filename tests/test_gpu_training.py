@@ -440,7 +440,7 @@ def test_train_loop_and_saved_state(tmp_path):
 # register-tiled kernels: F in {8, 16, 32}; X == F folds the index arithmetic; even X / even pooled X take the
 # paired-position phases, odd ones the single-position phases; other F: the generic kernel
 @pytest.mark.parametrize("T,X,F,N", [(8, 8, 8, 21), (6, 10, 4, 9), (16, 16, 16, 300), (4, 4, 3, 400), (8, 12, 8, 50),
-                                     (6, 10, 16, 40), (8, 7, 8, 30), (8, 8, 32, 20)])
+                                     (6, 10, 16, 40), (8, 7, 8, 30), (8, 8, 32, 20), (32, 32, 32, 5), (5, 7, 6, 12)])
 def test_conv3d_backward_against_autograd(T, X, F, N):
     """l2hmc_conv3d_backward vs torch autograd through the oracle's Conv3D/MaxPool3D stack (conv_net.py:247-260),
     with per-chain mask sets and more chains than partial rows (accumulation across CTA passes)."""
@@ -477,15 +477,48 @@ def test_conv3d_backward_against_autograd(T, X, F, N):
     a.mask, a.mask_invert, a.mask_alt, a.mask_invert_alt = _lib.dptr(tm0), 0, _lib.dptr(tm1), 1
     a.row_set = _lib.dptr(trs, torch.uint8)
     a.g_feat, a.g_in, a.partial = _lib.dptr(tg), _lib.dptr(tgin), _lib.dptr(part)
+    # recompute path (no tape); it refuses the shapes whose activations do not fit shared memory (32x32 with F = 32)
+    rc = lib.l2hmc_conv3d_backward(ctypes.byref(a), None)
+    recompute_ok = rc == 0
+    assert recompute_ok or (rc == _lib.L2HMC_ERR_UNSUPPORTED and T * X * F >= 32 * 32 * 32)
+    torch.cuda.synchronize()
+
+    def check(tgin_, part_, what):
+        tot = part_.double().sum(dim=0).cpu()
+        close_scaled(tgin_, torch.tensor(g_in0, dtype=torch.float64) + gx_ref, 2e-5, f"conv d/d input ({what})")
+        off = 0
+        for nm, ref in (("w1", g1), ("b1", gb1), ("w2", g2), ("b2", gb2)):
+            n = ref.numel()
+            close_scaled(tot[off:off + n], ref.reshape(-1), 5e-5, f"conv d/d {nm} ({what})")
+            off += n
+    if recompute_ok:
+        check(tgin, part, "recompute")
+    # tape path: the forward pass records P1 and the two pools' argmax codes, the adjoint runs over the non-zeros only
+    n_el = lib.l2hmc_conv3d_tape_elems(T, X, F)
+    assert n_el == ((T + 1) // 2) * ((X + 1) // 2) * F
+    p1 = torch.full((N, n_el), float("nan"), device="cuda")
+    a1 = torch.full((N, n_el), 77, dtype=torch.uint8, device="cuda")
+    a2 = torch.full((N, K), 77, dtype=torch.uint8, device="cuda")
+    tape = _lib.Conv3dTape()
+    tape.p1, tape.arg1, tape.arg2 = _lib.dptr(p1), _lib.dptr(a1, torch.uint8), _lib.dptr(a2, torch.uint8)
+    feat_dev = torch.empty(N, K, device="cuda")
+    _lib.check(lib.l2hmc_conv3d_features_tape(ctypes.byref(cw), _lib.dptr(tx), _lib.dptr(tm0), 0, _lib.dptr(tm1), 1,
+                                              _lib.dptr(trs, torch.uint8), N, T, X, _lib.dptr(feat_dev), ctypes.byref(tape),
+                                              None))
+    close_scaled(feat_dev, feat.detach(), 2e-5, "features recorded with the tape")
+    # the tape itself: P1 is the pooled conv-1 plane; codes are in range, dead exactly where the pooled value is zero
+    h1 = orc._maxpool3d_same(orc._conv3d_same_relu((mrow * x).reshape(N, T, X, 2, 1).detach(), leaves["k1"].detach(),
+                                                   leaves["b1"].detach())).reshape(N, -1)
+    close_scaled(p1, h1, 2e-5, "tape p1")
+    c1, c2 = a1.cpu().numpy(), a2.cpu().numpy()
+    assert ((c1 < 8) | (c1 == 255)).all() and ((c2 < 4) | (c2 == 255)).all()
+    assert ((c1 == 255) == (p1.cpu().numpy() == 0)).all() and ((c2 == 255) == (feat_dev.cpu().numpy() == 0)).all()
+    part2 = torch.zeros(prows, pcols, device="cuda")
+    tgin2 = cu(g_in0)
+    a.g_in, a.partial, a.tape = _lib.dptr(tgin2), _lib.dptr(part2), ctypes.pointer(tape)
     _lib.check(lib.l2hmc_conv3d_backward(ctypes.byref(a), None))
     torch.cuda.synchronize()
-    tot = part.double().sum(dim=0).cpu()
-    close_scaled(tgin, torch.tensor(g_in0, dtype=torch.float64) + gx_ref, 2e-5, "conv d/d input")
-    off = 0
-    for nm, ref in (("w1", g1), ("b1", gb1), ("w2", g2), ("b2", gb2)):
-        n = ref.numel()
-        close_scaled(tot[off:off + n], ref.reshape(-1), 5e-5, f"conv d/d {nm}")
-        off += n
+    check(tgin2, part2, "tape")
 
 
 def test_native_step_equals_python_walk(golden):
