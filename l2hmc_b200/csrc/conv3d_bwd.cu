@@ -17,7 +17,7 @@ namespace l2hmc {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxRows = 444;   // 3 resident CTAs per SM (72 KB of shared memory each at 16x16, F = 16)
+constexpr int kMaxRows = 592;   // 4 resident CTAs per SM of the tape kernel (the recompute kernel fits 3: a short second wave)
 
 struct ConvBwdParams {
   const float *w1, *b1, *w2, *b2;
