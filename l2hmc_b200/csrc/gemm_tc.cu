@@ -848,7 +848,8 @@ static bool gemm_wants_tc(const l2hmc_gemm_args* g) {
   long long k = 0;
   for (int s = 0; s < g->nseg; ++s) k += g->seg[s].K;
   if (k < 128) return false;
-  return static_cast<double>(g->M) * g->N * static_cast<double>(k) >= 2.5e8;
+  static const double min_mnk = getenv("L2HMC_TC_MIN_MNK") ? atof(getenv("L2HMC_TC_MIN_MNK")) : 2.5e8;   // diagnostics
+  return static_cast<double>(g->M) * g->N * static_cast<double>(k) >= min_mnk;
 }
 
 extern "C" size_t l2hmc_gemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {

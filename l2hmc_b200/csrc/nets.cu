@@ -17,6 +17,10 @@
 // tile, operands prefetched into registers while the previous K slab is multiplied.  Accumulation
 // is fmaf in K order (fp32); this path serves the shapes too small or ragged for the tcgen05
 // kernel in gemm_tc.cu (config 2: 128 chains x 512 hidden; tail rows).
+#include <cooperative_groups.h>
+
+#include <climits>
+
 #include "common.cuh"
 #include "nets.cuh"
 #include "update_math.cuh"
@@ -25,9 +29,11 @@ namespace l2hmc {
 namespace {
 
 constexpr int BM = 64, BK = 32, kThreads = 256;
-constexpr int AV = BK / 16;   // float4 A loads per thread and K slab
+constexpr int AV = BK / 16;    // float4 A loads per thread and K slab
+constexpr int kMaxSeg = 3;
+constexpr int kMaxChunks = 8;  // K chunks per output tile = portable cluster size
 
-enum Mode { kBiasRelu = 0, kHeadsStq = 1, kHeadsMomentum = 2, kHeadsPosition = 3 };
+enum Mode { kBiasRelu = 0, kHeadsStq = 1, kHeadsMomentum = 2, kHeadsPosition = 3, kGrad = 4 };
 
 struct Seg {
   const float* A;      // [rows, K] row-major, leading dimension lda
@@ -36,15 +42,21 @@ struct Seg {
   int invert;
   const float* mask_alt;   // rows with row_set != 0
   int invert_alt;
-  const float* W[3];   // [K, cols] row-major, leading dimension ldb (three for the heads)
+  const float* W[3];   // B_KC = false: [K, cols] row-major, leading dimension ldb (three for the heads)
+                       // B_KC = true:  [cols, K] row-major (the weight matrix of the forward layer; C = A . W^T)
   int ldb;
   int K;
 };
 
 struct DenseParams {
-  Seg seg[2];
+  Seg seg[kMaxSeg];
   int nseg;
   int rows, cols;       // cols = H (layers) or D (heads: per head)
+  // K chunking: the flattened (segment, 32-wide slab) sequence is cut into `nchunks` chunks of `sp` slabs; every chunk
+  // is summed in K order from zero and the chunk sums are added in chunk order.  `sp` depends on the K extents only, so
+  // an output element gets the same bits whatever the batch size or tile position -- whether one CTA walks the chunks
+  // (CL = false) or the `nchunks` CTAs of a cluster take one each and add them over distributed shared memory.
+  int sp, nchunks;
   const float* bias[3]; // layers: up to three biases summed; heads: b_s, b_tr, b_q
   const float* wt;      // t_layer kernel [2, cols] (nullable)
   float tau0, tau1;
@@ -67,36 +79,45 @@ struct DenseParams {
   float* uout;
   float* ld_part;       // [col tiles][rows]
   int32_t* flag;
+  // kGrad: C[r*ldc + c] (=|+=) scale[c] * (gate[r*ldg + c] > 0) * sum
+  float* C;
+  long long ldc, ldg;
+  int accumulate;
+  const float* gate;
+  const float* cscale;
+  const float* cscale_alt;
+  int cinv, cinv_alt;
 };
 
-// NG column groups of CW contiguous columns per thread: layers 1 x 4 (BN = 64), heads 3 x 2 (BN = 96)
-template <int NG, int CW, int MODE>
+// NG column groups of CW contiguous columns per thread: layers / gradients 1 x 4 (BN = 64), heads 3 x 2 (BN = 96).
+// CL: the K chunks of a tile are the CTAs of one cluster (blockIdx.z = chunk).
+template <int NG, int CW, int MODE, bool B_KC, bool CL>
 __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
   constexpr int GS = 16 * CW;        // columns per group in the tile
   constexpr int BN = NG * GS;
+  constexpr int BNP = BN + 4;        // padded row of the B tile / of the accumulator tile
   constexpr int NC = NG * CW;        // accumulator columns per thread
   constexpr int BV = (BK * BN / 4 + kThreads - 1) / kThreads;   // float4 B loads per thread
-  __shared__ __align__(16) float As[BK][BM + 4];
-  __shared__ __align__(16) float Bs[BK][BN];
+  constexpr int kAs = BK * (BM + 4), kBs = BK * BNP;
+  __shared__ __align__(16) float smem[2 * kAs + 2 * kBs];
+  static_assert(BM * BNP <= 2 * kAs + 2 * kBs, "the accumulator tile re-uses the operand buffers");
+  float* const As0 = smem;
+  float* const As1 = smem + kAs;
+  float* const Bs0 = smem + 2 * kAs;
+  float* const Bs1 = Bs0 + kBs;
+  float* const red = smem;           // [BM][BNP] after the main loop
 
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * BM;
   const int n0 = blockIdx.x * GS;    // first column (per group) of this tile
-
-  float acc[4][NC];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < NC; ++j) acc[i][j] = 0.f;
+  const int z = CL ? blockIdx.z : 0;
 
   // A: AV float4 along K per thread (k offsets ak + 16 q)
   const int ar = tid >> 2, ak = (tid & 3) * 4;
   const bool a_alt = p.row_set != nullptr && m0 + ar < p.rows && p.row_set[m0 + ar] != 0;
-  float a_reg[AV][4];
-  float b_reg[BV][4];
 
-  auto load_tile = [&](const Seg& s, int k0) {
+  auto load_tile = [&](float (&a_reg)[AV][4], float (&b_reg)[BV][4], const Seg& s, int k0) {
     const int gr = m0 + ar;
 #pragma unroll
     for (int q = 0; q < AV; ++q) {
@@ -131,67 +152,77 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) b_reg[q][i] = 0.f;
       if (idx < BK * BN / 4) {
-        const int k = idx / (BN / 4), c4 = (idx % (BN / 4)) * 4;
-        const int g = c4 / GS, c = c4 % GS;
-        const int gk = k0 + k, gc = n0 + c;
-        if (gk < s.K) {
-          const float* src = s.W[g] + static_cast<size_t>(gk) * s.ldb + gc;
-          if (gc + 3 < p.cols && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
-            const float4 t = *reinterpret_cast<const float4*>(src);
-            b_reg[q][0] = t.x, b_reg[q][1] = t.y, b_reg[q][2] = t.z, b_reg[q][3] = t.w;
-          } else {
+        if (B_KC) {       // float4 along K of output column n
+          const int n = idx / (BK / 4), k4 = (idx % (BK / 4)) * 4;
+          const int gk = k0 + k4, gc = n0 + n;
+          if (gc < p.cols) {
+            const float* src = s.W[0] + static_cast<size_t>(gc) * s.ldb + gk;
+            if (gk + 3 < s.K && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
+              const float4 t = *reinterpret_cast<const float4*>(src);
+              b_reg[q][0] = t.x, b_reg[q][1] = t.y, b_reg[q][2] = t.z, b_reg[q][3] = t.w;
+            } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (gc + i < p.cols) b_reg[q][i] = src[i];
+              for (int i = 0; i < 4; ++i)
+                if (gk + i < s.K) b_reg[q][i] = src[i];
+            }
+          }
+        } else {
+          const int k = idx / (BN / 4), c4 = (idx % (BN / 4)) * 4;
+          const int g = c4 / GS, c = c4 % GS;
+          const int gk = k0 + k, gc = n0 + c;
+          if (gk < s.K) {
+            const float* src = s.W[g] + static_cast<size_t>(gk) * s.ldb + gc;
+            if (gc + 3 < p.cols && ((reinterpret_cast<uintptr_t>(src) & 15u) == 0)) {
+              const float4 t = *reinterpret_cast<const float4*>(src);
+              b_reg[q][0] = t.x, b_reg[q][1] = t.y, b_reg[q][2] = t.z, b_reg[q][3] = t.w;
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; ++i)
+                if (gc + i < p.cols) b_reg[q][i] = src[i];
+            }
           }
         }
       }
     }
   };
-  auto store_tile = [&]() {
+  auto store_tile = [&](const float (&a_reg)[AV][4], const float (&b_reg)[BV][4], float* As, float* Bs) {
 #pragma unroll
     for (int q = 0; q < AV; ++q)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) As[ak + 16 * q + i][ar] = a_reg[q][i];
+      for (int i = 0; i < 4; ++i) As[(ak + 16 * q + i) * (BM + 4) + ar] = a_reg[q][i];
 #pragma unroll
     for (int q = 0; q < BV; ++q) {
       const int idx = tid + q * kThreads;
       if (idx < BK * BN / 4) {
-        const int k = idx / (BN / 4), c4 = (idx % (BN / 4)) * 4;
-        *reinterpret_cast<float4*>(&Bs[k][c4]) = make_float4(b_reg[q][0], b_reg[q][1], b_reg[q][2], b_reg[q][3]);
+        if (B_KC) {
+          const int n = idx / (BK / 4), k4 = (idx % (BK / 4)) * 4;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) Bs[(k4 + i) * BNP + n] = b_reg[q][i];
+        } else {
+          const int k = idx / (BN / 4), c4 = (idx % (BN / 4)) * 4;
+          *reinterpret_cast<float4*>(&Bs[k * BNP + c4]) = make_float4(b_reg[q][0], b_reg[q][1], b_reg[q][2], b_reg[q][3]);
+        }
       }
     }
   };
 
-  // flattened (segment, k0) slab sequence
-  int total_slabs = 0;
-  for (int s = 0; s < p.nseg; ++s) total_slabs += (p.seg[s].K + BK - 1) / BK;
-  int cur_seg = 0, cur_k0 = 0;
-  auto advance = [&]() {
-    cur_k0 += BK;
-    if (cur_k0 >= p.seg[cur_seg].K) ++cur_seg, cur_k0 = 0;
-  };
-  if (total_slabs > 0) load_tile(p.seg[0], 0);
-  for (int slab = 0; slab < total_slabs; ++slab) {
-    store_tile();
-    __syncthreads();
-    advance();
-    if (slab + 1 < total_slabs) load_tile(p.seg[cur_seg], cur_k0);
+  float acc[4][NC];
+  auto multiply = [&](const float* As, const float* Bs) {
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      const float4 a4 = *reinterpret_cast<const float4*>(&As[k][4 * ty]);
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[k * (BM + 4) + 4 * ty]);
       const float a[4] = {a4.x, a4.y, a4.z, a4.w};
       float b[NC];
 #pragma unroll
       for (int g = 0; g < NG; ++g) {
         if (CW == 4) {
-          const float4 t = *reinterpret_cast<const float4*>(&Bs[k][g * GS + 4 * tx]);
+          const float4 t = *reinterpret_cast<const float4*>(&Bs[k * BNP + g * GS + 4 * tx]);
           b[g * CW + 0] = t.x, b[g * CW + 1] = t.y, b[g * CW + 2] = t.z, b[g * CW + 3] = t.w;
         } else if (CW == 2) {
-          const float2 t = *reinterpret_cast<const float2*>(&Bs[k][g * GS + 2 * tx]);
+          const float2 t = *reinterpret_cast<const float2*>(&Bs[k * BNP + g * GS + 2 * tx]);
           b[g * CW + 0] = t.x, b[g * CW + 1] = t.y;
         } else {
-          b[g * CW] = Bs[k][g * GS + tx];
+          b[g * CW] = Bs[k * BNP + g * GS + tx];
         }
       }
 #pragma unroll
@@ -199,13 +230,84 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 #pragma unroll
         for (int j = 0; j < NC; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
+  };
+
+  // flattened (segment, k0) slab sequence
+  int nsl[kMaxSeg], total_slabs = 0;
+#pragma unroll
+  for (int s = 0; s < kMaxSeg; ++s) {
+    nsl[s] = s < p.nseg ? (p.seg[s].K + BK - 1) / BK : 0;
+    total_slabs += nsl[s];
+  }
+  auto load_slab = [&](float (&a_reg)[AV][4], float (&b_reg)[BV][4], int slab) {
+    int sg = 0;
+#pragma unroll
+    for (int s = 0; s < kMaxSeg - 1; ++s)
+      if (sg == s && slab >= nsl[s]) slab -= nsl[s], ++sg;
+    load_tile(a_reg, b_reg, p.seg[sg], slab * BK);
+  };
+
+  float tot[4][NC];
+  float ra0[AV][4], rb0[BV][4], ra1[AV][4], rb1[BV][4];
+  for (int c = CL ? z : 0; c < (CL ? z + 1 : p.nchunks); ++c) {
+    const int s0 = c * p.sp, n = min(total_slabs, s0 + p.sp) - s0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < NC; ++j) acc[i][j] = 0.f;
+    // two slabs of operands in flight in registers, two shared-memory buffers: one barrier per slab
+    if (n > 0) load_slab(ra0, rb0, s0);
+    if (n > 1) load_slab(ra1, rb1, s0 + 1);
+    for (int s = 0; s < n; s += 2) {
+      store_tile(ra0, rb0, As0, Bs0);
+      __syncthreads();
+      if (s + 2 < n) load_slab(ra0, rb0, s0 + s + 2);
+      multiply(As0, Bs0);
+      if (s + 1 < n) {
+        store_tile(ra1, rb1, As1, Bs1);
+        __syncthreads();
+        if (s + 3 < n) load_slab(ra1, rb1, s0 + s + 3);
+        multiply(As1, Bs1);
+      }
+    }
+    __syncthreads();                 // every thread is done with the operand buffers
+    if (!CL) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < NC; ++j) tot[i][j] = c == 0 ? acc[i][j] : __fadd_rn(tot[i][j], acc[i][j]);
+    }
+  }
+
+  // ------------------------------------------------------------------ accumulators -> shared memory
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+#pragma unroll
+      for (int j = 0; j < CW; ++j)
+        red[(4 * ty + i) * BNP + g * GS + CW * tx + j] = CL ? acc[i][g * CW + j] : tot[i][g * CW + j];
+  namespace cg = cooperative_groups;
+  int r_begin = 0, r_end = BM, nsrc = 1;
+  const float* src[kMaxChunks];
+  src[0] = red;
+  if (CL) {
+    cg::cluster_group cl = cg::this_cluster();
+    cl.sync();
+    nsrc = p.nchunks;
+    const int rs = (BM + nsrc - 1) / nsrc;       // rows of the tile this rank finishes
+    r_begin = min(BM, z * rs), r_end = min(BM, r_begin + rs);
+#pragma unroll
+    for (int q = 0; q < kMaxChunks; ++q) src[q] = q < nsrc ? cl.map_shared_rank(red, q) : red;
+  } else {
     __syncthreads();
   }
 
-  // ------------------------------------------------------------------ epilogue
+  // ------------------------------------------------------------------ epilogue: thread (tx, ty) finishes rows
+  // r_begin + ty + 16 t, columns CW tx + j of every group; chunk sums added in chunk order
   const int c0 = n0 + CW * tx;       // first owned column (per group)
+  float add[2][CW], bs[CW], bt[CW], bq[CW], es[CW], eq[CW], um[CW], um_alt[CW];
   if (MODE == kBiasRelu) {
-    float add[2][CW];
 #pragma unroll
     for (int j = 0; j < CW; ++j) {
       const int c = c0 + j;
@@ -221,26 +323,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
         add[1][j] = __fadd_rn(s, __fadd_rn(__fadd_rn(__fmul_rn(p.tau0_alt, w0), __fmul_rn(p.tau1_alt, w1)), b2));
       }
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = m0 + 4 * ty + i;
-      if (r >= p.rows) continue;
-      const int set = (p.row_set != nullptr && p.row_set[r] != 0) ? 1 : 0;
-      float o[CW];
-#pragma unroll
-      for (int j = 0; j < CW; ++j) o[j] = fmaxf(__fadd_rn(acc[i][j], set ? add[1][j] : add[0][j]), 0.f);
-      float* dst = p.out[0] + static_cast<size_t>(r) * p.cols + c0;
-      if (CW == 4 && c0 + 3 < p.cols && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
-        *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-      } else {
-#pragma unroll
-        for (int j = 0; j < CW; ++j)
-          if (c0 + j < p.cols) dst[j] = o[j];
-      }
-    }
-  } else {
-    // heads: acc[i][0..1] = S, [2..3] = T, [4..5] = Q pre-activations of outputs d = c0, c0 + 1
-    float bs[CW], bt[CW], bq[CW], es[CW], eq[CW], um[CW], um_alt[CW];
+  } else if (MODE != kGrad) {
 #pragma unroll
     for (int j = 0; j < CW; ++j) {
       const int d = c0 + j;
@@ -256,22 +339,88 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
         if (p.row_set) um_alt[j] = p.uinvert_alt ? __fsub_rn(1.f, p.umask_alt[d]) : p.umask_alt[d];
       }
     }
-    const float heps = __fmul_rn(0.5f, p.eps);
-    bool bad = false;
+  }
+  const float heps = __fmul_rn(0.5f, p.eps);
+  bool bad = false;
+  for (int base = r_begin; base < r_end; base += 16) {     // uniform trip count: the log-det shuffles need whole warps
+    const int rl = base + ty;
+    const int r = m0 + rl;
+    const bool rok = rl < r_end && r < p.rows;
+    float val[NC];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int r = m0 + 4 * ty + i;
-      const bool rok = r < p.rows;
-      const bool alt = p.row_set != nullptr && rok && p.row_set[r] != 0;
+    for (int j = 0; j < NC; ++j) val[j] = 0.f;
+    if (rok) {
+      float part[kMaxChunks][NC];
+#pragma unroll
+      for (int q = 0; q < kMaxChunks; ++q) {
+        if (q < nsrc) {
+#pragma unroll
+          for (int g = 0; g < NG; ++g) {
+            const float* at = src[q] + rl * BNP + g * GS + CW * tx;
+            if (CW == 4) {
+              const float4 t = *reinterpret_cast<const float4*>(at);
+              part[q][g * CW] = t.x, part[q][g * CW + 1] = t.y, part[q][g * CW + 2] = t.z, part[q][g * CW + 3] = t.w;
+            } else if (CW == 2) {
+              const float2 t = *reinterpret_cast<const float2*>(at);
+              part[q][g * CW] = t.x, part[q][g * CW + 1] = t.y;
+            } else {
+              part[q][g * CW] = *at;
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < NC; ++j) val[j] = part[0][j];
+#pragma unroll
+      for (int q = 1; q < kMaxChunks; ++q)
+        if (q < nsrc) {
+#pragma unroll
+          for (int j = 0; j < NC; ++j) val[j] = __fadd_rn(val[j], part[q][j]);
+        }
+    }
+    const bool alt = p.row_set != nullptr && rok && p.row_set[r] != 0;
+    if (MODE == kBiasRelu) {
+      if (!rok) continue;
+      float o[CW];
+#pragma unroll
+      for (int j = 0; j < CW; ++j) o[j] = fmaxf(__fadd_rn(val[j], alt ? add[1][j] : add[0][j]), 0.f);
+      float* dst = p.out[0] + static_cast<size_t>(r) * p.cols + c0;
+      if (CW == 4 && c0 + 3 < p.cols && ((reinterpret_cast<uintptr_t>(dst) & 15u) == 0)) {
+        *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (c0 + j < p.cols) dst[j] = o[j];
+      }
+    } else if (MODE == kGrad) {
+      if (!rok) continue;
+      const float* cs = alt ? p.cscale_alt : p.cscale;
+      const int cinv = alt ? p.cinv_alt : p.cinv;
+#pragma unroll
+      for (int j = 0; j < CW; ++j) {
+        const int c = c0 + j;
+        if (c >= p.cols) continue;
+        float v = val[j];
+        if (p.gate != nullptr && !(p.gate[static_cast<long long>(r) * p.ldg + c] > 0.f)) v = 0.f;
+        if (cs != nullptr) {
+          const float sc = cs[c];
+          v = __fmul_rn(v, cinv ? __fsub_rn(1.f, sc) : sc);
+        }
+        float* dst = p.C + static_cast<long long>(r) * p.ldc + c;
+        if (p.accumulate) v = __fadd_rn(*dst, v);
+        *dst = v;
+      }
+    } else {
+      // heads: val[0..CW) = S, [CW..2CW) = T, [2CW..3CW) = Q pre-activations of outputs d = c0 + j
       const int dir = alt ? p.dir_alt : p.dir;
       float ld = 0.f;
 #pragma unroll
       for (int j = 0; j < CW; ++j) {
         const int d = c0 + j;
         if (!(rok && d < p.cols)) continue;
-        const float S = __fmul_rn(tanhf(__fadd_rn(acc[i][j], bs[j])), es[j]);
-        const float Tr = __fadd_rn(acc[i][CW + j], bt[j]);
-        float Q = __fadd_rn(acc[i][2 * CW + j], bq[j]);
+        const float S = __fmul_rn(tanhf(__fadd_rn(val[j], bs[j])), es[j]);
+        const float Tr = __fadd_rn(val[CW + j], bt[j]);
+        float Q = __fadd_rn(val[2 * CW + j], bq[j]);
         if (p.tanh_on_q) Q = tanhf(Q);
         Q = __fmul_rn(Q, eq[j]);
         const size_t at = static_cast<size_t>(r) * p.cols + d;
@@ -295,8 +444,9 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
         if (tx == 0 && rok && p.ld_part) p.ld_part[static_cast<size_t>(blockIdx.x) * p.rows + r] = ld;
       }
     }
-    if (MODE != kHeadsStq) flag_nonfinite(p.flag, bad);
   }
+  if (MODE == kHeadsMomentum || MODE == kHeadsPosition) flag_nonfinite(p.flag, bad);
+  if (CL) cg::this_cluster().sync();       // this rank's tile stays alive until every rank has read it
 }
 
 // logdet[n] += sum_j part[j][n], j in fixed order (deterministic)
@@ -308,27 +458,68 @@ __global__ void logdet_reduce_kernel(const float* __restrict__ part, int tiles, 
   logdet[n] = __fadd_rn(logdet[n], s);
 }
 
-template <int NG, int CW, int MODE>
-int launch_dense(const DenseParams& p, cudaStream_t st) {
+// The K chunking rule: from the K extents only (never the batch size), so that a row's result does not depend on how
+// many rows were launched with it.  At least 2 slabs (64 products) per chunk, at most kMaxChunks chunks.
+void set_chunks(DenseParams& p) {
+  int total = 0;
+  for (int s = 0; s < p.nseg; ++s) total += (p.seg[s].K + BK - 1) / BK;
+  p.sp = std::max(2, (total + kMaxChunks - 1) / kMaxChunks);
+  p.nchunks = std::max(1, (total + p.sp - 1) / p.sp);
+}
+
+constexpr int kClusterBelowTiles = 148;   // fewer output tiles than SMs: spread the K chunks of a tile over a cluster
+
+template <int NG, int CW, int MODE, bool B_KC>
+int launch_dense(DenseParams p, cudaStream_t st) {
   constexpr int GS = 16 * CW;
-  dim3 grid((p.cols + GS - 1) / GS, (p.rows + BM - 1) / BM);
-  dense_kernel<NG, CW, MODE><<<grid, kThreads, 0, st>>>(p);
+  set_chunks(p);
+  const int ct = (p.cols + GS - 1) / GS, rt = (p.rows + BM - 1) / BM;
+  const bool cl = p.nchunks > 1 && ct * rt < kClusterBelowTiles;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(ct, rt, cl ? p.nchunks : 1), cfg.blockDim = dim3(kThreads), cfg.dynamicSmemBytes = 0, cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 1, attr.val.clusterDim.y = 1, attr.val.clusterDim.z = cl ? p.nchunks : 1;
+  cfg.attrs = &attr, cfg.numAttrs = 1;
+  const cudaError_t e = cl ? cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, true>, p)
+                           : cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, false>, p);
+  if (e != cudaSuccess) return check_launch("dense_kernel", 0);
   return check_launch("dense_kernel");
 }
 
-// Layers: 64-column tiles; when those leave most SMs idle (config 2: 256 stacked rows x 512 columns = 32 tiles),
-// 32-column tiles.  Every output element sums the same products in the same K order either way (bit-identical).
-int launch_layer(const DenseParams& p, cudaStream_t st) {
-  const int wide_tiles = ((p.cols + 63) / 64) * ((p.rows + BM - 1) / BM);
-  return wide_tiles < 74 ? launch_dense<1, 2, kBiasRelu>(p, st) : launch_dense<1, 4, kBiasRelu>(p, st);
-}
+int launch_layer(const DenseParams& p, cudaStream_t st) { return launch_dense<1, 4, kBiasRelu, false>(p, st); }
 
 }  // namespace
 
-// Heads: a CTA owns 32 outputs of all three heads; when that leaves most SMs idle (config 2: 256 stacked rows x 128
-// outputs = 16 CTAs), 16 outputs.  The per-row log-det partials are one per column tile either way.
-static bool heads_narrow(int D, int N) { return ((D + 31) / 32) * ((N + BM - 1) / BM) < 74; }
-int heads_col_tiles(int D, int N) { return heads_narrow(D, N) ? (D + 15) / 16 : (D + 31) / 32; }
+// The per-row log-det partials of the head kernel: one per 32-output column tile.
+int heads_col_tiles(int D, int /*N*/) { return (D + 31) / 32; }
+
+// C = A . B^T products of the backward pass with both operands K-contiguous (d act = d out . W^T: l2hmc_gemm_seg with
+// a_cs == 1 and b_rs == 1), up to three K segments, through the same chunked kernel as the forward layers.
+bool dense_grad_nt_ok(const l2hmc_gemm_args* g) {
+  if (g->nseg < 1 || g->nseg > kMaxSeg) return false;
+  for (int s = 0; s < g->nseg; ++s) {
+    const l2hmc_gemm_seg& sg = g->seg[s];
+    if (sg.a_cs != 1 || sg.b_rs != 1 || sg.a_rs > INT_MAX || sg.b_cs > INT_MAX || sg.a_rs < 0 || sg.b_cs < 0) return false;
+  }
+  return true;
+}
+
+int dense_grad_nt(const l2hmc_gemm_args* g, cudaStream_t st) {
+  DenseParams p{};
+  p.nseg = g->nseg;
+  for (int s = 0; s < g->nseg; ++s) {
+    const l2hmc_gemm_seg& sg = g->seg[s];
+    p.seg[s] = Seg{sg.A, static_cast<int>(sg.a_rs), nullptr, 0, nullptr, 0, {sg.B, nullptr, nullptr},
+                   static_cast<int>(sg.b_cs), sg.K};
+  }
+  p.rows = g->M, p.cols = g->N;
+  p.C = g->C, p.ldc = g->ldc, p.ldg = g->ldg, p.accumulate = g->accumulate, p.gate = g->relu_gate;
+  p.row_set = g->row_set;
+  p.cscale = g->col_scale, p.cinv = g->col_scale_invert;
+  p.cscale_alt = g->row_set ? g->col_scale_alt : g->col_scale, p.cinv_alt = g->row_set ? g->col_scale_invert_alt : g->col_scale_invert;
+  return launch_dense<1, 4, kGrad, true>(p, st);
+}
 
 // Layers 1, 2 and the heads on the FFMA path (also called by gemm_tc.cu for shapes it rejects).
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
@@ -371,15 +562,9 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
   p.eps = c->eps, p.dir = c->dir, p.uout = c->out, p.flag = c->nonfinite_flag;
   p.row_set = c->row_set, p.umask_alt = c->mask_alt, p.uinvert_alt = c->mask_invert_alt, p.dir_alt = c->dir_alt;
   p.ld_part = c->logdet ? ld_part : nullptr;
-  if (heads_narrow(D, N)) {
-    if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 1, kHeadsStq>(p, st);
-    else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 1, kHeadsMomentum>(p, st);
-    else rc = launch_dense<3, 1, kHeadsPosition>(p, st);
-  } else {
-    if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 2, kHeadsStq>(p, st);
-    else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 2, kHeadsMomentum>(p, st);
-    else rc = launch_dense<3, 2, kHeadsPosition>(p, st);
-  }
+  if (c->mode == L2HMC_NET_STQ) rc = launch_dense<3, 2, kHeadsStq, false>(p, st);
+  else if (c->mode == L2HMC_NET_MOMENTUM) rc = launch_dense<3, 2, kHeadsMomentum, false>(p, st);
+  else rc = launch_dense<3, 2, kHeadsPosition, false>(p, st);
   if (rc) return rc;
   if (c->mode != L2HMC_NET_STQ && c->logdet) {
     logdet_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, heads_col_tiles(D, N), N, c->logdet);

@@ -22,5 +22,7 @@ bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
 int heads_col_tiles(int D, int N);
+bool dense_grad_nt_ok(const l2hmc_gemm_args* g);
+int dense_grad_nt(const l2hmc_gemm_args* g, cudaStream_t st);
 
 }  // namespace l2hmc

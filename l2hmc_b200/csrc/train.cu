@@ -24,6 +24,7 @@
 #include <atomic>
 
 #include "common.cuh"
+#include "nets.cuh"
 #include "update_math.cuh"
 
 namespace l2hmc {
@@ -759,6 +760,7 @@ static int auto_ksplit(const l2hmc_gemm_args* g) {
 extern "C" size_t l2hmc_sgemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {
   if (!g || g->nseg < 1 || g->nseg > 3) return 0;
   if (skinny_slabs(g)) ksplit = skinny_slabs(g);
+  else if (ksplit == 0 && l2hmc::dense_grad_nt_ok(g)) return 0;
   if (ksplit == 0) ksplit = auto_ksplit(g);
   if (ksplit <= 1) return 0;
   return sizeof(float) * static_cast<size_t>(ksplit) * g->M * g->N;
@@ -774,6 +776,11 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
     L2HMC_REQUIRE(g->seg[s].A && g->seg[s].B && g->seg[s].K >= 0, "l2hmc_sgemm: bad segment %d", s);
   const int skinny = skinny_slabs(g);
   if (skinny) ksplit = skinny;
+  // d act = d out . W^T with both operands K-contiguous: the chunked kernel of the forward layers (nets.cu)
+  if (!skinny && ksplit == 0 && l2hmc::dense_grad_nt_ok(g)) {
+    if (g->row_set) L2HMC_REQUIRE(!g->col_scale == !g->col_scale_alt, "l2hmc_sgemm: col_scale and col_scale_alt go together");
+    return l2hmc::dense_grad_nt(g, static_cast<cudaStream_t>(stream));
+  }
   if (ksplit == 0) ksplit = auto_ksplit(g);
   if (ksplit < 1) ksplit = 1;
   if (ksplit > 1)

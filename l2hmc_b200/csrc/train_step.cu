@@ -128,7 +128,8 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
     // forward layers on tcgen05 when the stacked batch fills MMA tiles (same rule as l2hmc_net_run's AUTO path, from
     // 1024 rows: below that the FFMA layers are as fast and the step is launch-bound anyway)
     auto fits = [](const l2hmc_net_weights* w) { return w->K >= 64 && w->H >= 128 && w->D >= 64 && w->D % 16 == 0; };
-    pl.tc_forward = pl.R >= 1024 && fits(a->xnet) && fits(a->vnet);
+    static const int tc_min_rows = getenv("L2HMC_TC_MIN_ROWS") ? atoi(getenv("L2HMC_TC_MIN_ROWS")) : 1024;   // diagnostics
+    pl.tc_forward = pl.R >= tc_min_rows && fits(a->xnet) && fits(a->vnet);
     if (pl.tc_forward) {
       pl.xpack_bytes = l2hmc_net_pack_bytes(a->xnet->K, a->xnet->H, a->xnet->D);
       pl.vpack_bytes = l2hmc_net_pack_bytes(a->vnet->K, a->vnet->H, a->vnet->D);

@@ -301,16 +301,19 @@ def test_gradients_against_reference_goldens(golden):
     assert checked >= 3 + 2 * 33 + 49
 
 
-@pytest.mark.parametrize("T,X,N,M,metric", [(8, 8, 16, 5, "cos_diff"), (4, 6, 9, 3, "l2")])
-def test_gradients_against_oracle_config2_shapes(T, X, N, M, metric):
-    """Config-2 network shapes (8x8, H = 4D = 512, M = 5) against autodiff through the CPU oracle (fp32)."""
+@pytest.mark.parametrize("arch,T,X,N,M,metric", [("generic", 8, 8, 16, 5, "cos_diff"), ("generic", 4, 6, 9, 3, "l2"),
+                                                  ("conv3D", 8, 8, 12, 2, "cos_diff"), ("conv3D", 32, 32, 5, 1, "cos_diff")])
+def test_gradients_against_oracle_config2_shapes(arch, T, X, N, M, metric):
+    """Config-2 network shapes (8x8, H = 4D = 512, M = 5) against autodiff through the CPU oracle (fp32); the conv3D
+    front end at 8x8 and at BASELINE config 4's lattice (32x32, F = 32: the adjoint runs from the forward pass's
+    routing tape, the only path that fits that shape)."""
     import l2hmc_b200 as pkg
     from l2hmc_b200.gauge_model import GaugeModel
     rng = np.random.default_rng(N + M)
     D, eps, beta = 2 * T * X, 0.2, 2.5
     weights = {}
     for net, factor in (("XNet", 2.), ("VNet", 1.)):
-        w = orc.init_net_weights("generic", T, X, factor, rng)
+        w = orc.init_net_weights(arch, T, X, factor, rng)
         w["coeff_scale"] = (0.1 * rng.standard_normal((1, D))).astype(np.float32)
         w["coeff_transformation"] = (0.1 * rng.standard_normal((1, D))).astype(np.float32)
         for k in list(w):
@@ -324,11 +327,11 @@ def test_gradients_against_oracle_config2_shapes(T, X, N, M, metric):
                   rng.uniform(size=N).astype(np.float32), rng.uniform(size=N).astype(np.float32))
     draws_x, draws_z = dr(), dr()
     lw = dict(aux_weight=1., std_weight=1., charge_weight=1.)
-    od = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch="generic", mask=mask, xnet=weights["XNet"],
+    od = orc.OracleDynamics(T, X, M, eps, hmc=False, network_arch=arch, mask=mask, xnet=weights["XNet"],
                             vnet=weights["VNet"])
     ref_loss, ref_grads = tro.loss_and_grads(od, x, beta, draws_x, z, draws_z, metric=metric, loss_scale=1., **lw)
     lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=N)
-    dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch="generic", num_steps=M, eps=eps, weights=weights)
+    dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=M, eps=eps, weights=weights)
     dyn.set_masks(mask)
     model = GaugeModel(dict(time_size=T, space_size=X, num_samples=N, metric=metric, loss_scale=1., **lw), lattice=lat,
                        dynamics=dyn)
