@@ -274,6 +274,11 @@ int l2hmc_net_run(const l2hmc_net_weights* w, const l2hmc_net_call* call, void* 
  * fp32 accumulation in TMEM).  `packed` is caller-owned device memory of l2hmc_net_pack_bytes(K,H,D)
  * bytes; re-pack after the weights change.  w->packed is ignored by l2hmc_net_pack itself. */
 size_t l2hmc_net_pack_bytes(int K, int H, int D);
+/* Smallest batch N for which L2HMC_NET_PATH_AUTO takes the tcgen05 layers for a (K, H, D) network (INT_MAX when the
+ * shape never does).  Below it the chunked FFMA layers run, whose result for a chain does not depend on the batch it
+ * was launched with; a caller that splits a batch (l2hmc_b200/sampler.py) keeps every part on the same side of this
+ * number so that splitting does not change a bit.  No reference counterpart (dispatch detail of this library). */
+int l2hmc_net_tc_min_rows(int K, int H, int D);
 int l2hmc_net_pack(const l2hmc_net_weights* w, void* packed, size_t packed_bytes, void* stream);
 
 /* Diagnostic: C[M,Nc] = relu(A[M,K] . W[K,Nc]) through the tcgen05 layer kernel and its operand
@@ -550,6 +555,7 @@ typedef struct {
   float *gx, *gv;
   const float* gld;
   float *dA, *dg, *ps, *pq, *deps;
+  const float* eps_dev;   /* nullable: the step size read from device memory instead of `eps` (see l2hmc_train_args) */
 } l2hmc_update_bwd_args;
 int l2hmc_update_bwd(const l2hmc_update_bwd_args* a, void* stream);
 
@@ -681,6 +687,10 @@ typedef struct {
                                enqueued: a data-parallel caller starts averaging that bucket on a side stream under the
                                rest of the backward pass (hvd.DistributedOptimizer overlaps the same way,
                                gauge_model.py:941-943) */
+  const float* eps_dev;   /* nullable [1]: the trainable step size where the optimiser keeps it.  When given, every
+                             kernel reads it from there and `eps` is ignored, so the caller need not copy it to the
+                             host (and synchronise) after each optimiser step as the reference's session.run fetch of
+                             dynamics.eps does (gauge_model.py:1166) */
 } l2hmc_train_args;
 
 size_t l2hmc_u1_train_workspace_bytes(const l2hmc_train_args* a);

@@ -79,7 +79,8 @@ class UpdateBwdArgs(Structure):
                 ("S", c_void_p), ("T", c_void_p), ("Q", c_void_p), ("coeff_s", c_void_p), ("coeff_q", c_void_p),
                 ("mask", c_void_p), ("mask_alt", c_void_p), ("invert", c_int), ("invert_alt", c_int),
                 ("gx", c_void_p), ("gv", c_void_p), ("gld", c_void_p),
-                ("dA", c_void_p), ("dg", c_void_p), ("ps", c_void_p), ("pq", c_void_p), ("deps", c_void_p)]
+                ("dA", c_void_p), ("dg", c_void_p), ("ps", c_void_p), ("pq", c_void_p), ("deps", c_void_p),
+                ("eps_dev", c_void_p)]
 
 
 class Conv3dWeights(Structure):
@@ -153,7 +154,7 @@ class TrainArgs(Structure):
         ("xconv_in0_g", POINTER(Conv3dGrads)), ("xconv_in1_g", POINTER(Conv3dGrads)),
         ("vconv_in0_g", POINTER(Conv3dGrads)), ("vconv_in1_g", POINTER(Conv3dGrads)),
         ("nonfinite_flag", c_void_p), ("workspace", c_void_p), ("workspace_bytes", c_size_t),
-        ("first_bucket_event", c_void_p),
+        ("first_bucket_event", c_void_p), ("eps_dev", c_void_p),
     ]
 
 
@@ -206,6 +207,7 @@ SIGNATURES = {
     "l2hmc_net_workspace_bytes": [c_int, c_int, c_int, c_int],
     "l2hmc_net_run": [POINTER(NetWeights), POINTER(NetCall), c_void_p],
     "l2hmc_net_pack_bytes": [c_int, c_int, c_int],
+    "l2hmc_net_tc_min_rows": [c_int, c_int, c_int],
     "l2hmc_net_pack": [POINTER(NetWeights), c_void_p, c_size_t, c_void_p],
     "l2hmc_tc_selftest_bytes": [c_int, c_int, c_int],
     "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],

@@ -16,6 +16,22 @@ void set_error(const char* fmt, ...);
 int check_launch(const char* what, int launches = 1);   // also adds `launches` to l2hmc_launch_count()
 // C (=|+=) epilogue(sum_z partial[z][M][N]), z in fixed order: the second stage of every split-K product (train.cu)
 int launch_splitk_reduce(const float* partial, int ksplit, const l2hmc_gemm_args* g, cudaStream_t stream);
+// Several column sums of matrices with the same row count in two launches (train.cu); every sum is formed exactly as
+// l2hmc_col_sum forms it.  out[1], out[2] (nullable) receive copies of the sums.
+struct ColSumJob {
+  const float* B;
+  long long ld;
+  int cols;
+  float* out[3];
+};
+constexpr int kMaxColSumJobs = 8;
+size_t col_sum_multi_workspace_bytes(int rows, int max_cols, int njobs);
+int col_sum_multi(const ColSumJob* jobs, int njobs, int rows, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+// l2hmc_train_update_fwd with the step size optionally read from device memory (train.cu; used by train_step.cu)
+int train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S, const float* Tr,
+                     const float* Q, const float* mask, int invert, const float* mask_alt, int invert_alt,
+                     const uint8_t* row_set, float eps, const float* eps_dev, int dir, int dir_alt, int N, int D, float* out,
+                     float* logdet, int32_t* nonfinite_flag, void* stream);
 
 #define L2HMC_REQUIRE(cond, ...)          \
   do {                                    \

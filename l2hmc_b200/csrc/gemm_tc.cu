@@ -34,6 +34,8 @@
 #include <cstdlib>
 #include <string>
 
+#include <climits>
+
 #include "common.cuh"
 #include "nets.cuh"
 #include "tc_ptx.cuh"
@@ -583,9 +585,15 @@ bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
   return w->packed != nullptr && (w->D % 16) == 0;
 }
 
-// AUTO: dense-contraction shapes only (north star) -- enough chains to fill 128-row MMA tiles
+// AUTO: dense-contraction shapes only (north star) -- enough chains to fill 128-row MMA tiles and to beat the chunked
+// FFMA layers (measured, profiles/r2_small_ops_sweep.log: a tcgen05 net call costs ~50 us whatever the batch up to
+// ~2048 rows; the FFMA call costs 28 us at 256 x 512 hidden, 75 us at 1024 x 512): from N x H >= 2^19, at least 256.
+int tc_min_rows(int K, int H, int D) {
+  if (!(K >= 64 && H >= 128 && D >= 64 && D % 16 == 0)) return INT_MAX;
+  return std::max(256, (524288 + H - 1) / H);
+}
 bool tc_eligible(const l2hmc_net_weights* w, const l2hmc_net_call* c) {
-  return tc_supported(w, c) && c->N >= 256 && w->K >= 64 && w->H >= 128 && w->D >= 64;
+  return tc_supported(w, c) && c->N >= tc_min_rows(w->K, w->H, w->D);
 }
 
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st) {
@@ -778,6 +786,8 @@ TcGemmDims tc_gemm_dims(const l2hmc_gemm_args* g) {
 
 }  // namespace
 }  // namespace l2hmc
+
+extern "C" int l2hmc_net_tc_min_rows(int K, int H, int D) { return l2hmc::tc_min_rows(K, H, D); }
 
 extern "C" size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g) {
   if (!g || g->nseg < 1 || g->nseg > 3 || g->M <= 0 || g->N <= 0) return 0;

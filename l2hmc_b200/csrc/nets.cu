@@ -20,6 +20,8 @@
 #include <cooperative_groups.h>
 
 #include <climits>
+#include <cstdlib>
+#include <string>
 
 #include "common.cuh"
 #include "nets.cuh"
@@ -107,6 +109,9 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
   float* const Bs1 = Bs0 + kBs;
   float* const red = smem;           // [BM][BNP] after the main loop
 
+  // programmatic dependent launch: do not touch memory before the kernels ahead of this one in the stream have
+  // completed (a no-op unless launched with the attribute)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * BM;
@@ -279,6 +284,9 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
     }
   }
 
+  // the products are done: let the next kernel of the stream get its CTAs resident under this one's reduce / epilogue
+  // (it waits at its own griddepcontrol.wait until this grid has completed)
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   // ------------------------------------------------------------------ accumulators -> shared memory
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -480,7 +488,12 @@ int launch_dense(DenseParams p, cudaStream_t st) {
   cudaLaunchAttribute attr{};
   attr.id = cudaLaunchAttributeClusterDimension;
   attr.val.clusterDim.x = 1, attr.val.clusterDim.y = 1, attr.val.clusterDim.z = cl ? p.nchunks : 1;
-  cfg.attrs = &attr, cfg.numAttrs = 1;
+  cudaLaunchAttribute attrs[2];
+  attrs[0] = attr;
+  attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[1].val.programmaticStreamSerializationAllowed = 1;
+  static const bool pdl = !(getenv("L2HMC_PDL") && std::string(getenv("L2HMC_PDL")) == "0");     // diagnostics
+  cfg.attrs = attrs, cfg.numAttrs = pdl ? 2 : 1;
   const cudaError_t e = cl ? cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, true>, p)
                            : cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, false>, p);
   if (e != cudaSuccess) return check_launch("dense_kernel", 0);

@@ -17,6 +17,7 @@ struct TcDims {
 
 TcDims tc_dims(int K, int H, int D, int N);
 size_t tc_workspace_floats(int K, int H, int D, int N);
+int tc_min_rows(int K, int H, int D);
 bool tc_eligible(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);

@@ -238,6 +238,7 @@ constexpr int kRowThreads = 128;
 struct UpdFwdParams {
   int N, D;
   float eps;
+  const float* eps_dev;   // nullable: overrides eps
   int dir, dir_alt;
   const uint8_t* row_set;
   const float *x, *v, *g;
@@ -258,7 +259,8 @@ __global__ void __launch_bounds__(kRowThreads) train_update_fwd_kernel(const Upd
   const int dir = alt ? p.dir_alt : p.dir;
   const float* mask = alt ? p.mask_alt : p.mask;
   const int invert = alt ? p.invert_alt : p.invert;
-  const float heps = __fmul_rn(0.5f, p.eps);
+  const float eps = p.eps_dev != nullptr ? *p.eps_dev : p.eps;
+  const float heps = __fmul_rn(0.5f, eps);
   float ld = 0.f;
   bool bad = false;
   for (int d = threadIdx.x; d < p.D; d += kRowThreads) {
@@ -266,11 +268,11 @@ __global__ void __launch_bounds__(kRowThreads) train_update_fwd_kernel(const Upd
     const float S = p.S ? p.S[at] : 0.f, Tr = p.S ? p.T[at] : 0.f, Q = p.S ? p.Q[at] : 0.f;
     if (POSITION) {
       const float m = invert ? __fsub_rn(1.f, mask[d]) : mask[d];
-      p.out[at] = dir > 0 ? position_elem<1>(p.x[at], p.v[at], S, Tr, Q, m, p.eps, ld, bad)
-                          : position_elem<-1>(p.x[at], p.v[at], S, Tr, Q, m, p.eps, ld, bad);
+      p.out[at] = dir > 0 ? position_elem<1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad)
+                          : position_elem<-1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad);
     } else {
-      p.out[at] = dir > 0 ? momentum_elem<1>(p.v[at], p.g[at], S, Tr, Q, p.eps, heps, ld, bad)
-                          : momentum_elem<-1>(p.v[at], p.g[at], S, Tr, Q, p.eps, heps, ld, bad);
+      p.out[at] = dir > 0 ? momentum_elem<1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad)
+                          : momentum_elem<-1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad);
     }
   }
   const float tot = block_sum<kRowThreads>(ld, scratch);
@@ -315,7 +317,7 @@ __global__ void __launch_bounds__(kRowThreads) momentum_bwd_kernel(const UpdBwdP
   const int row = blockIdx.x;
   const bool alt = a.row_set != nullptr && a.row_set[row] != 0;
   const int dir = alt ? a.dir_alt : a.dir;
-  const float eps = a.eps, heps = 0.5f * a.eps;
+  const float eps = a.eps_dev != nullptr ? *a.eps_dev : a.eps, heps = 0.5f * eps;
   const float gld = a.gld ? a.gld[row] : 0.f;
   float de = 0.f;
   for (int d = threadIdx.x; d < a.D; d += kRowThreads) {
@@ -366,7 +368,7 @@ __global__ void __launch_bounds__(kRowThreads) position_bwd_kernel(const UpdBwdP
   const int dir = alt ? a.dir_alt : a.dir;
   const float* mask = alt ? a.mask_alt : a.mask;
   const int invert = alt ? a.invert_alt : a.invert;
-  const float eps = a.eps;
+  const float eps = a.eps_dev != nullptr ? *a.eps_dev : a.eps;
   const float gld = a.gld ? a.gld[row] : 0.f;
   float de = 0.f;
   for (int d = threadIdx.x; d < a.D; d += kRowThreads) {
@@ -671,6 +673,55 @@ __global__ void __launch_bounds__(256) colsum_stage2_kernel(const float* __restr
   }
 }
 
+// The same two stages for up to kMaxColSumJobs matrices of equal row count in one launch each (blockIdx.z / .y = job)
+struct ColSumJobs {
+  ColSumJob j[kMaxColSumJobs];
+  int rows, slabs;
+  float* partial;
+  size_t pstride;      // floats of partial per job
+};
+__global__ void __launch_bounds__(128) colsum_multi_stage1_kernel(const ColSumJobs q) {
+  const ColSumJob& jb = q.j[blockIdx.z];
+  const int c = blockIdx.x * 128 + threadIdx.x;
+  if (c >= jb.cols) return;
+  const float* __restrict__ B = jb.B;
+  const long long ld = jb.ld;
+  const int per = (q.rows + q.slabs - 1) / q.slabs;
+  const int r0 = blockIdx.y * per, r1 = min(q.rows, r0 + per);
+  float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  int r = r0;
+  for (; r + 7 < r1; r += 8) {
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = B[static_cast<long long>(r + j) * ld + c];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] += v[j];
+  }
+  for (; r < r1; ++r) s[0] += B[static_cast<long long>(r) * ld + c];
+  q.partial[blockIdx.z * q.pstride + static_cast<size_t>(blockIdx.y) * jb.cols + c] =
+      ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
+}
+__global__ void __launch_bounds__(256) colsum_multi_stage2_kernel(const ColSumJobs q) {
+  __shared__ float sm[8][32];
+  const ColSumJob& jb = q.j[blockIdx.y];
+  const float* __restrict__ partial = q.partial + blockIdx.y * q.pstride;
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
+  float s = 0.f;
+  if (c < jb.cols)
+    for (int k = g; k < q.slabs; k += 8) s += partial[static_cast<size_t>(k) * jb.cols + c];
+  sm[g][lane] = s;
+  __syncthreads();
+  if (g == 0 && c < jb.cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += sm[j][lane];
+    jb.out[0][c] = t;
+    if (jb.out[1]) jb.out[1][c] = t;
+    if (jb.out[2]) jb.out[2][c] = t;
+  }
+}
+
 // tf.train.AdamOptimizer (lr_t = lr sqrt(1 - b2^t) / (1 - b1^t) folded on the host):
 //   m = b1 m + (1 - b1) g;  v = b2 v + (1 - b2) g^2;  theta -= lr_t m / (sqrt(v) + eps)
 // with g scaled by clip / max(||g||, clip) when a global-norm clip is given (tf.clip_by_global_norm).
@@ -826,6 +877,15 @@ extern "C" int l2hmc_train_update_fwd(int position, const float* x, const float*
                                       const float* mask_alt, int invert_alt, const uint8_t* row_set, float eps, int dir,
                                       int dir_alt, int N, int D, float* out, float* logdet, int32_t* nonfinite_flag,
                                       void* stream) {
+  return l2hmc::train_update_fwd(position, x, v, g, S, Tr, Q, mask, invert, mask_alt, invert_alt, row_set, eps, nullptr,
+                                 dir, dir_alt, N, D, out, logdet, nonfinite_flag, stream);
+}
+
+// eps_dev (nullable) overrides eps: the step size read from device memory (l2hmc_train_args.eps_dev)
+int l2hmc::train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S, const float* Tr,
+                            const float* Q, const float* mask, int invert, const float* mask_alt, int invert_alt,
+                            const uint8_t* row_set, float eps, const float* eps_dev, int dir, int dir_alt, int N, int D,
+                            float* out, float* logdet, int32_t* nonfinite_flag, void* stream) {
   if (N == 0) return L2HMC_OK;
   L2HMC_REQUIRE(N > 0 && D > 0 && v && out, "l2hmc_train_update_fwd: bad arguments");
   L2HMC_REQUIRE((dir == 1 || dir == -1) && (!row_set || dir_alt == 1 || dir_alt == -1), "l2hmc_train_update_fwd: dir");
@@ -833,7 +893,7 @@ extern "C" int l2hmc_train_update_fwd(int position, const float* x, const float*
                 "l2hmc_train_update_fwd: S, T, Q go together");
   if (position) L2HMC_REQUIRE(x && mask && (!row_set || mask_alt), "l2hmc_train_update_fwd: position needs x and masks");
   else L2HMC_REQUIRE(g, "l2hmc_train_update_fwd: momentum needs g");
-  UpdFwdParams p{N, D, eps, dir, dir_alt, row_set, x, v, g, S, Tr, Q, mask, mask_alt, invert, invert_alt, out, logdet,
+  UpdFwdParams p{N, D, eps, eps_dev, dir, dir_alt, row_set, x, v, g, S, Tr, Q, mask, mask_alt, invert, invert_alt, out, logdet,
                  nonfinite_flag};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (position) train_update_fwd_kernel<true><<<N, kRowThreads, 0, st>>>(p);
@@ -937,6 +997,31 @@ extern "C" int l2hmc_col_sum(const float* B, long long ld, int rows, int cols, f
   colsum_stage1_kernel<<<dim3((cols + 127) / 128, slabs), 128, 0, st>>>(B, ld, rows, cols, slabs, partial);
   colsum_stage2_kernel<<<(cols + 31) / 32, 256, 0, st>>>(partial, slabs, cols, out);
   return check_launch("colsum_kernel", 2);
+}
+
+size_t l2hmc::col_sum_multi_workspace_bytes(int rows, int max_cols, int njobs) {
+  if (rows <= 0 || max_cols <= 0 || njobs <= 0) return 0;
+  return sizeof(float) * static_cast<size_t>(colsum_slabs(rows)) * max_cols * njobs;
+}
+
+int l2hmc::col_sum_multi(const ColSumJob* jobs, int njobs, int rows, void* workspace, size_t workspace_bytes,
+                         cudaStream_t st) {
+  L2HMC_REQUIRE(jobs && njobs >= 1 && njobs <= kMaxColSumJobs && rows > 0, "col_sum_multi: bad arguments");
+  ColSumJobs q{};
+  int max_cols = 0;
+  for (int i = 0; i < njobs; ++i) {
+    L2HMC_REQUIRE(jobs[i].B && jobs[i].out[0] && jobs[i].cols > 0 && jobs[i].ld >= jobs[i].cols, "col_sum_multi: bad job %d", i);
+    q.j[i] = jobs[i];
+    max_cols = std::max(max_cols, jobs[i].cols);
+  }
+  L2HMC_REQUIRE(workspace && workspace_bytes >= col_sum_multi_workspace_bytes(rows, max_cols, njobs),
+                "col_sum_multi: workspace too small");
+  q.rows = rows, q.slabs = colsum_slabs(rows);
+  q.partial = static_cast<float*>(workspace);
+  q.pstride = static_cast<size_t>(q.slabs) * max_cols;
+  colsum_multi_stage1_kernel<<<dim3((max_cols + 127) / 128, q.slabs, njobs), 128, 0, st>>>(q);
+  colsum_multi_stage2_kernel<<<dim3((max_cols + 31) / 32, njobs), 256, 0, st>>>(q);
+  return check_launch("colsum_multi_kernel", 2);
 }
 
 // ----------------------------------------------------------------------------------------------- no-allocation variant

@@ -32,15 +32,25 @@ __global__ void __launch_bounds__(128) pick_rows_kernel(const float* __restrict_
   for (int d = threadIdx.x; d < D; d += 128) out[static_cast<size_t>(row) * D + d] = src[d];
 }
 
-// (cos, sin, 1) per chain: the t_layer input of the call and the "input" of every bias
-__global__ void __launch_bounds__(256) tau_rows_kernel(const uint8_t* __restrict__ row_set, float c0, float s0, float c1,
-                                                       float s1, int R, float* out) {
+// (cos, sin, 1) per chain and network call: the t_layer input of the call and the "input" of every bias.  Call j of a
+// network belongs to leapfrog step j / 2; forward chains read time row `step`, backward chains row M - 1 - step.  The
+// (cos, sin) rows are a HOST array (l2hmc_train_args.ts): they travel as a kernel parameter.
+constexpr int kTauTableSteps = 128;
+struct TauTable {
+  float v[2 * kTauTableSteps];
+  int M;        // direct == 0: v holds all M rows, call j = j0 + blockIdx.y
+  int direct;   // direct == 1: v[0..1] = the forward chains' row, v[2..3] = the backward chains' row of call j0
+  int j0;
+};
+__global__ void __launch_bounds__(256) tau_rows_kernel(const uint8_t* __restrict__ row_set, const TauTable tb, int R,
+                                                       float* out) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= R) return;
+  const int j = tb.j0 + blockIdx.y, step = j >> 1;
   const bool alt = row_set[n] != 0;
-  out[3 * n] = alt ? c1 : c0;
-  out[3 * n + 1] = alt ? s1 : s0;
-  out[3 * n + 2] = 1.f;
+  const int row = tb.direct ? (alt ? 1 : 0) : (alt ? tb.M - 1 - step : step);
+  float* o = out + (static_cast<size_t>(j) * R + n) * 3;
+  o[0] = tb.v[2 * row], o[1] = tb.v[2 * row + 1], o[2] = 1.f;
 }
 
 struct Carve {
@@ -148,7 +158,7 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
       deferred(w->H, w->D), deferred(1, w->D), deferred(w->H, w->H), deferred(1, w->H), deferred(w->K, w->H);
       deferred(2, w->H);
       need(pl.R, w->H, 3, w->D, 0), need(pl.R, w->H, 1, w->H, 0), need(pl.R, w->K, 1, w->H, 0);   // per-call GEMMs
-      gw = std::max(gw, l2hmc_col_sum_workspace_bytes(K, 3 * std::max(w->H, w->D)));
+      gw = std::max(gw, col_sum_multi_workspace_bytes(K, std::max(w->H, w->D), 7));
     }
     pl.gemm_ws_bytes = gw;
     pl.gemm_ws = c.take<char>(gw);
@@ -218,10 +228,7 @@ int net_forward(const Ctx& c, const l2hmc_net_weights* w, const void* packed, Ne
   n.h1_out = t.h1 + off * t.H, n.h2_out = t.h2 + off * t.H;
   n.workspace = pl.net_ws, n.workspace_bytes = pl.net_ws_bytes;
   n.path = packed ? L2HMC_NET_PATH_TCGEN05 : L2HMC_NET_PATH_FFMA;
-  L2HMC_TRY(l2hmc_net_run(&ww, &n, c.stream));
-  tau_rows_kernel<<<(pl.R + 255) / 256, 256, 0, c.st>>>(pl.row_set, tau[0], tau[1], tau_alt[0], tau_alt[1], pl.R,
-                                                         t.tau1 + off * 3);
-  return check_launch("tau_rows_kernel");
+  return l2hmc_net_run(&ww, &n, c.stream);
 }
 
 // dA[j] -> dz2[j] -> dz1[j]
@@ -241,21 +248,20 @@ int weight_grads(const Ctx& c, const NetTape& t, const l2hmc_net_grads* g) {
   const int Rt = 2 * c.pl.M * c.pl.R, H = t.H, D = t.D, K = t.K;
   auto ks = [&](int M, int N) { return ksplit_for(M, N, Rt); };
   float* wk[3] = {g->w_s, g->w_tr, g->w_q};
-  float* bk[3] = {g->b_s, g->b_tr, g->b_q};
-  for (int s = 0; s < 3; ++s) {
+  for (int s = 0; s < 3; ++s)
     L2HMC_TRY(plain_gemm(c, H, D, l2hmc_gemm_seg{t.h2, 1, H, t.dA + s * D, 3LL * D, 1, Rt}, wk[s], D, 0, ks(H, D)));
-    L2HMC_TRY(col_sum(c, t.dA + s * D, 3LL * D, Rt, D, bk[s]));
-  }
   L2HMC_TRY(plain_gemm(c, H, H, l2hmc_gemm_seg{t.h1, 1, H, t.dz2, H, 1, Rt}, g->w_h, H, 0, ks(H, H)));
-  L2HMC_TRY(col_sum(c, t.dz2, H, Rt, H, g->b_h));
   L2HMC_TRY(plain_gemm(c, K, H, l2hmc_gemm_seg{t.in0, 1, K, t.dz1, H, 1, Rt}, g->w_in0, H, 0, ks(K, H)));
   L2HMC_TRY(plain_gemm(c, K, H, l2hmc_gemm_seg{t.in1, 1, K, t.dz1, H, 1, Rt}, g->w_in1, H, 0, ks(K, H)));
   L2HMC_TRY(plain_gemm(c, 2, H, l2hmc_gemm_seg{t.tau1, 1, 3, t.dz1, H, 1, Rt}, g->w_t, H, 0, ks(2, H)));
-  L2HMC_TRY(col_sum(c, t.dz1, H, Rt, H, g->b_in0));        // the three first-layer biases add into the same sum
-  for (float* b : {g->b_in1, g->b_t})
-    if (cudaMemcpyAsync(b, g->b_in0, H * sizeof(float), cudaMemcpyDeviceToDevice, c.st) != cudaSuccess) return L2HMC_ERR_CUDA;
-  L2HMC_TRY(col_sum(c, t.ps, D, Rt, D, g->coeff_s));
-  return col_sum(c, t.pq, D, Rt, D, g->coeff_q);
+  // the seven bias / coefficient gradients (batch sums of activation gradients) in two launches; the three first-layer
+  // biases add into the same sum
+  const ColSumJob jobs[7] = {
+      {t.dA, 3LL * D, D, {g->b_s, nullptr, nullptr}},        {t.dA + D, 3LL * D, D, {g->b_tr, nullptr, nullptr}},
+      {t.dA + 2 * D, 3LL * D, D, {g->b_q, nullptr, nullptr}}, {t.dz2, H, H, {g->b_h, nullptr, nullptr}},
+      {t.dz1, H, H, {g->b_in0, g->b_in1, g->b_t}},            {t.ps, D, D, {g->coeff_s, nullptr, nullptr}},
+      {t.pq, D, D, {g->coeff_q, nullptr, nullptr}}};
+  return col_sum_multi(jobs, 7, Rt, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.st);
 }
 
 int conv_weight_grads(const Ctx& c, const NetTape& t, const float* part, const l2hmc_conv3d_grads* g, int F) {
@@ -351,6 +357,25 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
   train_row_set_kernel<<<(R + 255) / 256, 256, 0, st>>>(a->u_dir, R, pl.row_set);
   pick_rows_kernel<<<R, 128, 0, st>>>(a->v_f, a->v_b, pl.row_set, D, Vs(0));
   L2HMC_TRY(check_launch("pick_rows_kernel", 2));
+  if (nets) {       // the time-embedding rows of all 2M calls of each network
+    for (NetTape* t : {&pl.xt, &pl.vt}) {
+      TauTable tb{};
+      if (M <= kTauTableSteps) {
+        for (int i = 0; i < 2 * M; ++i) tb.v[i] = a->ts[i];
+        tb.M = M, tb.direct = 0, tb.j0 = 0;
+        tau_rows_kernel<<<dim3((R + 255) / 256, 2 * M), 256, 0, st>>>(pl.row_set, tb, R, t->tau1);
+        L2HMC_TRY(check_launch("tau_rows_kernel"));
+      } else {
+        for (int j = 0; j < 2 * M; ++j) {
+          const int step = j >> 1, ib = M - 1 - step;
+          tb.v[0] = a->ts[2 * step], tb.v[1] = a->ts[2 * step + 1], tb.v[2] = a->ts[2 * ib], tb.v[3] = a->ts[2 * ib + 1];
+          tb.M = M, tb.direct = 1, tb.j0 = j;
+          tau_rows_kernel<<<dim3((R + 255) / 256, 1), 256, 0, st>>>(pl.row_set, tb, R, t->tau1);
+          L2HMC_TRY(check_launch("tau_rows_kernel"));
+        }
+      }
+    }
+  }
   cudaMemsetAsync(pl.sld, 0, R * sizeof(float), st);
   if (nets && pl.tc_forward) {      // the weights moved since the last step: refresh their TS32 copies
     L2HMC_TRY(l2hmc_net_pack(a->xnet, pl.xpack, pl.xpack_bytes, stream));
@@ -385,8 +410,8 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           L2HMC_TRY(net_forward(c, a->vnet, pl.tc_forward ? pl.vpack : nullptr, t, jv, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
-        L2HMC_TRY(l2hmc_train_update_fwd(0, nullptr, Vs(vi), g, S, Tr, Q, nullptr, 0, nullptr, 0, pl.row_set, eps, 1, -1, R,
-                                         D, Vs(vi + 1), pl.sld, a->nonfinite_flag, stream));
+        L2HMC_TRY(train_update_fwd(0, nullptr, Vs(vi), g, S, Tr, Q, nullptr, 0, nullptr, 0, pl.row_set, eps, a->eps_dev, 1,
+                                   -1, R, D, Vs(vi + 1), pl.sld, a->nonfinite_flag, stream));
         ++vi, ++jv;
       } else {                      // position update
         recs.push_back(Rec{1, jx, xi, vi, invs[q], invs_alt[q], step, ib, nullptr});
@@ -406,8 +431,8 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           L2HMC_TRY(net_forward(c, a->xnet, pl.tc_forward ? pl.xpack : nullptr, t, jx, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
-        L2HMC_TRY(l2hmc_train_update_fwd(1, Xs(xi), Vs(vi), nullptr, S, Tr, Q, row_f, invs[q], row_b, invs_alt[q], pl.row_set,
-                                         eps, 1, -1, R, D, Xs(xi + 1), pl.sld, a->nonfinite_flag, stream));
+        L2HMC_TRY(train_update_fwd(1, Xs(xi), Vs(vi), nullptr, S, Tr, Q, row_f, invs[q], row_b, invs_alt[q], pl.row_set, eps,
+                                   a->eps_dev, 1, -1, R, D, Xs(xi + 1), pl.sld, a->nonfinite_flag, stream));
         ++xi, ++jx;
       }
     }
@@ -439,7 +464,7 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
     const float* row_f = a->masks + static_cast<size_t>(rec.step) * D;
     const float* row_b = a->masks + static_cast<size_t>(rec.ib) * D;
     l2hmc_update_bwd_args u{};
-    u.N = R, u.D = D, u.eps = eps, u.dir = 1, u.dir_alt = -1, u.row_set = pl.row_set;
+    u.N = R, u.D = D, u.eps = eps, u.eps_dev = a->eps_dev, u.dir = 1, u.dir_alt = -1, u.row_set = pl.row_set;
     u.v = Vs(rec.vi), u.gv = pl.gv, u.gld = pl.a, u.deps = pl.deps;
     const l2hmc_net_weights* w = nullptr;
     NetTape* t = nullptr;

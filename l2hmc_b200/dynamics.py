@@ -179,6 +179,8 @@ class GaugeDynamics(object):
         self._eps_dev = torch.tensor(self._eps_host, dtype=torch.float32, device=self.device)
 
     def _eps(self):
+        if self._eps_host is None:          # stale after an optimiser step (training.FlatParams.sync_to_dynamics)
+            self._eps_host = float(self._eps_dev.item())
         return self._eps_host
 
     def raise_if_nonfinite(self):

@@ -42,11 +42,17 @@ class GaugeSampler(object):
         self.N, self.D = int(num_chains), dyn.x_dim
         if chunk_chains is None:
             chunk_chains = 2048 if self.nets else 8192
-        # balanced chunks; with networks every chunk keeps >= 256 chains when the batch has them, so that all chunks
-        # take the network path (tcgen05 from 256 rows) the whole batch would take and the results stay bit-identical
+        # balanced chunks; with networks, when the whole batch would take the tcgen05 layers (l2hmc_net_tc_min_rows)
+        # every chunk stays large enough to take them too, so that chunking does not change a bit (below that number
+        # the FFMA layers run, whose per-chain result does not depend on the batch size)
         nchunks = max(1, (self.N + int(chunk_chains) - 1) // int(chunk_chains))
-        if self.nets and self.N >= 256:
-            nchunks = min(nchunks, self.N // 256)
+        self.tc_min_rows = None
+        if self.nets:
+            net = dyn.position_fn
+            self.tc_min_rows = int(_lib.get_lib().l2hmc_net_tc_min_rows(int(net.num_features), int(net.num_hidden),
+                                                                        int(net.x_dim)))
+            if self.N >= self.tc_min_rows:
+                nchunks = min(nchunks, self.N // self.tc_min_rows)
         self.chunk = (self.N + nchunks - 1) // nchunks
         self.dev = dyn.device
         self.nchunks = (self.N + self.chunk - 1) // self.chunk

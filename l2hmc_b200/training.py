@@ -132,11 +132,12 @@ class FlatParams(object):
                 net._conv_structs = None
 
     def sync_to_dynamics(self):
-        """After an optimiser step: refresh the host copy of eps (one sync, like the reference's fetch of
-        dynamics.eps every step, gauge_model.py:1166) and drop the packed tensor-core weight copies."""
+        """After an optimiser step: the host copy of eps is stale (fetched -- one sync -- only when something asks for
+        it: the log row, an inference call; the reference fetches dynamics.eps every step, gauge_model.py:1166) and
+        the packed tensor-core weight copies are dropped."""
         dyn = self.dynamics
         dyn._eps_dev = self.flat[0]
-        dyn._eps_host = float(self.flat[0].item())
+        dyn._eps_host = None
         if not dyn.hmc:
             for net in (dyn.position_fn, dyn.momentum_fn):
                 net._struct = None
@@ -330,7 +331,9 @@ class TrainEngine(object):
         new = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
         a = _lib.TrainArgs()
         a.N, a.T, a.X, a.M = N, dyn.T, dyn.X, int(dyn.num_steps)
-        a.eps, a.beta = dyn._eps(), dyn._beta(beta)
+        # the step size is read by the kernels where the optimiser keeps it (flat[0]): no host copy, no sync per step
+        a.eps, a.beta = 0.0, dyn._beta(beta)
+        a.eps_dev = _lib.dptr(dyn._eps_dev)      # flat[0] once the arena exists; the tensor of the eps setter otherwise
         mask = dyn.mask if dyn.mask.is_contiguous() else dyn.mask.contiguous()
         a.masks = _lib.dptr(mask)
         ts = np.ascontiguousarray(dyn._ts_host, dtype=np.float32)

@@ -73,6 +73,18 @@ def main():
             out[f"net call S,T,Q, path {nm}"] = graph_time(lambda: net([v, x, (1.0, 0.0)]))
         except Exception as e:      # noqa
             out[f"net call S,T,Q, path {nm}"] = "n/a: " + str(e)[:80]
+    # FFMA layers against the tcgen05 layers by batch size: where l2hmc_net_run's AUTO rule should switch
+    for (T, arch, tag) in ((8, "generic", "8x8 generic K=128 H=512 D=128"), (16, "conv3D", "16x16 conv3D K=512 H=1024 D=512")):
+        for rows in (256, 512, 1024, 2048, 4096):
+            lat = pkg.GaugeLattice(T, T, 2, "U1", num_samples=rows)
+            np.random.seed(0)
+            dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=5, eps=0.1)
+            net = dyn.position_fn
+            Dd = 2 * T * T
+            x, v = rnd(rows, Dd), rnd(rows, Dd)
+            for path, nm in ((_lib.NET_PATH_FFMA, "ffma"), (_lib.NET_PATH_TCGEN05, "tcgen05")):
+                net.path = path
+                out[f"sweep {tag} rows={rows} path={nm}"] = graph_time(lambda: net([v, x, (1.0, 0.0)]), reps=20, replays=10)
     for k, val in out.items():
         print(json.dumps({"op": k, "us_per_call": val}))
 

@@ -31,7 +31,8 @@ def _reference_steps(dyn, x, beta, steps):
 
 
 @pytest.mark.parametrize("arch,T,N,chunk", [(None, 16, 700, 256), (None, 8, 64, 64), ("generic", 8, 200, 64),
-                                            ("conv3D", 8, 150, 64), ("generic", 8, 900, 256), ("conv3D", 16, 600, 128)])
+                                            ("conv3D", 8, 150, 64), ("generic", 8, 900, 256), ("conv3D", 16, 600, 128),
+                                            ("generic", 8, 2100, 256), ("conv3D", 16, 1100, 128)])
 def test_host_buffer_step_equals_apply_transition(arch, T, N, chunk):
     from l2hmc_b200.sampler import GaugeSampler
     D, beta, steps = 2 * T * T, 2.5, 3
@@ -39,9 +40,11 @@ def test_host_buffer_step_equals_apply_transition(arch, T, N, chunk):
     ref_rows, ref_x = _reference_steps(_make(arch, T, N), x, beta, steps)
     dyn = _make(arch, T, N)
     s = GaugeSampler(dyn, N, chunk_chains=chunk)
-    assert s.nchunks >= 2 or N <= chunk
-    if arch is not None and N >= 256:      # every chunk stays on the tensor-core path the whole batch takes
-        assert s.chunk >= 256
+    if arch is not None and N >= s.tc_min_rows:      # every chunk stays on the tensor-core path the whole batch takes
+        assert s.chunk >= s.tc_min_rows
+        assert s.nchunks >= 2 or N < 2 * s.tc_min_rows
+    else:                                            # HMC, or FFMA layers (batch-size independent): chunks as asked for
+        assert s.nchunks >= 2 or N <= chunk
     host = s.pinned_like(x)
     for k in range(steps):
         r = s.step(host, beta)
