@@ -27,11 +27,20 @@ struct ColSumJob {
 constexpr int kMaxColSumJobs = 8;
 size_t col_sum_multi_workspace_bytes(int rows, int max_cols, int njobs);
 int col_sum_multi(const ColSumJob* jobs, int njobs, int rows, void* workspace, size_t workspace_bytes, cudaStream_t stream);
-// l2hmc_train_update_fwd with the step size optionally read from device memory (train.cu; used by train_step.cu)
+// l2hmc_train_update_fwd with the step size optionally read from device memory and with extra outputs: the network
+// inputs of the calls that consume the new state, written by the kernel that produces it (train.cu; used by
+// train_step.cu instead of a copy / mask-product launch per call)
+struct UpdExtra {
+  float* copy[2];          // nullable: further copies of `out` (the in0 slots of the tape)
+  float* masked;           // nullable: nmask (*) out with the per-chain mask set (the in1 slot of the next position call)
+  const float* nmask;
+  const float* nmask_alt;
+  int ninv, ninv_alt;
+};
 int train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S, const float* Tr,
                      const float* Q, const float* mask, int invert, const float* mask_alt, int invert_alt,
                      const uint8_t* row_set, float eps, const float* eps_dev, int dir, int dir_alt, int N, int D, float* out,
-                     float* logdet, int32_t* nonfinite_flag, void* stream);
+                     float* logdet, int32_t* nonfinite_flag, const UpdExtra* extra, void* stream);
 
 #define L2HMC_REQUIRE(cond, ...)          \
   do {                                    \

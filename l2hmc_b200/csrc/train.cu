@@ -248,6 +248,7 @@ struct UpdFwdParams {
   float* out;
   float* logdet;
   int32_t* flag;
+  UpdExtra ex;
 };
 
 // One CTA per chain: the arithmetic of update_math.cuh with per-chain direction / mask set.
@@ -263,17 +264,24 @@ __global__ void __launch_bounds__(kRowThreads) train_update_fwd_kernel(const Upd
   const float heps = __fmul_rn(0.5f, eps);
   float ld = 0.f;
   bool bad = false;
+  const float* nmask = alt ? p.ex.nmask_alt : p.ex.nmask;
+  const int ninv = alt ? p.ex.ninv_alt : p.ex.ninv;
   for (int d = threadIdx.x; d < p.D; d += kRowThreads) {
     const size_t at = static_cast<size_t>(row) * p.D + d;
     const float S = p.S ? p.S[at] : 0.f, Tr = p.S ? p.T[at] : 0.f, Q = p.S ? p.Q[at] : 0.f;
+    float val;
     if (POSITION) {
       const float m = invert ? __fsub_rn(1.f, mask[d]) : mask[d];
-      p.out[at] = dir > 0 ? position_elem<1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad)
-                          : position_elem<-1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad);
+      val = dir > 0 ? position_elem<1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad)
+                    : position_elem<-1>(p.x[at], p.v[at], S, Tr, Q, m, eps, ld, bad);
     } else {
-      p.out[at] = dir > 0 ? momentum_elem<1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad)
-                          : momentum_elem<-1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad);
+      val = dir > 0 ? momentum_elem<1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad)
+                    : momentum_elem<-1>(p.v[at], p.g[at], S, Tr, Q, eps, heps, ld, bad);
     }
+    p.out[at] = val;
+    if (p.ex.copy[0] != nullptr) p.ex.copy[0][at] = val;
+    if (p.ex.copy[1] != nullptr) p.ex.copy[1][at] = val;
+    if (p.ex.masked != nullptr) p.ex.masked[at] = __fmul_rn(ninv ? __fsub_rn(1.f, nmask[d]) : nmask[d], val);
   }
   const float tot = block_sum<kRowThreads>(ld, scratch);
   if (threadIdx.x == 0 && p.logdet != nullptr) p.logdet[row] = __fadd_rn(p.logdet[row], tot);
@@ -878,14 +886,14 @@ extern "C" int l2hmc_train_update_fwd(int position, const float* x, const float*
                                       int dir_alt, int N, int D, float* out, float* logdet, int32_t* nonfinite_flag,
                                       void* stream) {
   return l2hmc::train_update_fwd(position, x, v, g, S, Tr, Q, mask, invert, mask_alt, invert_alt, row_set, eps, nullptr,
-                                 dir, dir_alt, N, D, out, logdet, nonfinite_flag, stream);
+                                 dir, dir_alt, N, D, out, logdet, nonfinite_flag, nullptr, stream);
 }
 
 // eps_dev (nullable) overrides eps: the step size read from device memory (l2hmc_train_args.eps_dev)
 int l2hmc::train_update_fwd(int position, const float* x, const float* v, const float* g, const float* S, const float* Tr,
                             const float* Q, const float* mask, int invert, const float* mask_alt, int invert_alt,
                             const uint8_t* row_set, float eps, const float* eps_dev, int dir, int dir_alt, int N, int D,
-                            float* out, float* logdet, int32_t* nonfinite_flag, void* stream) {
+                            float* out, float* logdet, int32_t* nonfinite_flag, const UpdExtra* extra, void* stream) {
   if (N == 0) return L2HMC_OK;
   L2HMC_REQUIRE(N > 0 && D > 0 && v && out, "l2hmc_train_update_fwd: bad arguments");
   L2HMC_REQUIRE((dir == 1 || dir == -1) && (!row_set || dir_alt == 1 || dir_alt == -1), "l2hmc_train_update_fwd: dir");
@@ -894,7 +902,8 @@ int l2hmc::train_update_fwd(int position, const float* x, const float* v, const 
   if (position) L2HMC_REQUIRE(x && mask && (!row_set || mask_alt), "l2hmc_train_update_fwd: position needs x and masks");
   else L2HMC_REQUIRE(g, "l2hmc_train_update_fwd: momentum needs g");
   UpdFwdParams p{N, D, eps, eps_dev, dir, dir_alt, row_set, x, v, g, S, Tr, Q, mask, mask_alt, invert, invert_alt, out, logdet,
-                 nonfinite_flag};
+                 nonfinite_flag, extra ? *extra : UpdExtra{}};
+  if (extra && extra->masked) L2HMC_REQUIRE(extra->nmask && (!row_set || extra->nmask_alt), "train_update_fwd: next mask missing");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (position) train_update_fwd_kernel<true><<<N, kRowThreads, 0, st>>>(p);
   else train_update_fwd_kernel<false><<<N, kRowThreads, 0, st>>>(p);

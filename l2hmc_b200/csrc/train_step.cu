@@ -385,6 +385,15 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
   std::vector<Rec> recs;
   recs.reserve(4 * M);
   int jx = 0, jv = 0, xi = 0, vi = 0;
+  // generic nets: the network inputs are copies / mask products of the states.  Every update kernel writes them for
+  // the calls that consume its result (UpdExtra); only the start state needs launches of its own.
+  const bool dense_in = nets && !conv;
+  auto slot = [&](float* base, int j, int K) { return base + static_cast<size_t>(j) * R * K; };
+  if (dense_in) {
+    L2HMC_TRY(copy(pl.vt.in0, Xs(0), RD));
+    L2HMC_TRY(l2hmc_mask_mul_sets(Xs(0), a->masks, 0, a->masks + static_cast<size_t>(M - 1) * D, 1, pl.row_set, R, D,
+                                  pl.xt.in1, stream));
+  }
   for (int step = 0; step < M; ++step) {
     const int ib = M - step - 1;
     const float* tau = a->ts + 2 * step;
@@ -404,14 +413,15 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
           if (conv) {   // momentum_fn([x, grad, t]): x through conv_v*, the force through conv_x*
             L2HMC_TRY(conv_fwd(c, a->vconv_in0, Xs(xi), t.in0 + off * t.K, conv_tape(c, 1, 0, jv), nullptr, 0, nullptr, 0));
             L2HMC_TRY(conv_fwd(c, a->vconv_in1, g, t.in1 + off * t.K, conv_tape(c, 1, 1, jv), nullptr, 0, nullptr, 0));
-          } else {
-            L2HMC_TRY(copy(t.in0 + off * t.K, Xs(xi), RD));
-          }
+          }             // (generic nets: in0 = x was written by the update that produced x)
           L2HMC_TRY(net_forward(c, a->vnet, pl.tc_forward ? pl.vpack : nullptr, t, jv, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
+        UpdExtra ex{};
+        if (dense_in && q == 0)       // the new v is position_fn's first input in both position updates of this step
+          ex.copy[0] = slot(pl.xt.in0, jx, pl.xt.K), ex.copy[1] = slot(pl.xt.in0, jx + 1, pl.xt.K);
         L2HMC_TRY(train_update_fwd(0, nullptr, Vs(vi), g, S, Tr, Q, nullptr, 0, nullptr, 0, pl.row_set, eps, a->eps_dev, 1,
-                                   -1, R, D, Vs(vi + 1), pl.sld, a->nonfinite_flag, stream));
+                                   -1, R, D, Vs(vi + 1), pl.sld, a->nonfinite_flag, &ex, stream));
         ++vi, ++jv;
       } else {                      // position update
         recs.push_back(Rec{1, jx, xi, vi, invs[q], invs_alt[q], step, ib, nullptr});
@@ -423,16 +433,25 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
             L2HMC_TRY(conv_fwd(c, a->xconv_in0, Vs(vi), t.in0 + off * t.K, conv_tape(c, 0, 0, jx), nullptr, 0, nullptr, 0));
             L2HMC_TRY(conv_fwd(c, a->xconv_in1, Xs(xi), t.in1 + off * t.K, conv_tape(c, 0, 1, jx), row_f, invs[q], row_b,
                                invs_alt[q]));
-          } else {
-            L2HMC_TRY(copy(t.in0 + off * t.K, Vs(vi), RD));
-            L2HMC_TRY(l2hmc_mask_mul_sets(Xs(xi), row_f, invs[q], row_b, invs_alt[q], pl.row_set, R, D, t.in1 + off * t.K,
-                                          stream));
-          }
+          }             // (generic nets: in0 = v and in1 = m * x were written by the updates that produced v and x)
           L2HMC_TRY(net_forward(c, a->xnet, pl.tc_forward ? pl.xpack : nullptr, t, jx, tau, tau_alt));
           S = t.S + off * D, Tr = t.T + off * D, Q = t.Q + off * D;
         }
+        UpdExtra ex{};
+        if (dense_in && q == 1) {     // the new x, masked for the second position update of this step
+          ex.masked = slot(pl.xt.in1, jx + 1, pl.xt.K);
+          ex.nmask = row_f, ex.ninv = invs[2], ex.nmask_alt = row_b, ex.ninv_alt = invs_alt[2];
+        } else if (dense_in) {        // q == 2: the new x is momentum_fn's first input in the next two momentum updates
+          ex.copy[0] = slot(pl.vt.in0, jv, pl.vt.K);       // ... and, masked, position_fn's second input in the next step
+          if (step + 1 < M) {
+            ex.copy[1] = slot(pl.vt.in0, jv + 1, pl.vt.K);
+            ex.masked = slot(pl.xt.in1, jx + 1, pl.xt.K);
+            ex.nmask = a->masks + static_cast<size_t>(step + 1) * D, ex.ninv = invs[1];
+            ex.nmask_alt = a->masks + static_cast<size_t>(M - step - 2) * D, ex.ninv_alt = invs_alt[1];
+          }
+        }
         L2HMC_TRY(train_update_fwd(1, Xs(xi), Vs(vi), nullptr, S, Tr, Q, row_f, invs[q], row_b, invs_alt[q], pl.row_set, eps,
-                                   a->eps_dev, 1, -1, R, D, Xs(xi + 1), pl.sld, a->nonfinite_flag, stream));
+                                   a->eps_dev, 1, -1, R, D, Xs(xi + 1), pl.sld, a->nonfinite_flag, &ex, stream));
         ++xi, ++jx;
       }
     }

@@ -376,3 +376,34 @@ def test_native_mc_step_equals_python_composition(pkg, arch, T, N, path, inject)
     for a, b in zip(*outs):
         assert torch.equal(a, b)
     assert 0 < int(outs[0][4].sum()) <= N
+
+
+@pytest.mark.parametrize("arch,T,X", [("generic", 8, 8), ("generic", 6, 10), ("conv3D", 8, 8)])
+def test_ffma_layers_do_not_depend_on_batch_size(arch, T, X):
+    """The chunked FFMA layers (nets.cu): a chain's S, T, Q and its fused sub-updates are the same BITS whether it is
+    launched alone, in a small batch (K chunks spread over a thread-block cluster) or in a large one (one CTA walks the
+    chunks) -- what lets the sampler chunk a batch and the ranks shard it without changing a result."""
+    import l2hmc_b200 as pkg
+    from l2hmc_b200 import _lib
+    from parity_util import trained_like_weights
+    D = 2 * T * X
+    rng = np.random.default_rng(T * X)
+    big = 9700                                   # > 148 output tiles: the one-CTA-per-tile path
+    x = rng.uniform(0, 2 * np.pi, (big, D)).astype(np.float32)
+    v = rng.standard_normal((big, D)).astype(np.float32)
+    ws = trained_like_weights(arch, T, X, np.random.default_rng(3), gain=1.0)
+    outs = {}
+    for n in (3, 200, big):
+        lat = pkg.GaugeLattice(T, X, 2, "U1", num_samples=n)
+        np.random.seed(1)
+        dyn = pkg.GaugeDynamics(lat, hmc=False, network_arch=arch, num_steps=2, eps=0.1, weights=ws)
+        net = dyn.position_fn
+        net.path = _lib.NET_PATH_FFMA
+        xs, vs = torch.as_tensor(x[:n]).cuda(), torch.as_tensor(v[:n]).cuda()
+        S, Tr, Q = net([vs, xs, (0.3, 0.7)], mask=dyn.mask[0], mask_invert=True)
+        ld = torch.zeros(n, device="cuda")
+        xo = net.position_update(xs, vs, (0.3, 0.7), dyn.mask[0], False, 0.1, 1, ld, dyn._flag)
+        outs[n] = [t.cpu() for t in (S, Tr, Q, xo, ld)]
+    for n in (3, 200):
+        for a, b, nm in zip(outs[n], outs[big], ("S", "T", "Q", "x_out", "logdet")):
+            assert torch.equal(a, b[:n]), f"{arch} {T}x{X}: {nm} of the first {n} chains differs between a {n}- and a {big}-chain launch"

@@ -41,7 +41,11 @@ def close_scaled(got, want, tol=2e-4, what=""):
                                          (1, 200, 777, True, False), (3, 64, 1000, True, True), (256, 512, 384, False, True),
                                          # M <= 4 over a long K with row-major B: the weighted-column-sum kernel
                                          (2, 1000, 5003, True, False), (4, 130, 2560, False, False),
-                                         (1, 64, 40960, True, False)])
+                                         (1, 64, 40960, True, False),
+                                         # both operands K-contiguous: the chunked dense kernel (clustered K chunks for
+                                         # few tiles, one CTA walking the chunks for many), ragged in every dimension
+                                         (130, 70, 100, False, True), (70, 33, 1030, False, True),
+                                         (9700, 200, 300, False, True), (5, 7, 3, False, True)])
 def test_sgemm_forms(M, N, K, ta, tb):
     from l2hmc_b200 import _lib
     from l2hmc_b200.training import _Gemm, _ptr
