@@ -1,5 +1,6 @@
 // C-ABI glue shared by all entry points: error text, version, device limits.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <atomic>
 
@@ -28,6 +29,15 @@ int check_launch(const char* what, int launches) {
     return L2HMC_ERR_CUDA;
   }
   return L2HMC_OK;
+}
+
+// L2HMC_PDL=0: launch every kernel without the programmatic-dependent-launch attribute (diagnostics)
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("L2HMC_PDL");
+    return !(e && e[0] == '0' && e[1] == 0);
+  }();
+  return on;
 }
 
 }  // namespace l2hmc

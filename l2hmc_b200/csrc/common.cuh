@@ -42,6 +42,28 @@ int train_update_fwd(int position, const float* x, const float* v, const float* 
                      const uint8_t* row_set, float eps, const float* eps_dev, int dir, int dir_alt, int N, int D, float* out,
                      float* logdet, int32_t* nonfinite_flag, const UpdExtra* extra, void* stream);
 
+// ---- programmatic dependent launch (PDL).  A kernel that starts with pdl_wait() may be launched with launch_pdl():
+// its CTAs become resident (launch latency, barrier / TMEM set-up before the wait) while the kernel ahead of it in the
+// stream is still running, once every CTA of THAT kernel has called pdl_trigger() or exited; pdl_wait() returns when
+// the kernels ahead have completed and their writes are visible.  Both instructions are no-ops in a kernel launched
+// without the attribute, and a kernel that never triggers simply releases its dependents at completion, so the two
+// halves can be adopted kernel by kernel.  Every thread calls pdl_wait() before its first global access (so a grid
+// never completes before the grids ahead of it).  L2HMC_PDL=0 launches everything without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr, cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 #define L2HMC_REQUIRE(cond, ...)          \
   do {                                    \
     if (!(cond)) {                        \

@@ -401,6 +401,8 @@ __global__ void __launch_bounds__(TH, 512 / TH) conv3d_tc_kernel(const ConvParam
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_in + CH * IN);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  pdl_wait();
+  pdl_trigger();
 
   {                                                                    // w2[kt][kx][kd = 0][f][c], hi / lo split
     constexpr int NW4 = F * C, PER = (NW4 + TH - 1) / TH;              // float4 groups; all loads of a thread in flight at once
@@ -674,7 +676,7 @@ int launch_tc(const ConvParams& p, int sms, int max_smem, cudaStream_t stream) {
         return L2HMC_ERR_CUDA;
       }
     }
-    kern<<<grid, TH, smem, stream>>>(p, CH, MT, ROWS);
+    launch_pdl(kern, dim3(grid), dim3(TH), smem, stream, p, CH, MT, ROWS);
     return check_launch("conv3d_tc_kernel");
   };
   if (pf <= 1) return go(conv3d_tc_kernel<F, 1, TH>);

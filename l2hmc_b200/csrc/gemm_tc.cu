@@ -146,6 +146,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // barriers and TMEM are set up: wait for the kernels ahead in the stream before touching global memory, and let the
+  // next kernel start its own set-up as soon as this grid's CTAs leave room
+  pdl_wait();
+  pdl_trigger();
   const uint32_t tmem_base = *tmem_slot;
   const int mn_tiles = p.m_tiles * p.n_tiles;
   const bool split = MODE == kTcPlain && p.ksplit > 1;
@@ -472,6 +476,8 @@ struct NetPrologueParams {
   float* bias_eff;
 };
 __global__ void __launch_bounds__(256) net_prologue_kernel(const NetPrologueParams q) {
+  pdl_wait();
+  pdl_trigger();
   if (blockIdx.y == 0) {
     ts32_from_rowmajor(q.in0, q.K, q.N, q.K, nullptr, 0, nullptr, 0, nullptr, q.acat, q.rg, 0, q.kbK);
   } else if (blockIdx.y == 1) {
@@ -523,6 +529,8 @@ __global__ void __launch_bounds__(256) ts32_to_rowmajor_kernel(const float* __re
 }
 
 __global__ void logdet_reduce_tc_kernel(const float* __restrict__ part, int tiles, int N, float* logdet) {
+  pdl_wait();
+  pdl_trigger();
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   float s = 0.f;
@@ -556,7 +564,7 @@ int launch_tc(const TcParams& p, cudaStream_t st) {
   const int sms = sm_count[slot];
   const int tiles = p.m_tiles * p.n_tiles * (MODE == kTcPlain && p.ksplit > 1 ? p.ksplit : 1);
   if (tiles == 0) return L2HMC_OK;
-  kern<<<std::min(tiles, sms), kTcThreads, smem, st>>>(p);
+  launch_pdl(kern, dim3(std::min(tiles, sms)), dim3(kTcThreads), smem, st, p);
   return check_launch("gemm_tc_kernel");
 }
 
@@ -615,7 +623,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   NetPrologueParams q{c->in0, c->in1, K, N, c->in1_mask, c->in1_mask_invert, c->in1_mask_alt, c->in1_mask_invert_alt,
                       c->row_set, acat, rg, d.kbK, w->b_in0, w->b_in1, w->b_t, w->w_t, c->tau_cos, c->tau_sin,
                       c->tau_cos_alt, c->tau_sin_alt, H, d.h_rows, bias_eff};
-  net_prologue_kernel<<<dim3(ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 3), 256, 0, st>>>(q);
+  launch_pdl(net_prologue_kernel, dim3(ew_grid(static_cast<size_t>(d.kbK) * rg * 64), 3), dim3(256), 0, st, q);
   int rc = check_launch("net_prologue_kernel");
   if (rc) return rc;
 
@@ -654,7 +662,7 @@ int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t
   else rc = launch_tc<192, kTcHeadsPosition>(p, st);
   if (rc) return rc;
   if (c->mode != L2HMC_NET_STQ && c->logdet) {
-    logdet_reduce_tc_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, 2 * d.d_tiles, N, c->logdet);
+    launch_pdl(logdet_reduce_tc_kernel, dim3((N + 255) / 256), dim3(256), 0, st, ld_part, 2 * d.d_tiles, N, c->logdet);
     rc = check_launch("logdet_reduce_tc_kernel");
   }
   // training tape (h1_out / h2_out): the layer epilogues above also wrote the hidden activations row-major fp32
@@ -723,6 +731,8 @@ struct Ts32Jobs {
   Ts32Job j[6];
 };
 __global__ void __launch_bounds__(256) ts32_from_strided_kernel(const Ts32Jobs jobs) {
+  pdl_wait();
+  pdl_trigger();
   const Ts32Job& jb = jobs.j[blockIdx.y];
   const float* __restrict__ src = jb.src;
   const long long rs = jb.rs, cs = jb.cs;
@@ -826,7 +836,7 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
   }
   int rc = L2HMC_OK;
   if (njobs > 0) {
-    ts32_from_strided_kernel<<<dim3(gx, njobs), 256, 0, st>>>(jobs);
+    launch_pdl(ts32_from_strided_kernel, dim3(gx, njobs), dim3(256), 0, st, jobs);
     rc = check_launch("ts32_from_strided_kernel");
   }
   if (rc) return rc;

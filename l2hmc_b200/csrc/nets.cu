@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 
   // programmatic dependent launch: do not touch memory before the kernels ahead of this one in the stream have
   // completed (a no-op unless launched with the attribute)
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  pdl_wait();
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
   const int m0 = blockIdx.y * BM;
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 
   // the products are done: let the next kernel of the stream get its CTAs resident under this one's reduce / epilogue
   // (it waits at its own griddepcontrol.wait until this grid has completed)
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  pdl_trigger();
   // ------------------------------------------------------------------ accumulators -> shared memory
 #pragma unroll
   for (int i = 0; i < 4; ++i)
@@ -459,6 +459,8 @@ __global__ void __launch_bounds__(kThreads) dense_kernel(const DenseParams p) {
 
 // logdet[n] += sum_j part[j][n], j in fixed order (deterministic)
 __global__ void logdet_reduce_kernel(const float* __restrict__ part, int tiles, int N, float* logdet) {
+  pdl_wait();
+  pdl_trigger();
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;
   float s = 0.f;
@@ -492,8 +494,7 @@ int launch_dense(DenseParams p, cudaStream_t st) {
   attrs[0] = attr;
   attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attrs[1].val.programmaticStreamSerializationAllowed = 1;
-  static const bool pdl = !(getenv("L2HMC_PDL") && std::string(getenv("L2HMC_PDL")) == "0");     // diagnostics
-  cfg.attrs = attrs, cfg.numAttrs = pdl ? 2 : 1;
+  cfg.attrs = attrs, cfg.numAttrs = pdl_enabled() ? 2 : 1;
   const cudaError_t e = cl ? cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, true>, p)
                            : cudaLaunchKernelEx(&cfg, dense_kernel<NG, CW, MODE, B_KC, false>, p);
   if (e != cudaSuccess) return check_launch("dense_kernel", 0);
@@ -580,7 +581,7 @@ int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream
   else rc = launch_dense<3, 2, kHeadsPosition, false>(p, st);
   if (rc) return rc;
   if (c->mode != L2HMC_NET_STQ && c->logdet) {
-    logdet_reduce_kernel<<<(N + 255) / 256, 256, 0, st>>>(ld_part, heads_col_tiles(D, N), N, c->logdet);
+    launch_pdl(logdet_reduce_kernel, dim3((N + 255) / 256), dim3(256), 0, st, ld_part, heads_col_tiles(D, N), N, c->logdet);
     rc = check_launch("logdet_reduce_kernel");
   }
   return rc;

@@ -145,6 +145,8 @@ template <int X, int I, bool FORCE, bool COS, bool QSUM, bool HAMIL>
 __global__ void __launch_bounds__(256) stencil_reg_kernel(const StencilParams p) {
   constexpr int SITES = 32 * I, D = 2 * SITES;
   constexpr unsigned kFull = 0xffffffffu;
+  pdl_wait();
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int warps = (blockDim.x >> 5) * gridDim.x;
   const int right = (lane & ~(X - 1)) | ((lane + 1) & (X - 1));
@@ -247,6 +249,8 @@ __global__ void __launch_bounds__(256) stencil_roll_kernel(const StencilParams p
   constexpr int SITES = 32 * I, D = 2 * SITES, PD = I < 8 ? I : 8;
   static_assert(I % PD == 0, "row count must be a multiple of the ring depth");
   constexpr unsigned kFull = 0xffffffffu;
+  pdl_wait();
+  pdl_trigger();
   const int lane = threadIdx.x & 31;
   const int warps = (blockDim.x >> 5) * gridDim.x;
   const int right = (lane & ~(X - 1)) | ((lane + 1) & (X - 1));
@@ -315,12 +319,12 @@ bool launch_reg(const StencilParams& p, int sms, cudaStream_t stream) {
   const bool q = p.q_float != nullptr || p.q_int != nullptr;
   const int blocks = min((p.N + 7) / 8, sms * 16);
   // the combinations the API can ask for: force [+ action]; action / plaq / Q observables; Hamiltonian
-  if (force && cosv && !q && !hamil) stencil_reg_kernel<X, I, true, true, false, false><<<blocks, 256, 0, stream>>>(p);
-  else if (force && !cosv && !q) stencil_reg_kernel<X, I, true, false, false, false><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && cosv && !q && !hamil) stencil_roll_kernel<X, I, true, false><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && cosv && q && !hamil) stencil_roll_kernel<X, I, true, true><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && !cosv && q) stencil_roll_kernel<X, I, false, true><<<blocks, 256, 0, stream>>>(p);
-  else if (!force && hamil && !q) stencil_reg_kernel<X, I, false, true, false, true><<<blocks, 256, 0, stream>>>(p);
+  if (force && cosv && !q && !hamil) launch_pdl(stencil_reg_kernel<X, I, true, true, false, false>, dim3(blocks), dim3(256), 0, stream, p);
+  else if (force && !cosv && !q) launch_pdl(stencil_reg_kernel<X, I, true, false, false, false>, dim3(blocks), dim3(256), 0, stream, p);
+  else if (!force && cosv && !q && !hamil) launch_pdl(stencil_roll_kernel<X, I, true, false>, dim3(blocks), dim3(256), 0, stream, p);
+  else if (!force && cosv && q && !hamil) launch_pdl(stencil_roll_kernel<X, I, true, true>, dim3(blocks), dim3(256), 0, stream, p);
+  else if (!force && !cosv && q) launch_pdl(stencil_roll_kernel<X, I, false, true>, dim3(blocks), dim3(256), 0, stream, p);
+  else if (!force && hamil && !q) launch_pdl(stencil_reg_kernel<X, I, false, true, false, true>, dim3(blocks), dim3(256), 0, stream, p);
   else return false;
   return true;
 }

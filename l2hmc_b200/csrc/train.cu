@@ -57,6 +57,8 @@ constexpr int kStages = 5;   // K slabs in flight: the training GEMMs at config 
 // A_KC / B_KC: the operand's K index is the contiguous one (only affects which threads read neighbouring words)
 template <bool A_KC, bool B_KC>
 __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ __align__(16) float As[kStages][GBK][GBM + 4];
   __shared__ __align__(16) float Bs[kStages][GBK][GBN + 4];
   const l2hmc_gemm_args& g = p.a;
@@ -199,6 +201,8 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
 
 // C[r][c] (=|+=) scale[c] * gate[r][c] * sum_z partial[z][r][c], z in fixed order (the epilogue of a split-K product)
 __global__ void splitk_reduce_kernel(const float* __restrict__ partial, int ksplit, const l2hmc_gemm_args g) {
+  pdl_wait();
+  pdl_trigger();
   const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   const size_t total = static_cast<size_t>(g.M) * g.N;
   if (idx >= total) return;
@@ -254,6 +258,8 @@ struct UpdFwdParams {
 // One CTA per chain: the arithmetic of update_math.cuh with per-chain direction / mask set.
 template <bool POSITION>
 __global__ void __launch_bounds__(kRowThreads) train_update_fwd_kernel(const UpdFwdParams p) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float scratch[kRowThreads / 32];
   const int row = blockIdx.x;
   const bool alt = p.row_set != nullptr && p.row_set[row] != 0;
@@ -320,6 +326,8 @@ __device__ __forceinline__ void heads_bwd(const l2hmc_update_bwd_args& a, int ro
 }
 
 __global__ void __launch_bounds__(kRowThreads) momentum_bwd_kernel(const UpdBwdParams pp) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float scratch[kRowThreads / 32];
   const l2hmc_update_bwd_args& a = pp.a;
   const int row = blockIdx.x;
@@ -369,6 +377,8 @@ __global__ void __launch_bounds__(kRowThreads) momentum_bwd_kernel(const UpdBwdP
 }
 
 __global__ void __launch_bounds__(kRowThreads) position_bwd_kernel(const UpdBwdParams pp) {
+  pdl_wait();
+  pdl_trigger();
   __shared__ float scratch[kRowThreads / 32];
   const l2hmc_update_bwd_args& a = pp.a;
   const int row = blockIdx.x;
@@ -450,6 +460,8 @@ __device__ __forceinline__ void site_adjoint(const float* c, int i, int T, int X
 }
 
 __global__ void __launch_bounds__(128) force_hvp_kernel(const HvpParams p, int warps_per_block) {
+  pdl_wait();
+  pdl_trigger();
   extern __shared__ __align__(16) float s_all[];
   const int T = p.T, X = p.X, SITES = T * X, D = 2 * SITES;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -867,7 +879,11 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   cudaLaunchAttribute attr{};
   attr.id = cudaLaunchAttributeClusterDimension;
   attr.val.clusterDim.x = 1, attr.val.clusterDim.y = 1, attr.val.clusterDim.z = cluster ? ksplit : 1;
-  cfg.attrs = &attr, cfg.numAttrs = 1;
+  cudaLaunchAttribute attrs[2];
+  attrs[0] = attr;
+  attrs[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attrs, cfg.numAttrs = l2hmc::pdl_enabled() ? 2 : 1;
   if (cudaLaunchKernelEx(&cfg, kern, p) != cudaSuccess) return check_launch("sgemm_kernel", 0);
   int rc = check_launch("sgemm_kernel");
   if (rc || ksplit == 1 || cluster) return rc;
@@ -876,7 +892,7 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
 
 int l2hmc::launch_splitk_reduce(const float* partial, int ksplit, const l2hmc_gemm_args* g, cudaStream_t stream) {
   const size_t total = static_cast<size_t>(g->M) * g->N;
-  splitk_reduce_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(partial, ksplit, *g);
+  launch_pdl(splitk_reduce_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, stream, partial, ksplit, *g);
   return check_launch("splitk_reduce_kernel");
 }
 
@@ -905,8 +921,8 @@ int l2hmc::train_update_fwd(int position, const float* x, const float* v, const 
                  nonfinite_flag, extra ? *extra : UpdExtra{}};
   if (extra && extra->masked) L2HMC_REQUIRE(extra->nmask && (!row_set || extra->nmask_alt), "train_update_fwd: next mask missing");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (position) train_update_fwd_kernel<true><<<N, kRowThreads, 0, st>>>(p);
-  else train_update_fwd_kernel<false><<<N, kRowThreads, 0, st>>>(p);
+  if (position) launch_pdl(train_update_fwd_kernel<true>, dim3(N), dim3(kRowThreads), 0, st, p);
+  else launch_pdl(train_update_fwd_kernel<false>, dim3(N), dim3(kRowThreads), 0, st, p);
   return check_launch("train_update_fwd_kernel");
 }
 
@@ -931,11 +947,11 @@ extern "C" int l2hmc_update_bwd(const l2hmc_update_bwd_args* a, void* stream) {
   UpdBwdParams p{*a};
   if (a->position) {
     L2HMC_REQUIRE(a->x && a->gx && a->mask && (!a->row_set || a->mask_alt), "l2hmc_update_bwd: position needs x, gx, masks");
-    position_bwd_kernel<<<a->N, kRowThreads, 0, st>>>(p);
+    launch_pdl(position_bwd_kernel, dim3(a->N), dim3(kRowThreads), 0, st, p);
     return check_launch("position_bwd_kernel");
   }
   L2HMC_REQUIRE(a->g && a->dg, "l2hmc_update_bwd: momentum needs g and dg");
-  momentum_bwd_kernel<<<a->N, kRowThreads, 0, st>>>(p);
+  launch_pdl(momentum_bwd_kernel, dim3(a->N), dim3(kRowThreads), 0, st, p);
   return check_launch("momentum_bwd_kernel");
 }
 
@@ -948,7 +964,7 @@ extern "C" int l2hmc_u1_force_hvp(const float* x, const float* w, float beta, in
   int rc = warp_per_chain_launch(force_hvp_kernel, sizeof(float) * 5u * T * X, N, "force_hvp_kernel", &grid, &warps, &smem);
   if (rc) return rc;
   HvpParams p{x, w, beta, N, T, X, out};
-  force_hvp_kernel<<<grid, warps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p, warps);
+  launch_pdl(force_hvp_kernel, dim3(grid), dim3(warps * 32), smem, static_cast<cudaStream_t>(stream), p, warps);
   return check_launch("force_hvp_kernel");
 }
 
