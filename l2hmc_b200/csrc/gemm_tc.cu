@@ -290,6 +290,19 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
                 for (int j = 0; j < 4; ++j)
                   if (n0 + j4 + j < p.cols) dst[j4 + j] = o[j];
               }
+              if (p.out_ts != nullptr && !split) {
+                // the same values as the A operand (TS32) of the product that consumes C next: K block n0 / 32 of its
+                // operand, columns past `cols` are this product's zero padding (o = 0 there)
+                const int kb = n0 >> 5;
+                if (kb < p.out_kb) {
+                  float h[4], l[4];
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) h[j] = tf32_hi(o[j]), l[j] = tf32_lo(o[j], h[j]);
+                  float* ts = p.out_ts + ((static_cast<size_t>(kb) * p.out_rg + (r >> 3)) * 2) * 256 + (r & 7) * 4 + (j4 >> 2) * 32;
+                  *reinterpret_cast<float4*>(ts) = make_float4(h[0], h[1], h[2], h[3]);
+                  *reinterpret_cast<float4*>(ts + 256) = make_float4(l[0], l[1], l[2], l[3]);
+                }
+              }
             }
           }
         }
@@ -806,6 +819,20 @@ extern "C" size_t l2hmc_tc_gemm_workspace_bytes(const l2hmc_gemm_args* g) {
 }
 
 extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t workspace_bytes, void* stream) {
+  return l2hmc::tc_gemm_chain(g, nullptr, nullptr, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+// Floats of the TS32 form of an [M, K] A operand (what tc_gemm_chain's a_ts / out_ts point to).
+size_t l2hmc::tc_gemm_ts_floats(int M, int K) {
+  return static_cast<size_t>((K + 31) / 32) * ((M + 127) / 128 * 128) * 64;
+}
+
+// l2hmc_tc_gemm for a CHAIN of products (the backward pass of the dense trunk: d z2 -> d z1 -> input gradients):
+// `out_ts` (nullable) also receives C in the tiled TF32 hi/lo form of an A operand [M, N], written by the epilogue;
+// `a_ts` (nullable, one K segment only) is segment 0's A already in that form -- the product that made it saved this
+// one an operand-conversion pass over A.  out_ts needs an unsplit product (every per-call product is).
+int l2hmc::tc_gemm_chain(const l2hmc_gemm_args* g, const float* a_ts_in, float* out_ts, void* workspace,
+                         size_t workspace_bytes, cudaStream_t st) {
   L2HMC_REQUIRE(g, "l2hmc_tc_gemm: null arguments");
   L2HMC_REQUIRE(g->M >= 0 && g->N >= 0 && g->nseg >= 1 && g->nseg <= 3, "l2hmc_tc_gemm: bad sizes M=%d N=%d nseg=%d", g->M,
                 g->N, g->nseg);
@@ -817,8 +844,9 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
   L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_tc_gemm_workspace_bytes(g) && aligned16(workspace),
                 "l2hmc_tc_gemm: workspace too small or misaligned (%zu < %zu bytes)", workspace_bytes,
                 l2hmc_tc_gemm_workspace_bytes(g));
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
   const TcGemmDims d = tc_gemm_dims(g);
+  L2HMC_REQUIRE(a_ts_in == nullptr || g->nseg == 1, "tc_gemm_chain: a pre-tiled A operand needs a single K segment");
+  L2HMC_REQUIRE(out_ts == nullptr || d.ksplit == 1, "tc_gemm_chain: the tiled output needs an unsplit product");
   float* a_ts = static_cast<float*>(workspace);
   float* b_ts = a_ts + d.a_floats;
   int kb0 = 0, njobs = 0, gx = 1;
@@ -827,8 +855,10 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
     const l2hmc_gemm_seg& sg = g->seg[s];
     const int nkb = (sg.K + 31) / 32;
     if (nkb == 0) continue;
-    jobs.j[njobs++] = Ts32Job{sg.A, sg.a_rs, sg.a_cs, g->M, sg.K, a_ts, d.rows_p / 8, kb0, nkb};
-    gx = std::max(gx, ew_grid(static_cast<size_t>(nkb) * (d.rows_p / 8) * 64));
+    if (a_ts_in == nullptr) {
+      jobs.j[njobs++] = Ts32Job{sg.A, sg.a_rs, sg.a_cs, g->M, sg.K, a_ts, d.rows_p / 8, kb0, nkb};
+      gx = std::max(gx, ew_grid(static_cast<size_t>(nkb) * (d.rows_p / 8) * 64));
+    }
     // B operand rows are the output columns: element (n, k) = B[k * b_rs + n * b_cs]
     jobs.j[njobs++] = Ts32Job{sg.B, sg.b_cs, sg.b_rs, g->N, sg.K, b_ts, d.n_p / 8, kb0, nkb};
     gx = std::max(gx, ew_grid(static_cast<size_t>(nkb) * (d.n_p / 8) * 64));
@@ -845,7 +875,8 @@ extern "C" int l2hmc_tc_gemm(const l2hmc_gemm_args* g, void* workspace, size_t w
     return L2HMC_ERR_INVALID;
   }
   TcParams p{};
-  p.A = a_ts, p.a_rg = d.rows_p / 8, p.B = b_ts, p.b_rg = d.n_p / 8, p.KB = d.kb;
+  p.A = a_ts_in ? a_ts_in : a_ts, p.a_rg = d.rows_p / 8, p.B = b_ts, p.b_rg = d.n_p / 8, p.KB = d.kb;
+  p.out_ts = out_ts, p.out_rg = d.rows_p / 8, p.out_kb = (g->N + 31) / 32;
   p.m_tiles = d.rows_p / 128;
   p.rows = g->M, p.cols = g->N;
   p.C = g->C, p.ldc = g->ldc, p.accumulate = g->accumulate, p.gate = g->relu_gate, p.ldg = g->ldg;
@@ -870,6 +901,11 @@ static bool gemm_wants_tc(const l2hmc_gemm_args* g) {
   if (k < 128) return false;
   static const double min_mnk = getenv("L2HMC_TC_MIN_MNK") ? atof(getenv("L2HMC_TC_MIN_MNK")) : 2.5e8;   // diagnostics
   return static_cast<double>(g->M) * g->N * static_cast<double>(k) >= min_mnk;
+}
+
+// this product runs on tcgen05 under l2hmc_gemm's dispatch and is not split over K: it can be a link of tc_gemm_chain
+bool l2hmc::tc_gemm_chainable(const l2hmc_gemm_args* g) {
+  return g && g->M > 0 && g->N > 0 && g->nseg >= 1 && g->nseg <= 3 && gemm_wants_tc(g) && tc_gemm_dims(g).ksplit == 1;
 }
 
 extern "C" size_t l2hmc_gemm_workspace_bytes(const l2hmc_gemm_args* g, int ksplit) {

@@ -23,6 +23,11 @@ bool tc_supported(const l2hmc_net_weights* w, const l2hmc_net_call* c);
 int net_run_tc(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
 int net_run_simt(const l2hmc_net_weights* w, const l2hmc_net_call* c, cudaStream_t st);
 int heads_col_tiles(int D, int N);
+// chained tcgen05 products (gemm_tc.cu): see tc_gemm_chain
+bool tc_gemm_chainable(const l2hmc_gemm_args* g);
+size_t tc_gemm_ts_floats(int M, int K);
+int tc_gemm_chain(const l2hmc_gemm_args* g, const float* a_ts, float* out_ts, void* workspace, size_t workspace_bytes,
+                  cudaStream_t st);
 bool dense_grad_nt_ok(const l2hmc_gemm_args* g);
 int dense_grad_nt(const l2hmc_gemm_args* g, cudaStream_t st);
 

@@ -11,10 +11,12 @@
 // gradients; weight gradients are deferred split-K GEMMs over the whole tape (see train.cu).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <initializer_list>
 #include <vector>
 
 #include "common.cuh"
+#include "nets.cuh"
 
 namespace l2hmc {
 namespace {
@@ -93,6 +95,9 @@ struct Plan {
   size_t tape_elems;
   void* gemm_ws;
   size_t gemm_ws_bytes;
+  // chained tcgen05 backward products (tc_gemm_chain): d z2 and d z1 of the current call in the tiled TF32 form
+  bool chain;
+  float *dz2_ts, *dz1_ts;
   size_t total;
 };
 
@@ -162,6 +167,22 @@ Plan make_plan(const l2hmc_train_args* a, void* base) {
     }
     pl.gemm_ws_bytes = gw;
     pl.gemm_ws = c.take<char>(gw);
+    // the per-call backward products d z2 = dA . Wheads^T, d z1 = d z2 . Wh^T, d in = d z1 . Win^T run on tcgen05 for
+    // both networks: each hands its result to the next already tiled (no operand-conversion pass over d z2 / d z1)
+    static const bool chain_on = !(getenv("L2HMC_TC_CHAIN") && getenv("L2HMC_TC_CHAIN")[0] == '0');   // diagnostics
+    pl.chain = chain_on;
+    size_t ts = 0;
+    for (const l2hmc_net_weights* w : {a->xnet, a->vnet}) {
+      auto tc = [&](int Mm, int Nn, int nseg, int Kk) {
+        l2hmc_gemm_args g{};
+        g.M = Mm, g.N = Nn, g.nseg = nseg;
+        for (int s = 0; s < nseg; ++s) g.seg[s].K = Kk;
+        return tc_gemm_chainable(&g);
+      };
+      pl.chain = pl.chain && tc(pl.R, w->H, 3, w->D) && tc(pl.R, w->H, 1, w->H) && tc(pl.R, w->K, 1, w->H);
+      ts = std::max(ts, tc_gemm_ts_floats(pl.R, w->H));
+    }
+    if (pl.chain) pl.dz2_ts = c.take<float>(ts), pl.dz1_ts = c.take<float>(ts);
     if (pl.conv) {
       pl.fg0 = c.take<float>(R * a->xnet->K), pl.fg1 = c.take<float>(R * a->xnet->K);
       pl.prow = l2hmc_conv3d_bwd_rows(pl.R), pl.pcol = l2hmc_conv3d_bwd_cols(a->xconv_in0->F);
@@ -194,7 +215,8 @@ struct Ctx {
 };
 
 int gemm(const Ctx& c, int M, int N, std::initializer_list<l2hmc_gemm_seg> segs, float* C, long long ldc, int accumulate,
-         const float* gate, long long ldg, const float* cs, int inv, const float* cs_alt, int inv_alt, bool sets, int ksplit) {
+         const float* gate, long long ldg, const float* cs, int inv, const float* cs_alt, int inv_alt, bool sets, int ksplit,
+         const float* a_ts = nullptr, float* out_ts = nullptr) {
   l2hmc_gemm_args g{};
   g.M = M, g.N = N, g.nseg = static_cast<int>(segs.size());
   int i = 0;
@@ -202,11 +224,14 @@ int gemm(const Ctx& c, int M, int N, std::initializer_list<l2hmc_gemm_seg> segs,
   g.C = C, g.ldc = ldc, g.accumulate = accumulate, g.relu_gate = gate, g.ldg = ldg;
   g.col_scale = cs, g.col_scale_invert = inv;
   g.row_set = sets ? c.pl.row_set : nullptr, g.col_scale_alt = cs_alt, g.col_scale_invert_alt = inv_alt;
+  if (a_ts != nullptr || out_ts != nullptr)       // a link of a tcgen05 chain (Plan::chain)
+    return tc_gemm_chain(&g, a_ts, out_ts, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.st);
   return l2hmc_gemm(&g, ksplit, c.pl.gemm_ws, c.pl.gemm_ws_bytes, c.stream);
 }
 
-int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long ldc, int accumulate = 0, int ksplit = 0) {
-  return gemm(c, M, N, {s}, C, ldc, accumulate, nullptr, 0, nullptr, 0, nullptr, 0, false, ksplit);
+int plain_gemm(const Ctx& c, int M, int N, l2hmc_gemm_seg s, float* C, long long ldc, int accumulate = 0, int ksplit = 0,
+               const float* a_ts = nullptr) {
+  return gemm(c, M, N, {s}, C, ldc, accumulate, nullptr, 0, nullptr, 0, nullptr, 0, false, ksplit, a_ts);
 }
 
 int col_sum(const Ctx& c, const float* B, long long ld, int rows, int cols, float* out) {
@@ -239,9 +264,11 @@ int net_backward(const Ctx& c, const l2hmc_net_weights* w, NetTape& t, int j) {
   L2HMC_TRY(gemm(c, c.pl.R, H,
                  {l2hmc_gemm_seg{dA, 3LL * D, 1, w->w_s, 1, D, D}, l2hmc_gemm_seg{dA + D, 3LL * D, 1, w->w_tr, 1, D, D},
                   l2hmc_gemm_seg{dA + 2 * D, 3LL * D, 1, w->w_q, 1, D, D}},
-                 t.dz2 + off * H, H, 0, t.h2 + off * H, H, nullptr, 0, nullptr, 0, false, 0));
+                 t.dz2 + off * H, H, 0, t.h2 + off * H, H, nullptr, 0, nullptr, 0, false, 0, nullptr,
+                 c.pl.chain ? c.pl.dz2_ts : nullptr));
   return gemm(c, c.pl.R, H, {l2hmc_gemm_seg{t.dz2 + off * H, H, 1, w->w_h, 1, H, H}}, t.dz1 + off * H, H, 0,
-              t.h1 + off * H, H, nullptr, 0, nullptr, 0, false, 0);
+              t.h1 + off * H, H, nullptr, 0, nullptr, 0, false, 0, c.pl.chain ? c.pl.dz2_ts : nullptr,
+              c.pl.chain ? c.pl.dz1_ts : nullptr);
 }
 
 int weight_grads(const Ctx& c, const NetTape& t, const l2hmc_net_grads* g) {
@@ -502,16 +529,17 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
         L2HMC_TRY(net_backward(c, w, *t, rec.j));
         const int H = t->H, K = t->K;
         const float* dz1 = t->dz1 + off * H;
+        const float* dz1_ts = pl.chain ? pl.dz1_ts : nullptr;
         if (conv) {
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K));
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K, 0, 0, dz1_ts));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K, 0, 0, dz1_ts));
           L2HMC_TRY(conv_bwd(c, a->vconv_in0, Xs(rec.xi), pl.fg0, pl.gx, pl.part[3], nullptr, 0, nullptr, 0,
                              conv_tape(c, 1, 0, rec.j)));
           L2HMC_TRY(conv_bwd(c, a->vconv_in1, rec.g, pl.fg1, pl.dg, pl.part[2], nullptr, 0, nullptr, 0,
                              conv_tape(c, 1, 1, rec.j)));
         } else {
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gx, D, 1));
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.dg, D, 1));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gx, D, 1, 0, dz1_ts));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.dg, D, 1, 0, dz1_ts));
         }
       }
       L2HMC_TRY(l2hmc_u1_force_hvp(Xs(rec.xi), pl.dg, beta, R, T, X, pl.gx, stream));
@@ -523,17 +551,18 @@ extern "C" int l2hmc_u1_train_grads(const l2hmc_train_args* a, void* stream) {
         L2HMC_TRY(net_backward(c, w, *t, rec.j));
         const int H = t->H, K = t->K;
         const float* dz1 = t->dz1 + off * H;
+        const float* dz1_ts = pl.chain ? pl.dz1_ts : nullptr;
         if (conv) {
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K));
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.fg0, K, 0, 0, dz1_ts));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}, pl.fg1, K, 0, 0, dz1_ts));
           L2HMC_TRY(conv_bwd(c, a->xconv_in0, Vs(rec.vi), pl.fg0, pl.gv, pl.part[1], nullptr, 0, nullptr, 0,
                              conv_tape(c, 0, 0, rec.j)));
           L2HMC_TRY(conv_bwd(c, a->xconv_in1, Xs(rec.xi), pl.fg1, pl.gx, pl.part[0], row_f, rec.inv, row_b, rec.inv_alt,
                              conv_tape(c, 0, 1, rec.j)));
         } else {
-          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gv, D, 1));
+          L2HMC_TRY(plain_gemm(c, R, K, l2hmc_gemm_seg{dz1, H, 1, w->w_in0, 1, H, H}, pl.gv, D, 1, 0, dz1_ts));
           L2HMC_TRY(gemm(c, R, K, {l2hmc_gemm_seg{dz1, H, 1, w->w_in1, 1, H, H}}, pl.gx, D, 1, nullptr, 0, row_f, rec.inv,
-                         row_b, rec.inv_alt, true, 0));
+                         row_b, rec.inv_alt, true, 0, dz1_ts));
         }
       }
     }
