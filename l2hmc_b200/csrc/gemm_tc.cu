@@ -237,6 +237,33 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
       for (int g = 0; g < NG; ++g)
 #pragma unroll
         for (int j = 0; j < 32; ++j) sum[g][j] = 0.f;
+      // plain epilogue: the ReLU gate of this thread's row and columns as one bit per column, fetched NOW -- while the
+      // MMAs of the tile run -- instead of after the accumulator arrives
+      uint32_t gate_bits[NG];
+#pragma unroll
+      for (int g = 0; g < NG; ++g) gate_bits[g] = 0xffffffffu;
+      if (MODE == kTcPlain && p.gate != nullptr && !split && r < p.rows) {
+#pragma unroll
+        for (int g = 0; g < NG; ++g) {
+          const int n0 = n_blk * BN + half * (BN / 2) + g * 32;
+          const float* gt = p.gate + static_cast<long long>(r) * p.ldg + n0;
+          uint32_t bits = 0;
+          if (n0 + 31 < p.cols && ((reinterpret_cast<uintptr_t>(gt) & 15u) == 0)) {
+#pragma unroll
+            for (int j4 = 0; j4 < 32; j4 += 4) {
+              const float4 t = *reinterpret_cast<const float4*>(gt + j4);
+              bits |= (t.x > 0.f ? 1u : 0u) << j4;
+              bits |= (t.y > 0.f ? 1u : 0u) << (j4 + 1);
+              bits |= (t.z > 0.f ? 1u : 0u) << (j4 + 2);
+              bits |= (t.w > 0.f ? 1u : 0u) << (j4 + 3);
+            }
+          } else {
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.cols && gt[j] > 0.f) bits |= 1u << j;
+          }
+          gate_bits[g] = bits;
+        }
+      }
       for (int chunk = 0; chunk < num_chunks; ++chunk) {
         mbar_wait(&tmem_full[acc], acc_phase);
         tc_fence_after();
@@ -268,7 +295,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
           for (int g = 0; g < NG; ++g) {
             const int n0 = n_blk * BN + half * (BN / 2) + g * 32;
             float* dst = crow + n0;
-            const float* gt = (p.gate && !split) ? p.gate + static_cast<long long>(r) * p.ldg + n0 : nullptr;
 #pragma unroll
             for (int j4 = 0; j4 < 32; j4 += 4) {
               float o[4];
@@ -277,7 +303,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
                 const int n = n0 + j4 + j;
                 float val = sum[g][j4 + j];
                 if (n < p.cols) {
-                  if (gt != nullptr && !(gt[j4 + j] > 0.f)) val = 0.f;
+                  if (!((gate_bits[g] >> (j4 + j)) & 1u)) val = 0.f;
                   if (cs != nullptr) val = __fmul_rn(val, cinv ? __fsub_rn(1.f, cs[n]) : cs[n]);
                   if (accumulate) val = __fadd_rn(dst[j4 + j], val);
                 }
