@@ -60,6 +60,12 @@ def main():
                          ksplit=ks))
         out[f"gx += dz1 . Win^T  256x128x512 ksplit={ks}"] = graph_time(
             lambda: gemm(R, K, [(_ptr(dz1), H, 1, _ptr(win), 1, H, H)], _ptr(gx), D, accumulate=True, ksplit=ks))
+    # small weight gradients over the whole tape: h2^T [512 x 2560] . dA [2560 x 128] (row-major operands, TN form)
+    Rt = 2560
+    h2t, dAt, gw = rnd(Rt, H), rnd(Rt, 3 * D), rnd(H, D)
+    for ks in (0, 8, 37):
+        out[f"dW = h2^T . dA  512x128x2560 ksplit={ks}"] = graph_time(
+            lambda: gemm(H, D, [(_ptr(h2t), 1, H, _ptr(dAt), 3 * D, 1, Rt)], _ptr(gw), D, ksplit=ks))
     # forward net call on the FFMA path (3 dense kernels) and the fused position update
     lat = pkg.GaugeLattice(8, 8, 2, "U1", num_samples=R)
     np.random.seed(0)

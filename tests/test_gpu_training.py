@@ -45,7 +45,10 @@ def close_scaled(got, want, tol=2e-4, what=""):
                                          # both operands K-contiguous: the chunked dense kernel (clustered K chunks for
                                          # few tiles, one CTA walking the chunks for many), ragged in every dimension
                                          (130, 70, 100, False, True), (70, 33, 1030, False, True),
-                                         (9700, 200, 300, False, True), (5, 7, 3, False, True)])
+                                         (9700, 200, 300, False, True), (5, 7, 3, False, True),
+                                         # A^T . B with both operands row-major (small weight gradients over a long K)
+                                         (512, 128, 2560, True, False), (130, 70, 1000, True, False),
+                                         (9, 33, 5000, True, False)])
 def test_sgemm_forms(M, N, K, ta, tb):
     from l2hmc_b200 import _lib
     from l2hmc_b200.training import _Gemm, _ptr
