@@ -677,8 +677,9 @@ def run_training(c):
                  "params": int(eng.params.size), "train_step_ms": ms,
                  "link_updates_per_s": world * N * D_ * M_ / (ms * 1e-3),
                  "note": "x- and z-chain forward with tape + backward + Adam + observables; the x-chain's advance is "
-                         "counted once; fp32: tcgen05 3xTF32 layers / backward products from 1024 stacked rows, FFMA "
-                         "(cp.async multi-stage, split-K) below"}
+                         "counted once; fp32: tcgen05 3xTF32 layers / backward products from 1024 stacked rows, chunked "
+                         "FFMA kernel (K chunks over a thread-block cluster) below; dependent kernels launched as "
+                         "programmatic dependents"}
         if tag.startswith("config2") and not c.no_cpu:
             from oracle import train_oracle as tro
             from oracle import u1_oracle as orc
