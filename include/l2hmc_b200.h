@@ -421,6 +421,17 @@ typedef struct {
 
 int l2hmc_mog_mc_step(const l2hmc_gmm* gmm, const l2hmc_mog_args* args, void* stream);
 
+/* Value of the MoG training loss, mog_model.py:324-355 (GaussianMixtureModel._create_loss):
+ *   v1 = |x - Lx|^2 * px + 1e-4,  v2 = |z - Lz|^2 * pz + 1e-4      (squared jump distances, per chain)
+ *   loss = scale * (mean 1/v1 + mean 1/v2) + (-mean v1 - mean v2) / scale
+ * with (Lx, px) = propose(x) and (Lz, pz) = propose(z ~ N(0,1)) from l2hmc_mog_mc_step.  x, Lx, z, Lz [N,k]; px, pz
+ * [N]; v1, v2 [N] nullable outputs; loss [1].  Two launches, fixed summation order (deterministic).  The VALUE only:
+ * the reference's MoG driver cannot run as shipped (mog_model.py:51) and SURVEY 8(f) does not ask for its gradient. */
+size_t l2hmc_mog_loss_workspace_bytes(void);
+int l2hmc_mog_loss(const float* x, const float* Lx, const float* px, const float* z, const float* Lz, const float* pz,
+                   long long N, int k, float scale, float* v1, float* v2, float* loss, void* workspace,
+                   size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------ loss value, run statistics
  * Training loss VALUE of gauge_model.py:728-803 (_calc_loss) given the two chains' transitions
  * (x --dynamics--> x_prop, px, x_out;  z ~ N(0,1) --dynamics--> pz): per chain

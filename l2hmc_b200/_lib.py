@@ -213,6 +213,9 @@ SIGNATURES = {
     "l2hmc_tc_selftest": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_gmm_energy_force": [POINTER(Gmm), c_void_p, c_float, c_int, c_void_p, c_void_p, c_void_p],
     "l2hmc_mog_mc_step": [POINTER(Gmm), POINTER(MogArgs), c_void_p],
+    "l2hmc_mog_loss_workspace_bytes": [],
+    "l2hmc_mog_loss": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_longlong, c_int, c_float,
+                       c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     "l2hmc_u1_l2hmc_mc_workspace_bytes": [POINTER(L2hmcMcArgs)],
     "l2hmc_u1_l2hmc_mc_step": [POINTER(L2hmcMcArgs), c_void_p],
     "l2hmc_u1_loss": [POINTER(LossParams), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
@@ -258,7 +261,7 @@ SIGNATURES = {
                                    c_int, c_int, c_int, c_void_p, c_void_p],
 }
 
-RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_launch_count": ctypes.c_ulonglong, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t,
+RESTYPES = {"l2hmc_last_error": c_char_p, "l2hmc_launch_count": ctypes.c_ulonglong, "l2hmc_net_workspace_bytes": c_size_t, "l2hmc_net_pack_bytes": c_size_t, "l2hmc_mog_loss_workspace_bytes": c_size_t,
             "l2hmc_tc_selftest_bytes": c_size_t, "l2hmc_u1_l2hmc_mc_workspace_bytes": c_size_t, "l2hmc_sgemm_workspace_bytes": c_size_t, "l2hmc_u1_train_workspace_bytes": c_size_t,
             "l2hmc_tc_gemm_workspace_bytes": c_size_t, "l2hmc_gemm_workspace_bytes": c_size_t, "l2hmc_col_sum_workspace_bytes": c_size_t}
 

@@ -457,3 +457,75 @@ extern "C" int l2hmc_mog_mc_step(const l2hmc_gmm* gmm, const l2hmc_mog_args* a, 
   if (p.k <= 4) return launch_mog_h<4>(p, st);
   return launch_mog_h<8>(p, st);
 }
+
+// ------------------------------------------------------------------ MoG training loss (value)
+namespace l2hmc {
+namespace {
+constexpr int kLossBlocks = 1024;
+// stage 1: per block, in fixed order, the four sums  sum 1/v1, sum 1/v2, sum v1, sum v2  with
+// v1 = |x - Lx|^2 * px + 1e-4,  v2 = |z - Lz|^2 * pz + 1e-4  (mog_model.py:344-347); v1, v2 optionally stored
+__global__ void __launch_bounds__(256) mog_loss_stage1_kernel(const float* __restrict__ x, const float* __restrict__ Lx,
+                                                              const float* __restrict__ px, const float* __restrict__ z,
+                                                              const float* __restrict__ Lz, const float* __restrict__ pz,
+                                                              long long N, int k, float* v1_out, float* v2_out,
+                                                              float* partial /* [gridDim.x][4] */) {
+  __shared__ float sm[4][8];
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long n = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x; n < N; n += static_cast<long long>(gridDim.x) * 256) {
+    float d1 = 0.f, d2 = 0.f;
+    for (int j = 0; j < k; ++j) {
+      const float a = __fsub_rn(x[n * k + j], Lx[n * k + j]), b = __fsub_rn(z[n * k + j], Lz[n * k + j]);
+      d1 = __fadd_rn(d1, __fmul_rn(a, a));
+      d2 = __fadd_rn(d2, __fmul_rn(b, b));
+    }
+    const float v1 = __fadd_rn(__fmul_rn(d1, px[n]), 1e-4f), v2 = __fadd_rn(__fmul_rn(d2, pz[n]), 1e-4f);
+    if (v1_out) v1_out[n] = v1;
+    if (v2_out) v2_out[n] = v2;
+    acc[0] += __fdiv_rn(1.f, v1), acc[1] += __fdiv_rn(1.f, v2), acc[2] += v1, acc[3] += v2;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+    if (lane == 0) sm[q][warp] = acc[q];
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sm[threadIdx.x][w];
+    partial[blockIdx.x * 4 + threadIdx.x] = t;
+  }
+}
+// stage 2: blocks in fixed order (double accumulation of <= 1024 partials), then
+// loss = scale * (mean 1/v1 + mean 1/v2) + (-mean v1 - mean v2) / scale   (mog_model.py:350-355)
+__global__ void mog_loss_stage2_kernel(const float* __restrict__ partial, int nb, long long N, float scale, float* loss) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double t[4] = {0., 0., 0., 0.};
+  for (int b = 0; b < nb; ++b)
+    for (int q = 0; q < 4; ++q) t[q] += static_cast<double>(partial[b * 4 + q]);
+  const float m[4] = {static_cast<float>(t[0] / N), static_cast<float>(t[1] / N), static_cast<float>(t[2] / N),
+                      static_cast<float>(t[3] / N)};
+  float l = __fmul_rn(scale, __fadd_rn(m[0], m[1]));
+  l = __fadd_rn(l, __fdiv_rn(__fsub_rn(-m[2], m[3]), scale));
+  loss[0] = l;
+}
+}  // namespace
+}  // namespace l2hmc
+
+extern "C" size_t l2hmc_mog_loss_workspace_bytes(void) { return sizeof(float) * 4 * l2hmc::kLossBlocks; }
+
+extern "C" int l2hmc_mog_loss(const float* x, const float* Lx, const float* px, const float* z, const float* Lz,
+                              const float* pz, long long N, int k, float scale, float* v1, float* v2, float* loss,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  L2HMC_REQUIRE(x && Lx && px && z && Lz && pz && loss, "l2hmc_mog_loss: null pointer");
+  L2HMC_REQUIRE(N > 0 && k >= 1 && scale != 0.f, "l2hmc_mog_loss: bad sizes N=%lld k=%d scale=%g", N, k, static_cast<double>(scale));
+  L2HMC_REQUIRE(workspace && workspace_bytes >= l2hmc_mog_loss_workspace_bytes(), "l2hmc_mog_loss: workspace too small");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = static_cast<int>(std::min<long long>(kLossBlocks, (N + 255) / 256));
+  float* partial = static_cast<float*>(workspace);
+  mog_loss_stage1_kernel<<<nb, 256, 0, st>>>(x, Lx, px, z, Lz, pz, N, k, v1, v2, partial);
+  mog_loss_stage2_kernel<<<1, 32, 0, st>>>(partial, nb, N, scale, loss);
+  return check_launch("mog_loss_kernel", 2);
+}

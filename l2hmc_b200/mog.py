@@ -250,3 +250,28 @@ def tunneling_rate(modes):
     indices (utils/trajectories.py:63-95 applied per chain)."""
     modes = torch.as_tensor(modes)
     return (modes[1:] != modes[:-1]).float().sum(dim=0) / (modes.shape[0] - 1)
+
+
+def loss(x, dynamics, scale=0.1, z=None, draws_x=None, draws_z=None):
+    """Value of GaussianMixtureModel's training loss (mog_model.py:324-355): Lx, px = propose(x, do_mh_step=True) and
+    Lz, pz = propose(z) with z ~ N(0, 1) (drawn here with torch when not given; the reference uses tf.random_normal),
+    then  loss = scale (mean 1/v1 + mean 1/v2) - (mean v1 + mean v2) / scale  with v = |jump|^2 p + 1e-4.
+    draws_x / draws_z: optional dicts of injected draws for the two propose calls (v_f, v_b, dir_mask, u_acc).
+    Returns (loss [1] CUDA tensor, dict(Lx, px, Lz, pz, x_out, v1, v2, z)).  The value only -- no gradient."""
+    x = to_device(x, dynamics.device).reshape(-1, dynamics.x_dim).contiguous()
+    N, k = x.shape
+    if z is None:
+        z = torch.randn(N, k, dtype=torch.float32, device=x.device)
+    z = to_device(z, dynamics.device).reshape(N, k).contiguous()
+    ox = dynamics.mc_step(x, **(draws_x or {}))
+    oz = dynamics.mc_step(z, **(draws_z or {}))
+    lib = _lib.get_lib()
+    need = int(lib.l2hmc_mog_loss_workspace_bytes())
+    ws = torch.empty((need + 3) // 4, dtype=torch.float32, device=x.device)
+    v1, v2 = torch.empty(N, dtype=torch.float32, device=x.device), torch.empty(N, dtype=torch.float32, device=x.device)
+    out = torch.empty(1, dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.l2hmc_mog_loss(_lib.dptr(x), _lib.dptr(ox["Lx"]), _lib.dptr(ox["px"]), _lib.dptr(z), _lib.dptr(oz["Lx"]),
+                                      _lib.dptr(oz["px"]), N, k, float(scale), _lib.dptr(v1), _lib.dptr(v2), _lib.dptr(out),
+                                      _lib.dptr(ws), need, _lib.stream_ptr()))
+    return out, dict(Lx=ox["Lx"], px=ox["px"], Lz=oz["Lx"], pz=oz["px"], x_out=ox["x_out"], v1=v1, v2=v2, z=z)

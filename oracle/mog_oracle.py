@@ -239,3 +239,13 @@ def calc_tunneling_rate(trajectory, means, num_distributions):
     d = np.linalg.norm(tr[:, :, None, :] - means[None, None, :, :], axis=-1)
     idx = d.argmin(axis=2)                               # (steps, N)
     return (idx[1:] != idx[:-1]).sum(axis=0) / (tr.shape[0] - 1)
+
+
+def mog_loss(x, Lx, px, z, Lz, pz, scale):
+    """mog_model.py:344-355: v = |jump|^2 * p + 1e-4 per chain; loss = scale (mean 1/v1 + mean 1/v2) - (mean v1 +
+    mean v2) / scale.  float64 numpy; returns (loss, v1, v2)."""
+    f = lambda a: np.asarray(a, np.float64)
+    v1 = ((f(x) - f(Lx)) ** 2).sum(axis=1) * f(px) + 1e-4
+    v2 = ((f(z) - f(Lz)) ** 2).sum(axis=1) * f(pz) + 1e-4
+    loss = scale * ((1.0 / v1).mean() + (1.0 / v2).mean()) + (-v1.mean() - v2.mean()) / scale
+    return loss, v1, v2

@@ -124,3 +124,29 @@ def test_mog_argument_errors():
     assert lib.l2hmc_mog_mc_step(None, None, None) == _lib.L2HMC_ERR_INVALID
     e, f = gmm.energy_force(np.zeros((0, 2), np.float32))
     assert e.shape == (0,) and f.shape == (0, 2)
+
+
+@pytest.mark.parametrize("N,k,scale", [(1000, 2, 0.1), (37, 4, 1.0), (300000, 2, 0.1)])
+def test_mog_loss_value_against_oracle(N, k, scale):
+    """mog_model.py:324-355 (loss VALUE): the CUDA two-stage sum against the float64 restatement on the SAME propose
+    outputs, and its run-to-run bits."""
+    from l2hmc_b200 import mog
+    from oracle import mog_oracle as mo
+    rng = np.random.default_rng(N)
+    mus = rng.standard_normal((3, k))
+    gmm = mog.GMM(mus, [0.1 * np.eye(k)] * 3, [0.3, 0.3, 0.4])
+    np.random.seed(7)
+    dyn = mog.Dynamics(k, gmm.get_energy_function(), trajectory_length=2, eps=0.1, seed=11)
+    x = (mus[rng.integers(0, 3, N)] + 0.3 * rng.standard_normal((N, k))).astype(np.float32)
+    z = rng.standard_normal((N, k)).astype(np.float32)
+    dyn._mc_step = 0
+    loss, o = mog.loss(x, dyn, scale=scale, z=z)
+    ref, v1, v2 = mo.mog_loss(x, o["Lx"].cpu().numpy(), o["px"].cpu().numpy(), z, o["Lz"].cpu().numpy(),
+                              o["pz"].cpu().numpy(), scale)
+    np.testing.assert_allclose(o["v1"].cpu().numpy(), v1, rtol=2e-6, atol=1e-10)
+    np.testing.assert_allclose(o["v2"].cpu().numpy(), v2, rtol=2e-6, atol=1e-10)
+    assert abs(float(loss) - ref) <= 1e-5 * abs(ref), (float(loss), ref)        # north-star fp32 tolerance
+    dyn._mc_step = 0
+    loss2, _ = mog.loss(x, dyn, scale=scale, z=z)
+    assert torch.equal(loss, loss2)
+    assert int(dyn._flag.item()) == 0

@@ -336,3 +336,15 @@ def test_loss_gradients_against_reference_goldens(golden):
             ref = g[f"{tag}.grad.{nm}"]
             scale = max(float(np.abs(ref).max()), 1e-12)
             np.testing.assert_allclose(grads[nm].numpy(), ref, rtol=2e-2, atol=2e-3 * scale, err_msg=f"{tag} {nm}")
+
+
+def test_mog_loss_restatement():
+    """mog_model.py:344-355 on hand-computable numbers."""
+    from oracle import mog_oracle as mo
+    x = np.array([[0., 0.], [1., 1.]]); Lx = np.array([[1., 0.], [1., 3.]]); px = np.array([0.5, 1.0])
+    z = np.array([[0., 0.], [0., 0.]]); Lz = np.array([[0., 2.], [0., 0.]]); pz = np.array([1.0, 0.3])
+    loss, v1, v2 = mo.mog_loss(x, Lx, px, z, Lz, pz, 0.1)
+    np.testing.assert_allclose(v1, [0.5 + 1e-4, 4.0 + 1e-4])
+    np.testing.assert_allclose(v2, [4.0 + 1e-4, 1e-4])
+    want = 0.1 * (np.mean(1 / v1) + np.mean(1 / v2)) - (np.mean(v1) + np.mean(v2)) / 0.1
+    assert abs(loss - want) < 1e-12
