@@ -372,17 +372,34 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
         const bool rok = r < p.rows;
         const float heps = __fmul_rn(0.5f, p.eps);
         const int dir = alt ? p.dir_alt : p.dir;
-        const float* umask = alt ? p.umask_alt : p.umask;
-        const int uinvert = alt ? p.uinvert_alt : p.uinvert;
         float ld = 0.f;
         bool bad = false;
+        // per-output constants of this thread's 32 outputs: lane l fetches those of output d = 64 n_blk + 32 half + l
+        // once (two expf per thread instead of two per element); the loop below reads them by shuffle
+        const int dl = n_blk * 64 + half * 32 + lane;
+        const bool dl_ok = dl < p.cols;
+        const float bs_l = dl_ok ? __ldg(p.b_s + dl) : 0.f, bt_l = dl_ok ? __ldg(p.b_tr + dl) : 0.f;
+        const float bq_l = dl_ok ? __ldg(p.b_q + dl) : 0.f;
+        const float es_l = dl_ok ? expf(__ldg(p.coeff_s + dl)) : 1.f, eq_l = dl_ok ? expf(__ldg(p.coeff_q + dl)) : 1.f;
+        float m0_l = 0.f, m1_l = 0.f;
+        if (MODE == kTcHeadsPosition && dl_ok) {
+          m0_l = __ldg(p.umask + dl);
+          if (p.uinvert) m0_l = __fsub_rn(1.f, m0_l);
+          if (p.row_set != nullptr) {
+            m1_l = __ldg(p.umask_alt + dl);
+            if (p.uinvert_alt) m1_l = __fsub_rn(1.f, m1_l);
+          }
+        }
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           const int d0 = n_blk * 64 + half * 32 + c * 16;
-          if (rok && d0 < p.cols) {       // cols is a multiple of 16 on this path
+          if (d0 < p.cols) {              // warp-uniform; cols is a multiple of 16 on this path
             const size_t at = static_cast<size_t>(r) * p.cols + d0;
             float a0[16], a1[16], o0[16], o1[16], o2[16];
-            if (MODE == kTcHeadsMomentum) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) a0[j] = a1[j] = 0.f;
+            if (!rok) {
+            } else if (MODE == kTcHeadsMomentum) {
 #pragma unroll
               for (int j = 0; j < 16; j += 4) {
                 *reinterpret_cast<float4*>(a0 + j) = *reinterpret_cast<const float4*>(p.uv + at + j);
@@ -397,28 +414,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) gemm_tc_kernel(const TcParams p
             }
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
-              const int d = d0 + j;
-              const float S = __fmul_rn(tanhf(__fadd_rn(sum[0][c * 16 + j], __ldg(p.b_s + d))),
-                                        expf(__ldg(p.coeff_s + d)));
-              const float Tr = __fadd_rn(sum[1][c * 16 + j], __ldg(p.b_tr + d));
-              float Q = __fadd_rn(sum[2][c * 16 + j], __ldg(p.b_q + d));
+              const int src = c * 16 + j;
+              const float bs = __shfl_sync(0xffffffffu, bs_l, src), es = __shfl_sync(0xffffffffu, es_l, src);
+              const float bt = __shfl_sync(0xffffffffu, bt_l, src), bq = __shfl_sync(0xffffffffu, bq_l, src);
+              const float eq = __shfl_sync(0xffffffffu, eq_l, src);
+              const float S = __fmul_rn(tanhf(__fadd_rn(sum[0][c * 16 + j], bs)), es);
+              const float Tr = __fadd_rn(sum[1][c * 16 + j], bt);
+              float Q = __fadd_rn(sum[2][c * 16 + j], bq);
               if (p.tanh_on_q) Q = tanhf(Q);
-              Q = __fmul_rn(Q, expf(__ldg(p.coeff_q + d)));
+              Q = __fmul_rn(Q, eq);
               if (MODE == kTcHeadsStq) {
                 o0[j] = S, o1[j] = Tr, o2[j] = Q;
               } else if (MODE == kTcHeadsMomentum) {
                 o0[j] = dir > 0 ? momentum_elem<1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad)
                                 : momentum_elem<-1>(a0[j], a1[j], S, Tr, Q, p.eps, heps, ld, bad);
               } else {
-                float m = __ldg(umask + d);
-                if (uinvert) m = __fsub_rn(1.f, m);
+                const float mf = __shfl_sync(0xffffffffu, m0_l, src), ma = __shfl_sync(0xffffffffu, m1_l, src);
+                const float m = alt ? ma : mf;
                 o0[j] = dir > 0 ? position_elem<1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad)
                                 : position_elem<-1>(a0[j], a1[j], S, Tr, Q, m, p.eps, ld, bad);
               }
             }
 #pragma unroll
             for (int j = 0; j < 16; j += 4) {
-              if (MODE == kTcHeadsStq) {
+              if (!rok) {
+              } else if (MODE == kTcHeadsStq) {
                 *reinterpret_cast<float4*>(p.S + at + j) = *reinterpret_cast<float4*>(o0 + j);
                 *reinterpret_cast<float4*>(p.T + at + j) = *reinterpret_cast<float4*>(o1 + j);
                 *reinterpret_cast<float4*>(p.Q + at + j) = *reinterpret_cast<float4*>(o2 + j);
