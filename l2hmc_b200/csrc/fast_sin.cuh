@@ -79,6 +79,33 @@ __device__ __forceinline__ void fast_sincos(float x, float* sn, float* cs) {
   *cs = q.fold ? -c : c;
 }
 
+// sin, cos and the projection of P onto [-pi, pi) from ONE range reduction (the trajectory ends of the fused MC-step
+// kernel need all three per plaquette).  sin and cos are fast_sincos's operations; the quotient j = rint(P / 2pi) of
+// the reduction is floor((P + pi) / 2pi) whenever |r| = |P - 2pi j| is clear of pi, so proj = P - 2pi j formed with the
+// reference's own two roundings is bit-identical to project_angle(P) (which needs an exact division); near the branch
+// cut (|r| >= 3.1415, probability ~3e-5) and for |P| > 4e4 the exact path is taken.
+__device__ __forceinline__ void sincos_and_project(float P, float* sn, float* cs, float* proj) {
+  if (__builtin_expect(fabsf(P) > 40000.f, 0)) {
+    sincosf(P, sn, cs);
+    *proj = project_angle(P);
+    return;
+  }
+  const float magic = 12582912.0f;
+  const float j = __fsub_rn(fmaf(P, 0.15915494309189535f, magic), magic);
+  float r = fmaf(j, -6.28125f, P);
+  r = fmaf(j, -0.0019350051879882812f, r);
+  r = fmaf(j, -3.019916050561733e-07f, r);
+  const float a = fabsf(r);
+  const float folded = __fadd_rn(__fsub_rn(3.14159274101257324f, a), -8.742277657347586e-08f);
+  const bool fold = a > 1.57079637050628662f;
+  const float aa = fold ? folded : a;
+  const float rr = __int_as_float(__float_as_int(aa) ^ (__float_as_int(r) & 0x80000000));
+  *sn = sin_poly(rr);
+  const float c = cos_poly(aa);
+  *cs = fold ? -c : c;
+  *proj = a < 3.1415f ? __fsub_rn(P, __fmul_rn(kTwoPi, j)) : project_angle(P);
+}
+
 // Two sines per instruction stream (FFMA2/FADD2/FMUL2): the same reduction, fold and polynomial
 // as fast_sin on each lane.  The caller guarantees |x| <= 4e4 on both lanes.
 __device__ __forceinline__ f32x2 fast_sin2(f32x2 x) {

@@ -1,9 +1,13 @@
 #!/bin/bash
-# Round-2: tcgen05 heads epilogue with hoisted per-output constants -- parity tests and MC-step timings.
+# Round-2: MC-step kernel with one range reduction per plaquette at the trajectory ends -- HMC parity tests and the bench line.
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_l2hmc.py tests/test_gpu_config4_shapes.py tests/test_gpu_sampler.py tests/test_gpu_kernels.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
-for i in 1 2; do
-  python scripts/profile_c3.py --iters 30 --warm 5 2>&1 | tail -n 1
-done | tee gpurun_out/o_c3.log
-python scripts/profile_c3.py --arch generic --size 32 --chains 2048 --steps 10 --eps 0.1 --iters 5 --warm 2 2>&1 | tail -n 1
+timeout 1200 python -m pytest tests/test_gpu_hmc.py tests/test_gpu_kernels.py tests/test_gpu_sampler.py tests/test_gpu_multirank.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
+timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/o_bench.json 2> gpurun_out/o_bench.err; echo "rc=$?"
+python - <<'P'
+import json
+for l in open("gpurun_out/o_bench.json"):
+    if l.startswith("{"):
+        d = json.loads(l)
+        print("value", d["value"], "ms", d["ms_per_step"], "e2e", d["e2e"]["value"], "resident", d["e2e"]["resident_run"]["value"], "mc", d["roofline_mc"])
+P
