@@ -1,13 +1,6 @@
 #!/bin/bash
-# Round-2: MC-step kernel with one range reduction per plaquette at the trajectory ends -- HMC parity tests and the bench line.
+# Round-2: packed two-plaquette cos / projection in the action and observables kernels -- parity and HBM fraction.
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_hmc.py tests/test_gpu_kernels.py tests/test_gpu_sampler.py tests/test_gpu_multirank.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
-timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/o_bench.json 2> gpurun_out/o_bench.err; echo "rc=$?"
-python - <<'P'
-import json
-for l in open("gpurun_out/o_bench.json"):
-    if l.startswith("{"):
-        d = json.loads(l)
-        print("value", d["value"], "ms", d["ms_per_step"], "e2e", d["e2e"]["value"], "resident", d["e2e"]["resident_run"]["value"], "mc", d["roofline_mc"])
-P
+timeout 1200 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_hmc.py tests/test_gpu_sampler.py tests/test_gpu_l2hmc.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
+timeout 300 python scripts/profile_k1k2.py 2>&1 | tee gpurun_out/o_k1k2.jsonl | grep -i "action\|observ\|hamil\|force" | cut -c1-300
