@@ -294,8 +294,11 @@ class GaugeModel(object):
         """np.mod(x_out, 2 pi) of the host loop (:1180) on the device (exact, l2hmc_mh_select's wrap)."""
         N, D = x.shape
         out = torch.empty_like(x)
-        ones = torch.ones(N, dtype=torch.float32, device=x.device)
-        zeros = torch.zeros(N, dtype=torch.float32, device=x.device)
+        consts = getattr(self, "_wrap_consts", None)          # accept probability 1 > uniform 0: every chain "accepts"
+        if consts is None or consts[0].numel() != N or consts[0].device != x.device:
+            consts = self._wrap_consts = (torch.ones(N, dtype=torch.float32, device=x.device),
+                                          torch.zeros(N, dtype=torch.float32, device=x.device))
+        ones, zeros = consts
         with torch.cuda.device(x.device):
             _lib.check(_lib.get_lib().l2hmc_mh_select(_lib.dptr(x), _lib.dptr(x), None, None, None, _lib.dptr(ones), None,
                                                       None, _lib.dptr(zeros), N, D, 1, None, None, None, _lib.dptr(out),
