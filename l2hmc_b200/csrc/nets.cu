@@ -6,17 +6,22 @@
 //   network/conv_net.py:262-280      dense trunk + heads of ConvNet3D.call
 //   dynamics/gauge_dynamics.py:486-590  the four sub-updates (epilogue modes MOMENTUM / POSITION)
 //
-// One tiled fp32 GEMM kernel, three uses:
+// One tiled fp32 GEMM kernel, four uses:
 //   layer 1   h1 = relu([in0 | m*in1] . [Wv ; Wx] + tau.Wt + bv + bx + bt)   two K segments, the
 //             position net's `mask * x` input folded into the A-tile load (no mask_mul pass)
 //   layer 2   h2 = relu(h1 . Wh + bh)
 //   heads     one GEMM over the three head matrices: a CTA owns 32 outputs d of ALL THREE heads, so
 //             every thread holds S, T, Q of the same (chain, d) and applies tanh/exp and -- in the
 //             update modes -- the leapfrog sub-update and its log-det without S,T,Q touching HBM.
-// CTA tile 64 rows x 64 (96 for the heads) columns x 16 K, 256 threads, 4 x 4 (4 x 6) register
-// tile, operands prefetched into registers while the previous K slab is multiplied.  Accumulation
-// is fmaf in K order (fp32); this path serves the shapes too small or ragged for the tcgen05
-// kernel in gemm_tc.cu (config 2: 128 chains x 512 hidden; tail rows).
+//   grad      d act = d out . W^T of the backward pass (both operands K-contiguous, up to three K
+//             segments; ReLU gate, column mask, accumulate) -- l2hmc_sgemm routes those here.
+// CTA tile 64 rows x 64 (96 for the heads) columns x 32 K, 256 threads, 4 x 4 (4 x 6) register
+// tile, two K slabs of operands in flight in registers, two shared-memory buffers.  K is cut into
+// fixed chunks (a function of the K extents only): fmaf in K order inside a chunk, chunk sums added
+// in chunk order -- by the CTAs of one thread-block cluster over distributed shared memory when the
+// launch has fewer tiles than SMs (small batches are latency-bound: config 2, 128-256 rows), by one
+// CTA walking the chunks otherwise; a row's result does not depend on the batch it is launched with.
+// This path serves the shapes too small or ragged for the tcgen05 kernel in gemm_tc.cu.
 #include <cooperative_groups.h>
 
 #include <climits>

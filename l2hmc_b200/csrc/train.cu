@@ -17,7 +17,8 @@
 // row_set).  The backward sweep produces only the per-call activation gradients (dA, dZ2, dZ1) and appends them to
 // the tape; every WEIGHT gradient is one deferred TN GEMM over the whole tape (K = calls x rows instead of `calls`
 // small GEMMs), split along K with a fixed-order second stage, so results are deterministic (no atomics anywhere).
-// Training shapes (configs 2-3) are small: these kernels are FFMA; the tcgen05 path serves inference.
+// The small-batch products run on the FMA pipe (sgemm_kernel here for the strided forms, the chunked dense kernel of
+// nets.cu for d act = d out . W^T); dense contractions go to tcgen05 (gemm_tc.cu, dispatch l2hmc_gemm).
 #include <cooperative_groups.h>
 
 #include <algorithm>
