@@ -117,12 +117,17 @@ class GaugeSampler(object):
             a.workspace, a.workspace_bytes = ctypes.c_void_p(ws.data_ptr() + off), buf["ws_bytes"]
         return a
 
-    def _enqueue_mc(self, xin, xout, n, chain0, beta, px, act, plaq, q, q_in, buf, ctr=None):
+    def _enqueue_mc(self, xin, xout, n, chain0, beta, px, act, plaq, q, q_in, buf, ctr=None, q_prev=None):
         """Charge of the input + one MC step (mod 2 pi, observables of the end state) on the current stream.
-        `ctr`: a device int64 holding the Philox MC-step counter (captured graphs); None = dyn._mc_step by value."""
+        `ctr`: a device int64 holding the Philox MC-step counter (captured graphs); None = dyn._mc_step by value.
+        `q_prev`: the charges the PREVIOUS step of a resident run reported for its x_out, which is this step's input
+        (same array, same kernel, an integer): copied instead of evaluating the charge of the input again."""
         dyn, lib = self.dyn, _lib.get_lib()
-        _lib.check(lib.l2hmc_u1_observables(_lib.dptr(xin), n, dyn.T, dyn.X, None, None, None,
-                                            _lib.dptr(q_in, torch.int32), _lib.stream_ptr()))
+        if q_prev is not None:
+            q_in.copy_(q_prev, non_blocking=True)
+        else:
+            _lib.check(lib.l2hmc_u1_observables(_lib.dptr(xin), n, dyn.T, dyn.X, None, None, None,
+                                                _lib.dptr(q_in, torch.int32), _lib.stream_ptr()))
         if self.nets:
             a = self._net_args(n, xin, xout, buf, chain0, beta, px, act, plaq, q, ctr)
             _lib.check(lib.l2hmc_u1_l2hmc_mc_step(ctypes.byref(a), _lib.stream_ptr()))
@@ -157,7 +162,7 @@ class GaugeSampler(object):
             torch.cuda.synchronize(self.dev)
             with torch.cuda.graph(g):
                 self._enqueue_mc(xin, xout, self.N, dyn.chain_offset, beta, fo[0], fo[1], fo[2], io[0], io[1], rs["net"],
-                                 ctr=ctr)
+                                 ctr=ctr, q_prev=rs["iobs"][1 - b][0])
                 _lib.check(_lib.get_lib().l2hmc_counter_add(ctypes.c_void_p(ctr.data_ptr()), 1, _lib.stream_ptr()))
             graphs[key] = g                           # capture does not execute: the replay below is the step
         graphs[key].replay()
@@ -237,6 +242,7 @@ class GaugeSampler(object):
             src = samples if isinstance(samples, torch.Tensor) else torch.as_tensor(np.asarray(samples, dtype=np.float32))
             rs["x"][rs["cur"]].copy_(src.reshape(N, D), non_blocking=True)
             rs["valid"] = True
+            rs["q_valid"] = False                     # the charge of these links has not been evaluated yet
         if not rs["valid"]:
             raise ValueError("GaugeSampler.run: no samples to start from")
         if rs.get("hist_steps", 0) < n_steps:     # pinned history, allocated once (pinning costs ~1 ms per 10 MB)
@@ -256,11 +262,15 @@ class GaugeSampler(object):
                     main.wait_event(copied[b])          # the observables of step k - 2 have left this buffer
                 xin, xout = rs["x"][rs["cur"]], rs["x"][1 - rs["cur"]]
                 fo, io = rs["fobs"][b], rs["iobs"][b]
-                if use_graph and rs.get("eager_steps", 0) > 0:
+                # the input of this step is the previous step's x_out whenever the run continues: its charge is known
+                q_prev = rs["iobs"][1 - b][0] if rs.get("q_valid", False) else None
+                if use_graph and rs.get("eager_steps", 0) > 0 and q_prev is not None:
                     self._replay(rs, b, beta)
                 else:
-                    self._enqueue_mc(xin, xout, N, dyn.chain_offset, beta, fo[0], fo[1], fo[2], io[0], io[1], rs["net"])
+                    self._enqueue_mc(xin, xout, N, dyn.chain_offset, beta, fo[0], fo[1], fo[2], io[0], io[1], rs["net"],
+                                     q_prev=q_prev)
                     rs["eager_steps"] = rs.get("eager_steps", 0) + 1
+                rs["q_valid"] = True
                 if stats is not None:
                     stats.update(fo[1], fo[2], io[0])
                 done = torch.cuda.Event()

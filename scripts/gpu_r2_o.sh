@@ -1,10 +1,13 @@
 #!/bin/bash
-# Round-2 experiment: K-chunk rule of the dense kernel (slabs per chunk minimum, maximum chunks per tile).
+# Round-2: resident run reuses the previous step's charges as the charge of its input -- sampler tests and the bench line.
 set -u
 mkdir -p gpurun_out
-for v in "L2HMC_DENSE_SP_MIN=2 L2HMC_DENSE_MAX_CHUNKS=8" "L2HMC_DENSE_SP_MIN=4 L2HMC_DENSE_MAX_CHUNKS=8" "L2HMC_DENSE_SP_MIN=1 L2HMC_DENSE_MAX_CHUNKS=8" "L2HMC_DENSE_SP_MIN=2 L2HMC_DENSE_MAX_CHUNKS=4" "L2HMC_DENSE_SP_MIN=3 L2HMC_DENSE_MAX_CHUNKS=6"; do
-  echo "== $v"
-  env $v timeout 300 python scripts/bench_small_ops.py 2>&1 | grep "ksplit=0\|path ffma" | grep -v "dW" | cut -c1-140
-  env $v timeout 300 python scripts/bench_train.py --cases c2 --iters 30 2>&1 | tail -n 1 | grep -o "train_step_ms\": [0-9.]*"
-  env $v python scripts/profile_c3.py --arch generic --size 8 --chains 128 --iters 100 --warm 10 2>&1 | tail -n 1 | grep -o "mc_step_ms\": [0-9.]*"
-done | tee gpurun_out/o_chunks.log
+timeout 1200 python -m pytest tests/test_gpu_sampler.py tests/test_gpu_multirank.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
+timeout 900 python bench.py --steps 20 --warmup 3 --no-l2hmc > gpurun_out/o_bench.json 2> gpurun_out/o_bench.err; echo "rc=$?"
+python - <<'P'
+import json
+for l in open("gpurun_out/o_bench.json"):
+    if l.startswith("{"):
+        d = json.loads(l)
+        print("value", d["value"], "ms", d["ms_per_step"], "e2e", d["e2e"]["value"], "resident", d["e2e"]["resident_run"]["value"], d["e2e"]["resident_run"]["ms_per_step"], d["e2e"]["resident_run"]["frac_of_device_resident_value"])
+P
