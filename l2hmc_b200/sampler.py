@@ -12,8 +12,9 @@ run() is the B200-first form of the same loop (:1358-1441): the links never leav
 only the per-chain observables (accept probability, action, plaquette, charge, and the charge of the step's input for
 charge_diff_op, :849-850) come back, overlapped with the next step; samples on request.
 
-charge_diff follows the reference exactly: |Q(samples fed) - Q(x_out)| (:718-725), with Q of the fed samples computed
-from the samples themselves (not cached from an earlier step).
+charge_diff follows the reference exactly: |Q(samples fed) - Q(x_out)| (:718-725).  step() evaluates Q of the samples
+it is fed from those samples; inside a resident run() the input of a step IS the previous step's x_out, so the integer
+charge that step reported for it is re-used (only the first step after new samples evaluates it).
 """
 import ctypes
 
