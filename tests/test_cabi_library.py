@@ -65,3 +65,18 @@ def test_host_helpers_match_oracle():
     for i in range(5):
         np.testing.assert_allclose(tt[i], orc.format_time(i, 5).numpy(), atol=1e-7)
     assert abs(u1_plaq_exact(2.0) - 0.6977746) < 1e-6
+
+
+def test_dispatch_and_size_helpers_need_no_device():
+    """Pure host functions of the library: the batch size from which the AUTO layer path takes tcgen05 (what the
+    sampler's chunk rule is built on), the conv feature / tape sizes and the MoG loss workspace."""
+    from l2hmc_b200 import _lib
+    lib = _lib.get_lib()
+    assert lib.l2hmc_net_tc_min_rows(128, 512, 128) == 1024          # 8x8 generic nets: max(256, 2^19 / 512)
+    assert lib.l2hmc_net_tc_min_rows(512, 1024, 512) == 512          # 16x16 conv3D trunk
+    assert lib.l2hmc_net_tc_min_rows(2048, 8192, 2048) == 256        # 32x32 generic nets
+    assert lib.l2hmc_net_tc_min_rows(120, 480, 120) == 2 ** 31 - 1   # D % 16 != 0: never tcgen05
+    assert lib.l2hmc_net_tc_min_rows(32, 512, 128) == 2 ** 31 - 1    # K < 64
+    assert lib.l2hmc_conv3d_num_features(16, 16, 16) == 4 * 4 * 32
+    assert lib.l2hmc_conv3d_tape_elems(16, 16, 16) == 8 * 8 * 16
+    assert lib.l2hmc_mog_loss_workspace_bytes() >= 4 * 4 * 1024
