@@ -55,8 +55,15 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 constexpr int kStages = 5;   // K slabs in flight: the training GEMMs at config 2 are 32-CTA launches, latency-bound
 
-// A_KC / B_KC: the operand's K index is the contiguous one (only affects which threads read neighbouring words)
-template <bool A_KC, bool B_KC>
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+}
+
+// A_KC / B_KC: the operand's K index is the contiguous one (only affects which threads read neighbouring words).
+// VEC4: A^T . B with A [K, M] and B [K, N] row-major, 16-byte aligned rows and M, N multiples of 4 (the weight
+// gradients over the tape): one 16-byte async copy per thread, operand and slab instead of four 4-byte ones.
+template <bool A_KC, bool B_KC, bool VEC4 = false>
 __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p) {
   pdl_wait();
   pdl_trigger();
@@ -108,7 +115,15 @@ __global__ void __launch_bounds__(kGemmThreads) sgemm_kernel(const GemmParams p)
   };
   skip_empty();
   auto issue = [&](int stage) {
-    if (iseg < g.nseg) {
+    if (iseg < g.nseg && VEC4) {
+      const l2hmc_gemm_seg& sg = g.seg[iseg];
+      const int kk = tid >> 4, c4 = (tid & 15) * 4, k = ik0 + kk;          // 16 K rows x 16 float4 per operand
+      const bool va = k < ike && m0 + c4 < g.M, vb = k < ike && n0 + c4 < g.N;
+      cp_async16(&As[stage][kk][c4], va ? sg.A + static_cast<long long>(k) * sg.a_cs + (m0 + c4) : sg.A, va);
+      cp_async16(&Bs[stage][kk][c4], vb ? sg.B + static_cast<long long>(k) * sg.b_rs + (n0 + c4) : sg.B, vb);
+      ik0 += GBK;
+      skip_empty();
+    } else if (iseg < g.nseg) {
       const l2hmc_gemm_seg& sg = g.seg[iseg];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -871,9 +886,15 @@ extern "C" int l2hmc_sgemm(const l2hmc_gemm_args* g, int ksplit, void* workspace
   GemmParams p{*g, ksplit, static_cast<float*>(workspace), cluster};
   dim3 grid((g->N + GBN - 1) / GBN, (g->M + GBM - 1) / GBM, ksplit);
   const bool akc = g->seg[0].a_cs == 1, bkc = g->seg[0].b_rs == 1 && g->seg[0].b_cs != 1;
+  bool vec4 = !akc && !bkc && g->M % 4 == 0 && g->N % 4 == 0;
+  for (int s = 0; s < g->nseg && vec4; ++s) {
+    const l2hmc_gemm_seg& sg = g->seg[s];
+    vec4 = sg.a_rs == 1 && sg.b_cs == 1 && sg.a_cs % 4 == 0 && sg.b_rs % 4 == 0 && l2hmc::aligned16(sg.A) && l2hmc::aligned16(sg.B);
+  }
   void (*kern)(const GemmParams) = akc && bkc ? sgemm_kernel<true, true>
                                    : akc      ? sgemm_kernel<true, false>
                                    : bkc      ? sgemm_kernel<false, true>
+                                   : vec4     ? sgemm_kernel<false, false, true>
                                               : sgemm_kernel<false, false>;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid, cfg.blockDim = dim3(kGemmThreads), cfg.dynamicSmemBytes = 0, cfg.stream = st;

@@ -590,7 +590,7 @@ class TrainEngine(object):
 
     def _ksplit(self, M, N, K):
         tiles = -(-M // 64) * -(-N // 64)
-        return int(max(1, min(64, -(-296 // tiles), K // 64)))
+        return int(max(1, min(64, -(-592 // tiles), K // 64)))      # the same rule as csrc/train_step.cu (bit-identical walks)
 
     def _weight_grads(self, name, tp):
         """One transposed GEMM over the whole tape per weight tensor (K = calls * R rows); biases and coeff_* are

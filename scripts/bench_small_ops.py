@@ -63,9 +63,13 @@ def main():
     # small weight gradients over the whole tape: h2^T [512 x 2560] . dA [2560 x 128] (row-major operands, TN form)
     Rt = 2560
     h2t, dAt, gw = rnd(Rt, H), rnd(Rt, 3 * D), rnd(H, D)
-    for ks in (0, 8, 37):
+    for ks in (0, 8, 19, 26, 32, 40, 64):
         out[f"dW = h2^T . dA  512x128x2560 ksplit={ks}"] = graph_time(
             lambda: gemm(H, D, [(_ptr(h2t), 1, H, _ptr(dAt), 3 * D, 1, Rt)], _ptr(gw), D, ksplit=ks))
+    win_t, dz1t, gwi = rnd(Rt, K), rnd(Rt, H), rnd(K, H)
+    for ks in (19, 32, 40, 64):
+        out[f"dW_in = in^T . dz1  128x512x2560 ksplit={ks}"] = graph_time(
+            lambda: gemm(K, H, [(_ptr(win_t), 1, K, _ptr(dz1t), H, 1, Rt)], _ptr(gwi), H, ksplit=ks))
     # forward net call on the FFMA path (3 dense kernels) and the fused position update
     lat = pkg.GaugeLattice(8, 8, 2, "U1", num_samples=R)
     np.random.seed(0)

@@ -1,13 +1,6 @@
 #!/bin/bash
-# Round-2: resident run reuses the previous step's charges as the charge of its input -- sampler tests and the bench line.
+# Round-2: 16-byte operand copies + wider K split for the small weight-gradient products -- training tests and step times.
 set -u
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests/test_gpu_sampler.py tests/test_gpu_multirank.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
-timeout 900 python bench.py --steps 20 --warmup 3 --no-l2hmc > gpurun_out/o_bench.json 2> gpurun_out/o_bench.err; echo "rc=$?"
-python - <<'P'
-import json
-for l in open("gpurun_out/o_bench.json"):
-    if l.startswith("{"):
-        d = json.loads(l)
-        print("value", d["value"], "ms", d["ms_per_step"], "e2e", d["e2e"]["value"], "resident", d["e2e"]["resident_run"]["value"], d["e2e"]["resident_run"]["ms_per_step"], d["e2e"]["resident_run"]["frac_of_device_resident_value"])
-P
+timeout 1200 python -m pytest tests/test_gpu_training.py tests/test_gpu_train_rows.py tests/test_gpu_config4_shapes.py -x -q > gpurun_out/o_tests.log 2>&1; echo "tests rc=$?"; tail -n 4 gpurun_out/o_tests.log
+for i in 1 2; do timeout 300 python scripts/bench_train.py --cases c2,c3 --iters 30 2>&1 | tail -n 2 | grep -o "train_step_ms\": [0-9.]*"; done

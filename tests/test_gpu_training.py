@@ -48,7 +48,9 @@ def close_scaled(got, want, tol=2e-4, what=""):
                                          (9700, 200, 300, False, True), (5, 7, 3, False, True),
                                          # A^T . B with both operands row-major (small weight gradients over a long K)
                                          (512, 128, 2560, True, False), (130, 70, 1000, True, False),
-                                         (9, 33, 5000, True, False)])
+                                         (9, 33, 5000, True, False),
+                                         # ... with M, N multiples of 4 and aligned rows: 16-byte operand copies
+                                         (64, 64, 37, True, False), (132, 68, 1000, True, False)])
 def test_sgemm_forms(M, N, K, ta, tb):
     from l2hmc_b200 import _lib
     from l2hmc_b200.training import _Gemm, _ptr
